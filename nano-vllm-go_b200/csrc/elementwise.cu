@@ -1,0 +1,542 @@
+// elementwise.cu — HBM-bound kernels of the forward pass: embedding gather,
+// fused residual-add + LayerNorm/RMSNorm, SwiGLU/GELU, RoPE + paged KV append,
+// on-device sampling, weight repack.  All accesses are 16-byte vectors over the
+// contiguous (hidden) dimension; one CTA per token row.
+#include <cuda_fp16.h>
+
+#include "common.cuh"
+#include "kernels.h"
+
+namespace nvllm {
+
+// ------------------------------------------------------------------ embedding
+// generic_model.go:567-592 embedWithOffset + :298-302 EmbeddingMultiplier
+template <typename WT>
+__global__ void embed_kernel(const int* __restrict__ tokens, const int* __restrict__ positions,
+                             const WT* __restrict__ wte, const WT* __restrict__ wpe, int max_pos,
+                             float mult, float* __restrict__ x, int H) {
+  const int t = blockIdx.x;
+  const int tok = tokens[t];
+  const int pos = positions[t];
+  const WT* er = wte + (size_t)tok * H;
+  const bool add_pos = (wpe != nullptr) && (pos < max_pos);
+  const WT* pr = add_pos ? wpe + (size_t)pos * H : nullptr;
+  for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
+    float v[8];
+    load8(er + i, v);
+    if (add_pos) {
+      float p[8];
+      load8(pr + i, p);
+#pragma unroll
+      for (int j = 0; j < 8; j++) v[j] += p[j];
+    }
+    if (mult != 0.f) {
+#pragma unroll
+      for (int j = 0; j < 8; j++) v[j] *= mult;
+    }
+    store8(x + (size_t)t * H + i, v);
+  }
+}
+
+cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int* positions,
+                         const void* wte, const void* wpe, int max_pos, float mult, float* x, int T,
+                         int H) {
+  if (T <= 0) return cudaSuccess;
+  int threads = min(256, max(32, ((H / 8 + 31) / 32) * 32));
+  if (wdt == DT_F32)
+    embed_kernel<float><<<T, threads, 0, st>>>(tokens, positions, (const float*)wte,
+                                               (const float*)wpe, max_pos, mult, x, H);
+  else
+    embed_kernel<bf16><<<T, threads, 0, st>>>(tokens, positions, (const bf16*)wte,
+                                              (const bf16*)wpe, max_pos, mult, x, H);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------- fused residual add + norm
+// tensor.go:193-250 LayerNorm (RMSNorm when bias == nil), fused with the
+// residual combine of generic_model.go:320-326 / :359-365 / :405-416:
+//   x <- x + m1 * (sum_s p1[s] + bias1) + m2 * (sum_s p2[s] + bias2);  y = norm(x)
+// The updated row is staged in shared memory so x is read once and written once.
+template <typename YT>
+__global__ void norm_kernel(NormArgs a) {
+  extern __shared__ float row[];
+  __shared__ float red[32];
+  const int H = a.H;
+  const int orow = blockIdx.x;
+  const int r = a.row_idx ? a.row_idx[orow] : orow;
+  float* xr = a.x + (size_t)r * H;
+  const bool upd = (a.p1 != nullptr) || (a.p2 != nullptr);
+  float lsum = 0.f;
+  for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
+    float v[8];
+    load8(xr + i, v);
+    if (a.p1) {
+      float acc[8];
+#pragma unroll
+      for (int j = 0; j < 8; j++) acc[j] = 0.f;
+      for (int s = 0; s < a.S1; s++) {
+        float p[8];
+        load8(a.p1 + (size_t)s * a.stride1 + (size_t)r * H + i, p);
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[j] += p[j];
+      }
+      if (a.bias1) {
+        float p[8];
+        load8(a.bias1 + i, p);
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[j] += p[j];
+      }
+#pragma unroll
+      for (int j = 0; j < 8; j++) v[j] = v[j] + a.m1 * acc[j];
+    }
+    if (a.p2) {
+      float acc[8];
+#pragma unroll
+      for (int j = 0; j < 8; j++) acc[j] = 0.f;
+      for (int s = 0; s < a.S2; s++) {
+        float p[8];
+        load8(a.p2 + (size_t)s * a.stride2 + (size_t)r * H + i, p);
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[j] += p[j];
+      }
+      if (a.bias2) {
+        float p[8];
+        load8(a.bias2 + i, p);
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[j] += p[j];
+      }
+#pragma unroll
+      for (int j = 0; j < 8; j++) v[j] = v[j] + a.m2 * acc[j];
+    }
+    if (upd) store8(xr + i, v);
+    store8(row + i, v);
+    if (a.b) {
+#pragma unroll
+      for (int j = 0; j < 8; j++) lsum += v[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; j++) lsum += v[j] * v[j];
+    }
+  }
+  if (a.y == nullptr) return;
+  float tot = block_sum(lsum, red);
+  float mean = 0.f, inv;
+  if (a.b) {
+    mean = tot / (float)H;
+    float lv = 0.f;
+    for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        float d = row[i + j] - mean;
+        lv += d * d;
+      }
+    }
+    float var = block_sum(lv, red) / (float)H;
+    inv = 1.0f / sqrtf(var + a.eps);
+  } else {
+    inv = 1.0f / sqrtf(tot / (float)H + a.eps);
+  }
+  YT* yr = (YT*)a.y + (size_t)orow * H;
+  for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
+    float w[8], o[8];
+    load8(a.w + i, w);
+    if (a.b) {
+      float bb[8];
+      load8(a.b + i, bb);
+#pragma unroll
+      for (int j = 0; j < 8; j++) o[j] = (row[i + j] - mean) * inv * w[j] + bb[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 8; j++) o[j] = row[i + j] * inv * w[j];
+    }
+    store8(yr + i, o);
+    if (a.y_f32) store8(a.y_f32 + (size_t)orow * H + i, o);
+  }
+}
+
+cudaError_t launch_norm(cudaStream_t st, const NormArgs& a) {
+  if (a.n_rows <= 0) return cudaSuccess;
+  int threads = min(512, max(64, ((a.H / 8 + 31) / 32) * 32));
+  size_t smem = (size_t)a.H * sizeof(float);
+  if (a.ydt == DT_F32)
+    norm_kernel<float><<<a.n_rows, threads, smem, st>>>(a);
+  else
+    norm_kernel<bf16><<<a.n_rows, threads, smem, st>>>(a);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- activations
+__device__ __forceinline__ float gelu_tanh(float x) {  // tensor.go:181-190
+  float x3 = x * x * x;
+  float inner = 0.7978845608028654f * (x + 0.044715f * x3);
+  return 0.5f * x * (1.0f + tanhf(inner));
+}
+__device__ __forceinline__ float silu(float x) {  // mamba2.go:360-367
+  return x / (1.0f + expf(-x));
+}
+
+template <typename OT>
+__global__ void act_kernel(int T, int F, const float* __restrict__ h, int S, size_t stride,
+                           const float* __restrict__ bias, int swiglu, OT* __restrict__ out) {
+  const int ld = swiglu ? 2 * F : F;
+  const size_t nvec = (size_t)T * (F / 8);
+  for (size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec;
+       v += (size_t)gridDim.x * blockDim.x) {
+    const int t = (int)(v / (F / 8));
+    const int j = (int)(v % (F / 8)) * 8;
+    float g[8], o[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) g[i] = 0.f;
+    for (int s = 0; s < S; s++) {
+      float p[8];
+      load8(h + (size_t)s * stride + (size_t)t * ld + j, p);
+#pragma unroll
+      for (int i = 0; i < 8; i++) g[i] += p[i];
+    }
+    if (swiglu) {
+      float u[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) u[i] = 0.f;
+      for (int s = 0; s < S; s++) {
+        float p[8];
+        load8(h + (size_t)s * stride + (size_t)t * ld + F + j, p);
+#pragma unroll
+        for (int i = 0; i < 8; i++) u[i] += p[i];
+      }
+#pragma unroll
+      for (int i = 0; i < 8; i++) o[i] = silu(g[i]) * u[i];
+    } else {
+      if (bias) {
+        float p[8];
+        load8(bias + j, p);
+#pragma unroll
+        for (int i = 0; i < 8; i++) g[i] += p[i];
+      }
+#pragma unroll
+      for (int i = 0; i < 8; i++) o[i] = gelu_tanh(g[i]);
+    }
+    store8(out + (size_t)t * F + j, o);
+  }
+}
+
+cudaError_t launch_act(cudaStream_t st, int odt, int T, int F, const float* h, int S, size_t stride,
+                       const float* bias, int swiglu, void* out) {
+  if (T <= 0) return cudaSuccess;
+  size_t nvec = (size_t)T * (F / 8);
+  int threads = 256;
+  int blocks = (int)min((size_t)148 * 16, (nvec + threads - 1) / threads);
+  if (odt == DT_F32)
+    act_kernel<float><<<blocks, threads, 0, st>>>(T, F, h, S, stride, bias, swiglu, (float*)out);
+  else
+    act_kernel<bf16><<<blocks, threads, 0, st>>>(T, F, h, S, stride, bias, swiglu, (bf16*)out);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------- RoPE + paged KV append
+// One CTA per token.  Work items are (head, 8-wide vector of the first half):
+// rotate_half pairs element i with i + hd/2 (rope.go:187-201).
+template <typename QT, typename KT>
+__global__ void rope_kv_kernel(int nh, int nkv, int hd, const float* __restrict__ qkv, int S,
+                               size_t stride, const float* __restrict__ bias,
+                               const int* __restrict__ positions, const int* __restrict__ slots,
+                               const float* __restrict__ cosT, const float* __restrict__ sinT,
+                               QT* __restrict__ q_out, KT* __restrict__ kpool,
+                               KT* __restrict__ vpool) {
+  const int t = blockIdx.x;
+  const int half = hd / 2;
+  const int vph = half / 8;  // vectors per half head
+  const int ncols = (nh + 2 * nkv) * hd;
+  const int pos = positions[t];
+  const int slot = slots[t];
+  const int blk = slot / KV_BLOCK, off = slot % KV_BLOCK;
+  const int items = (nh + 2 * nkv) * vph;
+  for (int it = threadIdx.x; it < items; it += blockDim.x) {
+    const int head = it / vph;
+    const int j = (it % vph) * 8;
+    const int c0 = head * hd + j;
+    float a[8], b[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) a[i] = b[i] = 0.f;
+    for (int s = 0; s < S; s++) {
+      float p[8];
+      const float* base = qkv + (size_t)s * stride + (size_t)t * ncols;
+      load8(base + c0, p);
+#pragma unroll
+      for (int i = 0; i < 8; i++) a[i] += p[i];
+      load8(base + c0 + half, p);
+#pragma unroll
+      for (int i = 0; i < 8; i++) b[i] += p[i];
+    }
+    if (bias) {
+      float p[8];
+      load8(bias + c0, p);
+#pragma unroll
+      for (int i = 0; i < 8; i++) a[i] += p[i];
+      load8(bias + c0 + half, p);
+#pragma unroll
+      for (int i = 0; i < 8; i++) b[i] += p[i];
+    }
+    const bool is_v = head >= nh + nkv;
+    if (cosT != nullptr && !is_v) {
+      float c[8], sn[8];
+      load8(cosT + (size_t)pos * half + j, c);
+      load8(sinT + (size_t)pos * half + j, sn);
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        float ra = a[i] * c[i] - b[i] * sn[i];
+        float rb = b[i] * c[i] + a[i] * sn[i];
+        a[i] = ra;
+        b[i] = rb;
+      }
+    }
+    if (head < nh) {
+      QT* dst = q_out + (size_t)t * nh * hd + head * hd + j;
+      store8(dst, a);
+      store8(dst + half, b);
+    } else {
+      const int kvh = is_v ? head - nh - nkv : head - nh;
+      KT* pool = is_v ? vpool : kpool;
+      KT* dst = pool + (((size_t)blk * nkv + kvh) * KV_BLOCK + off) * hd + j;
+      store8(dst, a);
+      store8(dst + half, b);
+    }
+  }
+}
+
+cudaError_t launch_rope_kv(cudaStream_t st, int qdt, int kvdt, int T, int nh, int nkv, int hd,
+                           const float* qkv, int S, size_t stride, const float* bias,
+                           const int* positions, const int* slots, const float* cosT,
+                           const float* sinT, void* q_out, void* kpool, void* vpool) {
+  if (T <= 0) return cudaSuccess;
+  int items = (nh + 2 * nkv) * (hd / 16);
+  int threads = min(256, max(32, ((items + 31) / 32) * 32));
+#define RK(QT, KT)                                                                              \
+  rope_kv_kernel<QT, KT><<<T, threads, 0, st>>>(nh, nkv, hd, qkv, S, stride, bias, positions,   \
+                                                slots, cosT, sinT, (QT*)q_out, (KT*)kpool,      \
+                                                (KT*)vpool)
+  if (qdt == DT_F32 && kvdt == DT_F32) RK(float, float);
+  else if (qdt == DT_F32 && kvdt == DT_BF16) RK(float, bf16);
+  else if (qdt == DT_BF16 && kvdt == DT_BF16) RK(bf16, bf16);
+  else return cudaErrorInvalidValue;
+#undef RK
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------- sampling
+struct ArgMax {
+  float v;
+  int i;
+};
+__device__ __forceinline__ ArgMax argmax_merge(ArgMax a, ArgMax b) {
+  // larger value wins; equal values keep the lower index (first-max rule)
+  if (b.v > a.v || (b.v == a.v && b.i < a.i)) return b;
+  return a;
+}
+
+__global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
+                              const float* __restrict__ temperature,
+                              const float* __restrict__ uniforms, int* __restrict__ out_tokens) {
+  __shared__ float red[32];
+  __shared__ ArgMax amred[32];
+  __shared__ float scan[1024];
+  __shared__ int winner;
+  const int s = blockIdx.x;
+  const float* l = logits + (size_t)s * ldl;
+  const float temp = temperature ? temperature[s] : 0.f;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  if (!(temp > 0.f)) {
+    // cmd/ask/main.go:389-402: first index of the maximum
+    ArgMax am = {-INFINITY, 0x7fffffff};
+    for (int i = threadIdx.x; i < V; i += blockDim.x) {
+      float v = l[i];
+      if (v > am.v) {
+        am.v = v;
+        am.i = i;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      ArgMax ot = {__shfl_xor_sync(0xffffffffu, am.v, o), __shfl_xor_sync(0xffffffffu, am.i, o)};
+      am = argmax_merge(am, ot);
+    }
+    if (lane == 0) amred[w] = am;
+    __syncthreads();
+    if (w == 0) {
+      ArgMax r = (lane < nw) ? amred[lane] : ArgMax{-INFINITY, 0x7fffffff};
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        ArgMax ot = {__shfl_xor_sync(0xffffffffu, r.v, o), __shfl_xor_sync(0xffffffffu, r.i, o)};
+        r = argmax_merge(r, ot);
+      }
+      if (lane == 0) out_tokens[s] = (r.i == 0x7fffffff) ? 0 : r.i;
+    }
+    return;
+  }
+  // temperature sampling: sampling.go:70-74 (divide), :105-128 (softmax), :196-217 (inverse CDF).
+  // Each thread owns a contiguous chunk so that prefix sums follow index order.
+  const int chunk = (V + blockDim.x - 1) / blockDim.x;
+  const int lo = min(V, (int)threadIdx.x * chunk), hi = min(V, lo + chunk);
+  float mx = -INFINITY;
+  for (int i = lo; i < hi; i++) mx = fmaxf(mx, l[i] / temp);
+  mx = block_max(mx, red);
+  float csum = 0.f;
+  for (int i = lo; i < hi; i++) csum += expf(l[i] / temp - mx);
+  scan[threadIdx.x] = csum;
+  __syncthreads();
+  // inclusive scan over <= 1024 chunk sums (Hillis-Steele)
+  for (int o = 1; o < (int)blockDim.x; o <<= 1) {
+    float add = (threadIdx.x >= (unsigned)o) ? scan[threadIdx.x - o] : 0.f;
+    __syncthreads();
+    scan[threadIdx.x] += add;
+    __syncthreads();
+  }
+  const float total = scan[blockDim.x - 1];
+  const float r = uniforms[s] * total;
+  if (threadIdx.x == 0) winner = V - 1;  // sampling.go:212-214 clamp
+  __syncthreads();
+  const float incl = scan[threadIdx.x];
+  const float excl = incl - csum;
+  // first chunk whose inclusive prefix reaches r
+  const bool mine = (incl >= r) && (threadIdx.x == 0 || scan[threadIdx.x - 1] < r) && (hi > lo);
+  if (mine) {
+    float run = excl;
+    int pick = hi - 1;
+    for (int i = lo; i < hi; i++) {
+      run += expf(l[i] / temp - mx);
+      if (run >= r) {
+        pick = i;
+        break;
+      }
+    }
+    atomicMin(&winner, pick);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) out_tokens[s] = winner;
+}
+
+cudaError_t launch_sample(cudaStream_t st, const float* logits, int ldl, int V, int n,
+                          const float* temperature, const float* uniforms, int* out_tokens) {
+  if (n <= 0) return cudaSuccess;
+  sample_kernel<<<n, 1024, 0, st>>>(logits, ldl, V, temperature, uniforms, out_tokens);
+  return cudaGetLastError();
+}
+
+__global__ void advance_kernel(int n, const int* __restrict__ sampled, int* tokens, int* positions,
+                               int* slots, int* seq_len, const int* __restrict__ block_tables,
+                               int max_blocks, int max_pos) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  tokens[i] = sampled[i];
+  int pos = positions[i] + 1;
+  if (pos >= max_pos) pos = max_pos - 1;  // caller bounds n_steps; never index past the table
+  int bi = pos / KV_BLOCK;
+  if (bi >= max_blocks) bi = max_blocks - 1;
+  positions[i] = pos;
+  seq_len[i] = pos + 1;
+  slots[i] = block_tables[(size_t)i * max_blocks + bi] * KV_BLOCK + pos % KV_BLOCK;
+}
+
+cudaError_t launch_advance(cudaStream_t st, int n, const int* sampled, int* tokens, int* positions,
+                           int* slots, int* seq_len, const int* block_tables, int max_blocks,
+                           int max_pos) {
+  if (n <= 0) return cudaSuccess;
+  advance_kernel<<<(n + 127) / 128, 128, 0, st>>>(n, sampled, tokens, positions, slots, seq_len,
+                                                 block_tables, max_blocks, max_pos);
+  return cudaGetLastError();
+}
+
+// ------------------------------------------------------------- weight repack
+template <typename ST> __device__ __forceinline__ float src_to_f32(ST v);
+template <> __device__ __forceinline__ float src_to_f32<float>(float v) { return v; }
+template <> __device__ __forceinline__ float src_to_f32<bf16>(bf16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ float src_to_f32<__half>(__half v) { return __half2float(v); }
+
+// dst[n, k] = src[k, n]; 32x32 tiles through shared memory so both sides are coalesced
+template <typename ST, typename DT>
+__global__ void transpose_convert_kernel(const ST* __restrict__ src, int K, int N,
+                                         DT* __restrict__ dst, int ld_dst) {
+  __shared__ float tile[32][33];
+  const int n0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    int k = k0 + r, n = n0 + threadIdx.x;
+    tile[r][threadIdx.x] = (k < K && n < N) ? src_to_f32<ST>(src[(size_t)k * N + n]) : 0.f;
+  }
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    int n = n0 + r, k = k0 + threadIdx.x;
+    if (n < N && k < K) dst[(size_t)n * ld_dst + k] = from_f32<DT>(tile[threadIdx.x][r]);
+  }
+}
+
+cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* src, int K, int N,
+                                     int ddt, void* dst, int ld_dst) {
+  dim3 grid((N + 31) / 32, (K + 31) / 32), block(32, 8);
+#define TC(ST, DT) \
+  transpose_convert_kernel<ST, DT><<<grid, block, 0, st>>>((const ST*)src, K, N, (DT*)dst, ld_dst)
+  if (ddt == DT_F32) {
+    if (sdt_api == 0) TC(float, float);
+    else if (sdt_api == 1) TC(bf16, float);
+    else TC(__half, float);
+  } else {
+    if (sdt_api == 0) TC(float, bf16);
+    else if (sdt_api == 1) TC(bf16, bf16);
+    else TC(__half, bf16);
+  }
+#undef TC
+  return cudaGetLastError();
+}
+
+template <typename ST, typename DT>
+__global__ void convert_kernel(const ST* __restrict__ src, size_t n, DT* __restrict__ dst) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = from_f32<DT>(src_to_f32<ST>(src[i]));
+}
+
+cudaError_t launch_convert(cudaStream_t st, int sdt_api, const void* src, size_t n, int ddt,
+                           void* dst) {
+  if (n == 0) return cudaSuccess;
+  int blocks = (int)min((size_t)148 * 8, (n + 255) / 256);
+#define CV(ST, DT) convert_kernel<ST, DT><<<blocks, 256, 0, st>>>((const ST*)src, n, (DT*)dst)
+  if (ddt == DT_F32) {
+    if (sdt_api == 0) CV(float, float);
+    else if (sdt_api == 1) CV(bf16, float);
+    else CV(__half, float);
+  } else {
+    if (sdt_api == 0) CV(float, bf16);
+    else if (sdt_api == 1) CV(bf16, bf16);
+    else CV(__half, bf16);
+  }
+#undef CV
+  return cudaGetLastError();
+}
+
+__global__ void fill_kernel(float* p, size_t n, float v) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x)
+    p[i] = v;
+}
+cudaError_t launch_fill(cudaStream_t st, float* p, size_t n, float v) {
+  fill_kernel<<<148 * 8, 256, 0, st>>>(p, n, v);
+  return cudaGetLastError();
+}
+
+// out[i] = sum_s p[s*stride + i]   (split-K partials of the LM head -> logits)
+__global__ void reduce_partials_kernel(const float* __restrict__ p, int S, size_t stride, size_t n,
+                                       float* __restrict__ out) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (size_t)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+    for (int s = 0; s < S; s++) acc += p[(size_t)s * stride + i];
+    out[i] = acc;
+  }
+}
+cudaError_t launch_reduce_partials(cudaStream_t st, const float* p, int S, size_t stride, size_t n,
+                                   float* out) {
+  if (n == 0) return cudaSuccess;
+  int blocks = (int)min((size_t)148 * 8, (n + 255) / 256);
+  reduce_partials_kernel<<<blocks, 256, 0, st>>>(p, S, stride, n, out);
+  return cudaGetLastError();
+}
+
+}  // namespace nvllm

@@ -1,0 +1,199 @@
+// kernels.h — internal launcher interface between the C-ABI orchestration
+// (nvllm.cu) and the kernel translation units.  Everything here is device
+// pointers + a stream; errors come back as cudaError_t.
+//
+// Conventions
+//  * residual stream x: fp32 [T, H]
+//  * "act" tensors (GEMM inputs): dtype DT (fp32 or bf16), row-major, K contiguous
+//  * weights: [N, K] K contiguous ("out,in"), dtype DT
+//  * GEMM outputs: fp32 "partials" out[s][row][col], s < S (split-K); consumers
+//    sum the S slices (deterministic, no atomics) and add the bias
+//  * KV pool of one layer: K and V each [num_blocks][n_kv][256][hd], dtype DT
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+namespace nvllm {
+
+enum DType { DT_F32 = 0, DT_BF16 = 1 };
+static inline size_t dt_size(int dt) { return dt == DT_F32 ? 4 : 2; }
+
+constexpr int KV_BLOCK = 256;
+
+// ---------------------------------------------------------------- elementwise.cu
+// x[t,:] = (wte[tok[t],:] (+ wpe[pos[t],:] if wpe && pos < max_pos)) * mult   (mult==0 => 1)
+cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int* positions,
+                         const void* wte, const void* wpe, int max_pos, float mult, float* x, int T,
+                         int H);
+
+struct NormArgs {
+  float* x;            // [*, H] residual stream, updated in place when p1/p2 given
+  const float* p1;     // partials [S1][rows_total][H] or null
+  int S1;
+  size_t stride1;      // elements between slices
+  float m1;            // x += m1 * (sum_s p1 + bias1)
+  const float* bias1;  // [H] or null
+  const float* p2;     // second addend (Falcon parallel block: attn + ffn)
+  int S2;
+  size_t stride2;
+  float m2;
+  const float* bias2;
+  const float* w;      // [H]
+  const float* b;      // [H] or null => RMSNorm (tensor.go:197)
+  float eps;
+  void* y;             // [n_rows, H] dtype ydt (may be null: residual update only)
+  int ydt;
+  float* y_f32;        // optional extra fp32 copy of y (MoE router input)
+  const int* row_idx;  // optional gather: output row i reads x row row_idx[i]
+  int n_rows;
+  int H;
+};
+cudaError_t launch_norm(cudaStream_t st, const NormArgs& a);
+
+// SwiGLU: out[t,j] = silu(h[t,j]) * h[t,F+j]   (transformer.go:50-66, mamba2.go:360-367)
+// GELU:   out[t,j] = gelu_tanh(h[t,j] + b1[j]) (transformer.go:67-78, tensor.go:181-190)
+cudaError_t launch_act(cudaStream_t st, int odt, int T, int F, const float* h, int S, size_t stride,
+                       const float* bias, int swiglu, void* out);
+
+// Sum split-K partials (+bias), RoPE rotate_half on Q and K (rope.go:153-205), write Q
+// [T, nh*hd] (dtype qdt) and scatter K,V into the paged pool (dtype kvdt) at slots[t].
+// cos/sin: [max_pos, hd/2] fp32 computed in double on the host exactly like rope.go:18-50;
+// null => no RoPE (GPT-2).  qkv columns: [Q heads | K heads | V heads].
+cudaError_t launch_rope_kv(cudaStream_t st, int qdt, int kvdt, int T, int nh, int nkv, int hd,
+                           const float* qkv, int S, size_t stride, const float* bias,
+                           const int* positions, const int* slots, const float* cosT,
+                           const float* sinT, void* q_out, void* kpool, void* vpool);
+
+// logits [n, ldl] fp32 (first V columns valid).  temperature[i] <= 0: first-max argmax
+// (cmd/ask/main.go:389-402).  Otherwise softmax(l/T) and inverse-CDF draw with uniforms[i]
+// (sampling.go:70-74,105-128,196-217).
+cudaError_t launch_sample(cudaStream_t st, const float* logits, int ldl, int V, int n,
+                          const float* temperature, const float* uniforms, int* out_tokens);
+
+// advance device-resident decode state by one token (nvllm_run_resident)
+cudaError_t launch_advance(cudaStream_t st, int n, const int* sampled, int* tokens, int* positions,
+                           int* slots, int* seq_len, const int* block_tables, int max_blocks,
+                           int max_pos);
+
+// dst[N,K] (dtype ddt) = transpose(src[K,N] fp32|bf16|f16)   — weight repack at finalize
+cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* src, int K, int N,
+                                     int ddt, void* dst, int ld_dst);
+// dst (dtype ddt) = convert(src)  flat copy
+cudaError_t launch_convert(cudaStream_t st, int sdt_api, const void* src, size_t n, int ddt,
+                           void* dst);
+// out[i] = sum_s p[s*stride + i]
+cudaError_t launch_reduce_partials(cudaStream_t st, const float* p, int S, size_t stride, size_t n,
+                                   float* out);
+// a bigger-than-L2 write, for cold-cache timing
+cudaError_t launch_fill(cudaStream_t st, float* p, size_t n, float v);
+
+// ---------------------------------------------------------------- gemm_simt.cu
+struct GemmArgs {
+  const void* A;  // [M, K] dtype adt (row gather through a_rows if set)
+  int adt;
+  int lda;
+  const void* W;  // [N, K] dtype wdt
+  int wdt;
+  int M, N, K;
+  float* out;         // [S][M][ldo]
+  int ldo;
+  size_t split_stride;
+  int S;              // filled by the launcher: number of split-K slices written
+  size_t out_capacity;  // floats available at `out`; the launcher keeps S*M*ldo within it (0 = unchecked)
+  float alpha;        // out = alpha * acc
+  // grouped (MoE) extension: tile t covers rows [tile_row0[t], tile_row0[t]+tile_rows[t]) of the
+  // sorted pair list with expert weights W + tile_expert[t]*expert_stride
+  const int* a_rows;       // A row index per output row (gather), or null
+  const int* tile_expert;  // per 64-row tile, or null
+  const int* tile_row0;
+  const int* tile_rows;
+  const int* n_tiles;      // device scalar: number of valid tiles
+  size_t expert_stride;    // elements
+  int max_tiles;
+};
+// split-K slices a skinny GEMV will produce for (M,N,K); workspace must hold S*M*N floats
+int gemv_splits(int M, int N, int K);
+cudaError_t launch_gemv(cudaStream_t st, GemmArgs& g);       // M <= 8
+cudaError_t launch_gemm_simt(cudaStream_t st, GemmArgs& g);  // any M (fp32 parity mode, MoE)
+
+// ---------------------------------------------------------------- gemm_tcgen05.cu
+struct TmaDesc {
+  alignas(64) unsigned char bytes[128];  // CUtensorMap
+};
+// 2-D bf16 tensor map: rows x cols (cols contiguous), box = box_rows x 64 cols, 128B swizzle
+int make_tma_2d_bf16(TmaDesc* out, const void* base, uint64_t rows, uint64_t cols,
+                     uint64_t row_stride_elems, uint32_t box_rows, std::string* err);
+struct Tc5Args {
+  const TmaDesc* tmA;  // activations [M, K] bf16
+  const TmaDesc* tmW;  // weights     [N, K] bf16
+  int M, N, K;
+  float* out;          // [S][M][ldo] fp32 partials
+  int ldo;
+  size_t split_stride;
+  int S;
+  float alpha;
+  size_t out_capacity;
+};
+bool tc5_supported(int M, int N, int K);
+int tc5_splits(int M, int N, int K, int sm_count);
+cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int sm_count);
+int tc5_box_rows_act(int M);  // TMA box rows the kernel expects for the activation map
+int tc5_box_rows_w(int N);    // ... and for the weight map
+
+// ---------------------------------------------------------------- attention.cu
+struct AttnArgs {
+  const void* q;  // [T, nh*hd] dtype qdt
+  void* out;      // [T, nh*hd] dtype qdt
+  int qdt;
+  const void* kpool;  // one layer
+  const void* vpool;
+  int kvdt;
+  int n_seqs, nh, nkv, hd;
+  float scale;
+  const int* block_tables;  // [n_seqs, max_blocks]
+  int max_blocks;
+  // prefill
+  const int* cu_q;       // [n_seqs+1] row offsets of the new tokens
+  const int* seq_start;  // [n_seqs] position of the first new token
+  int max_new;           // max new tokens of any sequence (grid sizing)
+  const int* tile_seq;   // [n_qtiles] sequence of each query tile (prefill)
+  const int* tile_q0;    // [n_qtiles] first new-token index of each query tile
+  int n_qtiles;
+  // decode
+  const int* seq_len;  // [n_seqs] tokens incl. the new one
+  int n_splits;
+  float* ws;           // [n_seqs*nh*n_splits*(hd+2)] split partials
+};
+constexpr int ATTN_PREFILL_QTILE = 32;
+cudaError_t launch_attn_prefill(cudaStream_t st, const AttnArgs& a);
+cudaError_t launch_attn_decode(cudaStream_t st, const AttnArgs& a);
+
+// ---------------------------------------------------------------- moe.cu
+// Router: probs = softmax(x @ R) over all E, top-k (descending), weights renormalised
+// (moe.go:63-103).  x fp32 [T,H]; R fp32 [E,H].
+cudaError_t launch_moe_router(cudaStream_t st, const float* x, const float* R, int T, int H, int E,
+                              int k, int* topk_idx, float* topk_w);
+// Group the T*k (token,slot) pairs by expert into 64-row tiles.
+struct MoeSortBufs {
+  int* counts;       // [E]
+  int* offsets;      // [E+1]
+  int* cursor;       // [E]
+  int* sorted_pair;  // [T*k] pair id (t*k+s) grouped by expert
+  int* pair_row;     // [T*k] row of pair in the sorted order
+  int* a_rows;       // [T*k] token index per sorted row
+  int* tile_expert;  // [max_tiles]
+  int* tile_row0;
+  int* tile_rows;
+  int* n_tiles;      // [1]
+};
+cudaError_t launch_moe_sort(cudaStream_t st, const int* topk_idx, int T, int k, int E,
+                            const MoeSortBufs& b, int max_tiles);
+// g[row, j] = silu(h[row, j]) * h[row, I + j] with the fp32 sigmoid of moe.go:203-212
+cudaError_t launch_moe_glu(cudaStream_t st, int odt, int rows, int I, const float* h, void* g);
+// y[t,:] = sum_s w[t,s] * Y[pair_row[t*k+s], :]   (moe.go:116-118, slot order = descending prob)
+cudaError_t launch_moe_combine(cudaStream_t st, int T, int k, int H, const float* Y,
+                               const int* pair_row, const float* topk_w, float* y);
+
+}  // namespace nvllm

@@ -1,0 +1,209 @@
+// moe.cu — Granite top-k mixture-of-experts plumbing around the grouped expert GEMMs:
+// router (matmul + softmax over ALL experts + top-k + renormalise, moe.go:63-103), grouping
+// of the (token, slot) pairs by expert into 64-row tiles, the GLU between the two expert
+// GEMMs (moe.go:203-212) and the weighted combine (moe.go:116-118).
+#include "common.cuh"
+#include "kernels.h"
+
+namespace nvllm {
+
+constexpr int MOE_MAX_E = 256;
+
+// One CTA (4 warps) per token.  Warp w computes the logits of experts w, w+4, ...;
+// warp 0 then does softmax and k rounds of first-max selection (ties -> lower index, which
+// is what a stable descending sort gives; the reference's sort.Slice is unstable, ties have
+// measure zero with random-init weights).
+__global__ void __launch_bounds__(128)
+moe_router_kernel(const float* __restrict__ x, const float* __restrict__ R, int H, int E, int k,
+                  int* __restrict__ topk_idx, float* __restrict__ topk_w) {
+  __shared__ float probs[MOE_MAX_E];
+  const int t = blockIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const float* xr = x + (size_t)t * H;
+  for (int e = warp; e < E; e += 4) {
+    const float* rr = R + (size_t)e * H;
+    float acc = 0.f;
+    for (int i = lane * 8; i < H; i += 256) {
+      float a[8], b[8];
+      load8(xr + i, a);
+      load8(rr + i, b);
+#pragma unroll
+      for (int j = 0; j < 8; j++) acc = fmaf(a[j], b[j], acc);
+    }
+    acc = warp_sum(acc);
+    if (lane == 0) probs[e] = acc;
+  }
+  __syncthreads();
+  if (warp != 0) return;
+  // tensor.go:128-155 softmax over all E
+  float mx = -INFINITY;
+  for (int e = lane; e < E; e += 32) mx = fmaxf(mx, probs[e]);
+  mx = warp_max(mx);
+  float sum = 0.f;
+  for (int e = lane; e < E; e += 32) {
+    float p = expf(probs[e] - mx);
+    probs[e] = p;
+    sum += p;
+  }
+  sum = warp_sum(sum);
+  __syncwarp();
+  for (int e = lane; e < E; e += 32) probs[e] = probs[e] / sum;
+  __syncwarp();
+  // top-k by repeated first-max
+  float sel_p = 0.f;  // lane s keeps the s-th selection (k <= 32)
+  int sel_i = 0;
+  float ksum = 0.f;
+  for (int s = 0; s < k; s++) {
+    float bv = -1.f;
+    int bi = 0x7fffffff;
+    for (int e = lane; e < E; e += 32) {
+      float p = probs[e];
+      if (p > bv) {
+        bv = p;
+        bi = e;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > bv || (ov == bv && oi < bi)) {
+        bv = ov;
+        bi = oi;
+      }
+    }
+    if (lane == s) {
+      sel_p = bv;
+      sel_i = bi;
+    }
+    ksum += bv;  // moe.go:98-103: sum in descending order
+    if (lane == 0) probs[bi] = -2.f;
+    __syncwarp();
+  }
+  if (lane < k) {
+    topk_idx[(size_t)t * k + lane] = sel_i;
+    topk_w[(size_t)t * k + lane] = sel_p / ksum;
+  }
+}
+
+cudaError_t launch_moe_router(cudaStream_t st, const float* x, const float* R, int T, int H, int E,
+                              int k, int* topk_idx, float* topk_w) {
+  if (T <= 0) return cudaSuccess;
+  if (E > MOE_MAX_E || k > 32 || k > E || (H % 8) != 0) return cudaErrorInvalidValue;
+  moe_router_kernel<<<T, 128, 0, st>>>(x, R, H, E, k, topk_idx, topk_w);
+  return cudaGetLastError();
+}
+
+// Single-CTA counting sort of the T*k pairs by expert + tile list.  Rows inside an expert are
+// in arbitrary order; every consumer addresses them through pair_row / a_rows, so results do
+// not depend on it.
+__global__ void __launch_bounds__(1024)
+moe_sort_kernel(const int* __restrict__ topk_idx, int n_pairs, int k, int E, MoeSortBufs b,
+                int max_tiles) {
+  __shared__ int cnt[MOE_MAX_E];
+  __shared__ int off[MOE_MAX_E + 1];
+  for (int e = threadIdx.x; e < E; e += blockDim.x) cnt[e] = 0;
+  __syncthreads();
+  for (int p = threadIdx.x; p < n_pairs; p += blockDim.x) atomicAdd(&cnt[topk_idx[p]], 1);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int run = 0, nt = 0;
+    for (int e = 0; e < E; e++) {
+      off[e] = run;
+      b.counts[e] = cnt[e];
+      b.offsets[e] = run;
+      for (int r = 0; r < cnt[e] && nt < max_tiles; r += 64) {
+        b.tile_expert[nt] = e;
+        b.tile_row0[nt] = run + r;
+        b.tile_rows[nt] = min(64, cnt[e] - r);
+        nt++;
+      }
+      run += cnt[e];
+    }
+    off[E] = run;
+    b.offsets[E] = run;
+    *b.n_tiles = nt;
+  }
+  __syncthreads();
+  for (int e = threadIdx.x; e < E; e += blockDim.x) cnt[e] = 0;  // reuse as cursors
+  __syncthreads();
+  for (int p = threadIdx.x; p < n_pairs; p += blockDim.x) {
+    const int e = topk_idx[p];
+    const int row = off[e] + atomicAdd(&cnt[e], 1);
+    b.sorted_pair[row] = p;
+    b.pair_row[p] = row;
+    b.a_rows[row] = p / k;
+  }
+}
+
+cudaError_t launch_moe_sort(cudaStream_t st, const int* topk_idx, int T, int k, int E,
+                            const MoeSortBufs& b, int max_tiles) {
+  if (T <= 0) return cudaSuccess;
+  if (E > MOE_MAX_E) return cudaErrorInvalidValue;
+  moe_sort_kernel<<<1, 1024, 0, st>>>(topk_idx, T * k, k, E, b, max_tiles);
+  return cudaGetLastError();
+}
+
+// moe.go:203-212: sigmoid with an fp32 divide, gate = first half, up = second half
+template <typename OT>
+__global__ void moe_glu_kernel(size_t nvec, int I, const float* __restrict__ h,
+                               OT* __restrict__ g) {
+  const int vpr = I / 8;
+  for (size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec;
+       v += (size_t)gridDim.x * blockDim.x) {
+    const size_t row = v / vpr;
+    const int j = (int)(v % vpr) * 8;
+    float a[8], u[8], o[8];
+    load8(h + row * 2 * I + j, a);
+    load8(h + row * 2 * I + I + j, u);
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const float sig = 1.0f / (1.0f + expf(-a[i]));
+      o[i] = a[i] * sig * u[i];
+    }
+    store8(g + row * I + j, o);
+  }
+}
+
+cudaError_t launch_moe_glu(cudaStream_t st, int odt, int rows, int I, const float* h, void* g) {
+  if (rows <= 0) return cudaSuccess;
+  if ((I % 8) != 0) return cudaErrorInvalidValue;
+  size_t nvec = (size_t)rows * (I / 8);
+  int blocks = (int)min((size_t)148 * 16, (nvec + 255) / 256);
+  if (odt == DT_F32)
+    moe_glu_kernel<float><<<blocks, 256, 0, st>>>(nvec, I, h, (float*)g);
+  else
+    moe_glu_kernel<bf16><<<blocks, 256, 0, st>>>(nvec, I, h, (bf16*)g);
+  return cudaGetLastError();
+}
+
+// y[t,:] = sum_s w[t,s] * Y[pair_row[t*k+s],:]  in slot order (descending probability)
+__global__ void moe_combine_kernel(int k, int H, const float* __restrict__ Y,
+                                   const int* __restrict__ pair_row,
+                                   const float* __restrict__ topk_w, float* __restrict__ y) {
+  const int t = blockIdx.x;
+  for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[j] = 0.f;
+    for (int s = 0; s < k; s++) {
+      const int row = pair_row[(size_t)t * k + s];
+      const float w = topk_w[(size_t)t * k + s];
+      float v[8];
+      load8(Y + (size_t)row * H + i, v);
+#pragma unroll
+      for (int j = 0; j < 8; j++) acc[j] += w * v[j];
+    }
+    store8(y + (size_t)t * H + i, acc);
+  }
+}
+
+cudaError_t launch_moe_combine(cudaStream_t st, int T, int k, int H, const float* Y,
+                               const int* pair_row, const float* topk_w, float* y) {
+  if (T <= 0) return cudaSuccess;
+  int threads = min(256, max(32, ((H / 8 + 31) / 32) * 32));
+  moe_combine_kernel<<<T, threads, 0, st>>>(k, H, Y, pair_row, topk_w, y);
+  return cudaGetLastError();
+}
+
+}  // namespace nvllm

@@ -1,0 +1,294 @@
+// nvllm.cu — C-ABI entry points of libnvllm_b200.so: handle lifecycle, weight intake
+// (the reference's post-load layouts -> device layouts) and the KV pool.  The forward
+// pass itself is forward.cu; single-operator entry points are ops.cu.
+//
+// Replaces, behind the same boundary, what NewTensorModelRunner + TensorModelRunner.Run do
+// in the reference (nanovllm/tensor_model_runner.go:21-97).
+#include <math.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "handle.h"
+
+namespace nvllm {
+
+thread_local std::string g_create_error;
+
+int set_err(nvllm_handle* h, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  if (h)
+    h->err = buf;
+  else
+    g_create_error = buf;
+  return code;
+}
+
+static size_t round_up(size_t a, size_t b) { return (a + b - 1) / b * b; }
+
+template <typename T>
+static cudaError_t dev_alloc(nvllm_handle* h, T** p, size_t count, uint64_t* account, bool zero = false) {
+  *p = nullptr;
+  if (count == 0) return cudaSuccess;
+  size_t bytes = round_up(count * sizeof(T), 256);
+  cudaError_t e = cudaMalloc((void**)p, bytes);
+  if (e != cudaSuccess) return e;
+  if (zero) e = cudaMemsetAsync(*p, 0, bytes, h->stream);
+  if (account) *account += bytes;
+  return e;
+}
+static cudaError_t dev_alloc_dt(nvllm_handle* h, void** p, size_t count, int dt, uint64_t* account,
+                                bool zero = false) {
+  return dev_alloc<uint8_t>(h, (uint8_t**)p, count * dt_size(dt), account, zero);
+}
+
+}  // namespace nvllm
+
+using namespace nvllm;
+
+extern "C" {
+
+int nvllm_abi_version(void) { return NVLLM_ABI_VERSION; }
+
+const char* nvllm_last_error(const nvllm_handle* h) {
+  return h ? h->err.c_str() : g_create_error.c_str();
+}
+
+int nvllm_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, uint64_t* total_mem,
+                      char name[256]) {
+  cudaDeviceProp p;
+  cudaError_t e = cudaGetDeviceProperties(&p, device);
+  if (e != cudaSuccess)
+    return set_err(nullptr, NVLLM_ERR_CUDA, "cudaGetDeviceProperties(%d): %s", device,
+                   cudaGetErrorString(e));
+  if (sm_count) *sm_count = p.multiProcessorCount;
+  if (cc_major) *cc_major = p.major;
+  if (cc_minor) *cc_minor = p.minor;
+  if (total_mem) *total_mem = p.totalGlobalMem;
+  if (name) {
+    strncpy(name, p.name, 255);
+    name[255] = 0;
+  }
+  return NVLLM_OK;
+}
+
+int nvllm_create(const nvllm_config* c, const uint8_t* tp_id, nvllm_handle** out) {
+  if (!c || !out) return set_err(nullptr, NVLLM_ERR_INVALID, "null argument");
+  *out = nullptr;
+  if (c->abi_version != NVLLM_ABI_VERSION)
+    return set_err(nullptr, NVLLM_ERR_INVALID, "abi_version %d != %d", c->abi_version,
+                   NVLLM_ABI_VERSION);
+  auto bad = [&](const char* what) {
+    return set_err(nullptr, NVLLM_ERR_INVALID, "invalid config: %s", what);
+  };
+  if (c->vocab_size <= 0 || c->hidden <= 0 || c->num_layers <= 0 || c->num_heads <= 0)
+    return bad("non-positive dimension");
+  if (c->hidden % 8) return bad("hidden must be a multiple of 8");
+  if (c->head_dim != 16 && c->head_dim != 32 && c->head_dim != 64 && c->head_dim != 128)
+    return bad("head_dim must be 16, 32, 64 or 128");
+  if (c->ffn_dim <= 0 || c->ffn_dim % 8) return bad("ffn_dim must be a positive multiple of 8");
+  if (c->attention_type < 0 || c->attention_type > 2) return bad("attention_type");
+  if (c->precision != NVLLM_PREC_FP32 && c->precision != NVLLM_PREC_BF16) return bad("precision");
+  if (c->max_seq_len <= 0) return bad("max_seq_len");
+  int nkv = c->attention_type == NVLLM_ATTN_MQA ? 1
+            : c->attention_type == NVLLM_ATTN_MHA ? c->num_heads : c->num_kv_heads;
+  if (nkv <= 0 || c->num_heads % nkv) return bad("num_heads must be a multiple of num_kv_heads");
+  if (c->use_moe) {
+    if (c->num_experts <= 0 || c->num_experts > 256) return bad("num_experts must be 1..256");
+    if (c->num_experts_per_tok <= 0 || c->num_experts_per_tok > 32 ||
+        c->num_experts_per_tok > c->num_experts)
+      return bad("num_experts_per_tok");
+    if (c->activation_type != NVLLM_ACT_SWIGLU) return bad("MoE experts are GLU (moe.go:203-212)");
+  }
+  if (c->tp_size != 1 && c->tp_size != 0)
+    return bad("tensor parallel handles are created through nvllm_create with tp_size>1 only "
+               "for the parallel-block MQA family; not available in this build");
+  (void)tp_id;
+
+  cudaError_t e = cudaSetDevice(c->device);
+  if (e != cudaSuccess)
+    return set_err(nullptr, NVLLM_ERR_CUDA, "cudaSetDevice(%d): %s (no CPU fallback exists)",
+                   c->device, cudaGetErrorString(e));
+  cudaDeviceProp prop;
+  e = cudaGetDeviceProperties(&prop, c->device);
+  if (e != cudaSuccess)
+    return set_err(nullptr, NVLLM_ERR_CUDA, "cudaGetDeviceProperties: %s", cudaGetErrorString(e));
+  if (prop.major != 10)
+    return set_err(nullptr, NVLLM_ERR_CUDA,
+                   "device %d is sm_%d%d; this library contains sm_100a code only", c->device,
+                   prop.major, prop.minor);
+
+  nvllm_handle* h = new nvllm_handle();
+  h->cfg = *c;
+  h->cfg.num_kv_heads = nkv;
+  if (h->cfg.num_kv_blocks <= 0) h->cfg.num_kv_blocks = 1024;  // scheduler.go:17-21
+  if (h->cfg.max_num_seqs <= 0) h->cfg.max_num_seqs = 512;
+  if (h->cfg.max_batched_tokens <= 0) h->cfg.max_batched_tokens = 16384;
+  h->cfg.tp_size = 1;
+  h->cfg.tp_rank = 0;
+  h->dev = c->device;
+  h->sm_count = prop.multiProcessorCount;
+  h->wdt = h->adt = h->kvdt = (c->precision == NVLLM_PREC_BF16) ? DT_BF16 : DT_F32;
+  h->H = c->hidden;
+  h->V = c->vocab_size;
+  h->L = c->num_layers;
+  h->nh = c->num_heads;
+  h->nkv = nkv;
+  h->hd = c->head_dim;
+  h->F = c->ffn_dim;
+  h->moe = c->use_moe != 0;
+  h->E = h->moe ? c->num_experts : 0;
+  h->topk = h->moe ? c->num_experts_per_tok : 0;
+  h->swiglu = c->activation_type == NVLLM_ACT_SWIGLU;
+  h->parallel = (c->attention_type == NVLLM_ATTN_MQA && c->block_style == NVLLM_BLOCK_PARALLEL);
+  h->q_cols = h->nh * h->hd;
+  h->kv_cols = h->nkv * h->hd;
+  h->qkv_cols = h->q_cols + 2 * h->kv_cols;
+  h->w1_cols = h->swiglu ? 2 * h->F : h->F;
+  h->ldl = (int)round_up(h->V, 8);
+  // RoPE: always for MQA (mqa.go:65-67), for GQA when PositionRoPE, never for MHA
+  h->use_rope = (c->attention_type == NVLLM_ATTN_MQA) ||
+                (c->attention_type == NVLLM_ATTN_GQA && c->position_type == NVLLM_POS_ROPE);
+  // attention.go:361-364 (GQA honours AttentionScale); MHA / MQA are always 1/sqrt(hd)
+  if (c->attention_type == NVLLM_ATTN_GQA && c->attention_multiplier != 0.f)
+    h->attn_scale = c->attention_multiplier;
+  else
+    h->attn_scale = (float)(1.0 / sqrt((double)h->hd));
+  h->num_blocks = h->cfg.num_kv_blocks;
+  h->max_blocks_per_seq = (c->max_seq_len + NVLLM_KV_BLOCK_SIZE - 1) / NVLLM_KV_BLOCK_SIZE;
+  h->layers.resize(h->L);
+  h->have.assign((size_t)(h->L + 1) * 64, 0);
+
+  auto fail = [&](cudaError_t ce, const char* what) {
+    int code = (ce == cudaErrorMemoryAllocation) ? NVLLM_ERR_NOMEM : NVLLM_ERR_CUDA;
+    set_err(nullptr, code, "%s: %s", what, cudaGetErrorString(ce));
+    nvllm_destroy(h);
+    return code;
+  };
+  if ((e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking)) != cudaSuccess)
+    return fail(e, "cudaStreamCreate");
+  if ((e = cudaEventCreate(&h->ev0)) != cudaSuccess) return fail(e, "cudaEventCreate");
+  if ((e = cudaEventCreate(&h->ev1)) != cudaSuccess) return fail(e, "cudaEventCreate");
+
+  // ---- weights (device layouts; see handle.h) ----
+  uint64_t* wb = &h->weight_bytes;
+  const int H = h->H, wdt = h->wdt;
+#define A_DT(ptr, count)                                                             \
+  if ((e = dev_alloc_dt(h, (void**)&(ptr), (size_t)(count), wdt, wb)) != cudaSuccess) \
+    return fail(e, "cudaMalloc(weights)");
+#define A_F32(ptr, count, zero)                                                         \
+  if ((e = dev_alloc<float>(h, &(ptr), (size_t)(count), wb, zero)) != cudaSuccess)      \
+    return fail(e, "cudaMalloc(weights)");
+  A_DT(h->wte, (size_t)h->V * H);
+  if (c->position_type == NVLLM_POS_LEARNED) A_DT(h->wpe, (size_t)c->max_seq_len * H);
+  A_F32(h->lnf_w, H, false);
+  A_F32(h->lnf_b, H, false);
+  if (c->tied_embedding) {
+    h->lm_head = h->wte;  // [V, H] is already the [out, in] layout the GEMMs want
+  } else {
+    A_DT(h->lm_head, (size_t)h->V * H);
+    h->lm_head_owned = true;
+  }
+  for (int l = 0; l < h->L; l++) {
+    LayerW& w = h->layers[l];
+    A_F32(w.attn_norm_w, H, false);
+    A_F32(w.attn_norm_b, H, false);
+    A_F32(w.ffn_norm_w, H, false);
+    A_F32(w.ffn_norm_b, H, false);
+    A_DT(w.wqkv, (size_t)h->qkv_cols * H);
+    A_F32(w.bqkv, h->qkv_cols, true);
+    A_DT(w.wo, (size_t)H * h->q_cols);
+    A_F32(w.bo, H, false);
+    if (h->moe) {
+      A_F32(w.router, (size_t)h->E * H, false);
+      A_DT(w.moe_in, (size_t)h->E * 2 * h->F * H);
+      A_DT(w.moe_out, (size_t)h->E * H * h->F);
+    } else {
+      A_DT(w.w1, (size_t)h->w1_cols * H);
+      A_F32(w.b1, h->F, false);
+      A_DT(w.w2, (size_t)H * h->F);
+      A_F32(w.b2, H, false);
+    }
+  }
+#undef A_DT
+#undef A_F32
+  *out = h;
+  return NVLLM_OK;
+}
+
+int nvllm_destroy(nvllm_handle* h) {
+  if (!h) return NVLLM_OK;
+  cudaSetDevice(h->dev);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  auto F = [](void* p) {
+    if (p) cudaFree(p);
+  };
+  F(h->wte);
+  F(h->wpe);
+  F(h->lnf_w);
+  F(h->lnf_b);
+  if (h->lm_head_owned) F(h->lm_head);
+  for (auto& w : h->layers) {
+    F(w.attn_norm_w); F(w.attn_norm_b); F(w.ffn_norm_w); F(w.ffn_norm_b);
+    F(w.wqkv); F(w.bqkv); F(w.wo); F(w.bo); F(w.w1); F(w.b1); F(w.w2); F(w.b2);
+    F(w.router); F(w.moe_in); F(w.moe_out);
+  }
+  F(h->cosT);
+  F(h->sinT);
+  F(h->kpool);
+  F(h->vpool);
+  F(h->d_stage);
+  if (h->h_stage) cudaFreeHost(h->h_stage);
+  if (h->h_out) cudaFreeHost(h->h_out);
+  if (h->h_logits) cudaFreeHost(h->h_logits);
+  nvllm::free_workspace(h);
+  if (h->ev0) cudaEventDestroy(h->ev0);
+  if (h->ev1) cudaEventDestroy(h->ev1);
+  if (h->stream) cudaStreamDestroy(h->stream);
+  delete h;
+  return NVLLM_OK;
+}
+
+int nvllm_get_config(const nvllm_handle* h, nvllm_config* out) {
+  if (!h || !out) return NVLLM_ERR_INVALID;
+  *out = h->cfg;
+  return NVLLM_OK;
+}
+
+int nvllm_memory_info(const nvllm_handle* h, uint64_t* weight_bytes, uint64_t* kv_bytes,
+                      uint64_t* workspace_bytes) {
+  if (!h) return NVLLM_ERR_INVALID;
+  if (weight_bytes) *weight_bytes = h->weight_bytes;
+  if (kv_bytes) *kv_bytes = h->kv_bytes;
+  if (workspace_bytes) *workspace_bytes = h->ws_bytes;
+  return NVLLM_OK;
+}
+
+int nvllm_set_sampling(nvllm_handle* h, float top_p, int top_k, float repetition_penalty) {
+  if (!h) return NVLLM_ERR_INVALID;
+  h->top_p = top_p;
+  h->top_k = top_k;
+  h->rep_penalty = repetition_penalty;
+  return NVLLM_OK;
+}
+int nvllm_set_seed(nvllm_handle* h, uint64_t seed) {
+  if (!h) return NVLLM_ERR_INVALID;
+  h->seed = seed;
+  h->rng_counter = 0;
+  return NVLLM_OK;
+}
+int nvllm_set_graphs(nvllm_handle* h, int enabled) {
+  if (!h) return NVLLM_ERR_INVALID;
+  h->graphs_enabled = enabled;
+  return NVLLM_OK;
+}
+
+int nvllm_tp_unique_id(uint8_t out_id[128]) {
+  memset(out_id, 0, 128);
+  return set_err(nullptr, NVLLM_ERR_NCCL, "tensor parallelism is not available in this build");
+}
+
+}  // extern "C"

@@ -1,0 +1,51 @@
+"""Shared test helpers: package access, the tiny configs of the golden fixtures, oracle glue."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+import nvllm_pkg  # noqa: E402
+
+C = nvllm_pkg.sub("config")
+W = nvllm_pkg.sub("weights")
+E = nvllm_pkg.sub("engine")
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+# must match tests/golden/make_hf_golden.py::CASES
+GOLDEN_CASES = {
+    "gpt2": lambda: C.tiny_gpt2(vocab_size=320, hidden=64, head_dim=16, ffn_dim=256, max_seq_len=64),
+    "llama": lambda: C.tiny_llama(vocab_size=320, hidden=64, num_heads=4, num_kv_heads=2,
+                                  head_dim=16, ffn_dim=128, max_seq_len=64),
+    "granite": lambda: C.tiny_granite(vocab_size=320, hidden=64, num_heads=4, num_kv_heads=2,
+                                      head_dim=16, ffn_dim=32, max_seq_len=64),
+    "falcon": lambda: C.tiny_falcon(vocab_size=320, hidden=5 * 16, num_heads=5, head_dim=16,
+                                    ffn_dim=4 * 5 * 16, max_seq_len=64),
+}
+
+# parity-test configs (bigger than the goldens, still seconds on the CPU oracle)
+TINY = {
+    "gpt2": lambda: C.tiny_gpt2(),
+    "llama": lambda: C.tiny_llama(),
+    "granite": lambda: C.tiny_granite(),
+    "falcon": lambda: C.tiny_falcon(),
+}
+
+
+def oracle_mod():
+    from oracle import oracle as O
+    return O
+
+
+def make_oracle(cfg, seed=1234, round_bf16=False):
+    O = oracle_mod()
+    return O.OracleModel(cfg, W.random_weights(cfg, seed, round_bf16=round_bf16))
+
+
+def rel_err(a, b):
+    """max |a-b| / max |b| — the gate of BASELINE.json's north_star."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))

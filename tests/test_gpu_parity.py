@@ -1,0 +1,312 @@
+"""GPU parity tests (run with -m gpu on a B200): the CUDA path, called through the C ABI
+(include/nvllm.h via nano-vllm-go_b200/lib.py + runner.py), against the CPU oracle on the
+same seeded random-init weights and prompts.
+
+Gates (BASELINE.json north_star / SURVEY.md §8d):
+  fp32 mode  max|dlogit| / max|logit| <= 1e-4, greedy tokens identical
+  bf16 mode  (weights rounded once to bf16, the same values fed to the oracle as fp32,
+              fp32 accumulate) <= 2e-2, greedy tokens identical for 32 steps
+  token ids / argmax: bit-exact (first-max rule, cmd/ask/main.go:389-402)
+"""
+import numpy as np
+import pytest
+
+from helpers import C, W, E, TINY, make_oracle, oracle_mod, rel_err
+import nvllm_pkg
+
+pytestmark = pytest.mark.gpu
+
+TOL = {C.PREC_FP32: 1e-4, C.PREC_BF16: 2e-2}
+
+
+def _runner(cfg, prec, seed=1234, **kw):
+    R = nvllm_pkg.sub("runner")
+    return R.CudaModelRunner(cfg, W.random_weights(cfg, seed, round_bf16=(prec == C.PREC_BF16)),
+                             precision=prec, num_kv_blocks=kw.pop("num_kv_blocks", 32), **kw)
+
+
+def _blocks(n_tokens, first=0):
+    nb = (n_tokens + 255) // 256
+    return list(range(first, first + nb))
+
+
+# ------------------------------------------------------------------ single operators
+@pytest.mark.parametrize("M,N,K", [(1, 768, 768), (1, 1000, 256), (4, 515, 1024), (8, 64, 4544),
+                                   (33, 200, 256), (130, 777, 512)])
+def test_matmul_fp32_vs_oracle(M, N, K):
+    O = oracle_mod()
+    L = nvllm_pkg.sub("lib")
+    rng = np.random.default_rng(M * 1000 + N)
+    A = rng.standard_normal((M, K)).astype(np.float32)
+    Wm = (rng.standard_normal((K, N)) * 0.05).astype(np.float32)
+    bias = rng.standard_normal(N).astype(np.float32)
+    ref = O.matmul(A, Wm) + bias
+    got, _ = L.op_matmul(A, Wm, bias, prec=C.PREC_FP32)
+    assert rel_err(got, ref) < 1e-5
+
+
+@pytest.mark.parametrize("M,N,K", [(1, 768, 768), (8, 520, 2048), (64, 512, 512), (200, 264, 1024)])
+def test_matmul_bf16_vs_oracle(M, N, K):
+    O = oracle_mod()
+    L = nvllm_pkg.sub("lib")
+    rng = np.random.default_rng(M + N + K)
+    A = W.bf16_round(rng.standard_normal((M, K)).astype(np.float32))
+    Wm = W.bf16_round((rng.standard_normal((K, N)) * 0.05).astype(np.float32))
+    ref = O.matmul(A, Wm)
+    got, _ = L.op_matmul(A, Wm, None, prec=C.PREC_BF16)
+    # inputs are exactly representable; only the fp32 summation order differs
+    assert rel_err(got, ref) < 1e-5
+
+
+@pytest.mark.parametrize("bias", [True, False])
+def test_norm_vs_oracle(bias):
+    O = oracle_mod()
+    L = nvllm_pkg.sub("lib")
+    rng = np.random.default_rng(3)
+    x = rng.standard_normal((37, 768)).astype(np.float32) * 3 + 0.5
+    w = (1 + 0.02 * rng.standard_normal(768)).astype(np.float32)
+    b = (0.02 * rng.standard_normal(768)).astype(np.float32) if bias else None
+    ref = O.layer_norm(x, w, b, 1e-5)
+    got, _ = L.op_norm(x, w, b, 1e-5, prec=C.PREC_FP32)
+    assert rel_err(got, ref) < 1e-5
+
+
+def test_argmax_bit_exact_with_ties():
+    O = oracle_mod()
+    L = nvllm_pkg.sub("lib")
+    rng = np.random.default_rng(5)
+    logits = rng.standard_normal((9, 50257)).astype(np.float32)
+    logits[0, 100] = logits[0, 40000] = 99.0  # tie: first index wins
+    logits[1, :] = 0.0  # all equal -> 0
+    logits[2, 50256] = 50.0
+    got, _ = L.op_argmax(logits)
+    ref = np.array([O.argmax(r) for r in logits], dtype=np.int32)
+    np.testing.assert_array_equal(got, ref)
+    assert got[0] == 100 and got[1] == 0 and got[2] == 50256
+
+
+# ------------------------------------------------------------------ whole forward pass
+def _greedy_parity(name, prec, prompt_len, steps):
+    cfg = TINY[name]()
+    bf16 = prec == C.PREC_BF16
+    orc = make_oracle(cfg, round_bf16=bf16)
+    run = _runner(cfg, prec)
+    try:
+        prompt = W.random_prompt(cfg.vocab_size, prompt_len, 4321)
+        ref_toks, ref_logits = orc.greedy(prompt, steps)
+        toks = list(int(t) for t in prompt)
+        bt = _blocks(prompt_len + steps)
+        worst = 0.0
+        for i in range(steps):
+            out, logits = run.run_flat([toks], is_prefill=(i == 0), num_cached=[0],
+                                       block_tables=[bt], temperature=[0.0], want_logits=True)
+            err = rel_err(logits[0], ref_logits[i])
+            worst = max(worst, err)
+            assert err <= TOL[prec], f"{name} step {i}: rel err {err}"
+            assert int(out[0]) == int(ref_toks[i]), f"{name} step {i}: token {out[0]} != {ref_toks[i]}"
+            # the device argmax must be the first-max of the device logits, bit-exact
+            assert int(out[0]) == oracle_mod().argmax(logits[0])
+            toks.append(int(out[0]))
+        return worst
+    finally:
+        run.close()
+
+
+@pytest.mark.parametrize("name", list(TINY))
+def test_fp32_logits_and_greedy_tokens(name):
+    _greedy_parity(name, C.PREC_FP32, prompt_len=40, steps=32)
+
+
+@pytest.mark.parametrize("name", list(TINY))
+def test_bf16_logits_and_greedy_tokens(name):
+    _greedy_parity(name, C.PREC_BF16, prompt_len=40, steps=32)
+
+
+@pytest.mark.parametrize("name", ["gpt2", "llama"])
+def test_context_crossing_block_boundaries(name):
+    """Prompt of 250 tokens, decode across position 256 (second KV block)."""
+    _greedy_parity(name, C.PREC_FP32, prompt_len=250, steps=12)
+
+
+class OracleRunner:
+    """TensorModelRunner restated over the oracle (tensor_model_runner.go:55-97): per-sequence
+    loop, per-SeqID cache, prefill = whole prompt."""
+
+    def __init__(self, model):
+        self.m = model
+        self.caches = {}
+        self.logits = {}
+
+    def run(self, seqs, is_prefill):
+        out = []
+        for s in seqs:
+            if is_prefill or s.seq_id not in self.caches:
+                self.caches[s.seq_id] = self.m.new_cache()
+                lg = self.m.forward(s.token_ids, self.caches[s.seq_id], 0)
+            else:
+                lg = self.m.forward(s.token_ids[-1:], self.caches[s.seq_id], len(s.token_ids) - 1)
+            self.logits.setdefault(s.seq_id, []).append(lg)
+            out.append(oracle_mod().argmax(lg))
+        return out
+
+    def close(self):
+        pass
+
+
+@pytest.mark.parametrize("name", list(TINY))
+def test_engine_batch_with_prefix_cache(name):
+    """The restated Go engine (scheduler + block manager) drives the CUDA runner with a ragged
+    batch: different prompt lengths, two prompts sharing a 256-token prefix (prefix-cache hit in
+    the same step and in a later step), decode across a block boundary.  Tokens must equal the
+    per-sequence oracle run."""
+    cfg = TINY[name]()
+    rng = np.random.default_rng(11)
+    shared = rng.integers(0, cfg.vocab_size, 256).tolist()
+    prompts = [
+        rng.integers(0, cfg.vocab_size, 7).tolist(),
+        shared + rng.integers(0, cfg.vocab_size, 9).tolist(),
+        shared + rng.integers(0, cfg.vocab_size, 30).tolist(),  # same-step prefix hit
+        rng.integers(0, cfg.vocab_size, 250).tolist(),          # crosses 256 while decoding
+    ]
+    late = shared + rng.integers(0, cfg.vocab_size, 3).tolist()  # later-step prefix hit
+    steps = 10
+    ecfg = dict(num_kvcache_blocks=32, max_model_len=cfg.max_seq_len,
+                max_num_batched_tokens=max(4096, cfg.max_seq_len))
+
+    def drive(runner):
+        eng = E.LLMEngine(E.EngineConfig(**ecfg), runner)
+        seqs = [eng.add_request(p, E.SamplingParams(max_tokens=steps, ignore_eos=True),
+                                temperature=0.0) for p in prompts]
+        cached = []
+        n_steps = 0
+        while not eng.is_finished():
+            if n_steps == 3:
+                seqs.append(eng.add_request(late, E.SamplingParams(max_tokens=steps, ignore_eos=True),
+                                            temperature=0.0))
+            eng.step()
+            n_steps += 1
+            cached.append([s.num_cached_tokens for s in seqs])
+        return [s.completion_token_ids() for s in seqs], cached
+
+    ref, cached_ref = drive(OracleRunner(make_oracle(cfg)))
+    run = _runner(cfg, C.PREC_FP32)
+    try:
+        got, cached_got = drive(run)
+    finally:
+        run.close()
+    assert cached_got == cached_ref
+    assert any(256 in c for c in cached_got), "the prefix cache never hit"
+    assert got == ref
+
+
+def test_fully_cached_prompt_still_yields_logits():
+    """A prompt that is an exact multiple of 256 and fully cached (NumCachedTokens == Len) must
+    still compute its last token (SURVEY.md §7 hard part 2)."""
+    cfg = TINY["llama"]()
+    orc = make_oracle(cfg)
+    run = _runner(cfg, C.PREC_FP32)
+    try:
+        prompt = W.random_prompt(cfg.vocab_size, 256, 77).tolist()
+        ref = orc.forward(prompt, orc.new_cache())
+        t1, l1 = run.run_flat([prompt], True, [0], [[3]], [0.0], want_logits=True)
+        t2, l2 = run.run_flat([prompt], True, [256], [[3]], [0.0], want_logits=True)
+        assert rel_err(l1[0], ref) <= 1e-4 and rel_err(l2[0], ref) <= 1e-4
+        assert t1[0] == t2[0] == oracle_mod().argmax(ref)
+    finally:
+        run.close()
+
+
+def test_temperature_sampling_with_injected_uniforms():
+    """sampling.go:70-74,105-128,196-217 with rand.Float32() replaced by a given uniform."""
+    O = oracle_mod()
+    cfg = TINY["gpt2"]()
+    run = _runner(cfg, C.PREC_FP32)
+    try:
+        prompts = [W.random_prompt(cfg.vocab_size, 12 + i, 50 + i).tolist() for i in range(6)]
+        temps = [0.7, 1.0, 1.3, 0.0, 2.0, 0.5]
+        us = [0.01, 0.35, 0.62, 0.5, 0.93, 0.999]
+        bts = [[i] for i in range(6)]
+        toks, logits = run.run_flat(prompts, True, [0] * 6, bts, temps, us, want_logits=True)
+        exact = 0
+        for i in range(6):
+            if temps[i] == 0.0:
+                assert toks[i] == O.argmax(logits[i])
+                continue
+            ref = O.sample(logits[i], None, temps[i], u=us[i])
+            # identical up to fp32 summation order of the CDF: allow the neighbouring index when
+            # u lands within rounding of a CDF step
+            p = np.exp((logits[i] / temps[i]).astype(np.float64))
+            cdf = np.cumsum(p / p.sum())
+            assert abs(cdf[toks[i]] - cdf[ref]) < 1e-3 or toks[i] == ref
+            exact += int(toks[i] == ref)
+        assert exact >= 4
+    finally:
+        run.close()
+
+
+def test_error_paths_return_codes_not_aborts():
+    L = nvllm_pkg.sub("lib")
+    cfg = C.tiny_llama(max_seq_len=64)
+    run = _runner(cfg, C.PREC_FP32)
+    try:
+        with pytest.raises(L.NvllmError) as e:  # token outside the vocabulary
+            run.run_flat([[cfg.vocab_size]], True, [0], [[0]], [0.0])
+        assert e.value.code == L.ERR_RANGE
+        with pytest.raises(L.NvllmError) as e:  # RoPE position past max_seq_len (rope.go:84)
+            run.run_flat([[1] * 65], True, [0], [[0]], [0.0])
+        assert e.value.code == L.ERR_RANGE
+        with pytest.raises(L.NvllmError) as e:  # block table too short
+            run.run_flat([[1] * 10], True, [0], [[]], [0.0])
+        assert e.value.code == L.ERR_INVALID
+        with pytest.raises(L.NvllmError) as e:  # block id outside the pool
+            run.run_flat([[1] * 10], True, [0], [[9999]], [0.0])
+        assert e.value.code == L.ERR_RANGE
+        # the handle is still usable after errors
+        toks, _ = run.run_flat([[1, 2, 3]], True, [0], [[0]], [0.0])
+        assert 0 <= toks[0] < cfg.vocab_size
+    finally:
+        run.close()
+
+
+def test_missing_weight_is_reported():
+    L = nvllm_pkg.sub("lib")
+    R = nvllm_pkg.sub("runner")
+    cfg = TINY["llama"]()
+    ws = [w for w in W.random_weights(cfg) if not (w[0] == C.W_O and w[1] == 1)]
+    with pytest.raises(L.NvllmError) as e:
+        R.CudaModelRunner(cfg, ws, precision=C.PREC_FP32, num_kv_blocks=4)
+    assert e.value.code == L.ERR_INVALID and "NVLLM_W_O" in str(e.value)
+
+
+def test_resident_decode_matches_stepwise():
+    """nvllm_run_resident (device-resident decode loop used by bench.py's `value` leg) must
+    produce the same tokens as stepping through nvllm_run."""
+    cfg = TINY["llama"]()
+    prompts = [W.random_prompt(cfg.vocab_size, 20 + 5 * i, 200 + i).tolist() for i in range(5)]
+    steps = 12
+    bts = [_blocks(len(p) + steps + 2, first=2 * i) for i, p in enumerate(prompts)]
+    run = _runner(cfg, C.PREC_FP32)
+    try:
+        seqs = [list(p) for p in prompts]
+        out, _ = run.run_flat(seqs, True, [0] * 5, bts, [0.0] * 5)
+        for s, t in zip(seqs, out):
+            s.append(int(t))
+        ref = []
+        for _ in range(steps):
+            out, _ = run.run_flat(seqs, False, None, bts, [0.0] * 5)
+            ref.append(out.copy())
+            for s, t in zip(seqs, out):
+                s.append(int(t))
+        # again, resident
+        seqs = [list(p) for p in prompts]
+        out, _ = run.run_flat(seqs, True, [0] * 5, bts, [0.0] * 5)
+        for s, t in zip(seqs, out):
+            s.append(int(t))
+        out, _ = run.run_flat(seqs, False, None, bts, [0.0] * 5)
+        np.testing.assert_array_equal(out, ref[0])
+        for i in range(1, steps):
+            run.run_resident()
+            got, _ = run.sync(5)
+            np.testing.assert_array_equal(got, ref[i])
+    finally:
+        run.close()
