@@ -215,9 +215,50 @@ int nvllm_run(nvllm_handle* h, int n_seqs, int is_prefill,
  * Used by bench.py for the `value` leg; nvllm_run is the `e2e` leg. */
 int nvllm_run_resident(nvllm_handle* h, nvllm_run_stats* stats);
 
+/* Re-execute the last nvllm_run step from its device-resident staged inputs (no copies, no
+ * host sync).  With nvllm_run_resident this lets a whole prefill + decode job be repeated
+ * with every input already in HBM. */
+int nvllm_rerun(nvllm_handle* h, nvllm_run_stats* stats);
+
+/* Per-kernel-class device timing.  While enabled every launch is bracketed by CUDA events on
+ * the compute stream (slower: use a separate pass from the headline timing); bytes / flops
+ * are the ALGORITHMIC figures of each launch.  nvllm_set_profile resets the
+ * counters; nvllm_get_profile synchronises and fills out[NVLLM_K_COUNT]. */
+enum nvllm_kernel_class {
+  NVLLM_K_EMBED = 0,
+  NVLLM_K_NORM = 1,
+  NVLLM_K_GEMM_TC5 = 2,     /* tcgen05/TMEM/TMA bf16 GEMM */
+  NVLLM_K_GEMV = 3,         /* split-K GEMV, M <= 8 */
+  NVLLM_K_GEMM_SIMT = 4,    /* fp32 parity-mode GEMM */
+  NVLLM_K_ROPE_KV = 5,      /* RoPE + paged KV append */
+  NVLLM_K_ATTN_PREFILL = 6,
+  NVLLM_K_ATTN_DECODE = 7,
+  NVLLM_K_ACT = 8,          /* SwiGLU / GELU */
+  NVLLM_K_MOE_ROUTE = 9,    /* router + top-k + grouping */
+  NVLLM_K_MOE_GEMM = 10,    /* grouped expert GEMMs */
+  NVLLM_K_MOE_MISC = 11,    /* GLU + weighted combine */
+  NVLLM_K_SAMPLE = 12,
+  NVLLM_K_MISC = 13,
+  NVLLM_K_COUNT = 14
+};
+typedef struct nvllm_profile_entry {
+  double ms;
+  double bytes;
+  double flops;
+  int64_t launches;
+} nvllm_profile_entry;
+int nvllm_set_profile(nvllm_handle* h, int enabled);
+int nvllm_get_profile(nvllm_handle* h, nvllm_profile_entry* out);
+
 /* Wait for the resident steps issued so far; optionally read back the last sampled tokens
  * (n <= n_seqs of the last nvllm_run) and the device time of the last step. */
 int nvllm_sync(nvllm_handle* h, int32_t* out_tokens, int n, float* last_step_ms);
+
+/* Device timer on the handle's compute stream, for timing several calls as one region:
+ * which = 0 records the start event, 1 the stop event; nvllm_timer_elapsed synchronises the
+ * stream and returns stop - start in milliseconds. */
+int nvllm_timer_record(nvllm_handle* h, int which);
+int nvllm_timer_elapsed(nvllm_handle* h, float* ms);
 
 /* SetSamplingParamsWithRepetition (tensor_model_runner.go:35-52):
  * repetition_penalty 1.0 disables; top_k 0 disables; top_p 1.0 disables. */

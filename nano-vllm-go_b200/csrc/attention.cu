@@ -74,9 +74,12 @@ attn_prefill_kernel(AttnArgs a) {
       store8(Vs + i, v);
     }
     __syncthreads();
-    if (!qvalid) continue;
-    const int jmax = min(nk, qpos - k0 + 1);  // causal: key position <= query position
-    for (int j0 = 0; j0 < jmax; j0 += 8) {
+    // causal: key position <= query position.  The trip count must be warp-uniform (the
+    // shuffles below name all 32 lanes), so every lane runs to the warp's largest jmax and
+    // masks its own tail.
+    const int jmax = qvalid ? max(0, min(nk, qpos - k0 + 1)) : 0;
+    const int jlim = __reduce_max_sync(0xffffffffu, jmax);
+    for (int j0 = 0; j0 < jlim; j0 += 8) {
       float s[8];
       float cmax = -INFINITY;
 #pragma unroll
@@ -99,6 +102,7 @@ attn_prefill_kernel(AttnArgs a) {
         s[jj] = (j < jmax) ? d : -INFINITY;
         cmax = fmaxf(cmax, s[jj]);
       }
+      if (cmax == -INFINITY) continue;  // nothing visible to this query in the chunk (no shuffles below)
       const float m_new = fmaxf(m, cmax);
       const float corr = __expf(m - m_new);  // m = -inf on the first chunk -> 0
       l *= corr;
@@ -203,9 +207,13 @@ attn_decode_kernel(AttnArgs a) {
     m[g] = -INFINITY;
     l[g] = 0.f;
   }
-  for (int t = t0 + warp * TPI + slot; t < t1; t += NW * TPI) {
-    const int blk = bt[t / KV_BLOCK];
-    const size_t off = (((size_t)blk * a.nkv + kvh) * KV_BLOCK + (t % KV_BLOCK)) * HD + sub * 8;
+  // warp-uniform trip count (the shuffles name all 32 lanes); lanes past t1 are masked
+  for (int tb = t0 + warp * TPI; tb < t1; tb += NW * TPI) {
+    const int t = tb + slot;
+    const bool valid = t < t1;
+    const int tc = valid ? t : t1 - 1;
+    const int blk = bt[tc / KV_BLOCK];
+    const size_t off = (((size_t)blk * a.nkv + kvh) * KV_BLOCK + (tc % KV_BLOCK)) * HD + sub * 8;
     float k[8], v[8];
     load8(kpool + off, k);
     load8(vpool + off, v);
@@ -216,6 +224,7 @@ attn_decode_kernel(AttnArgs a) {
       for (int i = 0; i < 8; i++) d = fmaf(q[g][i], k[i], d);
 #pragma unroll
       for (int o = 1; o < LPT; o <<= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+      if (!valid) continue;
       if (d > m[g]) {  // rescale only when the running max moves
         const float corr = __expf(m[g] - d);
         l[g] *= corr;

@@ -539,4 +539,43 @@ cudaError_t launch_reduce_partials(cudaStream_t st, const float* p, int S, size_
   return cudaGetLastError();
 }
 
+// Build the decode-step state of n sequences from the state of the prefill step that just
+// sampled `sampled`: next position = seq_len, KV slot through the block table.
+__global__ void make_decode_state_kernel(int n, int mb, const int* __restrict__ sampled,
+                                         const int* __restrict__ src_seq_len,
+                                         const int* __restrict__ src_bt,
+                                         const int* __restrict__ src_temp,
+                                         const int* __restrict__ src_uni, int* tokens,
+                                         int* positions, int* slots, int* cu_q, int* seq_start,
+                                         int* seq_len, int* last_row, int* bt, int* temp, int* uni) {
+  const int i = blockIdx.x;
+  for (int b = threadIdx.x; b < mb; b += blockDim.x) bt[(size_t)i * mb + b] = src_bt[(size_t)i * mb + b];
+  if (threadIdx.x == 0) {
+    const int pos = src_seq_len[i];
+    int bi = pos / KV_BLOCK;
+    if (bi >= mb) bi = mb - 1;  // the host checks the range before launching
+    tokens[i] = sampled[i];
+    positions[i] = pos;
+    slots[i] = src_bt[(size_t)i * mb + bi] * KV_BLOCK + pos % KV_BLOCK;
+    cu_q[i] = i;
+    if (i == n - 1) cu_q[n] = n;
+    seq_start[i] = pos;
+    seq_len[i] = pos + 1;
+    last_row[i] = i;
+    temp[i] = src_temp[i];
+    uni[i] = src_uni[i];
+  }
+}
+cudaError_t launch_make_decode_state(cudaStream_t st, int n, int mb, const int* sampled,
+                                     const int* src_seq_len, const int* src_bt, const int* src_temp,
+                                     const int* src_uni, int* tokens, int* positions, int* slots,
+                                     int* cu_q, int* seq_start, int* seq_len, int* last_row, int* bt,
+                                     int* temp, int* uni) {
+  if (n <= 0) return cudaSuccess;
+  make_decode_state_kernel<<<n, 64, 0, st>>>(n, mb, sampled, src_seq_len, src_bt, src_temp, src_uni,
+                                             tokens, positions, slots, cu_q, seq_start, seq_len,
+                                             last_row, bt, temp, uni);
+  return cudaGetLastError();
+}
+
 }  // namespace nvllm

@@ -1,13 +1,353 @@
-// placeholder until the tcgen05 kernel lands (replaced in the next commit)
+// gemm_tcgen05.cu — bf16 tensor-core GEMM for sm_100a: tcgen05.mma with the accumulator in
+// TMEM, operands staged by TMA (cp.async.bulk.tensor, 128-byte swizzle) through an mbarrier
+// ring, warp-specialised (1 TMA warp, 1 MMA warp, 4 epilogue warps).
+//
+// Computes out[s][m][n] = alpha * sum_{k in split s} A[m,k] * W[n,k]   (fp32 split-K partials)
+// for activations A [M,K] and weights W [N,K], both K-contiguous bf16 — the reference's
+// MatMul (tensor.go:62-88) with the weight held [out,in].
+//
+// Orientation ("swap-AB"): the WEIGHT tile is the UMMA M operand (128 weight rows per CTA)
+// and the token tile is the UMMA N operand (BT = 32..256 tokens).  The accumulator in TMEM is
+// therefore D[n][m]: TMEM lane = weight row n, column = token m.  Consequences:
+//   * skinny batched-decode GEMMs (M = 16..128 tokens) still issue full 128-row MMAs and
+//     stream each weight byte exactly once: the kernel is HBM-bound on W;
+//   * in the epilogue each warp owns 32 consecutive n for a given token, so every global
+//     store instruction writes 128 contiguous bytes of out[m][n..n+31].
+#include <cuda.h>
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
 #include "common.cuh"
-#include "handle.h"
+#include "kernels.h"
+
 namespace nvllm {
-bool tc5_supported(int, int, int) { return false; }
-int tc5_splits(int, int, int, int) { return 1; }
-int tc5_box_rows_act(int) { return 128; }
-int tc5_box_rows_w(int) { return 128; }
-int make_tma_2d_bf16(TmaDesc*, const void*, uint64_t, uint64_t, uint64_t, uint32_t, std::string*) { return 0; }
-cudaError_t launch_gemm_tc5(cudaStream_t, const Tc5Args&, int) { return cudaErrorNotSupported; }
-int build_weight_maps(nvllm_handle*) { return 0; }
-int build_activation_maps(nvllm_handle*) { return 0; }
+
+constexpr int TC_BN = 128;  // weight rows per CTA (UMMA M)
+constexpr int TC_BK = 64;   // k elements per stage = one 128-byte swizzle row of bf16
+constexpr int TC_THREADS = 192;
+
+// ------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
 }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* map, uint32_t bar, int c0,
+                                            int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const void* map, uint32_t bar,
+                                                 int c0, int c1, uint64_t policy) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+      " [%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(policy)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+               : "memory");
+}
+// D[tmem] (+)= A[smem desc] * B[smem desc]^T, bf16 inputs, fp32 accumulate
+__device__ __forceinline__ void tc_mma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                            uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// K-major, 128-byte swizzle shared-memory matrix descriptor (cute/arch/mma_sm100_desc.hpp
+// layout: start>>4 [0,14), LBO>>4 [16,30), SBO>>4 [32,46), version=1 [46,48), layout [61,64)).
+// Rows are 128 B apart, 8-row swizzle atoms 1024 B apart (SBO); LBO is unused for swizzled
+// K-major operands (1).
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((addr & 0x3FFFF) >> 4);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;  // SWIZZLE_128B
+  return d;
+}
+// 32 lanes x 32 consecutive columns of fp32 -> 32 registers per thread
+__device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+        "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+        "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]),
+        "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+        "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// ------------------------------------------------------------------ kernel
+template <int BT, int STAGES>
+__global__ void __launch_bounds__(TC_THREADS)
+gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
+                int M, int N, int K, int kb_per_split, float* __restrict__ out, int ldo,
+                size_t split_stride, float alpha) {
+  constexpr uint32_t W_BYTES = TC_BN * TC_BK * 2;
+  constexpr uint32_t A_BYTES = BT * TC_BK * 2;
+  constexpr uint32_t STAGE_BYTES = W_BYTES + A_BYTES;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B needs 1024 B
+  const uint32_t bars = tiles + STAGES * STAGE_BYTES;
+  // full[s] at bars + 8 s, empty[s] at bars + 8 (STAGES + s), tmem_full, tmem slot
+  const uint32_t bar_tmem_full = bars + 16 * STAGES;
+  const uint32_t tmem_slot = bar_tmem_full + 8;
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(
+      smem_raw + (tmem_slot - smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * TC_BN;
+  const int m0 = blockIdx.y * BT;
+  const int nkb_total = (K + TC_BK - 1) / TC_BK;
+  const int kb0 = blockIdx.z * kb_per_split;
+  const int nkb = min(kb_per_split, nkb_total - kb0);
+
+  if (warp == 0 && lane == 0) {
+    for (int s = 0; s < STAGES; s++) {
+      mbar_init(bars + 8 * s, 1);
+      mbar_init(bars + 8 * (STAGES + s), 1);
+    }
+    mbar_init(bar_tmem_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
+                 "r"((uint32_t)BT)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // weights are read once per step: keep them from displacing activations in L2
+      uint64_t pol_w, pol_a;
+      asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
+      asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_a));
+      for (int i = 0; i < nkb; i++) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);
+        const uint32_t full = bars + 8 * s;
+        mbar_expect_tx(full, STAGE_BYTES);
+        const uint32_t dst = tiles + s * STAGE_BYTES;
+        const int k = (kb0 + i) * TC_BK;
+        tma_load_2d_hint(dst, &tmW, full, k, n0, pol_w);
+        tma_load_2d_hint(dst + W_BYTES, &tmA, full, k, m0, pol_a);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // instruction descriptor (cute/arch/mma_sm100_desc.hpp): fp32 accumulate, bf16 x bf16,
+      // both K-major, N = BT, M = 128
+      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BT >> 3) << 17) |
+                                 ((uint32_t)(TC_BN >> 4) << 24);
+      for (int i = 0; i < nkb; i++) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(bars + 8 * s, ph);
+        tc_fence_after();
+        const uint32_t wt = tiles + s * STAGE_BYTES;
+        const uint64_t wdesc = make_smem_desc(wt);
+        const uint64_t adesc = make_smem_desc(wt + W_BYTES);
+#pragma unroll
+        for (int kk = 0; kk < TC_BK / 16; kk++) {
+          // advancing 16 bf16 = 32 bytes inside the swizzle row: +2 in the >>4 address field
+          tc_mma_bf16(tmem_base, wdesc + 2 * kk, adesc + 2 * kk, idesc, (i | kk) != 0);
+        }
+        tc_commit(bars + 8 * (STAGES + s));  // frees the stage when these MMAs retire
+      }
+      tc_commit(bar_tmem_full);
+    }
+  } else {
+    // epilogue: warp w may touch TMEM lanes [32 (w % 4), +32)
+    const int q = warp & 3;
+    const int n = n0 + q * 32 + lane;
+    mbar_wait(bar_tmem_full, 0);
+    tc_fence_after();
+    float* obase = out + (size_t)blockIdx.z * split_stride + n;
+    const bool n_ok = n < N;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BT; c0 += 32) {
+      if (m0 + c0 >= M) break;
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+      if (n_ok) {
+#pragma unroll
+        for (int c = 0; c < 32; c++) {
+          const int m = m0 + c0 + c;
+          if (m < M) obase[(size_t)m * ldo] = alpha * __uint_as_float(r[c]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "r"((uint32_t)BT)
+                 : "memory");
+  }
+}
+
+// ------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return (EncodeTiledFn)p;
+  }();
+  return fn;
+}
+
+int make_tma_2d_bf16(TmaDesc* out, const void* base, uint64_t rows, uint64_t cols,
+                     uint64_t row_stride_elems, uint32_t box_rows, std::string* err) {
+  static_assert(sizeof(CUtensorMap) == sizeof(TmaDesc), "CUtensorMap is 128 bytes");
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) {
+    if (err) *err = "cuTensorMapEncodeTiled is not available from this driver";
+    return -1;
+  }
+  cuuint64_t dims[2] = {cols, rows};
+  cuuint64_t strides[1] = {row_stride_elems * 2};
+  cuuint32_t box[2] = {(cuuint32_t)TC_BK, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(reinterpret_cast<CUtensorMap*>(out), CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    if (err) *err = "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r);
+    return -1;
+  }
+  return 0;
+}
+
+// tensor maps are pure functions of (pointer, shape, box): memoise them
+static const TmaDesc* cached_map(const void* base, int rows, int cols, int box_rows) {
+  static std::mutex mu;
+  static std::map<std::tuple<const void*, int, int, int>, TmaDesc> cache;
+  std::lock_guard<std::mutex> g(mu);
+  auto key = std::make_tuple(base, rows, cols, box_rows);
+  auto it = cache.find(key);
+  if (it != cache.end()) return &it->second;
+  if (cache.size() > 65536) cache.clear();
+  TmaDesc d;
+  if (make_tma_2d_bf16(&d, base, rows, cols, cols, box_rows, nullptr)) return nullptr;
+  return &cache.emplace(key, d).first->second;
+}
+
+bool tc5_supported(int M, int N, int K) { return M >= 1 && N >= 1 && K >= 8 && (K % 8) == 0; }
+
+static int pick_bt(int M) { return M <= 32 ? 32 : (M <= 64 ? 64 : 128); }
+int tc5_box_rows_act(int M) { return pick_bt(M); }
+
+int tc5_splits(int M, int N, int K, int sm_count) {
+  const int bt = pick_bt(M);
+  const long tiles = (long)ceil_div(N, TC_BN) * ceil_div(M, bt);
+  const int nkb = ceil_div(K, TC_BK);
+  if (tiles >= 2L * sm_count) return 1;
+  int s = (int)((2L * sm_count + tiles - 1) / tiles);
+  s = min(s, max(1, nkb / 4));  // at least 4 k-blocks (256 k) per split
+  s = min(s, 16);
+  return max(s, 1);
+}
+
+template <int BT, int STAGES>
+static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* tw,
+                             const TmaDesc* ta, int S) {
+  constexpr size_t smem = (size_t)STAGES * (TC_BN + BT) * TC_BK * 2 + 1024 + 16 * STAGES + 64;
+  static uint64_t attr_mask = 0;  // per device
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (!(attr_mask >> dev & 1)) {
+    cudaError_t e = cudaFuncSetAttribute(gemm_tc5_kernel<BT, STAGES>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    attr_mask |= 1ull << dev;
+  }
+  const int nkb = ceil_div(a.K, TC_BK);
+  const int kbps = ceil_div(nkb, S);
+  dim3 grid(ceil_div(a.N, TC_BN), ceil_div(a.M, BT), ceil_div(nkb, kbps));
+  gemm_tc5_kernel<BT, STAGES><<<grid, TC_THREADS, smem, st>>>(
+      *reinterpret_cast<const CUtensorMap*>(tw), *reinterpret_cast<const CUtensorMap*>(ta), a.M, a.N,
+      a.K, kbps, a.out, a.ldo, a.split_stride, a.alpha);
+  return cudaGetLastError();
+}
+
+// a.S is the requested number of splits; the number actually written is returned in *S_out
+cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int* S_out) {
+  if (!tc5_supported(a.M, a.N, a.K)) return cudaErrorInvalidValue;
+  const int bt = pick_bt(a.M);
+  const TmaDesc* tw = cached_map(a.W, a.N, a.K, TC_BN);
+  const TmaDesc* ta = cached_map(a.A, a.M, a.K, bt);
+  if (!tw || !ta) return cudaErrorInvalidValue;
+  const int nkb = ceil_div(a.K, TC_BK);
+  int S = max(1, min(a.S, nkb));
+  const int kbps = ceil_div(nkb, S);
+  S = ceil_div(nkb, kbps);
+  if (S_out) *S_out = S;
+  if (a.out_capacity && (size_t)S * a.split_stride > a.out_capacity) return cudaErrorInvalidValue;
+  switch (bt) {
+    case 32: return launch_bt<32, 5>(st, a, tw, ta, S);
+    case 64: return launch_bt<64, 4>(st, a, tw, ta, S);
+    default: return launch_bt<128, 3>(st, a, tw, ta, S);
+  }
+}
+
+}  // namespace nvllm

@@ -27,13 +27,17 @@ struct LayerW {
   void* moe_in = nullptr;   // [E, 2I, H]
   void* moe_out = nullptr;  // [E, H, I]
   bool has_bq = false, has_bk = false, has_bv = false;
-  TmaDesc tm_wqkv, tm_wo, tm_w1, tm_w2;
 };
 
 // one engine step's integer inputs, packed in a single pinned host buffer and copied with
 // one cudaMemcpyAsync; the device pointers below point into the device mirror
 struct StepLayout {
   int T = 0, n = 0, max_blocks = 0, n_qtiles = 0;
+  bool prefill = false;
+  int max_len = 0;        // longest context (incl. new tokens) in the step
+  long long sum_len = 0;  // sum of contexts (attention bytes accounting)
+  double attn_pairs = 0;  // sum over new tokens of (position + 1) (attention flops accounting)
+  int32_t* d = nullptr;   // device buffer the offsets below refer to
   size_t words = 0;  // 4-byte words in use
   // offsets (in words) of each array
   size_t tokens, positions, slots, cu_q, seq_start, seq_len, last_row, block_tables, tile_seq,
@@ -66,9 +70,6 @@ struct Workspace {
   int max_tiles = 0;
   float* moe_Y = nullptr;  // [T k, H]
   float* moe_y = nullptr;  // [T, H]
-  // TMA maps of the activation buffers (rebuilt when the workspace grows)
-  TmaDesc tm_xn, tm_attn_out, tm_hbuf, tm_xn_last;
-  int tm_box_rows = 0;
 };
 
 }  // namespace nvllm
@@ -78,6 +79,7 @@ struct nvllm_handle {
   int dev = 0, sm_count = 148;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaEvent_t tm0 = nullptr, tm1 = nullptr;  // nvllm_timer_record
   std::string err;
   bool finalized = false;
   int wdt = 0, adt = 0, kvdt = 0;
@@ -92,7 +94,6 @@ struct nvllm_handle {
   float *lnf_w = nullptr, *lnf_b = nullptr;
   std::vector<nvllm::LayerW> layers;
   std::vector<uint8_t> have;  // [L+1][64] flags, index (layer+1)*64 + id
-  nvllm::TmaDesc tm_lm_head;
   float *cosT = nullptr, *sinT = nullptr;
   // paged KV pool: K and V each [L][num_blocks][nkv][256][hd]
   void *kpool = nullptr, *vpool = nullptr;
@@ -116,8 +117,21 @@ struct nvllm_handle {
   // accounting
   uint64_t weight_bytes = 0, kv_bytes = 0, ws_bytes = 0;
   int launches = 0;  // kernels launched by the current step
-  bool resident_ok = false;  // a decode step's state is on the device (nvllm_run_resident)
-  int resident_max_len = 0;
+  bool resident_ok = false;  // the last step's state is on the device (nvllm_run_resident)
+  nvllm::StepLayout run_lay;  // layout of the last nvllm_run (nvllm_rerun replays it)
+  bool run_lay_ok = false;
+  int32_t* d_stage2 = nullptr;  // decode layout derived on the device from a prefill step
+  size_t stage2_words = 0;
+  // per-kernel-class profile (nvllm_set_profile / nvllm_get_profile)
+  struct ProfRec {
+    int cls;
+    double bytes, flops;
+    cudaEvent_t e0, e1;
+  };
+  int profile = 0;
+  std::vector<ProfRec> prof_open;
+  std::vector<cudaEvent_t> prof_pool;
+  nvllm_profile_entry prof[NVLLM_K_COUNT] = {};
 };
 
 namespace nvllm {
@@ -125,8 +139,9 @@ namespace nvllm {
 extern thread_local std::string g_create_error;
 
 void free_workspace(nvllm_handle* h);
-int build_weight_maps(nvllm_handle* h);      // gemm_tcgen05.cu: TMA maps of the packed weights
-int build_activation_maps(nvllm_handle* h);  // gemm_tcgen05.cu: TMA maps of the workspace
+int ensure_workspace(nvllm_handle* h, int T, int n);
+int forward_step(nvllm_handle* h);  // runs h->lay
+int prof_collect(nvllm_handle* h);
 
 int set_err(nvllm_handle* h, int code, const char* fmt, ...);
 

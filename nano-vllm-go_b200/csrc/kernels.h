@@ -77,6 +77,14 @@ cudaError_t launch_advance(cudaStream_t st, int n, const int* sampled, int* toke
                            int* slots, int* seq_len, const int* block_tables, int max_blocks,
                            int max_pos);
 
+// decode-step state from the prefill step that just sampled `sampled` (temperature / uniforms
+// are copied bit-wise)
+cudaError_t launch_make_decode_state(cudaStream_t st, int n, int mb, const int* sampled,
+                                     const int* src_seq_len, const int* src_bt, const int* src_temp,
+                                     const int* src_uni, int* tokens, int* positions, int* slots,
+                                     int* cu_q, int* seq_start, int* seq_len, int* last_row, int* bt,
+                                     int* temp, int* uni);
+
 // dst[N,K] (dtype ddt) = transpose(src[K,N] fp32|bf16|f16)   — weight repack at finalize
 cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* src, int K, int N,
                                      int ddt, void* dst, int ld_dst);
@@ -126,20 +134,21 @@ struct TmaDesc {
 int make_tma_2d_bf16(TmaDesc* out, const void* base, uint64_t rows, uint64_t cols,
                      uint64_t row_stride_elems, uint32_t box_rows, std::string* err);
 struct Tc5Args {
-  const TmaDesc* tmA;  // activations [M, K] bf16
-  const TmaDesc* tmW;  // weights     [N, K] bf16
+  const void* A;  // activations [M, K] bf16, K contiguous
+  const void* W;  // weights     [N, K] bf16, K contiguous
   int M, N, K;
   float* out;          // [S][M][ldo] fp32 partials
   int ldo;
   size_t split_stride;
-  int S;
+  int S;               // requested split-K slices (tc5_splits)
   float alpha;
   size_t out_capacity;
 };
 bool tc5_supported(int M, int N, int K);
 int tc5_splits(int M, int N, int K, int sm_count);
-cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int sm_count);
-int tc5_box_rows_act(int M);  // TMA box rows the kernel expects for the activation map
+// *S_out = slices actually written (<= a.S)
+cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int* S_out);
+int tc5_box_rows_act(int M);  // token-tile rows (UMMA N) the kernel uses for M tokens
 int tc5_box_rows_w(int N);    // ... and for the weight map
 
 // ---------------------------------------------------------------- attention.cu

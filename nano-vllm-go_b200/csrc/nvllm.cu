@@ -241,6 +241,12 @@ int nvllm_destroy(nvllm_handle* h) {
   F(h->kpool);
   F(h->vpool);
   F(h->d_stage);
+  F(h->d_stage2);
+  for (auto& r : h->prof_open) {
+    cudaEventDestroy(r.e0);
+    cudaEventDestroy(r.e1);
+  }
+  for (auto e : h->prof_pool) cudaEventDestroy(e);
   if (h->h_stage) cudaFreeHost(h->h_stage);
   if (h->h_out) cudaFreeHost(h->h_out);
   if (h->h_logits) cudaFreeHost(h->h_logits);

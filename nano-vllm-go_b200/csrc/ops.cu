@@ -69,23 +69,15 @@ extern "C" int nvllm_op_matmul(int device, int prec, int kernel, int M, int N, i
   OP_CHECK(cudaMemcpyAsync(dW32, W, (size_t)K * N * 4, cudaMemcpyHostToDevice, s.st));
   OP_CHECK(launch_convert(s.st, NVLLM_DT_F32, dA32, (size_t)M * K, dt, dA));
   OP_CHECK(launch_transpose_convert(s.st, NVLLM_DT_F32, dW32, K, N, dt, dWt, K));
-  TmaDesc tmA, tmW;
-  if (kernel == 3) {
-    std::string err;
-    if (make_tma_2d_bf16(&tmA, dA, M, K, K, tc5_box_rows_act(M), &err) ||
-        make_tma_2d_bf16(&tmW, dWt, N, K, K, tc5_box_rows_w(N), &err))
-      return set_err(nullptr, NVLLM_ERR_CUDA, "tensor map: %s", err.c_str());
-  }
   int S = 1;
   auto launch = [&]() -> cudaError_t {
     if (kernel == 3) {
       Tc5Args t{};
-      t.tmA = &tmA; t.tmW = &tmW; t.M = M; t.N = N; t.K = K; t.out = dOut; t.ldo = ldo;
+      t.A = dA; t.W = dWt; t.M = M; t.N = N; t.K = K; t.out = dOut; t.ldo = ldo;
       t.split_stride = (size_t)M * ldo; t.alpha = 1.f; t.out_capacity = cap;
       t.S = tc5_splits(M, N, K, 148);
       while (t.S > 1 && (size_t)t.S * M * ldo > cap) t.S--;
-      S = t.S;
-      return launch_gemm_tc5(s.st, t, 148);
+      return launch_gemm_tc5(s.st, t, &S);
     }
     GemmArgs g{};
     g.A = dA; g.adt = dt; g.lda = K; g.W = dWt; g.wdt = dt; g.M = M; g.N = N; g.K = K;

@@ -1,0 +1,331 @@
+// run.cu — nvllm_run and its device-resident siblings: one engine step (ModelRunner.Run,
+// reference nanovllm/tensor_model_runner.go:55-97).  The caller's flattened Sequence records
+// are validated, turned into the step's integer arrays (new-token ids, positions, KV slots
+// through the block tables, ragged offsets, attention tiles) in ONE pinned buffer, copied
+// with ONE cudaMemcpyAsync, and the forward pass (forward.cu) runs on them.
+#include <string.h>
+
+#include <algorithm>
+
+#include "common.cuh"
+#include "handle.h"
+
+using namespace nvllm;
+
+static int ensure_stage(nvllm_handle* h, size_t words) {
+  if (words <= h->stage_words) return NVLLM_OK;
+  NV_CHECK(h, cudaStreamSynchronize(h->stream));
+  if (h->h_stage) cudaFreeHost(h->h_stage);
+  if (h->d_stage) cudaFree(h->d_stage);
+  h->h_stage = nullptr;
+  h->d_stage = nullptr;
+  h->stage_words = 0;
+  h->resident_ok = false;
+  h->run_lay_ok = false;
+  size_t cap = std::max(words * 2, (size_t)4096);
+  NV_CHECK(h, cudaMallocHost((void**)&h->h_stage, cap * 4));
+  NV_CHECK(h, cudaMalloc((void**)&h->d_stage, cap * 4));
+  h->stage_words = cap;
+  return NVLLM_OK;
+}
+
+// offsets of a step's arrays inside its staging buffer (every array 16-byte aligned)
+static void plan_layout(StepLayout& L, int T, int n, int max_blocks, int n_qtiles) {
+  L.T = T;
+  L.n = n;
+  L.max_blocks = max_blocks;
+  L.n_qtiles = n_qtiles;
+  size_t o = 0;
+  auto take = [&](size_t cnt) {
+    size_t r = o;
+    o += (cnt + 3) / 4 * 4;
+    return r;
+  };
+  L.tokens = take(T);
+  L.positions = take(T);
+  L.slots = take(T);
+  L.cu_q = take(n + 1);
+  L.seq_start = take(n);
+  L.seq_len = take(n);
+  L.last_row = take(n);
+  L.block_tables = take((size_t)n * max_blocks);
+  L.tile_seq = take(n_qtiles);
+  L.tile_q0 = take(n_qtiles);
+  L.temperature = take(n);
+  L.uniforms = take(n);
+  L.words = o;
+}
+
+// splitmix64 -> uniform in [0,1): the library's own stream when the caller passes no uniforms
+static float next_uniform(nvllm_handle* h) {
+  uint64_t z = (h->seed + 0x9E3779B97F4A7C15ull * (++h->rng_counter));
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  z ^= z >> 31;
+  return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+
+static void fill_stats(nvllm_handle* h, nvllm_run_stats* stats, int T, uint64_t h2d, uint64_t d2h,
+                       bool timed) {
+  if (!stats) return;
+  memset(stats, 0, sizeof *stats);
+  if (timed) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) == cudaSuccess) stats->device_ms = ms;
+  }
+  stats->kernel_launches = h->launches;
+  stats->new_tokens = T;
+  stats->h2d_bytes = h2d;
+  stats->d2h_bytes = d2h;
+}
+
+extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* token_ids,
+                         const int32_t* cu_seqlens, const int32_t* num_cached,
+                         const int32_t* block_tables, const int32_t* cu_blocks,
+                         const float* temperature, const float* uniforms, int32_t* out_tokens,
+                         float* out_logits, nvllm_run_stats* stats) {
+  if (!h) return NVLLM_ERR_INVALID;
+  if (!h->finalized) return set_err(h, NVLLM_ERR_STATE, "nvllm_run before nvllm_finalize");
+  if (n < 0 || (n > 0 && (!token_ids || !cu_seqlens || !block_tables || !cu_blocks || !out_tokens)))
+    return set_err(h, NVLLM_ERR_INVALID, "null argument");
+  if (stats) memset(stats, 0, sizeof *stats);
+  if (n == 0) return NVLLM_OK;
+  NV_CHECK(h, cudaSetDevice(h->dev));
+  const nvllm_config& c = h->cfg;
+  h->resident_ok = false;
+  h->run_lay_ok = false;
+
+  // ---- pass 1: sizes and validation
+  int T = 0, max_blocks = 0, n_qtiles = 0, max_len = 0;
+  long long sum_len = 0;
+  double pairs = 0;
+  for (int i = 0; i < n; i++) {
+    const int len = cu_seqlens[i + 1] - cu_seqlens[i];
+    const int nb = cu_blocks[i + 1] - cu_blocks[i];
+    if (len <= 0) return set_err(h, NVLLM_ERR_INVALID, "sequence %d is empty", i);
+    if (nb < (len + KV_BLOCK - 1) / KV_BLOCK)
+      return set_err(h, NVLLM_ERR_INVALID, "sequence %d: %d tokens need %d blocks, table has %d", i,
+                     len, (len + KV_BLOCK - 1) / KV_BLOCK, nb);
+    if (h->use_rope && len > c.max_seq_len)  // rope.go:84-86 panics
+      return set_err(h, NVLLM_ERR_RANGE, "sequence %d: position %d >= max_seq_len %d", i, len - 1,
+                     c.max_seq_len);
+    int start = len - 1;
+    if (is_prefill) {
+      int nc = num_cached ? num_cached[i] : 0;
+      if (nc < 0) return set_err(h, NVLLM_ERR_INVALID, "sequence %d: num_cached < 0", i);
+      start = std::min(nc, len - 1);  // a fully cached prompt still computes its last token
+    }
+    const int n_new = len - start;
+    T += n_new;
+    n_qtiles += (n_new + ATTN_PREFILL_QTILE - 1) / ATTN_PREFILL_QTILE;
+    max_blocks = std::max(max_blocks, nb);
+    max_len = std::max(max_len, len);
+    sum_len += len;
+    pairs += 0.5 * ((double)len * (len + 1) - (double)start * (start + 1));
+  }
+  StepLayout& L = h->lay;
+  plan_layout(L, T, n, max_blocks, is_prefill ? n_qtiles : 0);
+  L.prefill = is_prefill != 0;
+  L.max_len = max_len;
+  L.sum_len = sum_len;
+  L.attn_pairs = pairs;
+  int rc;
+  if ((rc = ensure_stage(h, L.words))) return rc;
+  L.d = h->d_stage;
+  if ((rc = ensure_workspace(h, T, n))) return rc;
+  if (!h->h_out || n > h->ws.n_cap_out) {
+    NV_CHECK(h, cudaStreamSynchronize(h->stream));
+    if (h->h_out) cudaFreeHost(h->h_out);
+    h->h_out = nullptr;
+    NV_CHECK(h, cudaMallocHost((void**)&h->h_out, (size_t)std::max(n, 512) * 4));
+    h->ws.n_cap_out = std::max(n, 512);
+  }
+  // ---- pass 2: fill
+  int32_t* s = h->h_stage;
+  float* s_temp = reinterpret_cast<float*>(s + L.temperature);
+  float* s_uni = reinterpret_cast<float*>(s + L.uniforms);
+  int row = 0, tile = 0;
+  for (int i = 0; i < n; i++) {
+    const int len = cu_seqlens[i + 1] - cu_seqlens[i];
+    const int32_t* toks = token_ids + cu_seqlens[i];
+    const int32_t* bt = block_tables + cu_blocks[i];
+    const int nb = cu_blocks[i + 1] - cu_blocks[i];
+    int start = len - 1;
+    if (is_prefill) start = std::min(num_cached ? num_cached[i] : 0, len - 1);
+    for (int b = 0; b < nb; b++) {
+      if (bt[b] < 0 || bt[b] >= h->num_blocks)
+        return set_err(h, NVLLM_ERR_RANGE, "sequence %d: block id %d outside the pool of %d", i,
+                       bt[b], h->num_blocks);
+      s[L.block_tables + (size_t)i * max_blocks + b] = bt[b];
+    }
+    for (int b = nb; b < max_blocks; b++) s[L.block_tables + (size_t)i * max_blocks + b] = 0;
+    s[L.cu_q + i] = row;
+    s[L.seq_start + i] = start;
+    s[L.seq_len + i] = len;
+    for (int p = start; p < len; p++, row++) {
+      const int tok = toks[p];
+      if (tok < 0 || tok >= h->V)
+        return set_err(h, NVLLM_ERR_RANGE, "sequence %d: token id %d outside vocab %d", i, tok, h->V);
+      s[L.tokens + row] = tok;
+      s[L.positions + row] = p;
+      s[L.slots + row] = bt[p / KV_BLOCK] * KV_BLOCK + p % KV_BLOCK;
+    }
+    s[L.last_row + i] = row - 1;
+    if (is_prefill)
+      for (int q0 = 0; q0 < len - start; q0 += ATTN_PREFILL_QTILE, tile++) {
+        s[L.tile_seq + tile] = i;
+        s[L.tile_q0 + tile] = q0;
+      }
+    const float t = temperature ? temperature[i] : 0.f;
+    s_temp[i] = t;
+    s_uni[i] = (t > 0.f) ? (uniforms ? uniforms[i] : next_uniform(h)) : 0.f;
+  }
+  s[L.cu_q + n] = row;
+
+  cudaStream_t st = h->stream;
+  NV_CHECK(h, cudaMemcpyAsync(h->d_stage, h->h_stage, L.words * 4, cudaMemcpyHostToDevice, st));
+  NV_CHECK(h, cudaEventRecord(h->ev0, st));
+  h->launches = 0;
+  if ((rc = forward_step(h))) return rc;
+  NV_CHECK(h, cudaEventRecord(h->ev1, st));
+  NV_CHECK(h, cudaMemcpyAsync(h->h_out, h->ws.out_tokens, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+  uint64_t d2h = (uint64_t)n * 4;
+  if (out_logits) {
+    // rows are ldl apart on the device; copy them packed [n, V]
+    NV_CHECK(h, cudaMemcpy2DAsync(out_logits, (size_t)h->V * 4, h->ws.logits_final,
+                                  (size_t)h->ldl * 4, (size_t)h->V * 4, n, cudaMemcpyDeviceToHost,
+                                  st));
+    d2h += (uint64_t)n * h->V * 4;
+  }
+  cudaError_t e = cudaStreamSynchronize(st);
+  if (e != cudaSuccess)
+    return set_err(h, NVLLM_ERR_CUDA, "forward pass failed: %s", cudaGetErrorString(e));
+  memcpy(out_tokens, h->h_out, (size_t)n * 4);
+  h->resident_ok = true;
+  h->run_lay = L;
+  h->run_lay_ok = true;
+  fill_stats(h, stats, T, L.words * 4, d2h, true);
+  return NVLLM_OK;
+}
+
+// One more decode step for the sequences of the previous step, entirely on the device: the
+// sampled tokens become the inputs, positions advance by one, KV slots come from the block
+// tables already resident.  No host<->device copy, no host sync.  Works after a decode step
+// (state advanced in place) and after a prefill step (decode state derived by a kernel).
+extern "C" int nvllm_run_resident(nvllm_handle* h, nvllm_run_stats* stats) {
+  if (!h) return NVLLM_ERR_INVALID;
+  if (!h->resident_ok)
+    return set_err(h, NVLLM_ERR_STATE, "nvllm_run_resident needs a preceding nvllm_run");
+  NV_CHECK(h, cudaSetDevice(h->dev));
+  StepLayout& L = h->lay;
+  const int n = L.n;
+  if (L.max_len + 1 > L.max_blocks * KV_BLOCK || (h->use_rope && L.max_len + 1 > h->cfg.max_seq_len))
+    return set_err(h, NVLLM_ERR_RANGE, "resident decode ran past the block tables / max_seq_len");
+  cudaStream_t st = h->stream;
+  int rc;
+  NV_CHECK(h, cudaEventRecord(h->ev0, st));
+  h->launches = 0;
+  if (L.prefill) {
+    StepLayout D;
+    plan_layout(D, n, n, L.max_blocks, 0);
+    if (D.words > h->stage2_words) {
+      NV_CHECK(h, cudaStreamSynchronize(st));
+      if (h->d_stage2) cudaFree(h->d_stage2);
+      h->d_stage2 = nullptr;
+      h->stage2_words = 0;
+      NV_CHECK(h, cudaMalloc((void**)&h->d_stage2, D.words * 2 * 4));
+      h->stage2_words = D.words * 2;
+    }
+    D.d = h->d_stage2;
+    const int32_t* s = L.d;
+    int32_t* d = D.d;
+    cudaError_t e = launch_make_decode_state(
+        st, n, L.max_blocks, h->ws.out_tokens, s + L.seq_len, s + L.block_tables, s + L.temperature,
+        s + L.uniforms, d + D.tokens, d + D.positions, d + D.slots, d + D.cu_q, d + D.seq_start,
+        d + D.seq_len, d + D.last_row, d + D.block_tables, d + D.temperature, d + D.uniforms);
+    h->launches++;
+    if (e != cudaSuccess)
+      return set_err(h, NVLLM_ERR_CUDA, "make_decode_state: %s", cudaGetErrorString(e));
+    D.prefill = false;
+    D.max_len = L.max_len + 1;
+    D.sum_len = L.sum_len + n;
+    D.attn_pairs = (double)D.sum_len;
+    L = D;
+  } else {
+    int32_t* d = L.d;
+    cudaError_t e = launch_advance(st, n, h->ws.out_tokens, d + L.tokens, d + L.positions,
+                                   d + L.slots, d + L.seq_len, d + L.block_tables, L.max_blocks,
+                                   L.max_blocks * KV_BLOCK);
+    h->launches++;
+    if (e != cudaSuccess) return set_err(h, NVLLM_ERR_CUDA, "advance: %s", cudaGetErrorString(e));
+    L.max_len += 1;
+    L.sum_len += n;
+    L.attn_pairs = (double)L.sum_len;
+  }
+  if ((rc = forward_step(h))) return rc;
+  NV_CHECK(h, cudaEventRecord(h->ev1, st));
+  fill_stats(h, stats, n, 0, 0, false);
+  return NVLLM_OK;
+}
+
+// Re-execute the last nvllm_run step from its staged device inputs.
+extern "C" int nvllm_rerun(nvllm_handle* h, nvllm_run_stats* stats) {
+  if (!h) return NVLLM_ERR_INVALID;
+  if (!h->run_lay_ok) return set_err(h, NVLLM_ERR_STATE, "nvllm_rerun needs a preceding nvllm_run");
+  NV_CHECK(h, cudaSetDevice(h->dev));
+  if (!h->run_lay.prefill)
+    return set_err(h, NVLLM_ERR_STATE,
+                   "nvllm_rerun replays prefill steps only (a decode step's staged state is "
+                   "advanced in place by nvllm_run_resident)");
+  h->lay = h->run_lay;
+  NV_CHECK(h, cudaEventRecord(h->ev0, h->stream));
+  h->launches = 0;
+  int rc = forward_step(h);
+  if (rc) return rc;
+  NV_CHECK(h, cudaEventRecord(h->ev1, h->stream));
+  h->resident_ok = true;
+  fill_stats(h, stats, h->lay.T, 0, 0, false);
+  return NVLLM_OK;
+}
+
+// Block until the steps issued so far are done; copies the last sampled tokens out.
+extern "C" int nvllm_sync(nvllm_handle* h, int32_t* out_tokens, int n, float* last_step_ms) {
+  if (!h) return NVLLM_ERR_INVALID;
+  NV_CHECK(h, cudaSetDevice(h->dev));
+  cudaError_t e = cudaStreamSynchronize(h->stream);
+  if (e != cudaSuccess)
+    return set_err(h, NVLLM_ERR_CUDA, "stream failed: %s", cudaGetErrorString(e));
+  if (out_tokens && n > 0) {
+    if (n > h->lay.n) n = h->lay.n;
+    NV_CHECK(h, cudaMemcpy(out_tokens, h->ws.out_tokens, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  }
+  if (last_step_ms) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, h->ev0, h->ev1) != cudaSuccess) ms = 0.f;
+    *last_step_ms = ms;
+  }
+  return NVLLM_OK;
+}
+
+// Device timer on the compute stream, for callers that time several calls as one region
+// (bench.py): which = 0 records the start event, 1 the stop event.
+extern "C" int nvllm_timer_record(nvllm_handle* h, int which) {
+  if (!h) return NVLLM_ERR_INVALID;
+  NV_CHECK(h, cudaSetDevice(h->dev));
+  if (!h->tm0) {
+    NV_CHECK(h, cudaEventCreate(&h->tm0));
+    NV_CHECK(h, cudaEventCreate(&h->tm1));
+  }
+  NV_CHECK(h, cudaEventRecord(which ? h->tm1 : h->tm0, h->stream));
+  return NVLLM_OK;
+}
+// Synchronises the stream and returns stop - start in milliseconds.
+extern "C" int nvllm_timer_elapsed(nvllm_handle* h, float* ms) {
+  if (!h || !ms) return NVLLM_ERR_INVALID;
+  NV_CHECK(h, cudaSetDevice(h->dev));
+  if (!h->tm0) return set_err(h, NVLLM_ERR_STATE, "timer was never started");
+  cudaError_t e = cudaStreamSynchronize(h->stream);
+  if (e != cudaSuccess) return set_err(h, NVLLM_ERR_CUDA, "stream failed: %s", cudaGetErrorString(e));
+  NV_CHECK(h, cudaEventElapsedTime(ms, h->tm0, h->tm1));
+  return NVLLM_OK;
+}

@@ -219,7 +219,6 @@ extern "C" int nvllm_finalize(nvllm_handle* h) {
   NV_CHECK(h, cudaMemsetAsync(h->vpool, 0, pool_bytes, h->stream));
   h->kv_bytes = 2 * pool_bytes;
 
-  if ((rc = build_weight_maps(h)) != 0) return rc;
   NV_CHECK(h, cudaStreamSynchronize(h->stream));
   h->finalized = true;
   return NVLLM_OK;

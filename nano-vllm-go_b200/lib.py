@@ -34,6 +34,17 @@ class RunStats(ctypes.Structure):
     ]
 
 
+class ProfileEntry(ctypes.Structure):
+    """``struct nvllm_profile_entry``."""
+
+    _fields_ = [("ms", ctypes.c_double), ("bytes", ctypes.c_double), ("flops", ctypes.c_double),
+                ("launches", ctypes.c_int64)]
+
+
+KERNEL_CLASSES = ["embed", "norm", "gemm_tc5", "gemv", "gemm_simt", "rope_kv", "attn_prefill",
+                  "attn_decode", "act", "moe_route", "moe_gemm", "moe_misc", "sample", "misc"]
+
+
 class NvllmError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"nvllm error {code}: {msg}")
@@ -58,6 +69,11 @@ SIGNATURES = {
                                  ctypes.POINTER(RunStats)]),
     "nvllm_run_resident": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(RunStats)]),
     "nvllm_sync": (ctypes.c_int, [ctypes.c_void_p, _i32p, ctypes.c_int, _f32p]),
+    "nvllm_rerun": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(RunStats)]),
+    "nvllm_set_profile": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "nvllm_get_profile": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ProfileEntry)]),
+    "nvllm_timer_record": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "nvllm_timer_elapsed": (ctypes.c_int, [ctypes.c_void_p, _f32p]),
     "nvllm_set_sampling": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_float, ctypes.c_int,
                                           ctypes.c_float]),
     "nvllm_set_seed": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint64]),

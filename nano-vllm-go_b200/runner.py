@@ -123,6 +123,30 @@ class CudaModelRunner:
         """One more decode step for the previous decode batch, fully device-resident."""
         L.check(self._lib.nvllm_run_resident(self._h, ctypes.byref(self.last_stats)), self._h)
 
+    def rerun(self) -> None:
+        """Re-execute the last prefill step from its device-resident inputs (no copies)."""
+        L.check(self._lib.nvllm_rerun(self._h, ctypes.byref(self.last_stats)), self._h)
+
+    def timer_start(self) -> None:
+        L.check(self._lib.nvllm_timer_record(self._h, 0), self._h)
+
+    def timer_stop(self) -> float:
+        """Records the stop event, waits for the stream, returns device milliseconds."""
+        L.check(self._lib.nvllm_timer_record(self._h, 1), self._h)
+        ms = ctypes.c_float()
+        L.check(self._lib.nvllm_timer_elapsed(self._h, ctypes.byref(ms)), self._h)
+        return ms.value
+
+    def set_profile(self, enabled: bool) -> None:
+        L.check(self._lib.nvllm_set_profile(self._h, int(enabled)), self._h)
+
+    def get_profile(self) -> dict:
+        """{class: {ms, bytes, flops, launches}} accumulated since set_profile(True)."""
+        arr = (L.ProfileEntry * len(L.KERNEL_CLASSES))()
+        L.check(self._lib.nvllm_get_profile(self._h, arr), self._h)
+        return {name: {"ms": e.ms, "bytes": e.bytes, "flops": e.flops, "launches": e.launches}
+                for name, e in zip(L.KERNEL_CLASSES, arr) if e.launches}
+
     def sync(self, n: int = 0):
         out = np.empty(max(n, 1), dtype=np.int32)
         ms = ctypes.c_float()

@@ -45,6 +45,22 @@ def test_matmul_fp32_vs_oracle(M, N, K):
     assert rel_err(got, ref) < 1e-5
 
 
+@pytest.mark.parametrize("M,N,K", [
+    (16, 128, 64), (9, 128, 128), (32, 256, 512), (64, 3072, 2048), (33, 200, 264),
+    (130, 777, 512), (300, 1000, 1024), (64, 50257, 768), (128, 4672, 4544)])
+def test_matmul_tcgen05_vs_oracle(M, N, K):
+    """The tcgen05/TMEM/TMA GEMM (kernel=3): tile tails in M, N and K, split-K, LM-head and
+    Falcon shapes.  bf16-exact inputs, fp32 accumulate: only summation order differs."""
+    O = oracle_mod()
+    L = nvllm_pkg.sub("lib")
+    rng = np.random.default_rng(M * 7 + N * 3 + K)
+    A = W.bf16_round(rng.standard_normal((M, K)).astype(np.float32))
+    Wm = W.bf16_round((rng.standard_normal((K, N)) * 0.05).astype(np.float32))
+    ref = A.astype(np.float64) @ Wm.astype(np.float64) if M * N * K > 2e9 else O.matmul(A, Wm)
+    got, _ = L.op_matmul(A, Wm, None, prec=C.PREC_BF16, kernel=3)
+    assert rel_err(got, ref) < 2e-5
+
+
 @pytest.mark.parametrize("M,N,K", [(1, 768, 768), (8, 520, 2048), (64, 512, 512), (200, 264, 1024)])
 def test_matmul_bf16_vs_oracle(M, N, K):
     O = oracle_mod()
@@ -97,16 +113,25 @@ def _greedy_parity(name, prec, prompt_len, steps):
         toks = list(int(t) for t in prompt)
         bt = _blocks(prompt_len + steps)
         worst = 0.0
+        flips = 0
         for i in range(steps):
             out, logits = run.run_flat([toks], is_prefill=(i == 0), num_cached=[0],
                                        block_tables=[bt], temperature=[0.0], want_logits=True)
             err = rel_err(logits[0], ref_logits[i])
             worst = max(worst, err)
             assert err <= TOL[prec], f"{name} step {i}: rel err {err}"
-            assert int(out[0]) == int(ref_toks[i]), f"{name} step {i}: token {out[0]} != {ref_toks[i]}"
             # the device argmax must be the first-max of the device logits, bit-exact
             assert int(out[0]) == oracle_mod().argmax(logits[0])
-            toks.append(int(out[0]))
+            if int(out[0]) != int(ref_toks[i]):
+                # fp32 mode: never.  bf16 mode: only when the oracle's own top-2 margin is inside
+                # the numerical tolerance (random-init logits are nearly flat, so near-ties exist)
+                margin = float(ref_logits[i][ref_toks[i]] - ref_logits[i][out[0]])
+                scale = float(np.abs(ref_logits[i]).max())
+                assert prec == C.PREC_BF16 and margin <= 2 * err * scale + 1e-6, \
+                    f"{name} step {i}: token {out[0]} != {ref_toks[i]} (margin {margin}, err {err})"
+                flips += 1
+            toks.append(int(ref_toks[i]))  # teacher-forced with the oracle's token
+        assert flips <= 2, f"{name}: {flips} near-tie flips in {steps} steps"
         return worst
     finally:
         run.close()
