@@ -1,0 +1,285 @@
+// Package nanovllm — CudaModelRunner: the cgo shim that makes libnvllm_b200.so a drop-in
+// ModelRunner for the unchanged Go engine.
+//
+// Drop this file into the reference's nanovllm/ package (next to tensor_model_runner.go,
+// which it replaces at the call site) and build with
+//
+//	CGO_CFLAGS="-I<repo>/include" CGO_LDFLAGS="-L<repo>/nano-vllm-go_b200 -lnvllm_b200" go build ./...
+//
+// It implements exactly the interface of nanovllm/model_runner.go:9-16
+//
+//	Run(seqs []*Sequence, isPrefill bool) ([]int, error)
+//	Close() error
+//
+// plus the extras of TensorModelRunner (tensor_model_runner.go:35-52,100-111) and
+// GenericModelRunner (purego/generic_runner.go:184-196).  The image this library was built
+// in has no Go toolchain, so this file is shipped uncompiled; nano-vllm-go_b200/runner.py is
+// the same shim over ctypes and is what the tests exercise.
+package nanovllm
+
+/*
+#include <stdlib.h>
+#include "nvllm.h"
+*/
+import "C"
+
+import (
+	"fmt"
+	"runtime"
+	"unsafe"
+
+	"nano-vllm-go/purego/tensor"
+)
+
+// CudaModelRunner implements ModelRunner on one B200.
+type CudaModelRunner struct {
+	h           *C.nvllm_handle
+	cfg         *tensor.ModelConfig
+	temperature float32 // <= 0: greedy argmax (cmd/ask/main.go:389-402)
+
+	// reusable flattening buffers (no Go pointer is retained by the library)
+	tok, cuSeq, cached, bt, cuBt, out []C.int32_t
+	temp                              []C.float
+}
+
+func lastError(h *C.nvllm_handle) error {
+	return fmt.Errorf("nvllm: %s", C.GoString(C.nvllm_last_error(h)))
+}
+
+// NewCudaModelRunner replaces NewTensorModelRunner (tensor_model_runner.go:21-32): it loads
+// the model with the reference's own loader and hands every tensor, in the layout the loader
+// leaves it in (generic_loader.go:184-265,353-604), to the library.
+func NewCudaModelRunner(modelDir string, engineCfg *Config, device int, bf16 bool) (*CudaModelRunner, error) {
+	model, err := tensor.LoadModelFromDirectory(modelDir)
+	if err != nil {
+		return nil, fmt.Errorf("failed to load model: %w", err)
+	}
+	mc := model.Config
+	var cc C.nvllm_config
+	cc.abi_version = C.NVLLM_ABI_VERSION
+	cc.vocab_size = C.int32_t(mc.VocabSize)
+	cc.hidden = C.int32_t(mc.Hidden)
+	cc.num_layers = C.int32_t(mc.NumLayers)
+	cc.num_heads = C.int32_t(mc.NumHeads)
+	cc.num_kv_heads = C.int32_t(mc.NumKVHeads)
+	cc.head_dim = C.int32_t(mc.HeadDim)
+	cc.ffn_dim = C.int32_t(mc.FFNDim)
+	cc.max_seq_len = C.int32_t(mc.MaxSeqLen)
+	cc.attention_type = C.int32_t(attnEnum(mc.AttentionType))
+	cc.norm_type = C.int32_t(normEnum(mc.NormType))
+	cc.position_type = C.int32_t(posEnum(mc.PositionType))
+	cc.activation_type = C.int32_t(actEnum(mc.ActivationType))
+	cc.block_style = C.int32_t(blockEnum(mc.BlockStyle))
+	if model.LMHead == nil || mc.TiedEmbedding {
+		cc.tied_embedding = 1
+	}
+	if mc.UseMoE {
+		cc.use_moe = 1
+		cc.num_experts = C.int32_t(mc.NumExperts)
+		cc.num_experts_per_tok = C.int32_t(mc.NumExpertsPerTok)
+	}
+	cc.norm_eps = C.float(mc.NormEps)
+	cc.embedding_multiplier = C.float(mc.EmbeddingMultiplier)
+	cc.attention_multiplier = C.float(mc.AttentionMultiplier)
+	cc.residual_multiplier = C.float(mc.ResidualMultiplier)
+	cc.logits_scaling = C.float(mc.LogitsScaling)
+	cc.rope_base = C.double(mc.RoPEBase)
+	if bf16 {
+		cc.precision = C.NVLLM_PREC_BF16
+	}
+	cc.num_kv_blocks = C.int32_t(engineCfg.NumKVCacheBlocks)
+	cc.max_num_seqs = C.int32_t(engineCfg.MaxNumSeqs)
+	cc.max_batched_tokens = C.int32_t(engineCfg.MaxNumBatchedTokens)
+	cc.tp_size = 1
+	cc.device = C.int32_t(device)
+
+	runtime.LockOSThread()
+	defer runtime.UnlockOSThread()
+	var h *C.nvllm_handle
+	if rc := C.nvllm_create(&cc, nil, &h); rc != 0 {
+		return nil, lastError(nil)
+	}
+	r := &CudaModelRunner{h: h, cfg: mc}
+	set := func(id C.int, layer int, t *tensor.Tensor) error {
+		if t == nil {
+			return nil // optional tensors (biases) are simply not sent
+		}
+		if rc := C.nvllm_set_weight(h, id, C.int(layer), C.NVLLM_DT_F32,
+			unsafe.Pointer(&t.Data[0]), C.uint64_t(len(t.Data))); rc != 0 {
+			return lastError(h)
+		}
+		return nil
+	}
+	steps := []error{
+		set(C.NVLLM_W_TOKEN_EMBEDDING, -1, model.TokenEmbedding),
+		set(C.NVLLM_W_POS_EMBEDDING, -1, model.PosEmbedding),
+		set(C.NVLLM_W_FINAL_NORM_W, -1, model.LNFinal.Weight),
+		set(C.NVLLM_W_FINAL_NORM_B, -1, model.LNFinal.Bias),
+	}
+	if cc.tied_embedding == 0 {
+		steps = append(steps, set(C.NVLLM_W_LM_HEAD, -1, model.LMHead))
+	}
+	for l, b := range model.Blocks {
+		steps = append(steps, r.setBlock(set, l, b)...)
+	}
+	for _, e := range steps {
+		if e != nil {
+			C.nvllm_destroy(h)
+			return nil, e
+		}
+	}
+	if rc := C.nvllm_finalize(h); rc != 0 {
+		e := lastError(h)
+		C.nvllm_destroy(h)
+		return nil, e
+	}
+	return r, nil
+}
+
+// setBlock sends one GenericBlock (generic_model.go:22-31).
+func (r *CudaModelRunner) setBlock(set func(C.int, int, *tensor.Tensor) error, l int, b *tensor.GenericBlock) []error {
+	var es []error
+	if b.AttnLN != nil {
+		es = append(es, set(C.NVLLM_W_ATTN_NORM_W, l, b.AttnLN.Weight), set(C.NVLLM_W_ATTN_NORM_B, l, b.AttnLN.Bias))
+	}
+	if b.InputLN != nil { // parallel blocks (Falcon)
+		es = append(es, set(C.NVLLM_W_ATTN_NORM_W, l, b.InputLN.Weight), set(C.NVLLM_W_ATTN_NORM_B, l, b.InputLN.Bias))
+	}
+	if b.FFNLN != nil {
+		es = append(es, set(C.NVLLM_W_FFN_NORM_W, l, b.FFNLN.Weight), set(C.NVLLM_W_FFN_NORM_B, l, b.FFNLN.Bias))
+	}
+	switch a := b.Attention.(type) {
+	case *tensor.MultiHeadAttention:
+		es = append(es, set(C.NVLLM_W_Q, l, a.QWeight), set(C.NVLLM_W_K, l, a.KWeight), set(C.NVLLM_W_V, l, a.VWeight),
+			set(C.NVLLM_W_O, l, a.OutWeight), set(C.NVLLM_W_Q_BIAS, l, a.QBias), set(C.NVLLM_W_K_BIAS, l, a.KBias),
+			set(C.NVLLM_W_V_BIAS, l, a.VBias), set(C.NVLLM_W_O_BIAS, l, a.OutBias))
+	case *tensor.GroupedQueryAttention:
+		es = append(es, set(C.NVLLM_W_Q, l, a.QWeight), set(C.NVLLM_W_K, l, a.KWeight), set(C.NVLLM_W_V, l, a.VWeight),
+			set(C.NVLLM_W_O, l, a.OutWeight))
+	case *tensor.MultiQueryAttention:
+		es = append(es, set(C.NVLLM_W_Q, l, a.QWeight), set(C.NVLLM_W_KV, l, a.KVWeight), set(C.NVLLM_W_O, l, a.OutWeight),
+			set(C.NVLLM_W_Q_BIAS, l, a.QBias), set(C.NVLLM_W_O_BIAS, l, a.OutBias))
+	}
+	if b.MoE != nil {
+		es = append(es, set(C.NVLLM_W_MOE_ROUTER, l, b.MoE.RouterWeight), set(C.NVLLM_W_MOE_INPUT, l, b.MoE.InputLinear),
+			set(C.NVLLM_W_MOE_OUTPUT, l, b.MoE.OutputLinear))
+	} else if b.FFN != nil {
+		es = append(es, set(C.NVLLM_W_FFN_W1, l, b.FFN.W1), set(C.NVLLM_W_FFN_W2, l, b.FFN.W2),
+			set(C.NVLLM_W_FFN_B2, l, b.FFN.B2))
+		if r.cfg.ActivationType != tensor.ActivationSwiGLU {
+			es = append(es, set(C.NVLLM_W_FFN_B1, l, b.FFN.B1))
+		}
+	}
+	return es
+}
+
+// Run implements ModelRunner.Run (model_runner.go:11): one next token per scheduled
+// sequence, same order.  The whole batch is one device step.
+func (r *CudaModelRunner) Run(seqs []*Sequence, isPrefill bool) ([]int, error) {
+	n := len(seqs)
+	if n == 0 {
+		return nil, nil
+	}
+	r.tok, r.bt = r.tok[:0], r.bt[:0]
+	r.cuSeq = append(r.cuSeq[:0], 0)
+	r.cuBt = append(r.cuBt[:0], 0)
+	r.cached, r.temp = r.cached[:0], r.temp[:0]
+	for _, s := range seqs {
+		for _, t := range s.TokenIDs {
+			r.tok = append(r.tok, C.int32_t(t))
+		}
+		r.cuSeq = append(r.cuSeq, C.int32_t(len(r.tok)))
+		for _, b := range s.BlockTable {
+			r.bt = append(r.bt, C.int32_t(b))
+		}
+		r.cuBt = append(r.cuBt, C.int32_t(len(r.bt)))
+		r.cached = append(r.cached, C.int32_t(s.NumCachedTokens))
+		r.temp = append(r.temp, C.float(r.temperature))
+	}
+	if cap(r.out) < n {
+		r.out = make([]C.int32_t, n)
+	}
+	r.out = r.out[:n]
+	prefill := C.int(0)
+	if isPrefill {
+		prefill = 1
+	}
+	// cgo may move this goroutine between OS threads between calls; every entry point of the
+	// library does cudaSetDevice itself, so no thread pinning is needed here.
+	rc := C.nvllm_run(r.h, C.int(n), prefill, &r.tok[0], &r.cuSeq[0], &r.cached[0], &r.bt[0], &r.cuBt[0],
+		&r.temp[0], nil, &r.out[0], nil, nil)
+	if rc != 0 {
+		return nil, lastError(r.h)
+	}
+	res := make([]int, n)
+	for i := range res {
+		res[i] = int(r.out[i])
+	}
+	return res, nil
+}
+
+// Close implements ModelRunner.Close (model_runner.go:15).
+func (r *CudaModelRunner) Close() error {
+	if r.h != nil {
+		C.nvllm_destroy(r.h)
+		r.h = nil
+	}
+	return nil
+}
+
+// SetSamplingParams mirrors tensor_model_runner.go:35-42 (repetition penalty 1.2 by default).
+func (r *CudaModelRunner) SetSamplingParams(temperature, topP float32, topK int) {
+	r.SetSamplingParamsWithRepetition(temperature, topP, topK, 1.2)
+}
+
+// SetSamplingParamsWithRepetition mirrors tensor_model_runner.go:45-52.
+func (r *CudaModelRunner) SetSamplingParamsWithRepetition(temperature, topP float32, topK int, rep float32) {
+	r.temperature = temperature
+	C.nvllm_set_sampling(r.h, C.float(topP), C.int(topK), C.float(rep))
+}
+
+// ClearCache / ClearAllCaches (tensor_model_runner.go:100-111): KV state lives in the paged
+// pool and is addressed only through BlockTable, so there is nothing to free per sequence.
+func (r *CudaModelRunner) ClearCache(seqID int64) {}
+func (r *CudaModelRunner) ClearAllCaches()        {}
+
+// GetVocabSize / GetModelConfig (purego/generic_runner.go:184-196).
+func (r *CudaModelRunner) GetVocabSize() int                  { return r.cfg.VocabSize }
+func (r *CudaModelRunner) GetModelConfig() *tensor.ModelConfig { return r.cfg }
+
+func attnEnum(t tensor.AttentionType) int {
+	switch t {
+	case tensor.AttentionGQA:
+		return C.NVLLM_ATTN_GQA
+	case tensor.AttentionMQA:
+		return C.NVLLM_ATTN_MQA
+	}
+	return C.NVLLM_ATTN_MHA
+}
+func normEnum(t tensor.NormType) int {
+	if t == tensor.NormRMS {
+		return C.NVLLM_NORM_RMS
+	}
+	return C.NVLLM_NORM_LAYER
+}
+func posEnum(t tensor.PositionType) int {
+	switch t {
+	case tensor.PositionRoPE:
+		return C.NVLLM_POS_ROPE
+	case tensor.PositionLearned:
+		return C.NVLLM_POS_LEARNED
+	}
+	return C.NVLLM_POS_NONE
+}
+func actEnum(t tensor.ActivationType) int {
+	if t == tensor.ActivationSwiGLU {
+		return C.NVLLM_ACT_SWIGLU
+	}
+	return C.NVLLM_ACT_GELU
+}
+func blockEnum(t tensor.BlockStyle) int {
+	if t == tensor.BlockParallel {
+		return C.NVLLM_BLOCK_PARALLEL
+	}
+	return C.NVLLM_BLOCK_SEQUENTIAL
+}

@@ -333,5 +333,34 @@ def test_resident_decode_matches_stepwise():
             run.run_resident()
             got, _ = run.sync(5)
             np.testing.assert_array_equal(got, ref[i])
+        # resident straight after a prefill step (decode state derived on the device), twice:
+        # the second time from nvllm_rerun's replay of the staged prefill
+        first, _ = run.run_flat([list(p) for p in prompts], True, [0] * 5, bts, [0.0] * 5)
+        for rep in range(2):
+            if rep == 1:
+                run.rerun()
+                got, _ = run.sync(5)
+                np.testing.assert_array_equal(got, first)
+            for i in range(steps):
+                run.run_resident()
+                got, _ = run.sync(5)
+                np.testing.assert_array_equal(got, ref[i])
+    finally:
+        run.close()
+
+
+def test_profile_reports_every_kernel_class():
+    cfg = TINY["granite"]()
+    run = _runner(cfg, C.PREC_BF16)
+    try:
+        prompt = W.random_prompt(cfg.vocab_size, 40, 1).tolist()
+        run.set_profile(True)
+        run.run_flat([prompt], True, [0], [[0]], [0.0])
+        prof = run.get_profile()
+        for k in ("embed", "norm", "gemm_tc5", "rope_kv", "attn_prefill", "moe_route", "moe_gemm",
+                  "moe_misc", "sample"):
+            assert k in prof and prof[k]["ms"] > 0 and prof[k]["bytes"] > 0, k
+        assert prof["gemm_tc5"]["launches"] == 2 * cfg.num_layers
+        run.set_profile(False)
     finally:
         run.close()
