@@ -160,8 +160,36 @@ static cudaError_t prefill_dispatch(cudaStream_t st, const AttnArgs& a) {
   return cudaGetLastError();
 }
 
+int attn_prefill_qtile(int qdt, int kvdt, int hd) {
+  return attn_mma_supported(qdt, kvdt, hd) ? 64 : ATTN_PREFILL_QTILE;
+}
+
+int attn_decode_splits(int qdt, int kvdt, int n_seqs, int nh, int nkv, int hd, int max_len,
+                       int sm_count) {
+  int ctas, max_splits;
+  if (attn_mma_supported(qdt, kvdt, hd)) {
+    const int G = nh / nkv;
+    ctas = n_seqs * nkv * ((G + 15) / 16);
+    max_splits = (max_len + attn_decode_mma_tile(hd) - 1) / attn_decode_mma_tile(hd);
+  } else {
+    const int G = nh / nkv;
+    int gc = 1;
+    for (int c = 4; c >= 1; c--)
+      if (G % c == 0) {
+        gc = c;
+        break;
+      }
+    ctas = n_seqs * (nh / gc);
+    max_splits = (max_len + 255) / 256;
+  }
+  int ns = (2 * sm_count + ctas - 1) / ctas;
+  ns = min(ns, max_splits);
+  return max(1, min(ns, 32));
+}
+
 cudaError_t launch_attn_prefill(cudaStream_t st, const AttnArgs& a) {
   if (a.n_qtiles <= 0) return cudaSuccess;
+  if (attn_mma_supported(a.qdt, a.kvdt, a.hd)) return launch_attn_prefill_mma(st, a);
   if (a.qdt == DT_F32 && a.kvdt == DT_F32) return prefill_dispatch<float, float>(st, a);
   if (a.qdt == DT_F32 && a.kvdt == DT_BF16) return prefill_dispatch<float, bf16>(st, a);
   if (a.qdt == DT_BF16 && a.kvdt == DT_BF16) return prefill_dispatch<bf16, bf16>(st, a);
@@ -350,6 +378,12 @@ static cudaError_t decode_dispatch(cudaStream_t st, const AttnArgs& a) {
 
 cudaError_t launch_attn_decode(cudaStream_t st, const AttnArgs& a) {
   if (a.n_seqs <= 0) return cudaSuccess;
+  if (attn_mma_supported(a.qdt, a.kvdt, a.hd)) {
+    cudaError_t e = launch_attn_decode_mma(st, a);
+    if (e != cudaSuccess || a.n_splits == 1) return e;
+    attn_combine_kernel<bf16><<<dim3(a.n_seqs, a.nh), min(128, a.hd), 0, st>>>(a);
+    return cudaGetLastError();
+  }
   if (a.qdt == DT_F32 && a.kvdt == DT_F32) return decode_dispatch<float, float>(st, a);
   if (a.qdt == DT_F32 && a.kvdt == DT_BF16) return decode_dispatch<float, bf16>(st, a);
   if (a.qdt == DT_BF16 && a.kvdt == DT_BF16) return decode_dispatch<bf16, bf16>(st, a);

@@ -257,17 +257,8 @@ int forward_step(nvllm_handle* h) {
   at.tile_seq = d + L.tile_seq; at.tile_q0 = d + L.tile_q0; at.n_qtiles = L.n_qtiles;
   at.seq_len = d + L.seq_len;
   at.ws = w.attn_ws;
-  if (!is_prefill) {
-    const int G = h->nh / h->nkv;
-    int gc = 1;
-    for (int cc = 4; cc >= 1; cc--)
-      if (G % cc == 0) { gc = cc; break; }
-    const int groups = n * (h->nh / gc);
-    int ns = (2 * h->sm_count + groups - 1) / groups;
-    ns = std::min(ns, (L.max_len + 255) / 256);
-    ns = std::max(1, std::min(ns, 32));
-    at.n_splits = ns;
-  }
+  if (!is_prefill)
+    at.n_splits = attn_decode_splits(h->adt, h->kvdt, n, h->nh, h->nkv, h->hd, L.max_len, h->sm_count);
   const double qo_bytes = 2.0 * T * h->q_cols * asz;
   const double attn_flops = 4.0 * h->nh * h->hd * L.attn_pairs;
   const double attn_bytes = 2.0 * L.sum_len * h->nkv * h->hd * kvsz + qo_bytes;

@@ -175,9 +175,20 @@ struct AttnArgs {
   int n_splits;
   float* ws;           // [n_seqs*nh*n_splits*(hd+2)] split partials
 };
-constexpr int ATTN_PREFILL_QTILE = 32;
+constexpr int ATTN_PREFILL_QTILE = 32;  // SIMT (fp32 parity) kernel; the mma kernel uses 64
+// queries per tile of the kernel launch_attn_prefill will pick: the host builds tile_seq /
+// tile_q0 with it
+int attn_prefill_qtile(int qdt, int kvdt, int hd);
+// KV splits for a decode step of n_seqs sequences whose longest context is max_len
+int attn_decode_splits(int qdt, int kvdt, int n_seqs, int nh, int nkv, int hd, int max_len,
+                       int sm_count);
 cudaError_t launch_attn_prefill(cudaStream_t st, const AttnArgs& a);
 cudaError_t launch_attn_decode(cudaStream_t st, const AttnArgs& a);
+// attention_mma.cu (bf16, hd 64 / 128)
+bool attn_mma_supported(int qdt, int kvdt, int hd);
+int attn_decode_mma_tile(int hd);
+cudaError_t launch_attn_prefill_mma(cudaStream_t st, const AttnArgs& a);
+cudaError_t launch_attn_decode_mma(cudaStream_t st, const AttnArgs& a);
 
 // ---------------------------------------------------------------- moe.cu
 // Router: probs = softmax(x @ R) over all E, top-k (descending), weights renormalised

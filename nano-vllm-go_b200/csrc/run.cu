@@ -97,6 +97,7 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
 
   // ---- pass 1: sizes and validation
   int T = 0, max_blocks = 0, n_qtiles = 0, max_len = 0;
+  const int qtile = attn_prefill_qtile(h->adt, h->kvdt, h->hd);
   long long sum_len = 0;
   double pairs = 0;
   for (int i = 0; i < n; i++) {
@@ -117,7 +118,7 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
     }
     const int n_new = len - start;
     T += n_new;
-    n_qtiles += (n_new + ATTN_PREFILL_QTILE - 1) / ATTN_PREFILL_QTILE;
+    n_qtiles += (n_new + qtile - 1) / qtile;
     max_blocks = std::max(max_blocks, nb);
     max_len = std::max(max_len, len);
     sum_len += len;
@@ -172,7 +173,7 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
     }
     s[L.last_row + i] = row - 1;
     if (is_prefill)
-      for (int q0 = 0; q0 < len - start; q0 += ATTN_PREFILL_QTILE, tile++) {
+      for (int q0 = 0; q0 < len - start; q0 += qtile, tile++) {
         s[L.tile_seq + tile] = i;
         s[L.tile_q0 + tile] = q0;
       }

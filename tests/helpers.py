@@ -33,6 +33,17 @@ TINY = {
     "falcon": lambda: C.tiny_falcon(),
 }
 
+# head_dim 64 / 128 siblings: in bf16 mode these take the tensor-core attention kernels
+# (attention_mma.cu); G = query heads per kv head
+TINY_HD = {
+    "gpt2_hd64": lambda: C.tiny_gpt2(hidden=128, num_heads=2, num_kv_heads=2, head_dim=64),       # G=1
+    "llama_hd64": lambda: C.tiny_llama(hidden=256, num_heads=4, num_kv_heads=1, head_dim=64),     # G=4
+    "llama_hd128": lambda: C.tiny_llama(hidden=256, num_heads=2, num_kv_heads=1, head_dim=128),   # G=2
+    "granite_hd64": lambda: C.tiny_granite(hidden=128, num_heads=2, num_kv_heads=1, head_dim=64),
+    "falcon_g18": lambda: C.tiny_falcon(hidden=18 * 64, num_heads=18, head_dim=64,
+                                        ffn_dim=2 * 18 * 64),                                    # G=18
+}
+
 
 def oracle_mod():
     from oracle import oracle as O

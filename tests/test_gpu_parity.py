@@ -11,7 +11,7 @@ Gates (BASELINE.json north_star / SURVEY.md §8d):
 import numpy as np
 import pytest
 
-from helpers import C, W, E, TINY, make_oracle, oracle_mod, rel_err
+from helpers import C, W, E, TINY, TINY_HD, make_oracle, oracle_mod, rel_err
 import nvllm_pkg
 
 pytestmark = pytest.mark.gpu
@@ -102,8 +102,8 @@ def test_argmax_bit_exact_with_ties():
 
 
 # ------------------------------------------------------------------ whole forward pass
-def _greedy_parity(name, prec, prompt_len, steps):
-    cfg = TINY[name]()
+def _greedy_parity(name, prec, prompt_len, steps, table=None):
+    cfg = (table or TINY)[name]()
     bf16 = prec == C.PREC_BF16
     orc = make_oracle(cfg, round_bf16=bf16)
     run = _runner(cfg, prec)
@@ -145,6 +145,21 @@ def test_fp32_logits_and_greedy_tokens(name):
 @pytest.mark.parametrize("name", list(TINY))
 def test_bf16_logits_and_greedy_tokens(name):
     _greedy_parity(name, C.PREC_BF16, prompt_len=40, steps=32)
+
+
+@pytest.mark.parametrize("name", list(TINY_HD))
+@pytest.mark.parametrize("prec", [C.PREC_FP32, C.PREC_BF16])
+def test_head_dim_64_128_families(name, prec):
+    """head_dim 64 / 128: bf16 mode runs the tensor-core attention kernels (prefill tiles of 64
+    queries, decode with the query-head group as MMA rows, MQA group of 18 heads in 2 chunks)."""
+    _greedy_parity(name, prec, prompt_len=100, steps=12, table=TINY_HD)
+
+
+@pytest.mark.parametrize("name", ["llama_hd64", "llama_hd128", "falcon_g18"])
+def test_bf16_long_context_split_kv(name):
+    """700-token prompt: several KV tiles per CTA, split-KV decode (few CTAs -> splits),
+    three KV blocks."""
+    _greedy_parity(name, C.PREC_BF16, prompt_len=700, steps=6, table=TINY_HD)
 
 
 @pytest.mark.parametrize("name", ["gpt2", "llama"])
