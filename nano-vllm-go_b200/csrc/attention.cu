@@ -24,6 +24,8 @@ constexpr int PF_KT = 64;  // keys per shared-memory tile (divides KV_BLOCK)
 template <typename QT, typename KT, int HD>
 __global__ void __launch_bounds__(128)
 attn_prefill_kernel(AttnArgs a) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float smem[];
   float* Ks = smem;               // [PF_KT][HD]
   float* Vs = smem + PF_KT * HD;  // [PF_KT][HD]
@@ -147,7 +149,7 @@ static cudaError_t prefill_dispatch(cudaStream_t st, const AttnArgs& a) {
     if (smem > 48 * 1024)                                                                    \
       cudaFuncSetAttribute(attn_prefill_kernel<QT, KT, HD>,                                  \
                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);          \
-    attn_prefill_kernel<QT, KT, HD><<<grid, 128, smem, st>>>(a);                             \
+    (void)launch_k(attn_prefill_kernel<QT, KT, HD>, dim3(grid), dim3(128), smem, st, a);                             \
   }
   switch (a.hd) {
     case 16: PF(16); break;
@@ -201,6 +203,8 @@ cudaError_t launch_attn_prefill(cudaStream_t st, const AttnArgs& a) {
 template <typename QT, typename KT, int HD, int GC>
 __global__ void __launch_bounds__(128)
 attn_decode_kernel(AttnArgs a) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int LPT = HD / 8;    // lanes per token row
   constexpr int TPI = 32 / LPT;  // token rows per warp iteration
   constexpr int NW = 4;
@@ -324,6 +328,8 @@ attn_decode_kernel(AttnArgs a) {
 
 template <typename QT>
 __global__ void attn_combine_kernel(AttnArgs a) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int seq = blockIdx.x, h = blockIdx.y, HD = a.hd;
   const float* rec0 = a.ws + (((size_t)seq * a.nh + h) * a.n_splits) * (HD + 2);
   float mn = -INFINITY;
@@ -352,15 +358,15 @@ static cudaError_t decode_dispatch_gc(cudaStream_t st, const AttnArgs& a) {
     }
   dim3 grid(a.n_seqs, a.nh / gc, a.n_splits);
   switch (gc) {
-    case 4: attn_decode_kernel<QT, KT, HD, 4><<<grid, 128, 0, st>>>(a); break;
-    case 3: attn_decode_kernel<QT, KT, HD, 3><<<grid, 128, 0, st>>>(a); break;
-    case 2: attn_decode_kernel<QT, KT, HD, 2><<<grid, 128, 0, st>>>(a); break;
-    default: attn_decode_kernel<QT, KT, HD, 1><<<grid, 128, 0, st>>>(a); break;
+    case 4: (void)launch_k(attn_decode_kernel<QT, KT, HD, 4>, dim3(grid), dim3(128), 0, st, a); break;
+    case 3: (void)launch_k(attn_decode_kernel<QT, KT, HD, 3>, dim3(grid), dim3(128), 0, st, a); break;
+    case 2: (void)launch_k(attn_decode_kernel<QT, KT, HD, 2>, dim3(grid), dim3(128), 0, st, a); break;
+    default: (void)launch_k(attn_decode_kernel<QT, KT, HD, 1>, dim3(grid), dim3(128), 0, st, a); break;
   }
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   if (a.n_splits > 1) {
-    attn_combine_kernel<QT><<<dim3(a.n_seqs, a.nh), min(128, a.hd), 0, st>>>(a);
+    (void)launch_k(attn_combine_kernel<QT>, dim3(dim3(a.n_seqs, a.nh)), dim3(min(128, a.hd)), 0, st, a);
     e = cudaGetLastError();
   }
   return e;
@@ -381,7 +387,7 @@ cudaError_t launch_attn_decode(cudaStream_t st, const AttnArgs& a) {
   if (attn_mma_supported(a.qdt, a.kvdt, a.hd)) {
     cudaError_t e = launch_attn_decode_mma(st, a);
     if (e != cudaSuccess || a.n_splits == 1) return e;
-    attn_combine_kernel<bf16><<<dim3(a.n_seqs, a.nh), min(128, a.hd), 0, st>>>(a);
+    (void)launch_k(attn_combine_kernel<bf16>, dim3(dim3(a.n_seqs, a.nh)), dim3(min(128, a.hd)), 0, st, a);
     return cudaGetLastError();
   }
   if (a.qdt == DT_F32 && a.kvdt == DT_F32) return decode_dispatch<float, float>(st, a);

@@ -166,6 +166,8 @@ __device__ __forceinline__ void load_tile(uint32_t dst, const bf16* src, int row
 template <int HD>
 __global__ void __launch_bounds__(128)
 attn_prefill_mma_kernel(AttnArgs a) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int BM = 64, BN = 64;
   extern __shared__ __align__(128) uint8_t smem[];
   const uint32_t sQ = smem_addr(smem);
@@ -253,6 +255,8 @@ attn_prefill_mma_kernel(AttnArgs a) {
 template <int HD, int BN, int STAGES>
 __global__ void __launch_bounds__(128)
 attn_decode_mma_kernel(AttnArgs a, int G, int chunks) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int TILE_BYTES = BN * HD * 2;
   constexpr int WK = BN / 4;  // keys per warp per tile
   extern __shared__ __align__(128) uint8_t smem[];
@@ -380,7 +384,7 @@ static cudaError_t prefill_launch(cudaStream_t st, const AttnArgs& a) {
   cudaError_t e = cudaFuncSetAttribute(attn_prefill_mma_kernel<HD>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  attn_prefill_mma_kernel<HD><<<dim3(a.n_qtiles, a.nh), 128, smem, st>>>(a);
+  (void)launch_k(attn_prefill_mma_kernel<HD>, dim3(dim3(a.n_qtiles, a.nh)), dim3(128), smem, st, a);
   return cudaGetLastError();
 }
 cudaError_t launch_attn_prefill_mma(cudaStream_t st, const AttnArgs& a) {
@@ -396,8 +400,7 @@ static cudaError_t decode_launch(cudaStream_t st, const AttnArgs& a, int G, int 
   cudaError_t e = cudaFuncSetAttribute(attn_decode_mma_kernel<HD, BN, STAGES>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  attn_decode_mma_kernel<HD, BN, STAGES>
-      <<<dim3(a.n_seqs, a.nkv * chunks, a.n_splits), 128, smem, st>>>(a, G, chunks);
+  (void)launch_k(attn_decode_mma_kernel<HD, BN, STAGES>, dim3(dim3(a.n_seqs, a.nkv * chunks, a.n_splits)), dim3(128), smem, st, a, G, chunks);
   return cudaGetLastError();
 }
 int attn_decode_mma_tile(int hd) { return hd == 64 ? 128 : 64; }

@@ -15,6 +15,8 @@ template <typename WT>
 __global__ void embed_kernel(const int* __restrict__ tokens, const int* __restrict__ positions,
                              const WT* __restrict__ wte, const WT* __restrict__ wpe, int max_pos,
                              float mult, float* __restrict__ x, int H) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int t = blockIdx.x;
   const int tok = tokens[t];
   const int pos = positions[t];
@@ -44,10 +46,10 @@ cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int*
   if (T <= 0) return cudaSuccess;
   int threads = min(256, max(32, ((H / 8 + 31) / 32) * 32));
   if (wdt == DT_F32)
-    embed_kernel<float><<<T, threads, 0, st>>>(tokens, positions, (const float*)wte,
+    (void)launch_k(embed_kernel<float>, dim3(T), dim3(threads), 0, st, tokens, positions, (const float*)wte,
                                                (const float*)wpe, max_pos, mult, x, H);
   else
-    embed_kernel<bf16><<<T, threads, 0, st>>>(tokens, positions, (const bf16*)wte,
+    (void)launch_k(embed_kernel<bf16>, dim3(T), dim3(threads), 0, st, tokens, positions, (const bf16*)wte,
                                               (const bf16*)wpe, max_pos, mult, x, H);
   return cudaGetLastError();
 }
@@ -59,6 +61,8 @@ cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int*
 // The updated row is staged in shared memory so x is read once and written once.
 template <typename YT>
 __global__ void norm_kernel(NormArgs a) {
+  pdl_launch_dependents();
+  pdl_wait();
   extern __shared__ float row[];
   __shared__ float red[32];
   const int H = a.H;
@@ -159,9 +163,9 @@ cudaError_t launch_norm(cudaStream_t st, const NormArgs& a) {
   int threads = min(512, max(64, ((a.H / 8 + 31) / 32) * 32));
   size_t smem = (size_t)a.H * sizeof(float);
   if (a.ydt == DT_F32)
-    norm_kernel<float><<<a.n_rows, threads, smem, st>>>(a);
+    (void)launch_k(norm_kernel<float>, dim3(a.n_rows), dim3(threads), smem, st, a);
   else
-    norm_kernel<bf16><<<a.n_rows, threads, smem, st>>>(a);
+    (void)launch_k(norm_kernel<bf16>, dim3(a.n_rows), dim3(threads), smem, st, a);
   return cudaGetLastError();
 }
 
@@ -178,6 +182,8 @@ __device__ __forceinline__ float silu(float x) {  // mamba2.go:360-367
 template <typename OT>
 __global__ void act_kernel(int T, int F, const float* __restrict__ h, int S, size_t stride,
                            const float* __restrict__ bias, int swiglu, OT* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int ld = swiglu ? 2 * F : F;
   const size_t nvec = (size_t)T * (F / 8);
   for (size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec;
@@ -226,9 +232,9 @@ cudaError_t launch_act(cudaStream_t st, int odt, int T, int F, const float* h, i
   int threads = 256;
   int blocks = (int)min((size_t)148 * 16, (nvec + threads - 1) / threads);
   if (odt == DT_F32)
-    act_kernel<float><<<blocks, threads, 0, st>>>(T, F, h, S, stride, bias, swiglu, (float*)out);
+    (void)launch_k(act_kernel<float>, dim3(blocks), dim3(threads), 0, st, T, F, h, S, stride, bias, swiglu, (float*)out);
   else
-    act_kernel<bf16><<<blocks, threads, 0, st>>>(T, F, h, S, stride, bias, swiglu, (bf16*)out);
+    (void)launch_k(act_kernel<bf16>, dim3(blocks), dim3(threads), 0, st, T, F, h, S, stride, bias, swiglu, (bf16*)out);
   return cudaGetLastError();
 }
 
@@ -242,6 +248,8 @@ __global__ void rope_kv_kernel(int nh, int nkv, int hd, const float* __restrict_
                                const float* __restrict__ cosT, const float* __restrict__ sinT,
                                QT* __restrict__ q_out, KT* __restrict__ kpool,
                                KT* __restrict__ vpool) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int t = blockIdx.x;
   const int half = hd / 2;
   const int vph = half / 8;  // vectors per half head
@@ -311,7 +319,7 @@ cudaError_t launch_rope_kv(cudaStream_t st, int qdt, int kvdt, int T, int nh, in
   int items = (nh + 2 * nkv) * (hd / 16);
   int threads = min(256, max(32, ((items + 31) / 32) * 32));
 #define RK(QT, KT)                                                                              \
-  rope_kv_kernel<QT, KT><<<T, threads, 0, st>>>(nh, nkv, hd, qkv, S, stride, bias, positions,   \
+  (void)launch_k(rope_kv_kernel<QT, KT>, dim3(T), dim3(threads), 0, st, nh, nkv, hd, qkv, S, stride, bias, positions,   \
                                                 slots, cosT, sinT, (QT*)q_out, (KT*)kpool,      \
                                                 (KT*)vpool)
   if (qdt == DT_F32 && kvdt == DT_F32) RK(float, float);
@@ -336,6 +344,8 @@ __device__ __forceinline__ ArgMax argmax_merge(ArgMax a, ArgMax b) {
 __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
                               const float* __restrict__ temperature,
                               const float* __restrict__ uniforms, int* __restrict__ out_tokens) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float red[32];
   __shared__ ArgMax amred[32];
   __shared__ float scan[1024];
@@ -417,13 +427,15 @@ __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
 cudaError_t launch_sample(cudaStream_t st, const float* logits, int ldl, int V, int n,
                           const float* temperature, const float* uniforms, int* out_tokens) {
   if (n <= 0) return cudaSuccess;
-  sample_kernel<<<n, 1024, 0, st>>>(logits, ldl, V, temperature, uniforms, out_tokens);
+  (void)launch_k(sample_kernel, dim3(n), dim3(1024), 0, st, logits, ldl, V, temperature, uniforms, out_tokens);
   return cudaGetLastError();
 }
 
 __global__ void advance_kernel(int n, const int* __restrict__ sampled, int* tokens, int* positions,
                                int* slots, int* seq_len, const int* __restrict__ block_tables,
                                int max_blocks, int max_pos) {
+  pdl_launch_dependents();
+  pdl_wait();
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   tokens[i] = sampled[i];
@@ -440,7 +452,7 @@ cudaError_t launch_advance(cudaStream_t st, int n, const int* sampled, int* toke
                            int* slots, int* seq_len, const int* block_tables, int max_blocks,
                            int max_pos) {
   if (n <= 0) return cudaSuccess;
-  advance_kernel<<<(n + 127) / 128, 128, 0, st>>>(n, sampled, tokens, positions, slots, seq_len,
+  (void)launch_k(advance_kernel, dim3((n + 127) / 128), dim3(128), 0, st, n, sampled, tokens, positions, slots, seq_len,
                                                  block_tables, max_blocks, max_pos);
   return cudaGetLastError();
 }
@@ -524,6 +536,8 @@ cudaError_t launch_fill(cudaStream_t st, float* p, size_t n, float v) {
 // out[i] = sum_s p[s*stride + i]   (split-K partials of the LM head -> logits)
 __global__ void reduce_partials_kernel(const float* __restrict__ p, int S, size_t stride, size_t n,
                                        float* __restrict__ out) {
+  pdl_launch_dependents();
+  pdl_wait();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (size_t)gridDim.x * blockDim.x) {
     float acc = 0.f;
@@ -535,7 +549,7 @@ cudaError_t launch_reduce_partials(cudaStream_t st, const float* p, int S, size_
                                    float* out) {
   if (n == 0) return cudaSuccess;
   int blocks = (int)min((size_t)148 * 8, (n + 255) / 256);
-  reduce_partials_kernel<<<blocks, 256, 0, st>>>(p, S, stride, n, out);
+  (void)launch_k(reduce_partials_kernel, dim3(blocks), dim3(256), 0, st, p, S, stride, n, out);
   return cudaGetLastError();
 }
 
@@ -548,6 +562,8 @@ __global__ void make_decode_state_kernel(int n, int mb, const int* __restrict__ 
                                          const int* __restrict__ src_uni, int* tokens,
                                          int* positions, int* slots, int* cu_q, int* seq_start,
                                          int* seq_len, int* last_row, int* bt, int* temp, int* uni) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int i = blockIdx.x;
   for (int b = threadIdx.x; b < mb; b += blockDim.x) bt[(size_t)i * mb + b] = src_bt[(size_t)i * mb + b];
   if (threadIdx.x == 0) {
@@ -572,7 +588,7 @@ cudaError_t launch_make_decode_state(cudaStream_t st, int n, int mb, const int* 
                                      int* cu_q, int* seq_start, int* seq_len, int* last_row, int* bt,
                                      int* temp, int* uni) {
   if (n <= 0) return cudaSuccess;
-  make_decode_state_kernel<<<n, 64, 0, st>>>(n, mb, sampled, src_seq_len, src_bt, src_temp, src_uni,
+  (void)launch_k(make_decode_state_kernel, dim3(n), dim3(64), 0, st, n, mb, sampled, src_seq_len, src_bt, src_temp, src_uni,
                                              tokens, positions, slots, cu_q, seq_start, seq_len,
                                              last_row, bt, temp, uni);
   return cudaGetLastError();

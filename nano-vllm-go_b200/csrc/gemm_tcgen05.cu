@@ -39,6 +39,9 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
                : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
@@ -120,43 +123,65 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
 }
 
 // ------------------------------------------------------------------ kernel
+// Persistent: grid = min(units, #SM) CTAs, one per SM (the operand ring takes ~192 KB of
+// shared memory).  A unit is (token tile, weight tile, k split); CTA c runs units c, c + grid,
+// ... with the TMA ring never draining between units and two TMEM accumulators so the
+// epilogue of unit i overlaps the MMAs of unit i + 1.
+//
+// Programmatic dependent launch: the weight tiles of the first STAGES k-blocks do not depend
+// on the previous kernel, so the producer issues them BEFORE griddepcontrol.wait — the HBM
+// stream of this GEMM starts while the elementwise kernel in front of it is still running.
+// Only the activation tiles (and every global store) wait for the dependency.
+struct Tc5Sched {
+  int units, n_tiles, S, kbps, nkb_total;
+};
+__device__ __forceinline__ void tc5_unit(const Tc5Sched& sc, int u, int BT, int& n0, int& m0,
+                                         int& kb0, int& nkb, int& split) {
+  split = u % sc.S;
+  const int r = u / sc.S;
+  n0 = (r % sc.n_tiles) * TC_BN;
+  m0 = (r / sc.n_tiles) * BT;
+  kb0 = split * sc.kbps;
+  nkb = min(sc.kbps, sc.nkb_total - kb0);
+}
+
 template <int BT, int STAGES>
-__global__ void __launch_bounds__(TC_THREADS)
+__global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
-                int M, int N, int K, int kb_per_split, float* __restrict__ out, int ldo,
-                size_t split_stride, float alpha) {
+                int M, int N, Tc5Sched sc, float* __restrict__ out, int ldo, size_t split_stride,
+                float alpha, int w_reused) {
   constexpr uint32_t W_BYTES = TC_BN * TC_BK * 2;
   constexpr uint32_t A_BYTES = BT * TC_BK * 2;
   constexpr uint32_t STAGE_BYTES = W_BYTES + A_BYTES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t tiles = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B needs 1024 B
   const uint32_t bars = tiles + STAGES * STAGE_BYTES;
-  // full[s] at bars + 8 s, empty[s] at bars + 8 (STAGES + s), tmem_full, tmem slot
-  const uint32_t bar_tmem_full = bars + 16 * STAGES;
-  const uint32_t tmem_slot = bar_tmem_full + 8;
+  // full[s] at bars + 8 s, empty[s] at bars + 8 (STAGES + s), then tmem_full[2], tmem_empty[2]
+  const uint32_t bar_tfull = bars + 16 * STAGES;
+  const uint32_t bar_tempty = bar_tfull + 16;
+  const uint32_t tmem_slot = bar_tempty + 16;
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(
       smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * TC_BN;
-  const int m0 = blockIdx.y * BT;
-  const int nkb_total = (K + TC_BK - 1) / TC_BK;
-  const int kb0 = blockIdx.z * kb_per_split;
-  const int nkb = min(kb_per_split, nkb_total - kb0);
+  pdl_launch_dependents();
 
   if (warp == 0 && lane == 0) {
     for (int s = 0; s < STAGES; s++) {
       mbar_init(bars + 8 * s, 1);
       mbar_init(bars + 8 * (STAGES + s), 1);
     }
-    mbar_init(bar_tmem_full, 1);
+    for (int b = 0; b < 2; b++) {
+      mbar_init(bar_tfull + 8 * b, 1);
+      mbar_init(bar_tempty + 8 * b, 4);  // one arrival per epilogue warp
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
   }
   if (warp == 1) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tmem_slot),
-                 "r"((uint32_t)BT)
+                 "r"((uint32_t)(2 * BT))
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
@@ -164,23 +189,54 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  const int grid = gridDim.x;
 
   if (warp == 0) {
     if (lane == 0) {
-      // weights are read once per step: keep them from displacing activations in L2
+      // weights read once per step must not displace activations in L2; weights re-read by
+      // other token tiles (prefill) stay
       uint64_t pol_w, pol_a;
-      asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
+      if (w_reused)
+        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_w));
+      else
+        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
       asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_a));
-      for (int i = 0; i < nkb; i++) {
-        const int s = i % STAGES;
-        const uint32_t ph = (i / STAGES) & 1;
-        mbar_wait(bars + 8 * (STAGES + s), ph ^ 1);
-        const uint32_t full = bars + 8 * s;
-        mbar_expect_tx(full, STAGE_BYTES);
-        const uint32_t dst = tiles + s * STAGE_BYTES;
-        const int k = (kb0 + i) * TC_BK;
-        tma_load_2d_hint(dst, &tmW, full, k, n0, pol_w);
-        tma_load_2d_hint(dst + W_BYTES, &tmA, full, k, m0, pol_a);
+      int n0, m0, kb0, nkb, split;
+      // (1) weight tiles of the first STAGES k-blocks, before the dependency resolves
+      int pre = 0;
+      {
+        int u = blockIdx.x, kb = 0;
+        while (pre < STAGES && u < sc.units) {
+          tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split);
+          const uint32_t full = bars + 8 * pre;
+          mbar_expect_tx(full, STAGE_BYTES);
+          tma_load_2d_hint(tiles + pre * STAGE_BYTES, &tmW, full, (kb0 + kb) * TC_BK, n0, pol_w);
+          pre++;
+          if (++kb == nkb) {
+            kb = 0;
+            u += grid;
+          }
+        }
+      }
+      pdl_wait();
+      // (2) their activation tiles, then (3) the steady state
+      int u = blockIdx.x, kb = 0, i = 0;
+      while (u < sc.units) {
+        tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split);
+        for (; kb < nkb; kb++, i++) {
+          const int s = i % STAGES;
+          const uint32_t full = bars + 8 * s;
+          const uint32_t dst = tiles + s * STAGE_BYTES;
+          const int k = (kb0 + kb) * TC_BK;
+          if (i >= pre) {
+            mbar_wait(bars + 8 * (STAGES + s), ((i / STAGES) & 1) ^ 1);
+            mbar_expect_tx(full, STAGE_BYTES);
+            tma_load_2d_hint(dst, &tmW, full, k, n0, pol_w);
+          }
+          tma_load_2d_hint(dst + W_BYTES, &tmA, full, k, m0, pol_a);
+        }
+        kb = 0;
+        u += grid;
       }
     }
   } else if (warp == 1) {
@@ -189,50 +245,68 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       // both K-major, N = BT, M = 128
       constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BT >> 3) << 17) |
                                  ((uint32_t)(TC_BN >> 4) << 24);
-      for (int i = 0; i < nkb; i++) {
-        const int s = i % STAGES;
-        const uint32_t ph = (i / STAGES) & 1;
-        mbar_wait(bars + 8 * s, ph);
+      int n0, m0, kb0, nkb, split;
+      int i = 0, lu = 0;
+      for (int u = blockIdx.x; u < sc.units; u += grid, lu++) {
+        tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split);
+        const int buf = lu & 1;
+        mbar_wait(bar_tempty + 8 * buf, ((lu >> 1) & 1) ^ 1);  // epilogue drained this buffer
         tc_fence_after();
-        const uint32_t wt = tiles + s * STAGE_BYTES;
-        const uint64_t wdesc = make_smem_desc(wt);
-        const uint64_t adesc = make_smem_desc(wt + W_BYTES);
+        const uint32_t tacc = tmem_base + (uint32_t)(buf * BT);
+        for (int kb = 0; kb < nkb; kb++, i++) {
+          const int s = i % STAGES;
+          mbar_wait(bars + 8 * s, (i / STAGES) & 1);
+          tc_fence_after();
+          const uint32_t wt = tiles + s * STAGE_BYTES;
+          const uint64_t wdesc = make_smem_desc(wt);
+          const uint64_t adesc = make_smem_desc(wt + W_BYTES);
 #pragma unroll
-        for (int kk = 0; kk < TC_BK / 16; kk++) {
-          // advancing 16 bf16 = 32 bytes inside the swizzle row: +2 in the >>4 address field
-          tc_mma_bf16(tmem_base, wdesc + 2 * kk, adesc + 2 * kk, idesc, (i | kk) != 0);
+          for (int kk = 0; kk < TC_BK / 16; kk++) {
+            // advancing 16 bf16 = 32 bytes inside the swizzle row: +2 in the >>4 address field
+            tc_mma_bf16(tacc, wdesc + 2 * kk, adesc + 2 * kk, idesc, (kb | kk) != 0);
+          }
+          tc_commit(bars + 8 * (STAGES + s));  // frees the stage when these MMAs retire
         }
-        tc_commit(bars + 8 * (STAGES + s));  // frees the stage when these MMAs retire
+        tc_commit(bar_tfull + 8 * buf);
       }
-      tc_commit(bar_tmem_full);
     }
   } else {
     // epilogue: warp w may touch TMEM lanes [32 (w % 4), +32)
     const int q = warp & 3;
-    const int n = n0 + q * 32 + lane;
-    mbar_wait(bar_tmem_full, 0);
-    tc_fence_after();
-    float* obase = out + (size_t)blockIdx.z * split_stride + n;
-    const bool n_ok = n < N;
+    pdl_wait();  // global stores below must follow the previous kernel's completion
+    int n0, m0, kb0, nkb, split;
+    int lu = 0;
+    for (int u = blockIdx.x; u < sc.units; u += grid, lu++) {
+      tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split);
+      const int buf = lu & 1;
+      mbar_wait(bar_tfull + 8 * buf, (lu >> 1) & 1);
+      tc_fence_after();
+      const int n = n0 + q * 32 + lane;
+      float* obase = out + (size_t)split * split_stride + n;
+      const bool n_ok = n < N;
 #pragma unroll 1
-    for (int c0 = 0; c0 < BT; c0 += 32) {
-      if (m0 + c0 >= M) break;
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
-      if (n_ok) {
+      for (int c0 = 0; c0 < BT; c0 += 32) {
+        if (m0 + c0 >= M) break;
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
+        if (n_ok) {
 #pragma unroll
-        for (int c = 0; c < 32; c++) {
-          const int m = m0 + c0 + c;
-          if (m < M) obase[(size_t)m * ldo] = alpha * __uint_as_float(r[c]);
+          for (int c = 0; c < 32; c++) {
+            const int m = m0 + c0 + c;
+            if (m < M) obase[(size_t)m * ldo] = alpha * __uint_as_float(r[c]);
+          }
         }
       }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
-                 "r"((uint32_t)BT)
+                 "r"((uint32_t)(2 * BT))
                  : "memory");
   }
 }
@@ -294,40 +368,67 @@ static const TmaDesc* cached_map(const void* base, int rows, int cols, int box_r
 
 bool tc5_supported(int M, int N, int K) { return M >= 1 && N >= 1 && K >= 8 && (K % 8) == 0; }
 
-static int pick_bt(int M) { return M <= 32 ? 32 : (M <= 64 ? 64 : 128); }
+static int pick_bt(int M) { return M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256)); }
 int tc5_box_rows_act(int M) { return pick_bt(M); }
 
+// Split-K factor minimising the makespan of the persistent schedule: rounds of units over the
+// SMs x (k-blocks per unit + a fixed per-unit cost for the accumulator hand-off / epilogue),
+// plus what the consumer pays to re-read S partial slices.
 int tc5_splits(int M, int N, int K, int sm_count) {
   const int bt = pick_bt(M);
   const long tiles = (long)ceil_div(N, TC_BN) * ceil_div(M, bt);
   const int nkb = ceil_div(K, TC_BK);
   if (tiles >= 2L * sm_count) return 1;
-  int s = (int)((2L * sm_count + tiles - 1) / tiles);
-  s = min(s, max(1, nkb / 4));  // at least 4 k-blocks (256 k) per split
-  s = min(s, 16);
-  return max(s, 1);
+  int best = 1;
+  double best_cost = 1e30;
+  for (int s = 1; s <= 16 && s <= nkb; s++) {
+    const int kbps = ceil_div(nkb, s);
+    if (s > 1 && kbps < 2) break;
+    const int s_eff = ceil_div(nkb, kbps);
+    if (s_eff != s) continue;
+    const long units = tiles * s;
+    const long rounds = (units + sm_count - 1) / sm_count;
+    const double cost = (double)rounds * (kbps + 1.5) + 0.35 * s;
+    if (cost < best_cost - 1e-9) {
+      best_cost = cost;
+      best = s;
+    }
+  }
+  return best;
 }
+
+static bool g_pdl = true;
+void set_pdl_enabled(bool on) { g_pdl = on; }
+bool pdl_enabled() { return g_pdl; }
 
 template <int BT, int STAGES>
 static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* tw,
                              const TmaDesc* ta, int S) {
   constexpr size_t smem = (size_t)STAGES * (TC_BN + BT) * TC_BK * 2 + 1024 + 16 * STAGES + 64;
+  static_assert(smem <= 232448, "shared memory budget");
   static uint64_t attr_mask = 0;  // per device
+  static int sm_counts[64] = {0};
   int dev = 0;
   cudaGetDevice(&dev);
   if (!(attr_mask >> dev & 1)) {
     cudaError_t e = cudaFuncSetAttribute(gemm_tc5_kernel<BT, STAGES>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
+    cudaDeviceGetAttribute(&sm_counts[dev], cudaDevAttrMultiProcessorCount, dev);
     attr_mask |= 1ull << dev;
   }
-  const int nkb = ceil_div(a.K, TC_BK);
-  const int kbps = ceil_div(nkb, S);
-  dim3 grid(ceil_div(a.N, TC_BN), ceil_div(a.M, BT), ceil_div(nkb, kbps));
-  gemm_tc5_kernel<BT, STAGES><<<grid, TC_THREADS, smem, st>>>(
-      *reinterpret_cast<const CUtensorMap*>(tw), *reinterpret_cast<const CUtensorMap*>(ta), a.M, a.N,
-      a.K, kbps, a.out, a.ldo, a.split_stride, a.alpha);
-  return cudaGetLastError();
+  Tc5Sched sc;
+  sc.nkb_total = ceil_div(a.K, TC_BK);
+  sc.kbps = ceil_div(sc.nkb_total, S);
+  sc.S = ceil_div(sc.nkb_total, sc.kbps);
+  sc.n_tiles = ceil_div(a.N, TC_BN);
+  const int m_tiles = ceil_div(a.M, BT);
+  sc.units = sc.n_tiles * m_tiles * sc.S;
+  const int grid = min(sc.units, max(1, sm_counts[dev]));
+  return launch_k(gemm_tc5_kernel<BT, STAGES>, dim3(grid), dim3(TC_THREADS), smem, st,
+                  *reinterpret_cast<const CUtensorMap*>(tw),
+                  *reinterpret_cast<const CUtensorMap*>(ta), a.M, a.N, sc, a.out, a.ldo,
+                  a.split_stride, a.alpha, m_tiles > 1 ? 1 : 0);
 }
 
 // a.S is the requested number of splits; the number actually written is returned in *S_out
@@ -344,9 +445,10 @@ cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int* S_out) {
   if (S_out) *S_out = S;
   if (a.out_capacity && (size_t)S * a.split_stride > a.out_capacity) return cudaErrorInvalidValue;
   switch (bt) {
-    case 32: return launch_bt<32, 5>(st, a, tw, ta, S);
-    case 64: return launch_bt<64, 4>(st, a, tw, ta, S);
-    default: return launch_bt<128, 3>(st, a, tw, ta, S);
+    case 32: return launch_bt<32, 10>(st, a, tw, ta, S);
+    case 64: return launch_bt<64, 8>(st, a, tw, ta, S);
+    case 128: return launch_bt<128, 6>(st, a, tw, ta, S);
+    default: return launch_bt<256, 4>(st, a, tw, ta, S);
   }
 }
 

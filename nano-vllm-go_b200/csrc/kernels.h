@@ -149,7 +149,6 @@ int tc5_splits(int M, int N, int K, int sm_count);
 // *S_out = slices actually written (<= a.S)
 cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int* S_out);
 int tc5_box_rows_act(int M);  // token-tile rows (UMMA N) the kernel uses for M tokens
-int tc5_box_rows_w(int N);    // ... and for the weight map
 
 // ---------------------------------------------------------------- attention.cu
 struct AttnArgs {

@@ -16,6 +16,8 @@ constexpr int MOE_MAX_E = 256;
 __global__ void __launch_bounds__(128)
 moe_router_kernel(const float* __restrict__ x, const float* __restrict__ R, int H, int E, int k,
                   int* __restrict__ topk_idx, float* __restrict__ topk_w) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float probs[MOE_MAX_E];
   const int t = blockIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -90,7 +92,7 @@ cudaError_t launch_moe_router(cudaStream_t st, const float* x, const float* R, i
                               int k, int* topk_idx, float* topk_w) {
   if (T <= 0) return cudaSuccess;
   if (E > MOE_MAX_E || k > 32 || k > E || (H % 8) != 0) return cudaErrorInvalidValue;
-  moe_router_kernel<<<T, 128, 0, st>>>(x, R, H, E, k, topk_idx, topk_w);
+  (void)launch_k(moe_router_kernel, dim3(T), dim3(128), 0, st, x, R, H, E, k, topk_idx, topk_w);
   return cudaGetLastError();
 }
 
@@ -100,6 +102,8 @@ cudaError_t launch_moe_router(cudaStream_t st, const float* x, const float* R, i
 __global__ void __launch_bounds__(1024)
 moe_sort_kernel(const int* __restrict__ topk_idx, int n_pairs, int k, int E, MoeSortBufs b,
                 int max_tiles) {
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ int cnt[MOE_MAX_E];
   __shared__ int off[MOE_MAX_E + 1];
   for (int e = threadIdx.x; e < E; e += blockDim.x) cnt[e] = 0;
@@ -140,7 +144,7 @@ cudaError_t launch_moe_sort(cudaStream_t st, const int* topk_idx, int T, int k, 
                             const MoeSortBufs& b, int max_tiles) {
   if (T <= 0) return cudaSuccess;
   if (E > MOE_MAX_E) return cudaErrorInvalidValue;
-  moe_sort_kernel<<<1, 1024, 0, st>>>(topk_idx, T * k, k, E, b, max_tiles);
+  (void)launch_k(moe_sort_kernel, dim3(1), dim3(1024), 0, st, topk_idx, T * k, k, E, b, max_tiles);
   return cudaGetLastError();
 }
 
@@ -148,6 +152,8 @@ cudaError_t launch_moe_sort(cudaStream_t st, const int* topk_idx, int T, int k, 
 template <typename OT>
 __global__ void moe_glu_kernel(size_t nvec, int I, const float* __restrict__ h,
                                OT* __restrict__ g) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int vpr = I / 8;
   for (size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec;
        v += (size_t)gridDim.x * blockDim.x) {
@@ -171,9 +177,9 @@ cudaError_t launch_moe_glu(cudaStream_t st, int odt, int rows, int I, const floa
   size_t nvec = (size_t)rows * (I / 8);
   int blocks = (int)min((size_t)148 * 16, (nvec + 255) / 256);
   if (odt == DT_F32)
-    moe_glu_kernel<float><<<blocks, 256, 0, st>>>(nvec, I, h, (float*)g);
+    (void)launch_k(moe_glu_kernel<float>, dim3(blocks), dim3(256), 0, st, nvec, I, h, (float*)g);
   else
-    moe_glu_kernel<bf16><<<blocks, 256, 0, st>>>(nvec, I, h, (bf16*)g);
+    (void)launch_k(moe_glu_kernel<bf16>, dim3(blocks), dim3(256), 0, st, nvec, I, h, (bf16*)g);
   return cudaGetLastError();
 }
 
@@ -181,6 +187,8 @@ cudaError_t launch_moe_glu(cudaStream_t st, int odt, int rows, int I, const floa
 __global__ void moe_combine_kernel(int k, int H, const float* __restrict__ Y,
                                    const int* __restrict__ pair_row,
                                    const float* __restrict__ topk_w, float* __restrict__ y) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int t = blockIdx.x;
   for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
     float acc[8];
@@ -202,7 +210,7 @@ cudaError_t launch_moe_combine(cudaStream_t st, int T, int k, int H, const float
                                const int* pair_row, const float* topk_w, float* y) {
   if (T <= 0) return cudaSuccess;
   int threads = min(256, max(32, ((H / 8 + 31) / 32) * 32));
-  moe_combine_kernel<<<T, threads, 0, st>>>(k, H, Y, pair_row, topk_w, y);
+  (void)launch_k(moe_combine_kernel, dim3(T), dim3(threads), 0, st, k, H, Y, pair_row, topk_w, y);
   return cudaGetLastError();
 }
 

@@ -5,6 +5,7 @@
 // Replaces, behind the same boundary, what NewTensorModelRunner + TensorModelRunner.Run do
 // in the reference (nanovllm/tensor_model_runner.go:21-97).
 #include <math.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include "common.cuh"
@@ -121,6 +122,7 @@ int nvllm_create(const nvllm_config* c, const uint8_t* tp_id, nvllm_handle** out
                    "device %d is sm_%d%d; this library contains sm_100a code only", c->device,
                    prop.major, prop.minor);
 
+  if (const char* env = getenv("NVLLM_PDL")) set_pdl_enabled(atoi(env) != 0);  // debugging aid
   nvllm_handle* h = new nvllm_handle();
   h->cfg = *c;
   h->cfg.num_kv_heads = nkv;
