@@ -250,6 +250,14 @@ typedef struct nvllm_profile_entry {
 int nvllm_set_profile(nvllm_handle* h, int enabled);
 int nvllm_get_profile(nvllm_handle* h, nvllm_profile_entry* out);
 
+/* Diagnostics: device timeline of the instrumented kernels (GEMM, norm, RoPE+KV, decode
+ * attention).  nvllm_trace_begin arms a buffer of `capacity` records; every CTA of those
+ * kernels then appends {launch seq, kernel id, cta, sm, t_entry, t_after_dependency_wait,
+ * t_exit, extra} (8 x uint64, ns of %globaltimer).  nvllm_trace_end synchronises, disarms and
+ * copies up to max_records out.  Process-global; not for production runs. */
+int nvllm_trace_begin(nvllm_handle* h, int capacity);
+int nvllm_trace_end(nvllm_handle* h, uint64_t* out, int max_records, int* n_records);
+
 /* Wait for the resident steps issued so far; optionally read back the last sampled tokens
  * (n <= n_seqs of the last nvllm_run) and the device time of the last step. */
 int nvllm_sync(nvllm_handle* h, int32_t* out_tokens, int n, float* last_step_ms);

@@ -14,6 +14,8 @@
 //    GC query heads sharing a kv head, KV split).  HBM-bound: each K/V row is
 //    read once with 16-byte loads by hd/8 lanes; online softmax in registers;
 //    split partials merged by attn_combine_kernel.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -384,6 +386,12 @@ static cudaError_t decode_dispatch(cudaStream_t st, const AttnArgs& a) {
 
 cudaError_t launch_attn_decode(cudaStream_t st, const AttnArgs& a) {
   if (a.n_seqs <= 0) return cudaSuccess;
+  static const bool use_sk = [] {
+    const char* e = getenv("NVLLM_ATTN_SK");
+    return e ? atoi(e) != 0 : false;
+  }();
+  if (attn_mma_supported(a.qdt, a.kvdt, a.hd) && a.tickets && use_sk)
+    return launch_attn_decode_sk(st, a, a.tickets, a.sm_count, a.total_tiles);
   if (attn_mma_supported(a.qdt, a.kvdt, a.hd)) {
     cudaError_t e = launch_attn_decode_mma(st, a);
     if (e != cudaSuccess || a.n_splits == 1) return e;

@@ -81,6 +81,16 @@ __device__ __forceinline__ void store8(bf16* p, const float (&v)[8]) {
   *reinterpret_cast<uint4*>(p) = r;
 }
 
+// ---- activations (shared by act_kernel and the GEMM's fused epilogue) ---------
+__device__ __forceinline__ float gelu_tanh(float x) {  // tensor.go:181-190
+  float x3 = x * x * x;
+  float inner = 0.7978845608028654f * (x + 0.044715f * x3);
+  return 0.5f * x * (1.0f + tanhf(inner));
+}
+__device__ __forceinline__ float silu(float x) {  // mamba2.go:360-367
+  return x / (1.0f + expf(-x));
+}
+
 // ---- reductions -------------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
@@ -128,9 +138,18 @@ __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;"
 // pdl_wait() before the first dependent global access.
 bool pdl_enabled();
 void set_pdl_enabled(bool on);
+bool carveout_known(const void* fn);  // true once (fn, current device) has been configured
 template <typename... KArgs, typename... Args>
 static inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
                                    cudaStream_t st, Args&&... args) {
+  // Every kernel of the chain asks for the same (maximum) shared-memory carve-out: an SM only
+  // changes its L1/shared split when idle, so a kernel with a different preference could not
+  // become co-resident with its predecessor and the PDL overlap would be lost.
+  if (!carveout_known((const void*)kernel)) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout,
+                         cudaSharedmemCarveoutMaxShared);
+    (void)cudaGetLastError();
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = block;
@@ -142,6 +161,33 @@ static inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 blo
   cfg.attrs = attr;
   cfg.numAttrs = pdl_enabled() ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...);
+}
+
+// ---- device timeline trace (diagnostics; nvllm_trace_begin / nvllm_trace_end) -----------
+// Record = 8 x u64: launch seq, kernel id, CTA, SM, t_entry, t_after_wait, t_exit, extra
+// (ns of %globaltimer).  buf[0] = records written, buf[1] = capacity; records start at buf+8.
+struct Trace {
+  unsigned long long* buf;
+  int seq, kid;
+};
+Trace next_trace(int kid);  // {nullptr} unless tracing is on (host side, gemm_tcgen05.cu)
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void trace_rec(const Trace& t, unsigned long long t0,
+                                          unsigned long long t1, unsigned long long extra) {
+  if (!t.buf) return;
+  const unsigned long long t2 = gtime();
+  const unsigned long long slot = atomicAdd(t.buf, 1ull);
+  if (slot >= t.buf[1]) return;
+  unsigned sm;
+  asm volatile("mov.u32 %0, %%smid;" : "=r"(sm));
+  unsigned long long* r = t.buf + 8 + slot * 8;
+  r[0] = t.seq; r[1] = t.kid;
+  r[2] = blockIdx.x + (unsigned long long)gridDim.x * (blockIdx.y + (unsigned long long)gridDim.y * blockIdx.z);
+  r[3] = sm; r[4] = t0; r[5] = t1; r[6] = t2; r[7] = extra;
 }
 
 __host__ __device__ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

@@ -15,8 +15,8 @@ template <typename WT>
 __global__ void embed_kernel(const int* __restrict__ tokens, const int* __restrict__ positions,
                              const WT* __restrict__ wte, const WT* __restrict__ wpe, int max_pos,
                              float mult, float* __restrict__ x, int H) {
+  pdl_wait();  // step prologue: later kernels may read the step state before their own wait
   pdl_launch_dependents();
-  pdl_wait();
   const int t = blockIdx.x;
   const int tok = tokens[t];
   const int pos = positions[t];
@@ -59,34 +59,81 @@ cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int*
 // residual combine of generic_model.go:320-326 / :359-365 / :405-416:
 //   x <- x + m1 * (sum_s p1[s] + bias1) + m2 * (sum_s p2[s] + bias2);  y = norm(x)
 // The updated row is staged in shared memory so x is read once and written once.
+// sum of S split-K slices of 8 consecutive floats, slices `stride` apart; the loads of four
+// slices are issued together (one L2 round trip per group instead of one per slice)
+__device__ __forceinline__ void sum_partials8(const float* __restrict__ p, int S, size_t stride,
+                                              float (&acc)[8]) {
+#pragma unroll
+  for (int j = 0; j < 8; j++) acc[j] = 0.f;
+  int s = 0;
+  for (; s + 8 <= S; s += 8) {
+    float a[8][8];
+#pragma unroll
+    for (int q = 0; q < 8; q++) load8(p + (size_t)(s + q) * stride, a[q]);
+#pragma unroll
+    for (int q = 0; q < 8; q++)
+#pragma unroll
+      for (int j = 0; j < 8; j++) acc[j] += a[q][j];
+  }
+  for (; s + 4 <= S; s += 4) {
+    float a[8], b[8], c[8], d[8];
+    load8(p + (size_t)s * stride, a);
+    load8(p + (size_t)(s + 1) * stride, b);
+    load8(p + (size_t)(s + 2) * stride, c);
+    load8(p + (size_t)(s + 3) * stride, d);
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[j] = (((acc[j] + a[j]) + b[j]) + c[j]) + d[j];
+  }
+  for (; s < S; s++) {
+    float a[8];
+    load8(p + (size_t)s * stride, a);
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[j] += a[j];
+  }
+}
+
 template <typename YT>
-__global__ void norm_kernel(NormArgs a) {
+__global__ void norm_kernel(NormArgs a, Trace tr) {
+  const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
   pdl_launch_dependents();
-  pdl_wait();
   extern __shared__ float row[];
   __shared__ float red[32];
   const int H = a.H;
+  // norm weights / biases are immutable: fetch the first vector's worth before the
+  // dependency resolves (they come from HBM on first touch)
+  const int i0 = threadIdx.x * 8;
+  float w0[8], b0[8], bias1_0[8], bias2_0[8];
+#pragma unroll
+  for (int j = 0; j < 8; j++) w0[j] = b0[j] = bias1_0[j] = bias2_0[j] = 0.f;
+  if (i0 < H) {
+    if (a.y) {
+      load8(a.w + i0, w0);
+      if (a.b) load8(a.b + i0, b0);
+    }
+    if (a.p1 && a.bias1) load8(a.bias1 + i0, bias1_0);
+    if (a.p2 && a.bias2) load8(a.bias2 + i0, bias2_0);
+  }
+  pdl_wait();
+  const unsigned long long t_wait = tr.buf ? gtime() : 0ull;
   const int orow = blockIdx.x;
   const int r = a.row_idx ? a.row_idx[orow] : orow;
   float* xr = a.x + (size_t)r * H;
   const bool upd = (a.p1 != nullptr) || (a.p2 != nullptr);
   float lsum = 0.f;
-  for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
+  for (int i = i0; i < H; i += blockDim.x * 8) {
     float v[8];
     load8(xr + i, v);
     if (a.p1) {
       float acc[8];
-#pragma unroll
-      for (int j = 0; j < 8; j++) acc[j] = 0.f;
-      for (int s = 0; s < a.S1; s++) {
-        float p[8];
-        load8(a.p1 + (size_t)s * a.stride1 + (size_t)r * H + i, p);
-#pragma unroll
-        for (int j = 0; j < 8; j++) acc[j] += p[j];
-      }
+      sum_partials8(a.p1 + (size_t)r * H + i, a.S1, a.stride1, acc);
       if (a.bias1) {
         float p[8];
-        load8(a.bias1 + i, p);
+        if (i == i0) {
+#pragma unroll
+          for (int j = 0; j < 8; j++) p[j] = bias1_0[j];
+        } else {
+          load8(a.bias1 + i, p);
+        }
 #pragma unroll
         for (int j = 0; j < 8; j++) acc[j] += p[j];
       }
@@ -95,17 +142,15 @@ __global__ void norm_kernel(NormArgs a) {
     }
     if (a.p2) {
       float acc[8];
-#pragma unroll
-      for (int j = 0; j < 8; j++) acc[j] = 0.f;
-      for (int s = 0; s < a.S2; s++) {
-        float p[8];
-        load8(a.p2 + (size_t)s * a.stride2 + (size_t)r * H + i, p);
-#pragma unroll
-        for (int j = 0; j < 8; j++) acc[j] += p[j];
-      }
+      sum_partials8(a.p2 + (size_t)r * H + i, a.S2, a.stride2, acc);
       if (a.bias2) {
         float p[8];
-        load8(a.bias2 + i, p);
+        if (i == i0) {
+#pragma unroll
+          for (int j = 0; j < 8; j++) p[j] = bias2_0[j];
+        } else {
+          load8(a.bias2 + i, p);
+        }
 #pragma unroll
         for (int j = 0; j < 8; j++) acc[j] += p[j];
       }
@@ -123,12 +168,14 @@ __global__ void norm_kernel(NormArgs a) {
     }
   }
   if (a.y == nullptr) return;
+  const unsigned long long t_loads = tr.buf ? gtime() : 0ull;
   float tot = block_sum(lsum, red);
+  const unsigned long long t_red = tr.buf ? gtime() : 0ull;
   float mean = 0.f, inv;
   if (a.b) {
     mean = tot / (float)H;
     float lv = 0.f;
-    for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
+    for (int i = i0; i < H; i += blockDim.x * 8) {
 #pragma unroll
       for (int j = 0; j < 8; j++) {
         float d = row[i + j] - mean;
@@ -141,12 +188,19 @@ __global__ void norm_kernel(NormArgs a) {
     inv = 1.0f / sqrtf(tot / (float)H + a.eps);
   }
   YT* yr = (YT*)a.y + (size_t)orow * H;
-  for (int i = threadIdx.x * 8; i < H; i += blockDim.x * 8) {
-    float w[8], o[8];
-    load8(a.w + i, w);
+  for (int i = i0; i < H; i += blockDim.x * 8) {
+    float w[8], bb[8], o[8];
+    if (i == i0) {
+#pragma unroll
+      for (int j = 0; j < 8; j++) {
+        w[j] = w0[j];
+        bb[j] = b0[j];
+      }
+    } else {
+      load8(a.w + i, w);
+      if (a.b) load8(a.b + i, bb);
+    }
     if (a.b) {
-      float bb[8];
-      load8(a.b + i, bb);
 #pragma unroll
       for (int j = 0; j < 8; j++) o[j] = (row[i + j] - mean) * inv * w[j] + bb[j];
     } else {
@@ -156,6 +210,8 @@ __global__ void norm_kernel(NormArgs a) {
     store8(yr + i, o);
     if (a.y_f32) store8(a.y_f32 + (size_t)orow * H + i, o);
   }
+  if (threadIdx.x == 0 && tr.buf)
+    trace_rec(tr, t_entry, t_wait, ((t_loads - t_wait) << 32) | (t_red - t_wait));
 }
 
 cudaError_t launch_norm(cudaStream_t st, const NormArgs& a) {
@@ -163,22 +219,13 @@ cudaError_t launch_norm(cudaStream_t st, const NormArgs& a) {
   int threads = min(512, max(64, ((a.H / 8 + 31) / 32) * 32));
   size_t smem = (size_t)a.H * sizeof(float);
   if (a.ydt == DT_F32)
-    (void)launch_k(norm_kernel<float>, dim3(a.n_rows), dim3(threads), smem, st, a);
+    (void)launch_k(norm_kernel<float>, dim3(a.n_rows), dim3(threads), smem, st, a, next_trace(2));
   else
-    (void)launch_k(norm_kernel<bf16>, dim3(a.n_rows), dim3(threads), smem, st, a);
+    (void)launch_k(norm_kernel<bf16>, dim3(a.n_rows), dim3(threads), smem, st, a, next_trace(2));
   return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------- activations
-__device__ __forceinline__ float gelu_tanh(float x) {  // tensor.go:181-190
-  float x3 = x * x * x;
-  float inner = 0.7978845608028654f * (x + 0.044715f * x3);
-  return 0.5f * x * (1.0f + tanhf(inner));
-}
-__device__ __forceinline__ float silu(float x) {  // mamba2.go:360-367
-  return x / (1.0f + expf(-x));
-}
-
 template <typename OT>
 __global__ void act_kernel(int T, int F, const float* __restrict__ h, int S, size_t stride,
                            const float* __restrict__ bias, int swiglu, OT* __restrict__ out) {
@@ -193,24 +240,33 @@ __global__ void act_kernel(int T, int F, const float* __restrict__ h, int S, siz
     float g[8], o[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) g[i] = 0.f;
-    for (int s = 0; s < S; s++) {
-      float p[8];
-      load8(h + (size_t)s * stride + (size_t)t * ld + j, p);
-#pragma unroll
-      for (int i = 0; i < 8; i++) g[i] += p[i];
-    }
-    if (swiglu) {
-      float u[8];
-#pragma unroll
-      for (int i = 0; i < 8; i++) u[i] = 0.f;
+    if (!swiglu)
       for (int s = 0; s < S; s++) {
         float p[8];
-        load8(h + (size_t)s * stride + (size_t)t * ld + F + j, p);
+        load8(h + (size_t)s * stride + (size_t)t * ld + j, p);
 #pragma unroll
-        for (int i = 0; i < 8; i++) u[i] += p[i];
+        for (int i = 0; i < 8; i++) g[i] += p[i];
+      }
+    if (swiglu) {
+      // W1 rows are stored interleaved (weights.cu): column 2j = gate j, 2j + 1 = up j
+      float a[8], b[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) a[i] = b[i] = 0.f;
+      for (int s = 0; s < S; s++) {
+        float p[8];
+        const float* base = h + (size_t)s * stride + (size_t)t * ld + 2 * j;
+        load8(base, p);
+#pragma unroll
+        for (int i = 0; i < 8; i++) a[i] += p[i];
+        load8(base + 8, p);
+#pragma unroll
+        for (int i = 0; i < 8; i++) b[i] += p[i];
       }
 #pragma unroll
-      for (int i = 0; i < 8; i++) o[i] = silu(g[i]) * u[i];
+      for (int i = 0; i < 4; i++) {
+        o[i] = silu(a[2 * i]) * a[2 * i + 1];
+        o[4 + i] = silu(b[2 * i]) * b[2 * i + 1];
+      }
     } else {
       if (bias) {
         float p[8];
@@ -247,34 +303,39 @@ __global__ void rope_kv_kernel(int nh, int nkv, int hd, const float* __restrict_
                                const int* __restrict__ positions, const int* __restrict__ slots,
                                const float* __restrict__ cosT, const float* __restrict__ sinT,
                                QT* __restrict__ q_out, KT* __restrict__ kpool,
-                               KT* __restrict__ vpool) {
+                               KT* __restrict__ vpool, Trace tr) {
+  const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
   pdl_launch_dependents();
-  pdl_wait();
   const int t = blockIdx.x;
   const int half = hd / 2;
   const int vph = half / 8;  // vectors per half head
   const int ncols = (nh + 2 * nkv) * hd;
+  // positions / slots were written by the step's first kernel (which triggers its dependents
+  // only after its own wait) or by the host copy: stable here.  Fetch them and the first
+  // item's RoPE factors before the dependency on the QKV GEMM resolves.
   const int pos = positions[t];
   const int slot = slots[t];
   const int blk = slot / KV_BLOCK, off = slot % KV_BLOCK;
   const int items = (nh + 2 * nkv) * vph;
-  for (int it = threadIdx.x; it < items; it += blockDim.x) {
+  float c0v[8], s0v[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) c0v[i] = s0v[i] = 0.f;
+  const int it_first = blockIdx.y * blockDim.x + threadIdx.x;
+  if (cosT != nullptr && it_first < items) {
+    const int j = (it_first % vph) * 8;
+    load8(cosT + (size_t)pos * half + j, c0v);
+    load8(sinT + (size_t)pos * half + j, s0v);
+  }
+  pdl_wait();
+  const unsigned long long t_wait = tr.buf ? gtime() : 0ull;
+  for (int it = blockIdx.y * blockDim.x + threadIdx.x; it < items; it += gridDim.y * blockDim.x) {
     const int head = it / vph;
     const int j = (it % vph) * 8;
     const int c0 = head * hd + j;
     float a[8], b[8];
-#pragma unroll
-    for (int i = 0; i < 8; i++) a[i] = b[i] = 0.f;
-    for (int s = 0; s < S; s++) {
-      float p[8];
-      const float* base = qkv + (size_t)s * stride + (size_t)t * ncols;
-      load8(base + c0, p);
-#pragma unroll
-      for (int i = 0; i < 8; i++) a[i] += p[i];
-      load8(base + c0 + half, p);
-#pragma unroll
-      for (int i = 0; i < 8; i++) b[i] += p[i];
-    }
+    const float* base = qkv + (size_t)t * ncols + c0;
+    sum_partials8(base, S, stride, a);
+    sum_partials8(base + half, S, stride, b);
     if (bias) {
       float p[8];
       load8(bias + c0, p);
@@ -287,8 +348,16 @@ __global__ void rope_kv_kernel(int nh, int nkv, int hd, const float* __restrict_
     const bool is_v = head >= nh + nkv;
     if (cosT != nullptr && !is_v) {
       float c[8], sn[8];
-      load8(cosT + (size_t)pos * half + j, c);
-      load8(sinT + (size_t)pos * half + j, sn);
+      if (it == it_first) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+          c[i] = c0v[i];
+          sn[i] = s0v[i];
+        }
+      } else {
+        load8(cosT + (size_t)pos * half + j, c);
+        load8(sinT + (size_t)pos * half + j, sn);
+      }
 #pragma unroll
       for (int i = 0; i < 8; i++) {
         float ra = a[i] * c[i] - b[i] * sn[i];
@@ -309,6 +378,7 @@ __global__ void rope_kv_kernel(int nh, int nkv, int hd, const float* __restrict_
       store8(dst + half, b);
     }
   }
+  if (threadIdx.x == 0) trace_rec(tr, t_entry, t_wait, 0);
 }
 
 cudaError_t launch_rope_kv(cudaStream_t st, int qdt, int kvdt, int T, int nh, int nkv, int hd,
@@ -317,11 +387,16 @@ cudaError_t launch_rope_kv(cudaStream_t st, int qdt, int kvdt, int T, int nh, in
                            const float* sinT, void* q_out, void* kpool, void* vpool) {
   if (T <= 0) return cudaSuccess;
   int items = (nh + 2 * nkv) * (hd / 16);
-  int threads = min(256, max(32, ((items + 31) / 32) * 32));
+  // few tokens (decode): split each token's heads over several CTAs — a CTA pulls S partial
+  // slices of its columns out of L2 and one SM's intake would pace the kernel
+  int groups = 1;
+  while (T * groups < 256 && items / (groups * 2) >= 32) groups *= 2;
+  int per = (items + groups - 1) / groups;
+  int threads = min(256, max(32, ((per + 31) / 32) * 32));
 #define RK(QT, KT)                                                                              \
-  (void)launch_k(rope_kv_kernel<QT, KT>, dim3(T), dim3(threads), 0, st, nh, nkv, hd, qkv, S, stride, bias, positions,   \
+  (void)launch_k(rope_kv_kernel<QT, KT>, dim3(T, groups), dim3(threads), 0, st, nh, nkv, hd, qkv, S, stride, bias, positions,   \
                                                 slots, cosT, sinT, (QT*)q_out, (KT*)kpool,      \
-                                                (KT*)vpool)
+                                                (KT*)vpool, next_trace(3))
   if (qdt == DT_F32 && kvdt == DT_F32) RK(float, float);
   else if (qdt == DT_F32 && kvdt == DT_BF16) RK(float, bf16);
   else if (qdt == DT_BF16 && kvdt == DT_BF16) RK(bf16, bf16);
@@ -341,9 +416,22 @@ __device__ __forceinline__ ArgMax argmax_merge(ArgMax a, ArgMax b) {
   return a;
 }
 
+// order-preserving float -> uint32 key; the low word ~index makes atomicMax keep the LOWEST
+// index among equal values (first-max rule of cmd/ask/main.go:389-402)
+__device__ __forceinline__ unsigned long long argmax_key(float v, int i) {
+  uint32_t b = __float_as_uint(v);
+  b = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+  return ((unsigned long long)b << 32) | (uint32_t)(~(uint32_t)i);
+}
+
+// grid (n_seqs, chunks).  Greedy rows: every CTA reduces its slice of the vocabulary and
+// merges with one 64-bit atomicMax; the last CTA of the row (atomic ticket) publishes the
+// token and re-arms the scratch, so the kernel needs no separate init.  Temperature rows: CTA
+// chunk 0 runs the whole softmax / inverse-CDF draw.
 __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
                               const float* __restrict__ temperature,
-                              const float* __restrict__ uniforms, int* __restrict__ out_tokens) {
+                              const float* __restrict__ uniforms, int* __restrict__ out_tokens,
+                              unsigned long long* __restrict__ amax, int* __restrict__ ticket) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float red[32];
@@ -355,13 +443,25 @@ __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
   const float temp = temperature ? temperature[s] : 0.f;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
   if (!(temp > 0.f)) {
-    // cmd/ask/main.go:389-402: first index of the maximum
+    const int chunks = gridDim.y;
+    const int per = ((V + chunks - 1) / chunks + 3) & ~3;
+    const int lo = blockIdx.y * per, hi = min(V, lo + per);
     ArgMax am = {-INFINITY, 0x7fffffff};
-    for (int i = threadIdx.x; i < V; i += blockDim.x) {
-      float v = l[i];
-      if (v > am.v) {
-        am.v = v;
-        am.i = i;
+    // the forward pass has ldl % 8 == 0 and `per` % 4 == 0 (16-byte aligned slices); the
+    // single-operator entry point may pass any row stride
+    const bool vec = ((reinterpret_cast<uintptr_t>(l + lo)) & 15) == 0;
+    for (int i = lo + threadIdx.x * 4; i < hi; i += blockDim.x * 4) {
+      if (vec && i + 3 < hi) {
+        const float4 v = *reinterpret_cast<const float4*>(l + i);
+        if (v.x > am.v) { am.v = v.x; am.i = i; }
+        if (v.y > am.v) { am.v = v.y; am.i = i + 1; }
+        if (v.z > am.v) { am.v = v.z; am.i = i + 2; }
+        if (v.w > am.v) { am.v = v.w; am.i = i + 3; }
+      } else {
+        for (int j = i; j < min(hi, i + 4); j++) {
+          const float v = l[j];
+          if (v > am.v) { am.v = v; am.i = j; }
+        }
       }
     }
 #pragma unroll
@@ -378,10 +478,24 @@ __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
         ArgMax ot = {__shfl_xor_sync(0xffffffffu, r.v, o), __shfl_xor_sync(0xffffffffu, r.i, o)};
         r = argmax_merge(r, ot);
       }
-      if (lane == 0) out_tokens[s] = (r.i == 0x7fffffff) ? 0 : r.i;
+      if (lane == 0) {
+        if (chunks == 1) {
+          out_tokens[s] = (r.i == 0x7fffffff) ? 0 : r.i;
+        } else {
+          if (r.i != 0x7fffffff) atomicMax(amax + s, argmax_key(r.v, r.i));
+          __threadfence();
+          if (atomicAdd(ticket + s, 1) == chunks - 1) {
+            __threadfence();
+            const unsigned long long k = atomicExch(amax + s, 0ull);
+            out_tokens[s] = k ? (int)(~(uint32_t)(k & 0xffffffffu)) : 0;
+            ticket[s] = 0;
+          }
+        }
+      }
     }
     return;
   }
+  if (blockIdx.y != 0) return;
   // temperature sampling: sampling.go:70-74 (divide), :105-128 (softmax), :196-217 (inverse CDF).
   // Each thread owns a contiguous chunk so that prefix sums follow index order.
   const int chunk = (V + blockDim.x - 1) / blockDim.x;
@@ -425,17 +539,21 @@ __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
 }
 
 cudaError_t launch_sample(cudaStream_t st, const float* logits, int ldl, int V, int n,
-                          const float* temperature, const float* uniforms, int* out_tokens) {
+                          const float* temperature, const float* uniforms, int* out_tokens,
+                          unsigned long long* amax, int* ticket) {
   if (n <= 0) return cudaSuccess;
-  (void)launch_k(sample_kernel, dim3(n), dim3(1024), 0, st, logits, ldl, V, temperature, uniforms, out_tokens);
+  // ~8K logits per CTA keeps >= 2 waves of CTAs in flight for a large vocabulary
+  const int chunks = (amax && ticket) ? max(1, min(64, V / 8192)) : 1;
+  (void)launch_k(sample_kernel, dim3(n, chunks), dim3(chunks > 1 ? 256 : 1024), 0, st, logits, ldl,
+                 V, temperature, uniforms, out_tokens, amax, ticket);
   return cudaGetLastError();
 }
 
 __global__ void advance_kernel(int n, const int* __restrict__ sampled, int* tokens, int* positions,
                                int* slots, int* seq_len, const int* __restrict__ block_tables,
                                int max_blocks, int max_pos) {
+  pdl_wait();  // step prologue: later kernels may read the step state before their own wait
   pdl_launch_dependents();
-  pdl_wait();
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
   tokens[i] = sampled[i];
@@ -466,7 +584,7 @@ template <> __device__ __forceinline__ float src_to_f32<__half>(__half v) { retu
 // dst[n, k] = src[k, n]; 32x32 tiles through shared memory so both sides are coalesced
 template <typename ST, typename DT>
 __global__ void transpose_convert_kernel(const ST* __restrict__ src, int K, int N,
-                                         DT* __restrict__ dst, int ld_dst) {
+                                         DT* __restrict__ dst, int ld_dst, int glu_F) {
   __shared__ float tile[32][33];
   const int n0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
@@ -476,15 +594,18 @@ __global__ void transpose_convert_kernel(const ST* __restrict__ src, int K, int 
   __syncthreads();
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
     int n = n0 + r, k = k0 + threadIdx.x;
-    if (n < N && k < K) dst[(size_t)n * ld_dst + k] = from_f32<DT>(tile[threadIdx.x][r]);
+    // glu_F > 0: [gate | up] columns become interleaved rows (gate j -> 2j, up j -> 2j + 1) so
+    // that a GEMM tile holds matching gate / up rows for the fused SwiGLU epilogue
+    const int nd = (glu_F > 0) ? (n < glu_F ? 2 * n : 2 * (n - glu_F) + 1) : n;
+    if (n < N && k < K) dst[(size_t)nd * ld_dst + k] = from_f32<DT>(tile[threadIdx.x][r]);
   }
 }
 
 cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* src, int K, int N,
-                                     int ddt, void* dst, int ld_dst) {
+                                     int ddt, void* dst, int ld_dst, int glu_F) {
   dim3 grid((N + 31) / 32, (K + 31) / 32), block(32, 8);
 #define TC(ST, DT) \
-  transpose_convert_kernel<ST, DT><<<grid, block, 0, st>>>((const ST*)src, K, N, (DT*)dst, ld_dst)
+  transpose_convert_kernel<ST, DT><<<grid, block, 0, st>>>((const ST*)src, K, N, (DT*)dst, ld_dst, glu_F)
   if (ddt == DT_F32) {
     if (sdt_api == 0) TC(float, float);
     else if (sdt_api == 1) TC(bf16, float);
@@ -562,8 +683,8 @@ __global__ void make_decode_state_kernel(int n, int mb, const int* __restrict__ 
                                          const int* __restrict__ src_uni, int* tokens,
                                          int* positions, int* slots, int* cu_q, int* seq_start,
                                          int* seq_len, int* last_row, int* bt, int* temp, int* uni) {
+  pdl_wait();  // step prologue: later kernels may read the step state before their own wait
   pdl_launch_dependents();
-  pdl_wait();
   const int i = blockIdx.x;
   for (int b = threadIdx.x; b < mb; b += blockDim.x) bt[(size_t)i * mb + b] = src_bt[(size_t)i * mb + b];
   if (threadIdx.x == 0) {

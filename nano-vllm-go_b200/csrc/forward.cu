@@ -6,6 +6,7 @@
 // -> LM head on those rows only -> on-device argmax / temperature sampling.
 // Residual adds are folded into the following norm kernel; GEMMs emit fp32 split-K partials
 // that the consumer kernel sums.
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -19,7 +20,7 @@ namespace nvllm {
 void free_workspace(nvllm_handle* h) {
   Workspace& w = h->ws;
   void* ptrs[] = {w.x, w.xn, w.xn_f32, w.ws_a, w.ws_b, w.ws_c, w.q, w.attn_out, w.hbuf, w.xn_last,
-                  w.logits_p, w.logits, w.attn_ws, w.out_tokens, w.topk_idx, w.topk_w,
+                  w.logits_p, w.logits, w.attn_ws, w.attn_tickets, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
                   w.sort.counts, w.sort.offsets, w.sort.cursor, w.sort.sorted_pair, w.sort.pair_row,
                   w.sort.a_rows, w.sort.tile_expert, w.sort.tile_row0, w.sort.tile_rows,
                   w.sort.n_tiles, w.moe_Y, w.moe_y};
@@ -75,9 +76,21 @@ int ensure_workspace(nvllm_handle* h, int T, int n) {
   w.logits_p_floats = (size_t)std::max(nc, 64) * h->ldl;
   WS(w.logits_p, w.logits_p_floats * 4);
   WS(w.logits, (size_t)nc * h->ldl * 4);
-  w.attn_ws_floats = (size_t)nc * h->nh * 32 * (h->hd + 2);
+  w.attn_ws_floats = std::max((size_t)nc * h->nh * 32 * (h->hd + 2),
+                              attn_decode_sk_ws_floats(h->hd, h->sm_count));
   WS(w.attn_ws, w.attn_ws_floats * 4);
+  {
+    const size_t nt = (size_t)nc * h->nkv * ((h->nh / h->nkv + 15) / 16);
+    WS(w.attn_tickets, nt * 4);
+    if (cudaMemsetAsync(w.attn_tickets, 0, nt * 4, h->stream) != cudaSuccess)
+      return set_err(h, NVLLM_ERR_CUDA, "memset(attention tickets) failed");
+  }
   WS(w.out_tokens, (size_t)nc * 4);
+  WS(w.amax, (size_t)nc * 8);
+  WS(w.amax_ticket, (size_t)nc * 4);
+  if (cudaMemsetAsync(w.amax, 0, (size_t)nc * 8, h->stream) != cudaSuccess ||
+      cudaMemsetAsync(w.amax_ticket, 0, (size_t)nc * 4, h->stream) != cudaSuccess)
+    return set_err(h, NVLLM_ERR_CUDA, "memset(argmax scratch) failed");
   if (h->moe) {
     const size_t P = (size_t)Tc * h->topk;
     w.max_tiles = (int)(P / 64 + h->E);
@@ -116,6 +129,7 @@ struct ProfScope {
   nvllm_handle* h;
   int idx = -1;
   ProfScope(nvllm_handle* hh, int cls, double bytes, double flops) : h(hh) {
+    h->cur_cls = cls;
     if (!h->profile) return;
     nvllm_handle::ProfRec r{cls, bytes, flops, prof_event(h), prof_event(h)};
     cudaEventRecord(r.e0, h->stream);
@@ -155,6 +169,7 @@ struct Pending {  // a GEMM result still to be added to the residual stream
 
 #define LAUNCH(h, expr)                                                                       \
   do {                                                                                        \
+    if (((h)->skip_mask >> (h)->cur_cls) & 1) break; /* NVLLM_SKIP timing ablation */         \
     cudaError_t _e = (expr);                                                                  \
     (h)->launches++;                                                                          \
     if (_e != cudaSuccess)                                                                    \
@@ -163,8 +178,13 @@ struct Pending {  // a GEMM result still to be added to the residual stream
   } while (0)
 
 // C = A @ W^T into fp32 split-K partials at `out`
+// epi != 0 asks for the FFN activation to be fused into the GEMM epilogue (bf16 hidden state
+// written to epi_out); granted only on the tcgen05 path when the GEMM needs no split-K, in
+// which case res->S comes back 0 (no partials to reduce).
 static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int M, int N, int K,
-                    float alpha, float* out, size_t cap, int ldo, Pending* res) {
+                    float alpha, float* out, size_t cap, int ldo, Pending* res, int epi = 0,
+                    void* epi_out = nullptr, int epi_ld = 0, const float* epi_bias = nullptr,
+                    const void* pf_ptr = nullptr, size_t pf_bytes = 0) {
   res->p = out;
   res->stride = (size_t)M * ldo;
   const double flops = 2.0 * M * N * K;
@@ -184,6 +204,20 @@ static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int 
     t.A = A; t.W = W; t.M = M; t.N = N; t.K = K; t.out = out; t.ldo = ldo;
     t.split_stride = res->stride; t.alpha = alpha; t.out_capacity = cap;
     t.S = tc5_splits(M, N, K, h->sm_count);
+    if (M <= 128) {  // weight-streaming regime: warm L2 with the next big matrix
+      t.pf_ptr = pf_ptr;
+      t.pf_bytes = pf_bytes;
+    }
+    const long tiles = (long)ceil_div(N, 128) * ceil_div(M, tc5_box_rows_act(M));
+    if (epi && (t.S == 1 || 2 * tiles >= h->sm_count)) {
+      t.S = 1;
+      t.epi = epi; t.epi_out = epi_out; t.epi_ld = epi_ld; t.epi_bias = epi_bias;
+      const double obytes = (double)M * epi_ld * 2;
+      ProfScope ps(h, NVLLM_K_GEMM_TC5, io + obytes, flops);
+      LAUNCH(h, launch_gemm_tc5(h->stream, t, nullptr));
+      res->S = 0;
+      return NVLLM_OK;
+    }
     while (t.S > 1 && (size_t)t.S * M * ldo > cap) t.S--;
     ProfScope ps(h, NVLLM_K_GEMM_TC5, io + 4.0 * t.S * M * N, flops);
     LAUNCH(h, launch_gemm_tc5(h->stream, t, &res->S));
@@ -257,8 +291,26 @@ int forward_step(nvllm_handle* h) {
   at.tile_seq = d + L.tile_seq; at.tile_q0 = d + L.tile_q0; at.n_qtiles = L.n_qtiles;
   at.seq_len = d + L.seq_len;
   at.ws = w.attn_ws;
-  if (!is_prefill)
-    at.n_splits = attn_decode_splits(h->adt, h->kvdt, n, h->nh, h->nkv, h->hd, L.max_len, h->sm_count);
+  if (!is_prefill) {
+    static const bool use_sk = [] {
+      const char* e = getenv("NVLLM_ATTN_SK");
+      return e ? atoi(e) != 0 : false;
+    }();
+    if (attn_mma_supported(h->adt, h->kvdt, h->hd) && use_sk) {
+      at.n_splits = 1;
+      at.tickets = w.attn_tickets;
+      at.pool_blocks = h->num_blocks;
+      at.sm_count = h->sm_count;
+      const int bn = attn_decode_mma_tile(h->hd);
+      // LOWER bound of the step's key tiles (sum over sequences of ceil(len / bn)): the grid
+      // never exceeds it, so every CTA of the stream-K partition owns at least one tile
+      at.total_tiles = std::max<long long>(n, (L.sum_len + bn - 1) / bn) * h->nkv *
+                       ((h->nh / h->nkv + 15) / 16);
+    } else {
+      at.n_splits = attn_decode_splits(h->adt, h->kvdt, n, h->nh, h->nkv, h->hd, L.max_len,
+                                       h->sm_count);
+    }
+  }
   const double qo_bytes = 2.0 * T * h->q_cols * asz;
   const double attn_flops = 4.0 * h->nh * h->hd * L.attn_pairs;
   const double attn_bytes = 2.0 * L.sum_len * h->nkv * h->hd * kvsz + qo_bytes;
@@ -353,9 +405,10 @@ int forward_step(nvllm_handle* h) {
     } else {
       Pending h1;
       if ((rc = run_gemm(h, w.xn, H, lw.w1, T, h->w1_cols, H, 1.f, w.ws_a, w.ws_a_floats,
-                         h->w1_cols, &h1)))
+                         h->w1_cols, &h1, h->swiglu ? TC5_EPI_SWIGLU : TC5_EPI_GELU, w.hbuf, h->F,
+                         lw.b1)))
         return rc;
-      {
+      if (h1.S > 0) {
         ProfScope ps(h, NVLLM_K_ACT, (double)T * h->w1_cols * 4 * h1.S + (double)T * h->F * asz, 0);
         LAUNCH(h, launch_act(st, h->adt, T, h->F, h1.p, h1.S, h1.stride, lw.b1, h->swiglu ? 1 : 0,
                              w.hbuf));
@@ -385,7 +438,8 @@ int forward_step(nvllm_handle* h) {
   const float* d_uni = reinterpret_cast<const float*>(d + L.uniforms);
   {
     ProfScope ps(h, NVLLM_K_SAMPLE, (double)n * h->V * 4, 0);
-    LAUNCH(h, launch_sample(st, logits, h->ldl, h->V, n, d_temp, d_uni, w.out_tokens));
+    LAUNCH(h, launch_sample(st, logits, h->ldl, h->V, n, d_temp, d_uni, w.out_tokens, w.amax,
+                            w.amax_ticket));
   }
   h->ws.logits_final = logits;
   return NVLLM_OK;

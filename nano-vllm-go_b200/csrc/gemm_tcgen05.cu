@@ -14,12 +14,14 @@
 //   * in the epilogue each warp owns 32 consecutive n for a given token, so every global
 //     store instruction writes 128 contiguous bytes of out[m][n..n+31].
 #include <cuda.h>
+#include <stdlib.h>
 
 #include <map>
 #include <mutex>
 #include <tuple>
 
 #include "common.cuh"
+#include "tma.cuh"
 #include "kernels.h"
 
 namespace nvllm {
@@ -29,50 +31,6 @@ constexpr int TC_BK = 64;   // k elements per stage = one 128-byte swizzle row o
 constexpr int TC_THREADS = 192;
 
 // ------------------------------------------------------------------ PTX wrappers
-__device__ __forceinline__ uint32_t smem_u32(const void* p) {
-  return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
-  uint32_t ok;
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-      "selp.u32 %0, 1, 0, p;\n\t}"
-      : "=r"(ok)
-      : "r"(bar), "r"(parity)
-      : "memory");
-  return ok != 0;
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  while (!mbar_try_wait(bar, parity)) {
-  }
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* map, uint32_t bar, int c0,
-                                            int c1) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes"
-      " [%0], [%1, {%3, %4}], [%2];"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const void* map, uint32_t bar,
-                                                 int c0, int c1, uint64_t policy) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
-      " [%0], [%1, {%3, %4}], [%2], %5;"
-      ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "l"(policy)
-      : "memory");
-}
 __device__ __forceinline__ void tc_fence_before() {
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
 }
@@ -135,21 +93,37 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
 struct Tc5Sched {
   int units, n_tiles, S, kbps, nkb_total;
 };
+// rot: CTAs working on the same k range start at different k-blocks (and wrap), so that at any
+// instant they pull DIFFERENT activation tiles out of L2 — otherwise every CTA of a skinny
+// GEMM requests the same 8 KB A tile at the same time and the few L2 slices holding it pace
+// the whole kernel (measured: ~390 ns per k-block with W already in shared memory).
 __device__ __forceinline__ void tc5_unit(const Tc5Sched& sc, int u, int BT, int& n0, int& m0,
-                                         int& kb0, int& nkb, int& split) {
+                                         int& kb0, int& nkb, int& split, int& rot) {
   split = u % sc.S;
   const int r = u / sc.S;
-  n0 = (r % sc.n_tiles) * TC_BN;
-  m0 = (r / sc.n_tiles) * BT;
+  const int nt = r % sc.n_tiles, mt = r / sc.n_tiles;
+  n0 = nt * TC_BN;
+  m0 = mt * BT;
   kb0 = split * sc.kbps;
   nkb = min(sc.kbps, sc.nkb_total - kb0);
+  rot = (nt + 5 * mt) % nkb;
+}
+__device__ __forceinline__ int tc5_kb(int kb0, int kb, int rot, int nkb) {
+  const int k = kb + rot;
+  return kb0 + (k >= nkb ? k - nkb : k);
 }
 
 template <int BT, int STAGES>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
                 int M, int N, Tc5Sched sc, float* __restrict__ out, int ldo, size_t split_stride,
-                float alpha, int w_reused) {
+                float alpha, int w_reused, int epi, bf16* __restrict__ epi_out, int epi_ld,
+                const float* __restrict__ epi_bias, int prefetch, const uint8_t* __restrict__ pf_ptr,
+                unsigned long long pf_bytes, Trace tr) {
+  const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
+  unsigned long long t_wait = 0;
+  __shared__ unsigned long long tr_mma, tr_epi0, tr_epi1, tr_x[6];
+  __shared__ __align__(16) uint8_t epi_stage[4][32 * 48];
   constexpr uint32_t W_BYTES = TC_BN * TC_BK * 2;
   constexpr uint32_t A_BYTES = BT * TC_BK * 2;
   constexpr uint32_t STAGE_BYTES = W_BYTES + A_BYTES;
@@ -191,119 +165,233 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   const uint32_t tmem_base = *tmem_slot_ptr;
   const int grid = gridDim.x;
 
+  // The producer and MMA warps run their loops with ALL 32 lanes (warp-uniform control flow)
+  // and elect one lane only around the issue instructions: TMA and tcgen05 instructions take
+  // uniform-register operands, and inside a divergent `if (lane == 0)` region the compiler
+  // wraps every one of them in an elect/branch loop plus R2UR moves (~120 cycles per MMA
+  // measured on B200 — enough to make a skinny GEMM issue-bound instead of HBM-bound).
   if (warp == 0) {
-    if (lane == 0) {
-      // weights read once per step must not displace activations in L2; weights re-read by
-      // other token tiles (prefill) stay
-      uint64_t pol_w, pol_a;
-      if (w_reused)
-        asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_w));
-      else
-        asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
-      asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_a));
-      int n0, m0, kb0, nkb, split;
-      // (1) weight tiles of the first STAGES k-blocks, before the dependency resolves
-      int pre = 0;
-      {
-        int u = blockIdx.x, kb = 0;
-        while (pre < STAGES && u < sc.units) {
-          tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split);
-          const uint32_t full = bars + 8 * pre;
-          mbar_expect_tx(full, STAGE_BYTES);
-          tma_load_2d_hint(tiles + pre * STAGE_BYTES, &tmW, full, (kb0 + kb) * TC_BK, n0, pol_w);
-          pre++;
-          if (++kb == nkb) {
-            kb = 0;
-            u += grid;
-          }
+    // weights read once per step must not displace activations in L2; weights re-read by
+    // other token tiles (prefill) stay
+    uint64_t pol_w, pol_a;
+    if (w_reused)
+      asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_w));
+    else
+      asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
+    asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_a));
+    int n0, m0, kb0, nkb, split, rot;
+    // (1) weight tiles of the first STAGES k-blocks, before the dependency resolves
+    int pre = 0;
+    {
+      int u = blockIdx.x, kb = 0;
+      while ((prefetch & 1) && pre < STAGES && u < sc.units) {
+        tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split, rot);
+        const uint32_t full = bars + 8 * pre;
+        if (elect_one()) {
+          mbar_expect_tx(full, (prefetch & 2) ? W_BYTES : STAGE_BYTES);
+          tma_load_2d_hint(tiles + pre * STAGE_BYTES, &tmW, full,
+                           tc5_kb(kb0, kb, rot, nkb) * TC_BK, n0, pol_w);
         }
-      }
-      pdl_wait();
-      // (2) their activation tiles, then (3) the steady state
-      int u = blockIdx.x, kb = 0, i = 0;
-      while (u < sc.units) {
-        tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split);
-        for (; kb < nkb; kb++, i++) {
-          const int s = i % STAGES;
-          const uint32_t full = bars + 8 * s;
-          const uint32_t dst = tiles + s * STAGE_BYTES;
-          const int k = (kb0 + kb) * TC_BK;
-          if (i >= pre) {
-            mbar_wait(bars + 8 * (STAGES + s), ((i / STAGES) & 1) ^ 1);
-            mbar_expect_tx(full, STAGE_BYTES);
-            tma_load_2d_hint(dst, &tmW, full, k, n0, pol_w);
-          }
-          tma_load_2d_hint(dst + W_BYTES, &tmA, full, k, m0, pol_a);
+        __syncwarp();
+        pre++;
+        if (++kb == nkb) {
+          kb = 0;
+          u += grid;
         }
-        kb = 0;
-        u += grid;
       }
     }
+    // (1b) L2 prefetch of the weights a LATER kernel streams (immutable, so legal before the
+    // wait): this kernel's own stream leaves HBM idle while it waits for its dependency and
+    // during its epilogue; the next big GEMM then reads L2 instead of HBM.
+    if (pf_bytes) {
+      const unsigned long long per = ((pf_bytes + gridDim.x - 1) / gridDim.x + 127) & ~127ull;
+      const unsigned long long lo = per * blockIdx.x;
+      const unsigned long long hi = lo + per < pf_bytes ? lo + per : pf_bytes;
+      constexpr unsigned long long PIECE = 16384;
+      for (unsigned long long o = lo + (unsigned long long)lane * PIECE; o < hi; o += 32 * PIECE) {
+        const uint32_t sz = (uint32_t)((hi - o < PIECE ? hi - o : PIECE) & ~15ull);
+        if (sz)
+          asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(pf_ptr + o), "r"(sz)
+                       : "memory");
+      }
+    }
+    pdl_wait();
+    if (tr.buf) t_wait = gtime();
+    // (2) their activation tiles, then (3) the steady state
+    int u = blockIdx.x, kb = 0, i = 0;
+    while (u < sc.units) {
+      tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split, rot);
+      for (; kb < nkb; kb++, i++) {
+        const int s = i % STAGES;
+        const uint32_t full = bars + 8 * s;
+        const uint32_t dst = tiles + s * STAGE_BYTES;
+        const int k = tc5_kb(kb0, kb, rot, nkb) * TC_BK;
+        if (i >= pre) mbar_wait(bars + 8 * (STAGES + s), ((i / STAGES) & 1) ^ 1);
+        if (elect_one()) {
+          if (i >= pre) {
+            mbar_expect_tx(full, (prefetch & 2) ? W_BYTES : STAGE_BYTES);
+            tma_load_2d_hint(dst, &tmW, full, k, n0, pol_w);
+          }
+          if (!(prefetch & 2)) tma_load_2d_hint(dst + W_BYTES, &tmA, full, k, m0, pol_a);
+        }
+        __syncwarp();
+      }
+      kb = 0;
+      u += grid;
+    }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // instruction descriptor (cute/arch/mma_sm100_desc.hpp): fp32 accumulate, bf16 x bf16,
-      // both K-major, N = BT, M = 128
-      constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BT >> 3) << 17) |
-                                 ((uint32_t)(TC_BN >> 4) << 24);
-      int n0, m0, kb0, nkb, split;
-      int i = 0, lu = 0;
-      for (int u = blockIdx.x; u < sc.units; u += grid, lu++) {
-        tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split);
-        const int buf = lu & 1;
-        mbar_wait(bar_tempty + 8 * buf, ((lu >> 1) & 1) ^ 1);  // epilogue drained this buffer
+    // instruction descriptor (cute/arch/mma_sm100_desc.hpp): fp32 accumulate, bf16 x bf16,
+    // both K-major, N = BT, M = 128
+    constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BT >> 3) << 17) |
+                               ((uint32_t)(TC_BN >> 4) << 24);
+    int n0, m0, kb0, nkb, split, rot;
+    int i = 0, lu = 0;
+    for (int u = blockIdx.x; u < sc.units; u += grid, lu++) {
+      tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split, rot);
+      const int buf = lu & 1;
+      mbar_wait(bar_tempty + 8 * buf, ((lu >> 1) & 1) ^ 1);  // epilogue drained this buffer
+      tc_fence_after();
+      const uint32_t tacc = tmem_base + (uint32_t)(buf * BT);
+      for (int kb = 0; kb < nkb; kb++, i++) {
+        const int s = i % STAGES;
+        mbar_wait(bars + 8 * s, (i / STAGES) & 1);
         tc_fence_after();
-        const uint32_t tacc = tmem_base + (uint32_t)(buf * BT);
-        for (int kb = 0; kb < nkb; kb++, i++) {
-          const int s = i % STAGES;
-          mbar_wait(bars + 8 * s, (i / STAGES) & 1);
-          tc_fence_after();
-          const uint32_t wt = tiles + s * STAGE_BYTES;
-          const uint64_t wdesc = make_smem_desc(wt);
-          const uint64_t adesc = make_smem_desc(wt + W_BYTES);
+        if (tr.buf && lane == 0) {
+          if (i == 0) tr_x[0] = gtime();
+          tr_x[1] = gtime();
+        }
+        const uint32_t wt = tiles + s * STAGE_BYTES;
+        const uint64_t wdesc = make_smem_desc(wt);
+        const uint64_t adesc = make_smem_desc(wt + W_BYTES);
+        if (elect_one()) {
 #pragma unroll
           for (int kk = 0; kk < TC_BK / 16; kk++) {
             // advancing 16 bf16 = 32 bytes inside the swizzle row: +2 in the >>4 address field
             tc_mma_bf16(tacc, wdesc + 2 * kk, adesc + 2 * kk, idesc, (kb | kk) != 0);
           }
           tc_commit(bars + 8 * (STAGES + s));  // frees the stage when these MMAs retire
+          if (kb == nkb - 1) tc_commit(bar_tfull + 8 * buf);
         }
-        tc_commit(bar_tfull + 8 * buf);
+        __syncwarp();
       }
+      if (tr.buf && lane == 0) tr_mma = gtime();
     }
   } else {
     // epilogue: warp w may touch TMEM lanes [32 (w % 4), +32)
     const int q = warp & 3;
     pdl_wait();  // global stores below must follow the previous kernel's completion
-    int n0, m0, kb0, nkb, split;
+    int n0, m0, kb0, nkb, split, rot;
     int lu = 0;
     for (int u = blockIdx.x; u < sc.units; u += grid, lu++) {
-      tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split);
+      tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split, rot);
       const int buf = lu & 1;
       mbar_wait(bar_tfull + 8 * buf, (lu >> 1) & 1);
       tc_fence_after();
+      if (tr.buf && warp == 2 && lane == 0) tr_epi0 = gtime();
       const int n = n0 + q * 32 + lane;
-      float* obase = out + (size_t)split * split_stride + n;
       const bool n_ok = n < N;
+      if (epi == TC5_EPI_PARTIAL) {
+        float* obase = out + (size_t)split * split_stride + n;
 #pragma unroll 1
-      for (int c0 = 0; c0 < BT; c0 += 32) {
-        if (m0 + c0 >= M) break;
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
-        if (n_ok) {
+        for (int c0 = 0; c0 < BT; c0 += 32) {
+          if (m0 + c0 >= M) break;
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
+          if (tr.buf && warp == 2 && lane == 0 && c0 == 0) tr_x[2] = gtime();
+          if (n_ok) {
+            float* op = obase + (size_t)(m0 + c0) * ldo;
+            if (m0 + c0 + 32 <= M) {  // full chunk: straight-line stores, no per-row branch
 #pragma unroll
-          for (int c = 0; c < 32; c++) {
-            const int m = m0 + c0 + c;
-            if (m < M) obase[(size_t)m * ldo] = alpha * __uint_as_float(r[c]);
+              for (int c = 0; c < 32; c++) op[(size_t)c * ldo] = alpha * __uint_as_float(r[c]);
+            } else {
+#pragma unroll
+              for (int c = 0; c < 32; c++)
+                if (m0 + c0 + c < M) op[(size_t)c * ldo] = alpha * __uint_as_float(r[c]);
+            }
+          }
+          if (tr.buf && warp == 2 && lane == 0 && c0 == 0) tr_x[3] = gtime();
+        }
+      } else if (epi == TC5_EPI_SWIGLU) {
+        // rows are interleaved gate/up (weights.cu): even lane = gate j, odd lane = up j.  The
+        // pair splits the 32 tokens: the even lane finishes tokens 0..15, the odd lane 16..31
+        // (transformer.go:50-66: silu(gate) * up)
+        // Outputs are staged per warp in shared memory ([32 tokens][16 columns] bf16, rows
+        // 48 B apart: conflict-free 16-byte reads) so that each lane then writes 16 contiguous
+        // bytes of one token row instead of sixteen 2-byte stores.
+        const int odd = lane & 1, p = lane >> 1;
+        uint8_t* stg = epi_stage[q];
+        const int j0 = (n0 + q * 32) >> 1;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BT; c0 += 32) {
+          if (m0 + c0 >= M) break;
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
+#pragma unroll
+          for (int c = 0; c < 16; c++) {
+            const float mine = __uint_as_float(odd ? r[c + 16] : r[c]);
+            const float send = __uint_as_float(odd ? r[c] : r[c + 16]);
+            const float got = __shfl_xor_sync(0xffffffffu, send, 1);
+            const float g = alpha * (odd ? got : mine), u = alpha * (odd ? mine : got);
+            const float v = __fdividef(g, 1.0f + __expf(-g)) * u;
+            *reinterpret_cast<bf16*>(stg + (c + (odd ? 16 : 0)) * 48 + p * 2) =
+                __float2bfloat16_rn(v);
+          }
+          __syncwarp();
+          const int m = m0 + c0 + lane;
+          if (m < M) {
+            bf16* orow = epi_out + (size_t)m * epi_ld + j0;
+#pragma unroll
+            for (int hh = 0; hh < 2; hh++)
+              if (2 * (j0 + hh * 8) < N)
+                *reinterpret_cast<uint4*>(orow + hh * 8) =
+                    *reinterpret_cast<const uint4*>(stg + lane * 48 + hh * 16);
+          }
+          __syncwarp();
+        }
+      } else {
+        // GELU branch: gelu_tanh(h + b1)   (transformer.go:67-78)
+        const float b = (epi_bias && n_ok) ? epi_bias[n] : 0.f;
+        bf16* obase = epi_out + n;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BT; c0 += 32) {
+          if (m0 + c0 >= M) break;
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
+          if (n_ok) {
+            bf16* op = obase + (size_t)(m0 + c0) * epi_ld;
+            if (m0 + c0 + 32 <= M) {
+#pragma unroll
+              for (int c = 0; c < 32; c++)
+                op[(size_t)c * epi_ld] =
+                    __float2bfloat16_rn(gelu_tanh(alpha * __uint_as_float(r[c]) + b));
+            } else {
+#pragma unroll
+              for (int c = 0; c < 32; c++)
+                if (m0 + c0 + c < M)
+                  op[(size_t)c * epi_ld] =
+                      __float2bfloat16_rn(gelu_tanh(alpha * __uint_as_float(r[c]) + b));
+            }
           }
         }
       }
       tc_fence_before();
       __syncwarp();
+      if (tr.buf && warp == 2 && lane == 0) tr_epi1 = gtime();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
     }
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0 && tr.buf) {
+    // extra: (last MMA commit issued, epilogue saw the accumulator, epilogue stores issued)
+    // as 21-bit ns offsets from the dependency release
+    const unsigned long long a = (tr_mma - t_wait) & 0x1fffff, b = (tr_epi0 - t_wait) & 0x1fffff,
+                             c = (tr_epi1 - t_wait) & 0x1fffff;
+    trace_rec(tr, t_entry, t_wait, (a << 42) | (b << 21) | c);
+    Trace t2 = tr;
+    t2.kid = 9;
+    trace_rec(t2, tr_x[0] - t_wait, tr_x[1] - t_wait, ((tr_x[2] - t_wait) << 32) | (tr_x[3] - t_wait));
+  }
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
                  "r"((uint32_t)(2 * BT))
@@ -366,6 +454,10 @@ static const TmaDesc* cached_map(const void* base, int rows, int cols, int box_r
   return &cache.emplace(key, d).first->second;
 }
 
+const TmaDesc* tma_map_cached(const void* base, int rows, int cols, int box_rows) {
+  return cached_map(base, rows, cols, box_rows);
+}
+
 bool tc5_supported(int M, int N, int K) { return M >= 1 && N >= 1 && K >= 8 && (K % 8) == 0; }
 
 static int pick_bt(int M) { return M <= 32 ? 32 : (M <= 64 ? 64 : (M <= 128 ? 128 : 256)); }
@@ -397,6 +489,39 @@ int tc5_splits(int M, int N, int K, int sm_count) {
   return best;
 }
 
+bool carveout_known(const void* fn) {
+  static std::mutex mu;
+  static std::map<std::pair<const void*, int>, bool> seen;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> g(mu);
+  auto key = std::make_pair(fn, dev);
+  if (seen.count(key)) return true;
+  seen[key] = true;
+  return false;
+}
+
+// bit 0: weight prefetch before the dependency wait (default on); bit 1: timing experiment
+// only — skip the activation loads (results are garbage)
+static int prefetch_flags() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("NVLLM_PREFETCH");
+    v = e ? atoi(e) : 1;
+  }
+  return v;
+}
+static unsigned long long* g_trace_buf = nullptr;
+static int g_trace_seq = 0;
+void trace_set(unsigned long long* buf) {
+  g_trace_buf = buf;
+  g_trace_seq = 0;
+}
+Trace next_trace(int kid) {
+  Trace t{g_trace_buf, 0, kid};
+  if (g_trace_buf) t.seq = g_trace_seq++;
+  return t;
+}
 static bool g_pdl = true;
 void set_pdl_enabled(bool on) { g_pdl = on; }
 bool pdl_enabled() { return g_pdl; }
@@ -428,7 +553,10 @@ static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* t
   return launch_k(gemm_tc5_kernel<BT, STAGES>, dim3(grid), dim3(TC_THREADS), smem, st,
                   *reinterpret_cast<const CUtensorMap*>(tw),
                   *reinterpret_cast<const CUtensorMap*>(ta), a.M, a.N, sc, a.out, a.ldo,
-                  a.split_stride, a.alpha, m_tiles > 1 ? 1 : 0);
+                  a.split_stride, a.alpha, m_tiles > 1 ? 1 : 0, a.epi, (bf16*)a.epi_out, a.epi_ld,
+                  a.epi_bias, prefetch_flags(),
+                  (const uint8_t*)((prefetch_flags() & 4) ? nullptr : a.pf_ptr),
+                  (unsigned long long)((prefetch_flags() & 4) ? 0 : a.pf_bytes), next_trace(1));
 }
 
 // a.S is the requested number of splits; the number actually written is returned in *S_out
@@ -442,8 +570,12 @@ cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int* S_out) {
   int S = max(1, min(a.S, nkb));
   const int kbps = ceil_div(nkb, S);
   S = ceil_div(nkb, kbps);
+  if (a.epi != TC5_EPI_PARTIAL) {
+    if (!a.epi_out || (a.epi == TC5_EPI_SWIGLU && (a.N & 1))) return cudaErrorInvalidValue;
+    S = 1;
+  }
   if (S_out) *S_out = S;
-  if (a.out_capacity && (size_t)S * a.split_stride > a.out_capacity) return cudaErrorInvalidValue;
+  if (a.epi == TC5_EPI_PARTIAL && a.out_capacity && (size_t)S * a.split_stride > a.out_capacity) return cudaErrorInvalidValue;
   switch (bt) {
     case 32: return launch_bt<32, 10>(st, a, tw, ta, S);
     case 64: return launch_bt<64, 8>(st, a, tw, ta, S);

@@ -60,9 +60,12 @@ struct Workspace {
   const float* logits_final = nullptr;  // where the last step's summed logits live
   int n_cap_out = 0;
   size_t logits_p_floats = 0;
+  int* attn_tickets = nullptr;  // stream-K decode attention, [n * nkv * chunks]
   float* attn_ws = nullptr;
   size_t attn_ws_floats = 0;
   int* out_tokens = nullptr;  // [n]
+  unsigned long long* amax = nullptr;  // [n] argmax merge scratch (zero between kernels)
+  int* amax_ticket = nullptr;          // [n]
   // moe
   int* topk_idx = nullptr;
   float* topk_w = nullptr;
@@ -117,6 +120,8 @@ struct nvllm_handle {
   // accounting
   uint64_t weight_bytes = 0, kv_bytes = 0, ws_bytes = 0;
   int launches = 0;  // kernels launched by the current step
+  int cur_cls = 0;            // kernel class of the launch being issued
+  unsigned skip_mask = 0;     // NVLLM_SKIP: classes not launched (timing ablation only)
   bool resident_ok = false;  // the last step's state is on the device (nvllm_run_resident)
   nvllm::StepLayout run_lay;  // layout of the last nvllm_run (nvllm_rerun replays it)
   bool run_lay_ok = false;

@@ -70,7 +70,8 @@ cudaError_t launch_rope_kv(cudaStream_t st, int qdt, int kvdt, int T, int nh, in
 // (cmd/ask/main.go:389-402).  Otherwise softmax(l/T) and inverse-CDF draw with uniforms[i]
 // (sampling.go:70-74,105-128,196-217).
 cudaError_t launch_sample(cudaStream_t st, const float* logits, int ldl, int V, int n,
-                          const float* temperature, const float* uniforms, int* out_tokens);
+                          const float* temperature, const float* uniforms, int* out_tokens,
+                          unsigned long long* amax = nullptr, int* ticket = nullptr);
 
 // advance device-resident decode state by one token (nvllm_run_resident)
 cudaError_t launch_advance(cudaStream_t st, int n, const int* sampled, int* tokens, int* positions,
@@ -87,7 +88,7 @@ cudaError_t launch_make_decode_state(cudaStream_t st, int n, int mb, const int* 
 
 // dst[N,K] (dtype ddt) = transpose(src[K,N] fp32|bf16|f16)   — weight repack at finalize
 cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* src, int K, int N,
-                                     int ddt, void* dst, int ld_dst);
+                                     int ddt, void* dst, int ld_dst, int glu_F = 0);
 // dst (dtype ddt) = convert(src)  flat copy
 cudaError_t launch_convert(cudaStream_t st, int sdt_api, const void* src, size_t n, int ddt,
                            void* dst);
@@ -133,6 +134,8 @@ struct TmaDesc {
 // 2-D bf16 tensor map: rows x cols (cols contiguous), box = box_rows x 64 cols, 128B swizzle
 int make_tma_2d_bf16(TmaDesc* out, const void* base, uint64_t rows, uint64_t cols,
                      uint64_t row_stride_elems, uint32_t box_rows, std::string* err);
+// memoised tensor map (pure function of pointer, shape, box); null on failure
+const TmaDesc* tma_map_cached(const void* base, int rows, int cols, int box_rows);
 struct Tc5Args {
   const void* A;  // activations [M, K] bf16, K contiguous
   const void* W;  // weights     [N, K] bf16, K contiguous
@@ -143,7 +146,17 @@ struct Tc5Args {
   int S;               // requested split-K slices (tc5_splits)
   float alpha;
   size_t out_capacity;
+  // fused epilogue (needs S == 1): the activation is applied to the accumulator and the bf16
+  // FFN hidden state is written directly, no fp32 partials and no act kernel
+  int epi;              // TC5_EPI_*
+  void* epi_out;        // bf16 [M, epi_ld]
+  int epi_ld;
+  const float* epi_bias;  // [N] or null (GELU)
+  // weights of a later GEMM to pull into L2 while this one waits / drains (decode only)
+  const void* pf_ptr;
+  size_t pf_bytes;
 };
+enum { TC5_EPI_PARTIAL = 0, TC5_EPI_SWIGLU = 1, TC5_EPI_GELU = 2 };
 bool tc5_supported(int M, int N, int K);
 int tc5_splits(int M, int N, int K, int sm_count);
 // *S_out = slices actually written (<= a.S)
@@ -173,6 +186,12 @@ struct AttnArgs {
   const int* seq_len;  // [n_seqs] tokens incl. the new one
   int n_splits;
   float* ws;           // [n_seqs*nh*n_splits*(hd+2)] split partials
+  // stream-K decode (attention_mma.cu): ticket per (seq, kv head, head chunk), zero between
+  // kernels; total_tiles = host LOWER bound of the key tiles in the step (caps the grid)
+  int* tickets;
+  int pool_blocks;     // blocks in the layer's K / V pool (tensor-map extent)
+  int sm_count;
+  long long total_tiles;
 };
 constexpr int ATTN_PREFILL_QTILE = 32;  // SIMT (fp32 parity) kernel; the mma kernel uses 64
 // queries per tile of the kernel launch_attn_prefill will pick: the host builds tile_seq /
@@ -188,6 +207,9 @@ bool attn_mma_supported(int qdt, int kvdt, int hd);
 int attn_decode_mma_tile(int hd);
 cudaError_t launch_attn_prefill_mma(cudaStream_t st, const AttnArgs& a);
 cudaError_t launch_attn_decode_mma(cudaStream_t st, const AttnArgs& a);
+size_t attn_decode_sk_ws_floats(int hd, int sm_count);
+cudaError_t launch_attn_decode_sk(cudaStream_t st, const AttnArgs& a, int* tickets, int sm_count,
+                                  long long total_tiles_hint);
 
 // ---------------------------------------------------------------- moe.cu
 // Router: probs = softmax(x @ R) over all E, top-k (descending), weights renormalised

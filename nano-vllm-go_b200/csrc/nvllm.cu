@@ -125,6 +125,7 @@ int nvllm_create(const nvllm_config* c, const uint8_t* tp_id, nvllm_handle** out
   if (const char* env = getenv("NVLLM_PDL")) set_pdl_enabled(atoi(env) != 0);  // debugging aid
   nvllm_handle* h = new nvllm_handle();
   h->cfg = *c;
+  if (const char* env = getenv("NVLLM_SKIP")) h->skip_mask = (unsigned)strtoul(env, nullptr, 0);
   h->cfg.num_kv_heads = nkv;
   if (h->cfg.num_kv_blocks <= 0) h->cfg.num_kv_blocks = 1024;  // scheduler.go:17-21
   if (h->cfg.max_num_seqs <= 0) h->cfg.max_num_seqs = 512;

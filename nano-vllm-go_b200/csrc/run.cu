@@ -330,3 +330,41 @@ extern "C" int nvllm_timer_elapsed(nvllm_handle* h, float* ms) {
   NV_CHECK(h, cudaEventElapsedTime(ms, h->tm0, h->tm1));
   return NVLLM_OK;
 }
+
+// ---- diagnostics: device timeline (see include/nvllm.h)
+namespace nvllm {
+void trace_set(unsigned long long* buf);
+}
+static unsigned long long* g_trace_dev = nullptr;
+static int g_trace_cap = 0;
+extern "C" int nvllm_trace_begin(nvllm_handle* h, int capacity) {
+  if (!h || capacity <= 0) return NVLLM_ERR_INVALID;
+  NV_CHECK(h, cudaSetDevice(h->dev));
+  NV_CHECK(h, cudaStreamSynchronize(h->stream));
+  if (g_trace_dev) cudaFree(g_trace_dev);
+  g_trace_dev = nullptr;
+  const size_t words = 8 + (size_t)capacity * 8;
+  NV_CHECK(h, cudaMalloc((void**)&g_trace_dev, words * 8));
+  NV_CHECK(h, cudaMemset(g_trace_dev, 0, words * 8));
+  unsigned long long cap = (unsigned long long)capacity;
+  NV_CHECK(h, cudaMemcpy(g_trace_dev + 1, &cap, 8, cudaMemcpyHostToDevice));
+  g_trace_cap = capacity;
+  trace_set(g_trace_dev);
+  return NVLLM_OK;
+}
+extern "C" int nvllm_trace_end(nvllm_handle* h, uint64_t* out, int max_records, int* n_records) {
+  if (!h || !n_records) return NVLLM_ERR_INVALID;
+  NV_CHECK(h, cudaSetDevice(h->dev));
+  trace_set(nullptr);
+  if (!g_trace_dev) return set_err(h, NVLLM_ERR_STATE, "trace was not started");
+  NV_CHECK(h, cudaStreamSynchronize(h->stream));
+  unsigned long long n = 0;
+  NV_CHECK(h, cudaMemcpy(&n, g_trace_dev, 8, cudaMemcpyDeviceToHost));
+  if (n > (unsigned long long)g_trace_cap) n = g_trace_cap;
+  if ((int)n > max_records) n = max_records;
+  if (out && n) NV_CHECK(h, cudaMemcpy(out, g_trace_dev + 8, n * 64, cudaMemcpyDeviceToHost));
+  *n_records = (int)n;
+  cudaFree(g_trace_dev);
+  g_trace_dev = nullptr;
+  return NVLLM_OK;
+}

@@ -45,6 +45,7 @@ extern "C" int nvllm_set_weight(nvllm_handle* h, int id, int layer, int dtype, c
 
   // what to do with this tensor
   enum { FLAT_DT, FLAT_F32, TRANSPOSE_DT, TRANSPOSE_F32 } mode = FLAT_F32;
+  int glu_F = 0;  // > 0: interleave the [gate | up] halves row by row
   void* dst = nullptr;
   size_t expect = 0;
   int K = 0, N = 0, ld = 0;  // transpose: src [K, N] -> dst [N, ld]
@@ -89,7 +90,9 @@ extern "C" int nvllm_set_weight(nvllm_handle* h, int id, int layer, int dtype, c
     case NVLLM_W_O_BIAS: dst = w->bo; expect = H; break;
     case NVLLM_W_FFN_W1:
       if (h->moe) return set_err(h, NVLLM_ERR_INVALID, "MoE model takes MOE_INPUT/MOE_OUTPUT");
-      mode = TRANSPOSE_DT; dst = w->w1; K = H; N = h->w1_cols; ld = H; expect = (size_t)H * N; break;
+      mode = TRANSPOSE_DT; dst = w->w1; K = H; N = h->w1_cols; ld = H; expect = (size_t)H * N;
+      if (h->swiglu) glu_F = F;
+      break;
     case NVLLM_W_FFN_B1:
       if (h->moe || h->swiglu)  // transformer.go:50-66: the SwiGLU branch never adds B1
         return set_err(h, NVLLM_ERR_INVALID, "FFN_B1 only exists on the GELU branch");
@@ -121,7 +124,9 @@ extern "C" int nvllm_set_weight(nvllm_handle* h, int id, int layer, int dtype, c
   switch (mode) {
     case FLAT_DT: e = launch_convert(h->stream, dtype, stage, numel, h->wdt, dst); break;
     case FLAT_F32: e = launch_convert(h->stream, dtype, stage, numel, DT_F32, dst); break;
-    case TRANSPOSE_DT: e = launch_transpose_convert(h->stream, dtype, stage, K, N, h->wdt, dst, ld); break;
+    case TRANSPOSE_DT:
+      e = launch_transpose_convert(h->stream, dtype, stage, K, N, h->wdt, dst, ld, glu_F);
+      break;
     default: e = launch_transpose_convert(h->stream, dtype, stage, K, N, DT_F32, dst, ld); break;
   }
   if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);  // host buffer is free on return

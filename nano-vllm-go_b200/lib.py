@@ -72,6 +72,9 @@ SIGNATURES = {
     "nvllm_rerun": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(RunStats)]),
     "nvllm_set_profile": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "nvllm_get_profile": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ProfileEntry)]),
+    "nvllm_trace_begin": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "nvllm_trace_end": (ctypes.c_int, [ctypes.c_void_p, _u64p, ctypes.c_int,
+                                       ctypes.POINTER(ctypes.c_int)]),
     "nvllm_timer_record": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "nvllm_timer_elapsed": (ctypes.c_int, [ctypes.c_void_p, _f32p]),
     "nvllm_set_sampling": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_float, ctypes.c_int,

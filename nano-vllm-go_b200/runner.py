@@ -127,6 +127,17 @@ class CudaModelRunner:
         """Re-execute the last prefill step from its device-resident inputs (no copies)."""
         L.check(self._lib.nvllm_rerun(self._h, ctypes.byref(self.last_stats)), self._h)
 
+    def trace_begin(self, capacity: int = 1 << 16) -> None:
+        L.check(self._lib.nvllm_trace_begin(self._h, capacity), self._h)
+
+    def trace_end(self, max_records: int = 1 << 16) -> np.ndarray:
+        """[n, 8] uint64: seq, kernel id, cta, sm, t_entry, t_after_wait, t_exit, extra (ns)."""
+        out = np.zeros((max_records, 8), dtype=np.uint64)
+        n = ctypes.c_int()
+        L.check(self._lib.nvllm_trace_end(self._h, out.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)),
+                                          max_records, ctypes.byref(n)), self._h)
+        return out[:n.value]
+
     def timer_start(self) -> None:
         L.check(self._lib.nvllm_timer_record(self._h, 0), self._h)
 
