@@ -102,29 +102,86 @@ class ClockSampler:
                 "samples": len(sm), "reasons": sorted(reasons)}
 
 
-class Job:
-    """The cfg2 job on one replica: block tables from the restated Go block manager."""
+# BASELINE.json configs[0..4] (SURVEY.md §8d "Prompts")
+CONFIGS = {
+    1: dict(model="gpt2", batch=1, prompt_len=32, decode_steps=64, shared_prefix=0, tp=False,
+            label="configs[0]: 1 sequence, 32-token prompt + 64 greedy decode steps"),
+    2: dict(model="llama-3.2-1b", batch=64, prompt_len=512, decode_steps=256, shared_prefix=0, tp=False,
+            label="configs[1]: batch 64 continuous batching, 512-token prefill + 256 greedy decode steps"),
+    3: dict(model="granite-moe-1b", batch=128, prompt_len=128, decode_steps=256, shared_prefix=0,
+            tp=False, label="configs[2]: batch 128, 128-token prefill + 256 decode steps (context 128->384), "
+                            "top-8 of 32 experts"),
+    4: dict(model="falcon-7b", batch=1, prompt_len=2048, decode_steps=32, shared_prefix=0, tp=True,
+            label="configs[3]: tensor parallel over all ranks, 1 sequence, 2048-token prefill + 32 greedy "
+                  "decode steps (RoPE table extended to 2112 positions for the decode tail)"),
+    5: dict(model="llama-3.2-3b", batch=16, prompt_len=4096, decode_steps=0, shared_prefix=3840,
+            tp=False, label="configs[4]: per replica 16 prompts x 4096 tokens sharing a 3840-token "
+                            "prefix (15 KV blocks): request 0 cold, 15 prefix-cache hits "
+                            "(NumCachedTokens=3840); prefill only (positions stop at MaxSeqLen 4096)"),
+}
 
-    def __init__(self, cfg, batch, prompt_len, decode_steps, seed0):
+
+class Job:
+    """One bench "step" on one replica (or one tensor-parallel group): the prefill step(s) the Go
+    scheduler would issue for the request set, then D decode steps.  Block tables and
+    NumCachedTokens come from the restated Go block manager (nano-vllm-go_b200/engine.py)."""
+
+    def __init__(self, cfg, batch, prompt_len, decode_steps, seed0, shared_prefix=0):
         self.cfg, self.n, self.P, self.D = cfg, batch, prompt_len, decode_steps
-        self.max_len = prompt_len + decode_steps + 1
-        self.prompts = np.stack([W.random_prompt(cfg.vocab_size, prompt_len, seed0 + i)
-                                 for i in range(batch)])
+        self.max_len = prompt_len + decode_steps + (1 if decode_steps else 0)
+        V = cfg.vocab_size
+        if shared_prefix:
+            common = W.random_prompt(V, shared_prefix, seed0 + 99991)
+            self.prompts = np.stack([np.concatenate(
+                [common, W.random_prompt(V, prompt_len - shared_prefix, seed0 + i)]) for i in range(batch)])
+        else:
+            self.prompts = np.stack([W.random_prompt(V, prompt_len, seed0 + i) for i in range(batch)])
         nb = (self.max_len + 255) // 256
+        self.nb = nb
         bm = E.BlockManager(batch * nb, 256)
-        self.tables = []
-        for i in range(batch):  # allocate the final extent up front (ABI allows nb >= needed)
-            s = E.Sequence(list(range(i * 7, i * 7 + self.max_len)))
+        seqs = []
+        for i in range(batch):
+            s = E.Sequence([int(t) for t in self.prompts[i]])
             bm.allocate(s)
-            self.tables.append(s.block_table)
+            seqs.append(s)
+        # decode tail: take the blocks the sequence will grow into up front (the ABI allows a
+        # block table longer than needed), from the same free list the Go engine would use
+        for s in seqs:
+            while len(s.block_table) < nb:
+                bid = bm.free_block_ids[0]
+                bm._allocate_block(bid)
+                s.block_table.append(bid)
+        self.tables = [s.block_table for s in seqs]
+        self.num_cached = np.asarray([s.num_cached_tokens for s in seqs], dtype=np.int32)
         self.num_blocks = batch * nb
         self.bt = np.asarray(self.tables, dtype=np.int32).reshape(-1)
         self.cub = np.arange(0, (batch + 1) * nb, nb, dtype=np.int32)
         self.temp = np.zeros(batch, dtype=np.float32)
+        # one prefill step for the whole request set, as scheduler.go:45-71 issues it: cache hits
+        # ride in the SAME step as the request whose blocks they hit (both are allocated before
+        # Run); the library appends every new K/V of a layer before any attention read of it
+        self.prefill_steps = [list(range(batch))]
         self.tokens_per_step = batch * (prompt_len + decode_steps)
+        self.computed_tokens_per_step = int(batch * (prompt_len + decode_steps) - self.num_cached.sum())
 
-    # ---- device-resident pass: nothing crosses PCIe inside
+    def _prefill_args(self, idx):
+        flat = self.prompts[idx].reshape(-1).astype(np.int32)
+        cu = np.arange(0, (len(idx) + 1) * self.P, self.P, dtype=np.int32)
+        bt = np.asarray([self.tables[i] for i in idx], dtype=np.int32).reshape(-1)
+        cub = np.arange(0, (len(idx) + 1) * self.nb, self.nb, dtype=np.int32)
+        return len(idx), True, flat, cu, self.num_cached[idx].copy(), bt, cub, self.temp[:len(idx)], None
+
+    @property
+    def simple(self):
+        return len(self.prefill_steps) == 1
+
+    def stage(self, run, step=0):
+        """Upload one prefill step's inputs (outside any timed region; runs the step once)."""
+        run.run_arrays(*self._prefill_args(self.prefill_steps[step]))
+
+    # ---- device-resident pass: nothing crosses PCIe inside a timed segment
     def run_resident(self, run):
+        """Simple jobs (one prefill step, staged beforehand): rerun + D resident decode steps."""
         launches = 0
         run.rerun()
         launches += run.last_stats.kernel_launches
@@ -133,28 +190,44 @@ class Job:
             launches += run.last_stats.kernel_launches
         return launches
 
-    def stage(self, run):
-        """Upload the prefill step's inputs once (outside any timed region)."""
-        flat = self.prompts.reshape(-1).astype(np.int32)
-        cu = np.arange(0, (self.n + 1) * self.P, self.P, dtype=np.int32)
-        run.run_arrays(self.n, True, flat, cu, np.zeros(self.n, np.int32), self.bt, self.cub,
-                       self.temp, None)
+    def run_resident_timed(self, run):
+        """Jobs with several prefill steps: stage each (untimed), time its device-resident
+        re-execution; returns (device ms summed over the segments, launches)."""
+        ms, launches = 0.0, 0
+        for k in range(len(self.prefill_steps)):
+            self.stage(run, k)
+            run.sync()
+            run.timer_start()
+            run.rerun()
+            if k == len(self.prefill_steps) - 1:
+                for _ in range(self.D):
+                    run.run_resident()
+            ms += run.timer_stop()
+            launches += run.last_stats.kernel_launches
+        return ms, launches
 
     # ---- end-to-end pass through nvllm_run with host buffers every step
     def run_e2e(self, run):
         n, P = self.n, self.P
+        h2d = d2h = 0
+        first = np.zeros(n, dtype=np.int32)
+        for idx in self.prefill_steps:
+            out, _ = run.run_arrays(*self._prefill_args(idx))
+            h2d += run.last_stats.h2d_bytes
+            d2h += run.last_stats.d2h_bytes
+            first[idx] = out
+        if not self.D:
+            return h2d, d2h, first
         tok = np.zeros((n, self.max_len), dtype=np.int32)
         tok[:, :P] = self.prompts
-        lens = np.full(n, P, dtype=np.int64)
+        tok[:, P] = first
+        lens = np.full(n, P + 1, dtype=np.int64)
         cols = np.arange(self.max_len)[None, :]
-        h2d = d2h = 0
         cu = np.zeros(n + 1, dtype=np.int32)
-        nc = np.zeros(n, np.int32)
-        for step in range(self.D + 1):
+        for _ in range(self.D):
             np.cumsum(lens, out=cu[1:])
             flat = tok[cols < lens[:, None]]
-            out, _ = run.run_arrays(n, step == 0, flat, cu, nc if step == 0 else None, self.bt,
-                                    self.cub, self.temp, None)
+            out, _ = run.run_arrays(n, False, flat, cu, None, self.bt, self.cub, self.temp, None)
             h2d += run.last_stats.h2d_bytes
             d2h += run.last_stats.d2h_bytes
             tok[np.arange(n), lens] = out
@@ -162,7 +235,7 @@ class Job:
         return h2d, d2h, tok
 
 
-def make_runner(cfg, job, device, keep_host=None):
+def make_runner(cfg, job, device, keep_host=None, tp_size=1, tp_rank=0, tp_id=None):
     R = nvllm_pkg.sub("runner")
 
     def gen():
@@ -171,9 +244,10 @@ def make_runner(cfg, job, device, keep_host=None):
                 keep_host.append((wid, layer, a))
             yield wid, layer, a
 
+    max_T = max(len(g) for g in job.prefill_steps) * job.P
     return R.CudaModelRunner(cfg, gen(), precision=C.PREC_BF16, num_kv_blocks=job.num_blocks,
-                             device=device, max_num_seqs=job.n,
-                             max_batched_tokens=job.n * job.P, weight_dtype=C.DT_BF16)
+                             device=device, max_num_seqs=job.n, max_batched_tokens=max_T,
+                             weight_dtype=C.DT_BF16, tp_size=tp_size, tp_rank=tp_rank, tp_id=tp_id)
 
 
 def cpu_oracle_sample(cfg, weights, budget_s, prompt_tokens=None):
@@ -207,10 +281,12 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--model", default="llama-3.2-1b", choices=sorted(C.PRESETS))
-    ap.add_argument("--batch", type=int, default=64)
-    ap.add_argument("--prompt-len", type=int, default=512)
-    ap.add_argument("--decode-steps", type=int, default=256)
+    ap.add_argument("--config", type=int, default=2, choices=sorted(CONFIGS),
+                    help="BASELINE.json configs[N-1]; the default (2) is the config the metric is quoted on")
+    ap.add_argument("--model", default=None, choices=sorted(C.PRESETS))
+    ap.add_argument("--batch", type=int, default=None)
+    ap.add_argument("--prompt-len", type=int, default=None)
+    ap.add_argument("--decode-steps", type=int, default=None)
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
@@ -219,13 +295,28 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-    cfg = C.PRESETS[args.model]()
-    config = {"workload": f"{cfg.name} bf16 weights/fp32 accumulate, batch {args.batch} continuous "
-                          f"batching, {args.prompt_len}-token prefill + {args.decode_steps} greedy "
-                          f"decode steps (BASELINE.json configs[1])",
-              "global_batch": args.batch * world, "prompt_len": args.prompt_len,
-              "decode_steps": args.decode_steps, "parallelism": f"dp{world} replicas",
-              "l2": "inputs larger than L2 (2.5 GB of weights + KV per step >> 126 MB)"}
+    spec = dict(CONFIGS[args.config])
+    for k, v in (("model", args.model), ("batch", args.batch), ("prompt_len", args.prompt_len),
+                 ("decode_steps", args.decode_steps)):
+        if v is not None:
+            spec[k] = v
+            spec["label"] = "custom"
+    cfg = C.PRESETS[spec["model"]]()
+    need_pos = spec["prompt_len"] + spec["decode_steps"] + 1
+    if args.config == 4 and cfg.max_seq_len < need_pos:
+        from dataclasses import replace
+        cfg = replace(cfg, max_seq_len=need_pos + 31)
+    tp = world if (spec["tp"] and world > 1) else 1
+    replicas = 1 if tp > 1 else world
+    config = {"workload": f"{cfg.name} bf16 weights/fp32 accumulate, {spec['label']} "
+                          f"(BASELINE.json configs[{args.config - 1}])",
+              "global_batch": spec["batch"] * replicas, "prompt_len": spec["prompt_len"],
+              "decode_steps": spec["decode_steps"],
+              "parallelism": f"tp{tp}" if tp > 1 else f"dp{world} replicas",
+              "l2": "inputs larger than L2 (weights + KV streamed per step >> 126 MB)"
+                    if cfg.matmul_params() * 2 > 2 * 126e6 else
+                    "weights + KV of this model fit the 126 MB L2 only partly; no flush between steps"}
+    scaling = "strong" if tp > 1 else "weak"
     metric = "prefill+decode tokens/s (whole job)"
 
     if args.impl == "reference":
@@ -265,9 +356,16 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     device = local_rank
 
-    job = Job(cfg, args.batch, args.prompt_len, args.decode_steps, seed0=4321 + 1000 * rank)
+    # replicas draw disjoint request sets; the ranks of a tensor-parallel group share one
+    job = Job(cfg, spec["batch"], spec["prompt_len"], spec["decode_steps"],
+              seed0=4321 + (0 if tp > 1 else 1000 * rank), shared_prefix=spec["shared_prefix"])
     keep = [] if (rank == 0 and not args.no_cpu_baseline) else None
-    run = make_runner(cfg, job, device, keep)
+    tp_id = None
+    if tp > 1:
+        box = [nvllm_pkg.sub("lib").tp_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        tp_id = box[0]
+    run = make_runner(cfg, job, device, keep, tp_size=tp, tp_rank=rank if tp > 1 else 0, tp_id=tp_id)
     mem = run.memory_info()
 
     def barrier():
@@ -294,7 +392,7 @@ def main():
         t = torch.tensor([ms], device=f"cuda:{device}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
-    value = world * job.tokens_per_step * args.steps / (ms / 1e3)
+    value = replicas * job.tokens_per_step * args.steps / (ms / 1e3)
 
     # ---- e2e leg: host buffers through nvllm_run every step
     job.run_e2e(run)  # warm (staging buffers sized)
@@ -311,7 +409,7 @@ def main():
         t = torch.tensor([e2e_s], device=f"cuda:{device}")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-    e2e = world * job.tokens_per_step * args.steps / e2e_s
+    e2e = replicas * job.tokens_per_step * args.steps / e2e_s
 
     # ---- separate profiled pass: per-kernel-class time, phase split, roofline
     peaks = load_peaks()
@@ -336,9 +434,12 @@ def main():
         for _ in range(job.D):
             run.run_resident()
         t_decode = run.timer_stop()
+        new_tok = int(job.n * job.P - job.num_cached.sum())
         phases = {"prefill_ms": t_prefill, "decode_ms": t_decode,
                   "prefill_tok_s": job.n * job.P / (t_prefill / 1e3),
-                  "decode_tok_s": job.n * job.D / (t_decode / 1e3)}
+                  "prefill_computed_tok_s": new_tok / (t_prefill / 1e3),
+                  "prefix_cached_tokens": int(job.num_cached.sum()),
+                  "decode_tok_s": job.n * job.D / (t_decode / 1e3) if job.D else None}
         best = None
         for phase, prof in (("prefill", prof_prefill), ("decode", prof_decode)):
             for name, e in prof.items():
@@ -377,7 +478,7 @@ def main():
     if rank == 0:
         line = {"metric": metric, "value": value, "unit": "tokens/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+                "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "bf16",
                 "data": "synthetic", "config": config, "clocks": clocks,
                 "e2e": {"value": e2e, "unit": "tokens/s", "h2d_bytes_per_step": h2d // args.steps,
                         "d2h_bytes_per_step": d2h // args.steps},

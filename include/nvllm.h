@@ -239,7 +239,8 @@ enum nvllm_kernel_class {
   NVLLM_K_MOE_MISC = 11,    /* GLU + weighted combine */
   NVLLM_K_SAMPLE = 12,
   NVLLM_K_MISC = 13,
-  NVLLM_K_COUNT = 14
+  NVLLM_K_COMM = 14,        /* tensor-parallel partial sum + NCCL all-reduce / all-gather */
+  NVLLM_K_COUNT = 15
 };
 typedef struct nvllm_profile_entry {
   double ms;

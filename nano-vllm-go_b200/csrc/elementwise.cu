@@ -424,6 +424,83 @@ __device__ __forceinline__ unsigned long long argmax_key(float v, int i) {
   return ((unsigned long long)b << 32) | (uint32_t)(~(uint32_t)i);
 }
 
+// Tensor-parallel LM head: the row's logits are V / vsplit slices gathered rank-major.  One
+// CTA (blockIdx.y == 0) per row; same arithmetic and scan order as the plain path below.
+__device__ __noinline__ void sample_split_rows(const float* __restrict__ logits, int V, int n,
+                                               int vsplit, const float* __restrict__ temperature,
+                                               const float* __restrict__ uniforms,
+                                               int* __restrict__ out_tokens, float* red,
+                                               ArgMax* amred, float* scan, int* winner) {
+  if (blockIdx.y != 0) return;
+  const int s = blockIdx.x;
+  auto at = [&](int v) -> float {
+    const int r = v / vsplit;
+    return logits[(size_t)r * n * vsplit + (size_t)s * vsplit + (v - r * vsplit)];
+  };
+  const float temp = temperature ? temperature[s] : 0.f;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  if (!(temp > 0.f)) {
+    ArgMax am = {-INFINITY, 0x7fffffff};
+    for (int i = threadIdx.x; i < V; i += blockDim.x) {
+      const float v = at(i);
+      if (v > am.v) { am.v = v; am.i = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      ArgMax ot = {__shfl_xor_sync(0xffffffffu, am.v, o), __shfl_xor_sync(0xffffffffu, am.i, o)};
+      am = argmax_merge(am, ot);
+    }
+    if (lane == 0) amred[w] = am;
+    __syncthreads();
+    if (w == 0) {
+      ArgMax r = (lane < nw) ? amred[lane] : ArgMax{-INFINITY, 0x7fffffff};
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        ArgMax ot = {__shfl_xor_sync(0xffffffffu, r.v, o), __shfl_xor_sync(0xffffffffu, r.i, o)};
+        r = argmax_merge(r, ot);
+      }
+      if (lane == 0) out_tokens[s] = (r.i == 0x7fffffff) ? 0 : r.i;
+    }
+    return;
+  }
+  const int chunk = (V + blockDim.x - 1) / blockDim.x;
+  const int lo = min(V, (int)threadIdx.x * chunk), hi = min(V, lo + chunk);
+  float mx = -INFINITY;
+  for (int i = lo; i < hi; i++) mx = fmaxf(mx, at(i) / temp);
+  mx = block_max(mx, red);
+  float csum = 0.f;
+  for (int i = lo; i < hi; i++) csum += expf(at(i) / temp - mx);
+  scan[threadIdx.x] = csum;
+  __syncthreads();
+  for (int o = 1; o < (int)blockDim.x; o <<= 1) {
+    float add = (threadIdx.x >= (unsigned)o) ? scan[threadIdx.x - o] : 0.f;
+    __syncthreads();
+    scan[threadIdx.x] += add;
+    __syncthreads();
+  }
+  const float total = scan[blockDim.x - 1];
+  const float r = uniforms[s] * total;
+  if (threadIdx.x == 0) *winner = V - 1;
+  __syncthreads();
+  const float incl = scan[threadIdx.x];
+  const float excl = incl - csum;
+  const bool mine = (incl >= r) && (threadIdx.x == 0 || scan[threadIdx.x - 1] < r) && (hi > lo);
+  if (mine) {
+    float run = excl;
+    int pick = hi - 1;
+    for (int i = lo; i < hi; i++) {
+      run += expf(at(i) / temp - mx);
+      if (run >= r) {
+        pick = i;
+        break;
+      }
+    }
+    atomicMin(winner, pick);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) out_tokens[s] = *winner;
+}
+
 // grid (n_seqs, chunks).  Greedy rows: every CTA reduces its slice of the vocabulary and
 // merges with one 64-bit atomicMax; the last CTA of the row (atomic ticket) publishes the
 // token and re-arms the scratch, so the kernel needs no separate init.  Temperature rows: CTA
@@ -431,7 +508,8 @@ __device__ __forceinline__ unsigned long long argmax_key(float v, int i) {
 __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
                               const float* __restrict__ temperature,
                               const float* __restrict__ uniforms, int* __restrict__ out_tokens,
-                              unsigned long long* __restrict__ amax, int* __restrict__ ticket) {
+                              unsigned long long* __restrict__ amax, int* __restrict__ ticket,
+                              int vsplit) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float red[32];
@@ -439,6 +517,11 @@ __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
   __shared__ float scan[1024];
   __shared__ int winner;
   const int s = blockIdx.x;
+  if (vsplit > 0) {
+    sample_split_rows(logits, V, gridDim.x, vsplit, temperature, uniforms, out_tokens, red, amred,
+                      scan, &winner);
+    return;
+  }
   const float* l = logits + (size_t)s * ldl;
   const float temp = temperature ? temperature[s] : 0.f;
   const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = blockDim.x >> 5;
@@ -540,12 +623,12 @@ __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
 
 cudaError_t launch_sample(cudaStream_t st, const float* logits, int ldl, int V, int n,
                           const float* temperature, const float* uniforms, int* out_tokens,
-                          unsigned long long* amax, int* ticket) {
+                          unsigned long long* amax, int* ticket, int vsplit) {
   if (n <= 0) return cudaSuccess;
   // ~8K logits per CTA keeps >= 2 waves of CTAs in flight for a large vocabulary
-  const int chunks = (amax && ticket) ? max(1, min(64, V / 8192)) : 1;
+  const int chunks = (amax && ticket && vsplit == 0) ? max(1, min(64, V / 8192)) : 1;
   (void)launch_k(sample_kernel, dim3(n, chunks), dim3(chunks > 1 ? 256 : 1024), 0, st, logits, ldl,
-                 V, temperature, uniforms, out_tokens, amax, ticket);
+                 V, temperature, uniforms, out_tokens, amax, ticket, vsplit);
   return cudaGetLastError();
 }
 
@@ -581,31 +664,37 @@ template <> __device__ __forceinline__ float src_to_f32<float>(float v) { return
 template <> __device__ __forceinline__ float src_to_f32<bf16>(bf16 v) { return __bfloat162float(v); }
 template <> __device__ __forceinline__ float src_to_f32<__half>(__half v) { return __half2float(v); }
 
-// dst[n, k] = src[k, n]; 32x32 tiles through shared memory so both sides are coalesced
+// dst[n * row_mul + row_add, k] = src[k, n] for k < K, n < N; src rows are ld_src apart (a
+// column slice of a wider matrix: tensor-parallel shards).  32x32 tiles through shared memory
+// so both sides are coalesced.  row_mul = 2: [gate | up] halves become interleaved rows (gate j
+// -> 2j, up j -> 2j + 1) so that a GEMM tile holds matching gate / up rows for the fused
+// SwiGLU epilogue.
 template <typename ST, typename DT>
-__global__ void transpose_convert_kernel(const ST* __restrict__ src, int K, int N,
-                                         DT* __restrict__ dst, int ld_dst, int glu_F) {
+__global__ void transpose_convert_kernel(const ST* __restrict__ src, size_t ld_src, int K, int N,
+                                         DT* __restrict__ dst, int ld_dst, int row_mul,
+                                         int row_add) {
   __shared__ float tile[32][33];
   const int n0 = blockIdx.x * 32, k0 = blockIdx.y * 32;
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
     int k = k0 + r, n = n0 + threadIdx.x;
-    tile[r][threadIdx.x] = (k < K && n < N) ? src_to_f32<ST>(src[(size_t)k * N + n]) : 0.f;
+    tile[r][threadIdx.x] = (k < K && n < N) ? src_to_f32<ST>(src[(size_t)k * ld_src + n]) : 0.f;
   }
   __syncthreads();
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
     int n = n0 + r, k = k0 + threadIdx.x;
-    // glu_F > 0: [gate | up] columns become interleaved rows (gate j -> 2j, up j -> 2j + 1) so
-    // that a GEMM tile holds matching gate / up rows for the fused SwiGLU epilogue
-    const int nd = (glu_F > 0) ? (n < glu_F ? 2 * n : 2 * (n - glu_F) + 1) : n;
-    if (n < N && k < K) dst[(size_t)nd * ld_dst + k] = from_f32<DT>(tile[threadIdx.x][r]);
+    if (n < N && k < K)
+      dst[((size_t)n * row_mul + row_add) * ld_dst + k] = from_f32<DT>(tile[threadIdx.x][r]);
   }
 }
 
-cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* src, int K, int N,
-                                     int ddt, void* dst, int ld_dst, int glu_F) {
+cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* src, size_t ld_src,
+                                     int K, int N, int ddt, void* dst, int ld_dst, int row_mul,
+                                     int row_add) {
+  if (K <= 0 || N <= 0) return cudaSuccess;
   dim3 grid((N + 31) / 32, (K + 31) / 32), block(32, 8);
-#define TC(ST, DT) \
-  transpose_convert_kernel<ST, DT><<<grid, block, 0, st>>>((const ST*)src, K, N, (DT*)dst, ld_dst, glu_F)
+#define TC(ST, DT)                                                                            \
+  transpose_convert_kernel<ST, DT><<<grid, block, 0, st>>>((const ST*)src, ld_src, K, N, (DT*)dst, \
+                                                           ld_dst, row_mul, row_add)
   if (ddt == DT_F32) {
     if (sdt_api == 0) TC(float, float);
     else if (sdt_api == 1) TC(bf16, float);

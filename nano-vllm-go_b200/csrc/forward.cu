@@ -19,7 +19,7 @@ namespace nvllm {
 // ------------------------------------------------------------------ workspace
 void free_workspace(nvllm_handle* h) {
   Workspace& w = h->ws;
-  void* ptrs[] = {w.x, w.xn, w.xn_f32, w.ws_a, w.ws_b, w.ws_c, w.q, w.attn_out, w.hbuf, w.xn_last,
+  void* ptrs[] = {w.tp_buf, w.x, w.xn, w.xn_f32, w.ws_a, w.ws_b, w.ws_c, w.q, w.attn_out, w.hbuf, w.xn_last,
                   w.logits_p, w.logits, w.attn_ws, w.attn_tickets, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
                   w.sort.counts, w.sort.offsets, w.sort.cursor, w.sort.sorted_pair, w.sort.pair_row,
                   w.sort.a_rows, w.sort.tile_expert, w.sort.tile_row0, w.sort.tile_rows,
@@ -73,9 +73,12 @@ int ensure_workspace(nvllm_handle* h, int T, int n) {
   WS(w.attn_out, (size_t)Tc * h->q_cols * asz);
   WS(w.hbuf, h->moe ? (size_t)Tc * h->topk * h->F * asz : (size_t)Tc * h->F * asz);
   WS(w.xn_last, nc * H * asz);
-  w.logits_p_floats = (size_t)std::max(nc, 64) * h->ldl;
+  if (h->tp > 1) WS(w.tp_buf, Tc * H * 4);
+  // tp > 1: this rank's LM-head slice is Vl wide and the gathered logits are [tp][n][Vl]
+  const size_t lcols = h->tp > 1 ? (size_t)h->Vl : (size_t)h->ldl;
+  w.logits_p_floats = (size_t)std::max(nc, 64) * lcols;
   WS(w.logits_p, w.logits_p_floats * 4);
-  WS(w.logits, (size_t)nc * h->ldl * 4);
+  WS(w.logits, (size_t)nc * lcols * h->tp * 4);
   w.attn_ws_floats = std::max((size_t)nc * h->nh * 32 * (h->hd + 2),
                               attn_decode_sk_ws_floats(h->hd, h->sm_count));
   WS(w.attn_ws, w.attn_ws_floats * 4);
@@ -255,6 +258,33 @@ static int run_norm(nvllm_handle* h, float* x, Pending* p1, Pending* p2, const f
   return NVLLM_OK;
 }
 
+// Tensor parallel: the pending row-parallel GEMM results are this rank's partial sums.  Fold
+// them (split-K slices, multipliers, rank-0 biases) into one [T, H] buffer, sum it over the
+// ranks and hand it to the norm as a single finished addend.
+static int tp_reduce_pending(nvllm_handle* h, Pending* p1, Pending* p2, int T) {
+  if (h->tp <= 1) return NVLLM_OK;
+  Pending* a = (p1 && p1->p) ? p1 : nullptr;
+  Pending* b = (p2 && p2->p) ? p2 : nullptr;
+  if (!a) { a = b; b = nullptr; }
+  if (!a) return NVLLM_OK;
+  Workspace& w = h->ws;
+  {
+    const double n = (double)T * h->H * 4;
+    ProfScope ps(h, NVLLM_K_COMM, n * (a->S + (b ? b->S : 0) + 1) + 2.0 * n, 0);
+    LAUNCH(h, launch_tp_partial(h->stream, T, h->H, a->p, a->S, a->stride, a->m, a->bias,
+                                b ? b->p : nullptr, b ? b->S : 0, b ? b->stride : 0,
+                                b ? b->m : 0.f, b ? b->bias : nullptr, w.tp_buf));
+    int rc = tp_all_reduce_f32(h, w.tp_buf, (size_t)T * h->H);
+    if (rc) return rc;
+    h->launches++;
+  }
+  if (p1) *p1 = Pending();
+  if (p2) *p2 = Pending();
+  Pending& o = p1 ? *p1 : *p2;
+  o.p = w.tp_buf; o.S = 1; o.stride = 0; o.m = 1.f; o.bias = nullptr;
+  return NVLLM_OK;
+}
+
 // ------------------------------------------------------------------ forward pass
 // Inputs are the device arrays of h->lay (already on the device).
 int forward_step(nvllm_handle* h) {
@@ -318,6 +348,7 @@ int forward_step(nvllm_handle* h) {
   for (int l = 0; l < h->L; l++) {
     const LayerW& lw = h->layers[l];
     // ---- attention sub-block
+    if ((rc = tp_reduce_pending(h, &p1, &p2, T))) return rc;
     if ((rc = run_norm(h, w.x, &p1, &p2, lw.attn_norm_w, lw.attn_norm_b, w.xn, nullptr, nullptr, T)))
       return rc;
     Pending qkv;
@@ -355,6 +386,7 @@ int forward_step(nvllm_handle* h) {
     if (h->parallel) {
       ffn_out = w.ws_c;  // FFN reads the same normed input (generic_model.go:395-418)
     } else {
+      if ((rc = tp_reduce_pending(h, &p1, nullptr, T))) return rc;
       if ((rc = run_norm(h, w.x, &p1, nullptr, lw.ffn_norm_w, lw.ffn_norm_b, w.xn,
                          h->moe ? w.xn_f32 : nullptr, nullptr, T)))
         return rc;
@@ -421,25 +453,49 @@ int forward_step(nvllm_handle* h) {
   }
   // final norm on the last token of each sequence only (the reference norms and projects all
   // T rows, generic_model.go:464-470, then keeps row T-1, :595-604)
+  if ((rc = tp_reduce_pending(h, &p1, &p2, T))) return rc;
   if ((rc = run_norm(h, w.x, &p1, &p2, h->lnf_w, h->lnf_b, w.xn_last, nullptr, d + L.last_row, n)))
     return rc;
   const float alpha = (c.logits_scaling != 0.f) ? 1.0f / c.logits_scaling : 1.f;
   Pending lg;
-  if ((rc = run_gemm(h, w.xn_last, H, h->lm_head, n, h->V, H, alpha, w.logits_p,
-                     w.logits_p_floats, h->ldl, &lg)))
-    return rc;
-  const float* logits = lg.p;
-  if (lg.S > 1) {
-    ProfScope ps(h, NVLLM_K_MISC, (double)n * h->ldl * 4 * (lg.S + 1), 0);
-    LAUNCH(h, launch_reduce_partials(st, lg.p, lg.S, lg.stride, (size_t)n * h->ldl, w.logits));
+  const float* logits = nullptr;
+  int vsplit = 0;
+  if (h->tp > 1) {
+    // vocabulary-parallel LM head: this rank's Vl_valid rows -> slot `rank` of [tp][n][Vl],
+    // then one all-gather; every rank samples the same token from the same gathered logits
+    const int Vl = h->Vl;
+    float* slot = w.logits + (size_t)h->rank * n * Vl;
+    if (h->Vl_valid > 0) {
+      if ((rc = run_gemm(h, w.xn_last, H, h->lm_head, n, h->Vl_valid, H, alpha, w.logits_p,
+                         w.logits_p_floats, Vl, &lg)))
+        return rc;
+      ProfScope ps(h, NVLLM_K_MISC, (double)n * Vl * 4 * (lg.S + 1), 0);
+      LAUNCH(h, launch_reduce_partials(st, lg.p, lg.S, lg.stride, (size_t)n * Vl, slot));
+    }
+    {
+      ProfScope ps(h, NVLLM_K_COMM, (double)n * Vl * 4 * h->tp, 0);
+      if ((rc = tp_all_gather_f32(h, w.logits, (size_t)n * Vl))) return rc;
+      h->launches++;
+    }
     logits = w.logits;
+    vsplit = Vl;
+  } else {
+    if ((rc = run_gemm(h, w.xn_last, H, h->lm_head, n, h->V, H, alpha, w.logits_p,
+                       w.logits_p_floats, h->ldl, &lg)))
+      return rc;
+    logits = lg.p;
+    if (lg.S > 1) {
+      ProfScope ps(h, NVLLM_K_MISC, (double)n * h->ldl * 4 * (lg.S + 1), 0);
+      LAUNCH(h, launch_reduce_partials(st, lg.p, lg.S, lg.stride, (size_t)n * h->ldl, w.logits));
+      logits = w.logits;
+    }
   }
   const float* d_temp = reinterpret_cast<const float*>(d + L.temperature);
   const float* d_uni = reinterpret_cast<const float*>(d + L.uniforms);
   {
     ProfScope ps(h, NVLLM_K_SAMPLE, (double)n * h->V * 4, 0);
     LAUNCH(h, launch_sample(st, logits, h->ldl, h->V, n, d_temp, d_uni, w.out_tokens, w.amax,
-                            w.amax_ticket));
+                            w.amax_ticket, vsplit));
   }
   h->ws.logits_final = logits;
   return NVLLM_OK;

@@ -56,7 +56,8 @@ struct Workspace {
   void* hbuf = nullptr;      // [T, F] or [T k, I]
   void* xn_last = nullptr;   // [n, H]
   float* logits_p = nullptr; // [S][n][ldl]
-  float* logits = nullptr;   // [n][ldl]
+  float* logits = nullptr;   // [n][ldl]  (tp > 1: [tp][n][Vl], rank-major slices)
+  float* tp_buf = nullptr;   // [T, H] fp32 partial sums handed to the all-reduce (tp > 1)
   const float* logits_final = nullptr;  // where the last step's summed logits live
   int n_cap_out = 0;
   size_t logits_p_floats = 0;
@@ -91,6 +92,13 @@ struct nvllm_handle {
   int q_cols = 0, kv_cols = 0, qkv_cols = 0, w1_cols = 0, ldl = 0;
   bool swiglu = false, moe = false, parallel = false, use_rope = false;
   float attn_scale = 0.f;
+  // tensor parallel (tp.cu): nh / nkv / F / q_cols / ... above are this rank's LOCAL extents;
+  // *_g are the model's.  Heads are padded to a multiple of tp (Falcon 71 -> 72, zero weights).
+  int tp = 1, rank = 0;
+  int nh_g = 0, nkv_g = 0, F_g = 0;
+  int Vl = 0;        // LM-head rows per rank (slot width of the gathered logits), multiple of 8
+  int Vl_valid = 0;  // rows of this rank's slice that exist (last rank may be short)
+  void* nccl = nullptr;  // ncclComm_t
   // weights
   void *wte = nullptr, *wpe = nullptr, *lm_head = nullptr;
   bool lm_head_owned = false;
@@ -149,6 +157,13 @@ int forward_step(nvllm_handle* h);  // runs h->lay
 int prof_collect(nvllm_handle* h);
 
 int set_err(nvllm_handle* h, int code, const char* fmt, ...);
+
+// tp.cu — tensor-parallel group over NCCL (loaded with dlopen: no link-time dependency)
+int tp_unique_id(uint8_t out_id[128]);
+int tp_init(nvllm_handle* h, const uint8_t* id);  // ncclCommInitRank(tp, id, rank)
+void tp_destroy(nvllm_handle* h);
+int tp_all_reduce_f32(nvllm_handle* h, float* buf, size_t count);           // in place, sum
+int tp_all_gather_f32(nvllm_handle* h, float* buf, size_t count_per_rank);  // in place, slot = rank
 
 #define NV_CHECK(h, expr)                                                                   \
   do {                                                                                      \

@@ -69,9 +69,12 @@ cudaError_t launch_rope_kv(cudaStream_t st, int qdt, int kvdt, int T, int nh, in
 // logits [n, ldl] fp32 (first V columns valid).  temperature[i] <= 0: first-max argmax
 // (cmd/ask/main.go:389-402).  Otherwise softmax(l/T) and inverse-CDF draw with uniforms[i]
 // (sampling.go:70-74,105-128,196-217).
+// vsplit > 0: the logits are vocabulary slices gathered rank-major, [V / vsplit][n][vsplit]
+// (tensor-parallel LM head); logit v of row s lives at (v / vsplit) * n * vsplit + s * vsplit +
+// v % vsplit.  vsplit = 0: plain [n, ldl].
 cudaError_t launch_sample(cudaStream_t st, const float* logits, int ldl, int V, int n,
                           const float* temperature, const float* uniforms, int* out_tokens,
-                          unsigned long long* amax = nullptr, int* ticket = nullptr);
+                          unsigned long long* amax = nullptr, int* ticket = nullptr, int vsplit = 0);
 
 // advance device-resident decode state by one token (nvllm_run_resident)
 cudaError_t launch_advance(cudaStream_t st, int n, const int* sampled, int* tokens, int* positions,
@@ -86,9 +89,11 @@ cudaError_t launch_make_decode_state(cudaStream_t st, int n, int mb, const int* 
                                      int* cu_q, int* seq_start, int* seq_len, int* last_row, int* bt,
                                      int* temp, int* uni);
 
-// dst[N,K] (dtype ddt) = transpose(src[K,N] fp32|bf16|f16)   — weight repack at finalize
-cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* src, int K, int N,
-                                     int ddt, void* dst, int ld_dst, int glu_F = 0);
+// dst[n*row_mul + row_add, k] (dtype ddt) = src[k, n] (fp32|bf16|f16, rows ld_src apart) for
+// k < K, n < N — weight repack (and tensor-parallel column / row slicing) at load
+cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* src, size_t ld_src,
+                                     int K, int N, int ddt, void* dst, int ld_dst, int row_mul = 1,
+                                     int row_add = 0);
 // dst (dtype ddt) = convert(src)  flat copy
 cudaError_t launch_convert(cudaStream_t st, int sdt_api, const void* src, size_t n, int ddt,
                            void* dst);
@@ -97,6 +102,13 @@ cudaError_t launch_reduce_partials(cudaStream_t st, const float* p, int S, size_
                                    float* out);
 // a bigger-than-L2 write, for cold-cache timing
 cudaError_t launch_fill(cudaStream_t st, float* p, size_t n, float v);
+
+// ---------------------------------------------------------------- tp.cu
+// out[t,:] = m1 * (sum_s p1 + bias1) + m2 * (sum_s p2 + bias2): a rank's share of a residual
+// update, summed over ranks by the all-reduce that follows (p2 may be null)
+cudaError_t launch_tp_partial(cudaStream_t st, int T, int H, const float* p1, int S1, size_t stride1,
+                              float m1, const float* bias1, const float* p2, int S2, size_t stride2,
+                              float m2, const float* bias2, float* out);
 
 // ---------------------------------------------------------------- gemm_simt.cu
 struct GemmArgs {

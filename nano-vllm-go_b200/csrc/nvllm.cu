@@ -8,6 +8,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
+
 #include "common.cuh"
 #include "handle.h"
 
@@ -104,10 +106,20 @@ int nvllm_create(const nvllm_config* c, const uint8_t* tp_id, nvllm_handle** out
       return bad("num_experts_per_tok");
     if (c->activation_type != NVLLM_ACT_SWIGLU) return bad("MoE experts are GLU (moe.go:203-212)");
   }
-  if (c->tp_size != 1 && c->tp_size != 0)
-    return bad("tensor parallel handles are created through nvllm_create with tp_size>1 only "
-               "for the parallel-block MQA family; not available in this build");
-  (void)tp_id;
+  const int tp = c->tp_size > 1 ? c->tp_size : 1;
+  const int rank = tp > 1 ? c->tp_rank : 0;
+  int nh_pad = c->num_heads;
+  if (tp > 1) {
+    if (!tp_id) return bad("tp_size > 1 needs the NCCL unique id of the group (nvllm_tp_unique_id)");
+    if (rank < 0 || rank >= tp) return bad("tp_rank outside [0, tp_size)");
+    if (c->use_moe) return bad("tensor parallelism is not offered for MoE models");
+    if (nkv == 1) {
+      nh_pad = (c->num_heads + tp - 1) / tp * tp;  // Falcon: 71 -> 72 zero-weight heads
+    } else if (c->num_heads % tp || nkv % tp) {
+      return bad("num_heads and num_kv_heads must be multiples of tp_size");
+    }
+    if (c->ffn_dim % tp || (c->ffn_dim / tp) % 8) return bad("ffn_dim / tp_size must be a multiple of 8");
+  }
 
   cudaError_t e = cudaSetDevice(c->device);
   if (e != cudaSuccess)
@@ -130,18 +142,23 @@ int nvllm_create(const nvllm_config* c, const uint8_t* tp_id, nvllm_handle** out
   if (h->cfg.num_kv_blocks <= 0) h->cfg.num_kv_blocks = 1024;  // scheduler.go:17-21
   if (h->cfg.max_num_seqs <= 0) h->cfg.max_num_seqs = 512;
   if (h->cfg.max_batched_tokens <= 0) h->cfg.max_batched_tokens = 16384;
-  h->cfg.tp_size = 1;
-  h->cfg.tp_rank = 0;
+  h->cfg.tp_size = tp;
+  h->cfg.tp_rank = rank;
+  h->tp = tp;
+  h->rank = rank;
   h->dev = c->device;
   h->sm_count = prop.multiProcessorCount;
   h->wdt = h->adt = h->kvdt = (c->precision == NVLLM_PREC_BF16) ? DT_BF16 : DT_F32;
   h->H = c->hidden;
   h->V = c->vocab_size;
   h->L = c->num_layers;
-  h->nh = c->num_heads;
-  h->nkv = nkv;
+  h->nh_g = c->num_heads;
+  h->nkv_g = nkv;
+  h->F_g = c->ffn_dim;
+  h->nh = nh_pad / tp;
+  h->nkv = (nkv == 1) ? 1 : nkv / tp;
   h->hd = c->head_dim;
-  h->F = c->ffn_dim;
+  h->F = c->ffn_dim / tp;
   h->moe = c->use_moe != 0;
   h->E = h->moe ? c->num_experts : 0;
   h->topk = h->moe ? c->num_experts_per_tok : 0;
@@ -152,6 +169,8 @@ int nvllm_create(const nvllm_config* c, const uint8_t* tp_id, nvllm_handle** out
   h->qkv_cols = h->q_cols + 2 * h->kv_cols;
   h->w1_cols = h->swiglu ? 2 * h->F : h->F;
   h->ldl = (int)round_up(h->V, 8);
+  h->Vl = tp > 1 ? (int)round_up((h->V + tp - 1) / tp, 8) : h->ldl;
+  h->Vl_valid = tp > 1 ? std::max(0, std::min(h->Vl, h->V - rank * h->Vl)) : h->V;
   // RoPE: always for MQA (mqa.go:65-67), for GQA when PositionRoPE, never for MHA
   h->use_rope = (c->attention_type == NVLLM_ATTN_MQA) ||
                 (c->attention_type == NVLLM_ATTN_GQA && c->position_type == NVLLM_POS_ROPE);
@@ -179,8 +198,8 @@ int nvllm_create(const nvllm_config* c, const uint8_t* tp_id, nvllm_handle** out
   // ---- weights (device layouts; see handle.h) ----
   uint64_t* wb = &h->weight_bytes;
   const int H = h->H, wdt = h->wdt;
-#define A_DT(ptr, count)                                                             \
-  if ((e = dev_alloc_dt(h, (void**)&(ptr), (size_t)(count), wdt, wb)) != cudaSuccess) \
+#define A_DT(ptr, count)                                                                       \
+  if ((e = dev_alloc_dt(h, (void**)&(ptr), (size_t)(count), wdt, wb, tp > 1)) != cudaSuccess) \
     return fail(e, "cudaMalloc(weights)");
 #define A_F32(ptr, count, zero)                                                         \
   if ((e = dev_alloc<float>(h, &(ptr), (size_t)(count), wb, zero)) != cudaSuccess)      \
@@ -190,9 +209,10 @@ int nvllm_create(const nvllm_config* c, const uint8_t* tp_id, nvllm_handle** out
   A_F32(h->lnf_w, H, false);
   A_F32(h->lnf_b, H, false);
   if (c->tied_embedding) {
-    h->lm_head = h->wte;  // [V, H] is already the [out, in] layout the GEMMs want
+    // [V, H] is already the [out, in] layout the GEMMs want; a TP rank reads its row slice
+    h->lm_head = (char*)h->wte + (size_t)rank * (tp > 1 ? h->Vl : 0) * H * dt_size(wdt);
   } else {
-    A_DT(h->lm_head, (size_t)h->V * H);
+    A_DT(h->lm_head, (size_t)(tp > 1 ? h->Vl : h->V) * H);
     h->lm_head_owned = true;
   }
   for (int l = 0; l < h->L; l++) {
@@ -218,6 +238,14 @@ int nvllm_create(const nvllm_config* c, const uint8_t* tp_id, nvllm_handle** out
   }
 #undef A_DT
 #undef A_F32
+  if (tp > 1) {
+    int rc = tp_init(h, tp_id);
+    if (rc) {
+      g_create_error = h->err;
+      nvllm_destroy(h);
+      return rc;
+    }
+  }
   *out = h;
   return NVLLM_OK;
 }
@@ -254,6 +282,7 @@ int nvllm_destroy(nvllm_handle* h) {
   if (h->h_out) cudaFreeHost(h->h_out);
   if (h->h_logits) cudaFreeHost(h->h_logits);
   nvllm::free_workspace(h);
+  nvllm::tp_destroy(h);
   if (h->ev0) cudaEventDestroy(h->ev0);
   if (h->ev1) cudaEventDestroy(h->ev1);
   if (h->stream) cudaStreamDestroy(h->stream);
@@ -296,8 +325,8 @@ int nvllm_set_graphs(nvllm_handle* h, int enabled) {
 }
 
 int nvllm_tp_unique_id(uint8_t out_id[128]) {
-  memset(out_id, 0, 128);
-  return set_err(nullptr, NVLLM_ERR_NCCL, "tensor parallelism is not available in this build");
+  if (!out_id) return set_err(nullptr, NVLLM_ERR_INVALID, "null argument");
+  return tp_unique_id(out_id);
 }
 
 }  // extern "C"

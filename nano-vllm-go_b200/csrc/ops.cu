@@ -68,7 +68,7 @@ extern "C" int nvllm_op_matmul(int device, int prec, int kernel, int M, int N, i
   OP_CHECK(cudaMemcpyAsync(dA32, A, (size_t)M * K * 4, cudaMemcpyHostToDevice, s.st));
   OP_CHECK(cudaMemcpyAsync(dW32, W, (size_t)K * N * 4, cudaMemcpyHostToDevice, s.st));
   OP_CHECK(launch_convert(s.st, NVLLM_DT_F32, dA32, (size_t)M * K, dt, dA));
-  OP_CHECK(launch_transpose_convert(s.st, NVLLM_DT_F32, dW32, K, N, dt, dWt, K));
+  OP_CHECK(launch_transpose_convert(s.st, NVLLM_DT_F32, dW32, (size_t)N, K, N, dt, dWt, K));
   int S = 1;
   auto launch = [&]() -> cudaError_t {
     if (kernel == 3) {

@@ -193,9 +193,20 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
   uint64_t d2h = (uint64_t)n * 4;
   if (out_logits) {
     // rows are ldl apart on the device; copy them packed [n, V]
-    NV_CHECK(h, cudaMemcpy2DAsync(out_logits, (size_t)h->V * 4, h->ws.logits_final,
-                                  (size_t)h->ldl * 4, (size_t)h->V * 4, n, cudaMemcpyDeviceToHost,
-                                  st));
+    if (h->tp > 1) {  // gathered rank-major vocabulary slices [tp][n][Vl]
+      for (int r = 0; r < h->tp; r++) {
+        const int c0 = r * h->Vl, cn = std::min(h->Vl, h->V - c0);
+        if (cn <= 0) break;
+        NV_CHECK(h, cudaMemcpy2DAsync(out_logits + c0, (size_t)h->V * 4,
+                                      h->ws.logits_final + (size_t)r * n * h->Vl,
+                                      (size_t)h->Vl * 4, (size_t)cn * 4, n,
+                                      cudaMemcpyDeviceToHost, st));
+      }
+    } else {
+      NV_CHECK(h, cudaMemcpy2DAsync(out_logits, (size_t)h->V * 4, h->ws.logits_final,
+                                    (size_t)h->ldl * 4, (size_t)h->V * 4, n,
+                                    cudaMemcpyDeviceToHost, st));
+    }
     d2h += (uint64_t)n * h->V * 4;
   }
   cudaError_t e = cudaStreamSynchronize(st);

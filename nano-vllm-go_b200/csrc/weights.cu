@@ -9,6 +9,7 @@
 // transpose run on the device; the host buffer is only read during the call.
 #include <math.h>
 
+#include <algorithm>
 #include <vector>
 
 #include "common.cuh"
@@ -29,6 +30,17 @@ static int stage_in(nvllm_handle* h, const void* host, size_t bytes, void** dev)
   return NVLLM_OK;
 }
 
+// One device-side repack of (a slice of) the staged tensor.
+struct Repack {
+  bool transpose;   // true: dst[n*row_mul+row_add, k] = src[k, n]; false: flat convert
+  bool to_f32;      // destination dtype fp32 (norms, biases, router) instead of the weight dtype
+  size_t src_off;   // elements into the staged tensor
+  size_t ld_src;    // transpose: source row stride
+  int K, N;         // transpose: extent taken; flat: N = element count
+  void* dst;
+  int ld_dst, row_mul, row_add;
+};
+
 extern "C" int nvllm_set_weight(nvllm_handle* h, int id, int layer, int dtype, const void* host,
                                 uint64_t numel) {
   if (!h) return NVLLM_ERR_INVALID;
@@ -36,99 +48,145 @@ extern "C" int nvllm_set_weight(nvllm_handle* h, int id, int layer, int dtype, c
   if (dtype < 0 || dtype > 2) return set_err(h, NVLLM_ERR_INVALID, "bad dtype %d", dtype);
   if (h->finalized) return set_err(h, NVLLM_ERR_STATE, "set_weight after finalize");
   NV_CHECK(h, cudaSetDevice(h->dev));
-  const int H = h->H, V = h->V, F = h->F;
+  const int H = h->H, V = h->V;
   const bool model_level = id < 16;
   if (!model_level && (layer < 0 || layer >= h->L))
     return set_err(h, NVLLM_ERR_INVALID, "layer %d out of range for weight %d", layer, id);
   if (id < 0 || id >= 64) return set_err(h, NVLLM_ERR_INVALID, "unknown weight id %d", id);
   LayerW* w = model_level ? nullptr : &h->layers[layer];
-
-  // what to do with this tensor
-  enum { FLAT_DT, FLAT_F32, TRANSPOSE_DT, TRANSPOSE_F32 } mode = FLAT_F32;
-  int glu_F = 0;  // > 0: interleave the [gate | up] halves row by row
-  void* dst = nullptr;
-  size_t expect = 0;
-  int K = 0, N = 0, ld = 0;  // transpose: src [K, N] -> dst [N, ld]
   const bool mqa = h->cfg.attention_type == NVLLM_ATTN_MQA;
+  const size_t wsz = dt_size(h->wdt);
+
+  // The caller always hands the FULL tensor (reference post-load layout); with tp > 1 this rank
+  // keeps its slice: Q / K / V / W1 columns and O / W2 rows by head / FFN unit (Megatron
+  // column -> row split), LM head by vocabulary rows.  Padding heads (Falcon 71 -> 72) keep the
+  // zeros their buffers were allocated with.
+  const int rank = h->rank;
+  const int hd = h->hd;
+  const int qg = h->nh_g * hd;                       // real global Q columns
+  const int q0 = rank * h->q_cols;                   // this rank's first Q column
+  const int qn = std::max(0, std::min(h->q_cols, qg - q0));  // real (non-padding) columns here
+  const int kvg = h->nkv_g * hd;
+  const bool kv_split = h->nkv_g > 1 && h->tp > 1;   // MQA's single KV head is replicated
+  const int kv0 = kv_split ? rank * h->kv_cols : 0;
+  const int Fg = h->F_g, Fl = h->F, f0 = rank * h->F;
+  Repack ops[2];
+  int n_ops = 1;
+  size_t expect = 0;
+  Repack& r = ops[0];
+  r = Repack{false, true, 0, 0, 0, 0, nullptr, 0, 1, 0};
+  auto flat_f32 = [&](float* dst, size_t off, size_t cnt, size_t full) {
+    r.dst = dst; r.src_off = off; r.N = (int)cnt; expect = full;
+  };
+  auto tr = [&](Repack& o, void* dst, size_t off, size_t ld_src, int K, int N, int ld_dst,
+                int mul = 1, int add = 0) {
+    o = Repack{true, false, off, ld_src, K, N, dst, ld_dst, mul, add};
+  };
   switch (id) {
-    case NVLLM_W_TOKEN_EMBEDDING: mode = FLAT_DT; dst = h->wte; expect = (size_t)V * H; break;
+    case NVLLM_W_TOKEN_EMBEDDING:
+      r.to_f32 = false; r.dst = h->wte; r.N = 0; expect = (size_t)V * H;
+      r.N = -1;  // whole tensor (count may exceed int)
+      break;
     case NVLLM_W_POS_EMBEDDING:
       if (!h->wpe) return set_err(h, NVLLM_ERR_INVALID, "model has no learned positions");
-      mode = FLAT_DT; dst = h->wpe; expect = (size_t)h->cfg.max_seq_len * H; break;
-    case NVLLM_W_FINAL_NORM_W: dst = h->lnf_w; expect = H; break;
-    case NVLLM_W_FINAL_NORM_B: dst = h->lnf_b; expect = H; break;
+      r.to_f32 = false; r.dst = h->wpe; r.N = -1; expect = (size_t)h->cfg.max_seq_len * H; break;
+    case NVLLM_W_FINAL_NORM_W: flat_f32(h->lnf_w, 0, H, H); break;
+    case NVLLM_W_FINAL_NORM_B: flat_f32(h->lnf_b, 0, H, H); break;
     case NVLLM_W_LM_HEAD:
       if (!h->lm_head_owned)
         return set_err(h, NVLLM_ERR_INVALID, "tied_embedding is set: LM head is the embedding");
-      mode = TRANSPOSE_DT; dst = h->lm_head; K = H; N = V; ld = H; expect = (size_t)H * V; break;
-    case NVLLM_W_ATTN_NORM_W: dst = w->attn_norm_w; expect = H; break;
-    case NVLLM_W_ATTN_NORM_B: dst = w->attn_norm_b; expect = H; break;
-    case NVLLM_W_FFN_NORM_W: dst = w->ffn_norm_w; expect = H; break;
-    case NVLLM_W_FFN_NORM_B: dst = w->ffn_norm_b; expect = H; break;
+      expect = (size_t)H * V;
+      tr(r, h->lm_head, (size_t)rank * h->Vl * (h->tp > 1), V, H, h->Vl_valid, H);
+      break;
+    case NVLLM_W_ATTN_NORM_W: flat_f32(w->attn_norm_w, 0, H, H); break;
+    case NVLLM_W_ATTN_NORM_B: flat_f32(w->attn_norm_b, 0, H, H); break;
+    case NVLLM_W_FFN_NORM_W: flat_f32(w->ffn_norm_w, 0, H, H); break;
+    case NVLLM_W_FFN_NORM_B: flat_f32(w->ffn_norm_b, 0, H, H); break;
     case NVLLM_W_Q:
-      mode = TRANSPOSE_DT; dst = w->wqkv; K = H; N = h->q_cols; ld = H; expect = (size_t)H * N; break;
+      expect = (size_t)H * qg;
+      tr(r, w->wqkv, q0, qg, H, qn, H);
+      break;
     case NVLLM_W_K:
     case NVLLM_W_V: {
       if (mqa) return set_err(h, NVLLM_ERR_INVALID, "MQA takes the fused NVLLM_W_KV");
-      mode = TRANSPOSE_DT; K = H; N = h->kv_cols; ld = H; expect = (size_t)H * N;
+      expect = (size_t)H * kvg;
       size_t row0 = h->q_cols + (id == NVLLM_W_V ? h->kv_cols : 0);
-      dst = (char*)w->wqkv + row0 * H * dt_size(h->wdt);
+      tr(r, (char*)w->wqkv + row0 * H * wsz, kv0, kvg, H, h->kv_cols, H);
       break;
     }
     case NVLLM_W_KV:
       if (!mqa) return set_err(h, NVLLM_ERR_INVALID, "NVLLM_W_KV is MQA only");
-      mode = TRANSPOSE_DT; K = H; N = 2 * h->hd; ld = H; expect = (size_t)H * N;
-      dst = (char*)w->wqkv + (size_t)h->q_cols * H * dt_size(h->wdt);
+      expect = (size_t)H * 2 * hd;
+      tr(r, (char*)w->wqkv + (size_t)h->q_cols * H * wsz, 0, 2 * hd, H, 2 * hd, H);
       break;
     case NVLLM_W_O:
-      mode = TRANSPOSE_DT; dst = w->wo; K = h->q_cols; N = H; ld = h->q_cols;
-      expect = (size_t)h->q_cols * H; break;
-    case NVLLM_W_Q_BIAS: dst = w->bqkv; expect = h->q_cols; w->has_bq = true; break;
-    case NVLLM_W_K_BIAS: dst = w->bqkv + h->q_cols; expect = h->kv_cols; w->has_bk = true; break;
+      expect = (size_t)qg * H;
+      tr(r, w->wo, (size_t)q0 * H, H, qn, H, h->q_cols);
+      break;
+    case NVLLM_W_Q_BIAS: flat_f32(w->bqkv, q0, qn, qg); w->has_bq = true; break;
+    case NVLLM_W_K_BIAS: flat_f32(w->bqkv + h->q_cols, kv0, h->kv_cols, kvg); w->has_bk = true; break;
     case NVLLM_W_V_BIAS:
-      dst = w->bqkv + h->q_cols + h->kv_cols; expect = h->kv_cols; w->has_bv = true; break;
-    case NVLLM_W_O_BIAS: dst = w->bo; expect = H; break;
+      flat_f32(w->bqkv + h->q_cols + h->kv_cols, kv0, h->kv_cols, kvg); w->has_bv = true; break;
+    case NVLLM_W_O_BIAS: flat_f32(w->bo, 0, H, H); break;
     case NVLLM_W_FFN_W1:
       if (h->moe) return set_err(h, NVLLM_ERR_INVALID, "MoE model takes MOE_INPUT/MOE_OUTPUT");
-      mode = TRANSPOSE_DT; dst = w->w1; K = H; N = h->w1_cols; ld = H; expect = (size_t)H * N;
-      if (h->swiglu) glu_F = F;
+      if (h->swiglu) {  // [gate | up] columns -> interleaved rows (gate j -> 2j, up j -> 2j + 1)
+        expect = (size_t)H * 2 * Fg;
+        tr(ops[0], w->w1, f0, 2 * (size_t)Fg, H, Fl, H, 2, 0);
+        tr(ops[1], w->w1, (size_t)Fg + f0, 2 * (size_t)Fg, H, Fl, H, 2, 1);
+        n_ops = 2;
+      } else {
+        expect = (size_t)H * Fg;
+        tr(r, w->w1, f0, Fg, H, Fl, H);
+      }
       break;
     case NVLLM_W_FFN_B1:
       if (h->moe || h->swiglu)  // transformer.go:50-66: the SwiGLU branch never adds B1
         return set_err(h, NVLLM_ERR_INVALID, "FFN_B1 only exists on the GELU branch");
-      dst = w->b1; expect = F; break;
+      flat_f32(w->b1, f0, Fl, Fg); break;
     case NVLLM_W_FFN_W2:
       if (h->moe) return set_err(h, NVLLM_ERR_INVALID, "MoE model takes MOE_INPUT/MOE_OUTPUT");
-      mode = TRANSPOSE_DT; dst = w->w2; K = F; N = H; ld = F; expect = (size_t)F * H; break;
+      expect = (size_t)Fg * H;
+      tr(r, w->w2, (size_t)f0 * H, H, Fl, H, Fl);
+      break;
     case NVLLM_W_FFN_B2:
       if (h->moe) return set_err(h, NVLLM_ERR_INVALID, "MoE layers have no B2");
-      dst = w->b2; expect = H; break;
+      flat_f32(w->b2, 0, H, H); break;
     case NVLLM_W_MOE_ROUTER:
       if (!h->moe) return set_err(h, NVLLM_ERR_INVALID, "not a MoE model");
-      mode = TRANSPOSE_F32; dst = w->router; K = H; N = h->E; ld = H; expect = (size_t)H * N; break;
+      expect = (size_t)H * h->E;
+      tr(r, w->router, 0, h->E, H, h->E, H);
+      r.to_f32 = true;
+      break;
     case NVLLM_W_MOE_INPUT:
       if (!h->moe) return set_err(h, NVLLM_ERR_INVALID, "not a MoE model");
-      mode = FLAT_DT; dst = w->moe_in; expect = (size_t)h->E * 2 * F * H; break;
+      r.to_f32 = false; r.dst = w->moe_in; r.N = -1; expect = (size_t)h->E * 2 * Fg * H; break;
     case NVLLM_W_MOE_OUTPUT:
       if (!h->moe) return set_err(h, NVLLM_ERR_INVALID, "not a MoE model");
-      mode = FLAT_DT; dst = w->moe_out; expect = (size_t)h->E * H * F; break;
+      r.to_f32 = false; r.dst = w->moe_out; r.N = -1; expect = (size_t)h->E * H * Fg; break;
     default: return set_err(h, NVLLM_ERR_INVALID, "unknown weight id %d", id);
   }
   if (numel != expect)
     return set_err(h, NVLLM_ERR_INVALID, "weight %d (layer %d): numel %llu, expected %llu", id,
                    layer, (unsigned long long)numel, (unsigned long long)expect);
   void* stage = nullptr;
-  int rc = stage_in(h, host, numel * api_dt_size(dtype), &stage);
+  const size_t ssz = api_dt_size(dtype);
+  int rc = stage_in(h, host, numel * ssz, &stage);
   if (rc) return rc;
-  cudaError_t e;
-  switch (mode) {
-    case FLAT_DT: e = launch_convert(h->stream, dtype, stage, numel, h->wdt, dst); break;
-    case FLAT_F32: e = launch_convert(h->stream, dtype, stage, numel, DT_F32, dst); break;
-    case TRANSPOSE_DT:
-      e = launch_transpose_convert(h->stream, dtype, stage, K, N, h->wdt, dst, ld, glu_F);
-      break;
-    default: e = launch_transpose_convert(h->stream, dtype, stage, K, N, DT_F32, dst, ld); break;
+  cudaError_t e = cudaSuccess;
+  for (int i = 0; i < n_ops && e == cudaSuccess; i++) {
+    const Repack& o = ops[i];
+    const void* src = (const char*)stage + o.src_off * ssz;
+    const int ddt = o.to_f32 ? DT_F32 : h->wdt;
+    if (o.transpose)
+      e = launch_transpose_convert(h->stream, dtype, src, o.ld_src, o.K, o.N, ddt, o.dst, o.ld_dst,
+                                   o.row_mul, o.row_add);
+    else
+      e = launch_convert(h->stream, dtype, src, o.N < 0 ? (size_t)numel : (size_t)o.N, ddt, o.dst);
   }
+  // row-parallel output biases are added once: ranks other than 0 hold zeros
+  if (e == cudaSuccess && h->rank != 0 && (id == NVLLM_W_O_BIAS || id == NVLLM_W_FFN_B2))
+    e = cudaMemsetAsync(ops[0].dst, 0, (size_t)H * 4, h->stream);
   if (e == cudaSuccess) e = cudaStreamSynchronize(h->stream);  // host buffer is free on return
   cudaFree(stage);
   if (e != cudaSuccess)

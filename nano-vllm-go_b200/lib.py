@@ -42,7 +42,7 @@ class ProfileEntry(ctypes.Structure):
 
 
 KERNEL_CLASSES = ["embed", "norm", "gemm_tc5", "gemv", "gemm_simt", "rope_kv", "attn_prefill",
-                  "attn_decode", "act", "moe_route", "moe_gemm", "moe_misc", "sample", "misc"]
+                  "attn_decode", "act", "moe_route", "moe_gemm", "moe_misc", "sample", "misc", "comm"]
 
 
 class NvllmError(RuntimeError):
@@ -133,6 +133,14 @@ def _fp(a):
 
 def _ip(a):
     return a.ctypes.data_as(_i32p) if a is not None else None
+
+
+def tp_unique_id() -> bytes:
+    """128-byte NCCL unique id for a tensor-parallel group (make it on one rank, hand the same
+    bytes to every rank's nvllm_create)."""
+    buf = (ctypes.c_uint8 * 128)()
+    check(load().nvllm_tp_unique_id(buf))
+    return bytes(buf)
 
 
 def device_info(device: int = 0) -> dict:

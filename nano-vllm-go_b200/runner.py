@@ -36,20 +36,31 @@ class CudaModelRunner:
     def __init__(self, cfg: C.ModelConfig, weights: Iterable[Tuple[int, int, np.ndarray]],
                  precision: int = C.PREC_BF16, num_kv_blocks: int = -1, device: int = 0,
                  max_num_seqs: int = 512, max_batched_tokens: int = 16384,
-                 weight_dtype: Optional[int] = None):
+                 weight_dtype: Optional[int] = None, tp_size: int = 1, tp_rank: int = 0,
+                 tp_id: Optional[bytes] = None):
         """Replaces NewTensorModelRunner(modelDir) (tensor_model_runner.go:21-32): instead of a
         directory, takes the tensors in the layouts LoadModel leaves them in
         (generic_loader.go:184-265), as (weight_id, layer, ndarray) triples.
 
         weight_dtype: dtype the host buffers are handed over in (DT_F32 default; DT_BF16 sends
-        bf16 bit patterns, halving the upload)."""
+        bf16 bit patterns, halving the upload).
+
+        tp_size > 1: this runner is rank tp_rank of a tensor-parallel group (one runner per GPU,
+        every rank handed the same FULL tensors and the same Run calls); tp_id is the 128-byte
+        group id from tp_unique_id(), created on one rank and distributed by the host code."""
         self._lib = L.load()
         self.cfg = cfg
         self.precision = precision
         self._h = ctypes.c_void_p()
         cc = cfg.to_c(precision, num_kv_blocks=num_kv_blocks, max_num_seqs=max_num_seqs,
-                      max_batched_tokens=max_batched_tokens, device=device)
-        L.check(self._lib.nvllm_create(ctypes.byref(cc), None, ctypes.byref(self._h)))
+                      max_batched_tokens=max_batched_tokens, device=device, tp_size=tp_size,
+                      tp_rank=tp_rank)
+        idbuf = None
+        if tp_size > 1:
+            if tp_id is None or len(tp_id) != 128:
+                raise ValueError("tp_size > 1 needs the 128-byte tp_id of the group")
+            idbuf = (ctypes.c_uint8 * 128).from_buffer_copy(tp_id)
+        L.check(self._lib.nvllm_create(ctypes.byref(cc), idbuf, ctypes.byref(self._h)))
         try:
             for wid, layer, arr in weights:
                 self.set_weight(wid, layer, arr, weight_dtype)
