@@ -708,18 +708,32 @@ cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* s
   return cudaGetLastError();
 }
 
+// glu_I > 0: src is a stack of [2 glu_I, cols] matrices whose first glu_I rows are GLU gates and
+// last glu_I rows the matching ups (HF MoE input_linear, generic_loader.go:578-586); dst
+// interleaves them (gate j -> row 2j, up j -> row 2j + 1) so that a 128-row weight tile holds
+// complete gate / up pairs for the fused SwiGLU epilogue.
 template <typename ST, typename DT>
-__global__ void convert_kernel(const ST* __restrict__ src, size_t n, DT* __restrict__ dst) {
+__global__ void convert_kernel(const ST* __restrict__ src, size_t n, DT* __restrict__ dst, int glu_I,
+                               int cols) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
-       i += (size_t)gridDim.x * blockDim.x)
-    dst[i] = from_f32<DT>(src_to_f32<ST>(src[i]));
+       i += (size_t)gridDim.x * blockDim.x) {
+    size_t o = i;
+    if (glu_I > 0) {
+      const size_t row = i / cols, c = i - row * cols;
+      const size_t e = row / (2 * (size_t)glu_I), q = row - e * 2 * glu_I;
+      const size_t g = q / glu_I, j = q - g * glu_I;
+      o = (e * 2 * glu_I + 2 * j + g) * cols + c;
+    }
+    dst[o] = from_f32<DT>(src_to_f32<ST>(src[i]));
+  }
 }
 
 cudaError_t launch_convert(cudaStream_t st, int sdt_api, const void* src, size_t n, int ddt,
-                           void* dst) {
+                           void* dst, int glu_I, int cols) {
   if (n == 0) return cudaSuccess;
   int blocks = (int)min((size_t)148 * 8, (n + 255) / 256);
-#define CV(ST, DT) convert_kernel<ST, DT><<<blocks, 256, 0, st>>>((const ST*)src, n, (DT*)dst)
+#define CV(ST, DT) \
+  convert_kernel<ST, DT><<<blocks, 256, 0, st>>>((const ST*)src, n, (DT*)dst, glu_I, cols)
   if (ddt == DT_F32) {
     if (sdt_api == 0) CV(float, float);
     else if (sdt_api == 1) CV(bf16, float);

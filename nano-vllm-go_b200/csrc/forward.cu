@@ -23,7 +23,7 @@ void free_workspace(nvllm_handle* h) {
                   w.logits_p, w.logits, w.attn_ws, w.attn_tickets, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
                   w.sort.counts, w.sort.offsets, w.sort.cursor, w.sort.sorted_pair, w.sort.pair_row,
                   w.sort.a_rows, w.sort.tile_expert, w.sort.tile_row0, w.sort.tile_rows,
-                  w.sort.n_tiles, w.moe_Y, w.moe_y};
+                  w.sort.n_tiles, w.moe_Y, w.moe_y, w.moe_xs};
   for (void* p : ptrs)
     if (p) cudaFree(p);
   int keep = w.n_cap_out;
@@ -96,7 +96,7 @@ int ensure_workspace(nvllm_handle* h, int T, int n) {
     return set_err(h, NVLLM_ERR_CUDA, "memset(argmax scratch) failed");
   if (h->moe) {
     const size_t P = (size_t)Tc * h->topk;
-    w.max_tiles = (int)(P / 64 + h->E);
+    w.max_tiles = (int)(P / 32 + h->E);  // token tiles are >= 32 rows
     WS(w.xn_f32, Tc * H * 4);
     WS(w.topk_idx, P * 4);
     WS(w.topk_w, P * 4);
@@ -111,6 +111,7 @@ int ensure_workspace(nvllm_handle* h, int T, int n) {
     WS(w.sort.tile_rows, w.max_tiles * 4);
     WS(w.sort.n_tiles, 4);
     WS(w.moe_Y, P * H * 4);
+    if (h->adt == DT_BF16) WS(w.moe_xs, P * H * 2);
     WS(w.moe_y, Tc * H * 4);
   }
 #undef WS
@@ -394,40 +395,74 @@ int forward_step(nvllm_handle* h) {
     Pending& pf = h->parallel ? p2 : p1;
     if (h->moe) {
       const int k = h->topk, I = h->F, P = T * k;
+      // bf16 mode: grouped tcgen05 GEMMs over the expert-sorted rows; fp32 parity mode (and
+      // shapes TMA cannot address): the SIMT fp32 tiles
+      const bool tc = h->adt == DT_BF16 && h->wdt == DT_BF16 && tc5_supported(P, 2 * I, H) &&
+                      tc5_supported(P, H, I) && (I % 8) == 0;
+      const int tile = tc ? tc5_group_tile((P + h->E - 1) / h->E) : 64;
       {
         ProfScope ps(h, NVLLM_K_MOE_ROUTE, (double)T * H * 4 + (double)h->E * H * 4, 2.0 * T * H * h->E);
         LAUNCH(h, launch_moe_router(st, w.xn_f32, lw.router, T, H, h->E, k, w.topk_idx, w.topk_w));
-        LAUNCH(h, launch_moe_sort(st, w.topk_idx, T, k, h->E, w.sort, w.max_tiles));
+        LAUNCH(h, launch_moe_sort(st, w.topk_idx, T, k, h->E, w.sort, w.max_tiles, tile));
       }
       const double wsz = dt_size(h->wdt);
       const int e_touched = std::min(h->E, P);
-      GemmArgs g{};
-      g.A = w.xn; g.adt = h->adt; g.lda = H; g.W = lw.moe_in; g.wdt = h->wdt;
-      g.M = P; g.N = 2 * I; g.K = H; g.out = w.ws_a; g.ldo = 2 * I; g.alpha = 1.f;
-      g.a_rows = w.sort.a_rows; g.tile_expert = w.sort.tile_expert; g.tile_row0 = w.sort.tile_row0;
-      g.tile_rows = w.sort.tile_rows; g.n_tiles = w.sort.n_tiles;
-      g.expert_stride = (size_t)2 * I * H; g.max_tiles = w.max_tiles;
-      {
-        ProfScope ps(h, NVLLM_K_MOE_GEMM,
-                     (double)e_touched * 2 * I * H * wsz + (double)P * H * asz + (double)P * 2 * I * 4,
-                     2.0 * P * 2 * I * H);
-        LAUNCH(h, launch_gemm_simt(st, g));
-      }
-      {
-        ProfScope ps(h, NVLLM_K_MOE_MISC, (double)P * I * (8 + asz), 0);
-        LAUNCH(h, launch_moe_glu(st, h->adt, P, I, w.ws_a, w.hbuf));
-      }
-      GemmArgs g2{};
-      g2.A = w.hbuf; g2.adt = h->adt; g2.lda = I; g2.W = lw.moe_out; g2.wdt = h->wdt;
-      g2.M = P; g2.N = H; g2.K = I; g2.out = w.moe_Y; g2.ldo = H; g2.alpha = 1.f;
-      g2.tile_expert = w.sort.tile_expert; g2.tile_row0 = w.sort.tile_row0;
-      g2.tile_rows = w.sort.tile_rows; g2.n_tiles = w.sort.n_tiles;
-      g2.expert_stride = (size_t)H * I; g2.max_tiles = w.max_tiles;
-      {
-        ProfScope ps(h, NVLLM_K_MOE_GEMM,
-                     (double)e_touched * H * I * wsz + (double)P * I * asz + (double)P * H * 4,
-                     2.0 * P * H * I);
-        LAUNCH(h, launch_gemm_simt(st, g2));
+      if (tc) {
+        {
+          ProfScope ps(h, NVLLM_K_MOE_MISC, (double)P * H * 2 * 2, 0);
+          LAUNCH(h, launch_moe_gather(st, P, H, w.xn, w.sort.a_rows, w.moe_xs));
+        }
+        Tc5Args t{};
+        t.A = w.moe_xs; t.W = lw.moe_in; t.M = P; t.N = 2 * I; t.K = H;
+        t.S = 1; t.alpha = 1.f; t.epi = TC5_EPI_SWIGLU; t.epi_out = w.hbuf; t.epi_ld = I;
+        t.g_experts = h->E; t.g_tile = tile; t.g_max_tiles = w.max_tiles;
+        t.g_tile_expert = w.sort.tile_expert; t.g_tile_row0 = w.sort.tile_row0;
+        t.g_tile_rows = w.sort.tile_rows; t.g_n_tiles = w.sort.n_tiles;
+        {
+          ProfScope ps(h, NVLLM_K_MOE_GEMM,
+                       (double)e_touched * 2 * I * H * wsz + (double)P * H * asz + (double)P * I * asz,
+                       2.0 * P * 2 * I * H);
+          LAUNCH(h, launch_gemm_tc5(st, t, nullptr));
+        }
+        Tc5Args t2 = t;
+        t2.A = w.hbuf; t2.W = lw.moe_out; t2.N = H; t2.K = I;
+        t2.epi = TC5_EPI_PARTIAL; t2.epi_out = nullptr; t2.out = w.moe_Y; t2.ldo = H;
+        t2.split_stride = 0; t2.out_capacity = 0;
+        {
+          ProfScope ps(h, NVLLM_K_MOE_GEMM,
+                       (double)e_touched * H * I * wsz + (double)P * I * asz + (double)P * H * 4,
+                       2.0 * P * H * I);
+          LAUNCH(h, launch_gemm_tc5(st, t2, nullptr));
+        }
+      } else {
+        GemmArgs g{};
+        g.A = w.xn; g.adt = h->adt; g.lda = H; g.W = lw.moe_in; g.wdt = h->wdt;
+        g.M = P; g.N = 2 * I; g.K = H; g.out = w.ws_a; g.ldo = 2 * I; g.alpha = 1.f;
+        g.a_rows = w.sort.a_rows; g.tile_expert = w.sort.tile_expert; g.tile_row0 = w.sort.tile_row0;
+        g.tile_rows = w.sort.tile_rows; g.n_tiles = w.sort.n_tiles;
+        g.expert_stride = (size_t)2 * I * H; g.max_tiles = w.max_tiles;
+        {
+          ProfScope ps(h, NVLLM_K_MOE_GEMM,
+                       (double)e_touched * 2 * I * H * wsz + (double)P * H * asz + (double)P * 2 * I * 4,
+                       2.0 * P * 2 * I * H);
+          LAUNCH(h, launch_gemm_simt(st, g));
+        }
+        {
+          ProfScope ps(h, NVLLM_K_MOE_MISC, (double)P * I * (8 + asz), 0);
+          LAUNCH(h, launch_moe_glu(st, h->adt, P, I, w.ws_a, w.hbuf));
+        }
+        GemmArgs g2{};
+        g2.A = w.hbuf; g2.adt = h->adt; g2.lda = I; g2.W = lw.moe_out; g2.wdt = h->wdt;
+        g2.M = P; g2.N = H; g2.K = I; g2.out = w.moe_Y; g2.ldo = H; g2.alpha = 1.f;
+        g2.tile_expert = w.sort.tile_expert; g2.tile_row0 = w.sort.tile_row0;
+        g2.tile_rows = w.sort.tile_rows; g2.n_tiles = w.sort.n_tiles;
+        g2.expert_stride = (size_t)H * I; g2.max_tiles = w.max_tiles;
+        {
+          ProfScope ps(h, NVLLM_K_MOE_GEMM,
+                       (double)e_touched * H * I * wsz + (double)P * I * asz + (double)P * H * 4,
+                       2.0 * P * H * I);
+          LAUNCH(h, launch_gemm_simt(st, g2));
+        }
       }
       {
         ProfScope ps(h, NVLLM_K_MOE_MISC, (double)P * H * 4 + (double)T * H * 4, 0);

@@ -92,21 +92,46 @@ __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&r)[32])
 // Only the activation tiles (and every global store) wait for the dependency.
 struct Tc5Sched {
   int units, n_tiles, S, kbps, nkb_total;
+  // grouped (mixture-of-experts) mode, g_expert != nullptr: token tile t covers rows
+  // [g_row0[t], g_row0[t] + g_rows[t]) of the expert-sorted activations and multiplies expert
+  // g_expert[t]'s [g_N, K] weight matrix (experts stacked row-wise in W); the tile list lives
+  // on the device (moe_sort_kernel), so units = *g_ntiles * n_tiles is read after the wait
+  const int* g_expert;
+  const int* g_row0;
+  const int* g_rows;
+  const int* g_ntiles;
+  int g_N;
 };
 // rot: CTAs working on the same k range start at different k-blocks (and wrap), so that at any
 // instant they pull DIFFERENT activation tiles out of L2 — otherwise every CTA of a skinny
 // GEMM requests the same 8 KB A tile at the same time and the few L2 slices holding it pace
 // the whole kernel (measured: ~390 ns per k-block with W already in shared memory).
-__device__ __forceinline__ void tc5_unit(const Tc5Sched& sc, int u, int BT, int& n0, int& m0,
-                                         int& kb0, int& nkb, int& split, int& rot) {
-  split = u % sc.S;
+struct Tc5Unit {
+  int n0;     // first output column (weight row inside the expert)
+  int wrow;   // first weight row in the stacked weight tensor (TMA coordinate)
+  int m0;     // first token row
+  int m_end;  // one past the last valid token row of this tile
+  int kb0, nkb, split, rot;
+};
+__device__ __forceinline__ Tc5Unit tc5_unit(const Tc5Sched& sc, int u, int BT, int M) {
+  Tc5Unit t;
+  t.split = u % sc.S;
   const int r = u / sc.S;
   const int nt = r % sc.n_tiles, mt = r / sc.n_tiles;
-  n0 = nt * TC_BN;
-  m0 = mt * BT;
-  kb0 = split * sc.kbps;
-  nkb = min(sc.kbps, sc.nkb_total - kb0);
-  rot = (nt + 5 * mt) % nkb;
+  t.n0 = nt * TC_BN;
+  if (sc.g_expert) {
+    t.m0 = sc.g_row0[mt];
+    t.m_end = t.m0 + sc.g_rows[mt];
+    t.wrow = sc.g_expert[mt] * sc.g_N + t.n0;
+  } else {
+    t.m0 = mt * BT;
+    t.m_end = M;
+    t.wrow = t.n0;
+  }
+  t.kb0 = t.split * sc.kbps;
+  t.nkb = min(sc.kbps, sc.nkb_total - t.kb0);
+  t.rot = (nt + 5 * mt) % t.nkb;
+  return t;
 }
 __device__ __forceinline__ int tc5_kb(int kb0, int kb, int rot, int nkb) {
   const int k = kb + rot;
@@ -138,6 +163,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool grouped = sc.g_expert != nullptr;
   pdl_launch_dependents();
 
   if (warp == 0 && lane == 0) {
@@ -179,22 +205,22 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     else
       asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol_w));
     asm volatile("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol_a));
-    int n0, m0, kb0, nkb, split, rot;
-    // (1) weight tiles of the first STAGES k-blocks, before the dependency resolves
+    // (1) weight tiles of the first STAGES k-blocks, before the dependency resolves (dense
+    // mode only: a grouped GEMM learns which expert a tile multiplies from the previous kernel)
     int pre = 0;
     {
       int u = blockIdx.x, kb = 0;
-      while ((prefetch & 1) && pre < STAGES && u < sc.units) {
-        tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split, rot);
+      while ((prefetch & 1) && !grouped && pre < STAGES && u < sc.units) {
+        const Tc5Unit t = tc5_unit(sc, u, BT, M);
         const uint32_t full = bars + 8 * pre;
         if (elect_one()) {
           mbar_expect_tx(full, (prefetch & 2) ? W_BYTES : STAGE_BYTES);
           tma_load_2d_hint(tiles + pre * STAGE_BYTES, &tmW, full,
-                           tc5_kb(kb0, kb, rot, nkb) * TC_BK, n0, pol_w);
+                           tc5_kb(t.kb0, kb, t.rot, t.nkb) * TC_BK, t.wrow, pol_w);
         }
         __syncwarp();
         pre++;
-        if (++kb == nkb) {
+        if (++kb == t.nkb) {
           kb = 0;
           u += grid;
         }
@@ -217,22 +243,23 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     }
     pdl_wait();
     if (tr.buf) t_wait = gtime();
+    const int units = grouped ? *sc.g_ntiles * sc.n_tiles : sc.units;
     // (2) their activation tiles, then (3) the steady state
     int u = blockIdx.x, kb = 0, i = 0;
-    while (u < sc.units) {
-      tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split, rot);
-      for (; kb < nkb; kb++, i++) {
+    while (u < units) {
+      const Tc5Unit t = tc5_unit(sc, u, BT, M);
+      for (; kb < t.nkb; kb++, i++) {
         const int s = i % STAGES;
         const uint32_t full = bars + 8 * s;
         const uint32_t dst = tiles + s * STAGE_BYTES;
-        const int k = tc5_kb(kb0, kb, rot, nkb) * TC_BK;
+        const int k = tc5_kb(t.kb0, kb, t.rot, t.nkb) * TC_BK;
         if (i >= pre) mbar_wait(bars + 8 * (STAGES + s), ((i / STAGES) & 1) ^ 1);
         if (elect_one()) {
           if (i >= pre) {
             mbar_expect_tx(full, (prefetch & 2) ? W_BYTES : STAGE_BYTES);
-            tma_load_2d_hint(dst, &tmW, full, k, n0, pol_w);
+            tma_load_2d_hint(dst, &tmW, full, k, t.wrow, pol_w);
           }
-          if (!(prefetch & 2)) tma_load_2d_hint(dst + W_BYTES, &tmA, full, k, m0, pol_a);
+          if (!(prefetch & 2)) tma_load_2d_hint(dst + W_BYTES, &tmA, full, k, t.m0, pol_a);
         }
         __syncwarp();
       }
@@ -244,10 +271,11 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     // both K-major, N = BT, M = 128
     constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BT >> 3) << 17) |
                                ((uint32_t)(TC_BN >> 4) << 24);
-    int n0, m0, kb0, nkb, split, rot;
+    if (grouped) pdl_wait();  // the tile list is the previous kernel's output
+    const int units = grouped ? *sc.g_ntiles * sc.n_tiles : sc.units;
     int i = 0, lu = 0;
-    for (int u = blockIdx.x; u < sc.units; u += grid, lu++) {
-      tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split, rot);
+    for (int u = blockIdx.x; u < units; u += grid, lu++) {
+      const int nkb = tc5_unit(sc, u, BT, M).nkb;
       const int buf = lu & 1;
       mbar_wait(bar_tempty + 8 * buf, ((lu >> 1) & 1) ^ 1);  // epilogue drained this buffer
       tc_fence_after();
@@ -280,10 +308,12 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     // epilogue: warp w may touch TMEM lanes [32 (w % 4), +32)
     const int q = warp & 3;
     pdl_wait();  // global stores below must follow the previous kernel's completion
-    int n0, m0, kb0, nkb, split, rot;
+    const int units = grouped ? *sc.g_ntiles * sc.n_tiles : sc.units;
     int lu = 0;
-    for (int u = blockIdx.x; u < sc.units; u += grid, lu++) {
-      tc5_unit(sc, u, BT, n0, m0, kb0, nkb, split, rot);
+    for (int u = blockIdx.x; u < units; u += grid, lu++) {
+      const Tc5Unit t = tc5_unit(sc, u, BT, M);
+      const int n0 = t.n0, m0 = t.m0, split = t.split;
+      const int M = t.m_end;  // rows past the tile's extent belong to the next expert / are padding
       const int buf = lu & 1;
       mbar_wait(bar_tfull + 8 * buf, (lu >> 1) & 1);
       tc_fence_after();
@@ -542,32 +572,47 @@ static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* t
     cudaDeviceGetAttribute(&sm_counts[dev], cudaDevAttrMultiProcessorCount, dev);
     attr_mask |= 1ull << dev;
   }
-  Tc5Sched sc;
+  Tc5Sched sc{};
   sc.nkb_total = ceil_div(a.K, TC_BK);
   sc.kbps = ceil_div(sc.nkb_total, S);
   sc.S = ceil_div(sc.nkb_total, sc.kbps);
   sc.n_tiles = ceil_div(a.N, TC_BN);
-  const int m_tiles = ceil_div(a.M, BT);
+  int m_tiles = ceil_div(a.M, BT);
+  if (a.g_experts > 0) {
+    sc.g_expert = a.g_tile_expert;
+    sc.g_row0 = a.g_tile_row0;
+    sc.g_rows = a.g_tile_rows;
+    sc.g_ntiles = a.g_n_tiles;
+    sc.g_N = a.N;
+    m_tiles = min(a.g_max_tiles, a.M / BT + a.g_experts);  // upper bound; the kernel reads the count
+  }
   sc.units = sc.n_tiles * m_tiles * sc.S;
   const int grid = min(sc.units, max(1, sm_counts[dev]));
+  const bool w_reused = a.g_experts > 0 ? a.M > 2 * BT * a.g_experts : m_tiles > 1;
   return launch_k(gemm_tc5_kernel<BT, STAGES>, dim3(grid), dim3(TC_THREADS), smem, st,
                   *reinterpret_cast<const CUtensorMap*>(tw),
                   *reinterpret_cast<const CUtensorMap*>(ta), a.M, a.N, sc, a.out, a.ldo,
-                  a.split_stride, a.alpha, m_tiles > 1 ? 1 : 0, a.epi, (bf16*)a.epi_out, a.epi_ld,
+                  a.split_stride, a.alpha, w_reused ? 1 : 0, a.epi, (bf16*)a.epi_out, a.epi_ld,
                   a.epi_bias, prefetch_flags(),
                   (const uint8_t*)((prefetch_flags() & 4) ? nullptr : a.pf_ptr),
                   (unsigned long long)((prefetch_flags() & 4) ? 0 : a.pf_bytes), next_trace(1));
 }
 
 // a.S is the requested number of splits; the number actually written is returned in *S_out
+int tc5_group_tile(int rows_per_expert) { return pick_bt(rows_per_expert + rows_per_expert / 4); }
+
 cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int* S_out) {
   if (!tc5_supported(a.M, a.N, a.K)) return cudaErrorInvalidValue;
-  const int bt = pick_bt(a.M);
-  const TmaDesc* tw = cached_map(a.W, a.N, a.K, TC_BN);
+  const bool grouped = a.g_experts > 0;
+  if (grouped && (!a.g_tile_expert || !a.g_tile_row0 || !a.g_tile_rows || !a.g_n_tiles ||
+                  (a.g_tile != 32 && a.g_tile != 64 && a.g_tile != 128 && a.g_tile != 256)))
+    return cudaErrorInvalidValue;
+  const int bt = grouped ? a.g_tile : pick_bt(a.M);
+  const TmaDesc* tw = cached_map(a.W, grouped ? a.N * a.g_experts : a.N, a.K, TC_BN);
   const TmaDesc* ta = cached_map(a.A, a.M, a.K, bt);
   if (!tw || !ta) return cudaErrorInvalidValue;
   const int nkb = ceil_div(a.K, TC_BK);
-  int S = max(1, min(a.S, nkb));
+  int S = grouped ? 1 : max(1, min(a.S, nkb));
   const int kbps = ceil_div(nkb, S);
   S = ceil_div(nkb, kbps);
   if (a.epi != TC5_EPI_PARTIAL) {

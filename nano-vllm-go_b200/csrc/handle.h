@@ -74,6 +74,7 @@ struct Workspace {
   int max_tiles = 0;
   float* moe_Y = nullptr;  // [T k, H]
   float* moe_y = nullptr;  // [T, H]
+  void* moe_xs = nullptr;  // [T k, H] bf16: normed activations in expert-sorted order
 };
 
 }  // namespace nvllm

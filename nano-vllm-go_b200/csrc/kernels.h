@@ -94,9 +94,10 @@ cudaError_t launch_make_decode_state(cudaStream_t st, int n, int mb, const int* 
 cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* src, size_t ld_src,
                                      int K, int N, int ddt, void* dst, int ld_dst, int row_mul = 1,
                                      int row_add = 0);
-// dst (dtype ddt) = convert(src)  flat copy
+// dst (dtype ddt) = convert(src)  flat copy; glu_I > 0: rows of `cols` elements, each
+// [2 glu_I, cols] matrix of the stack rewritten with gate / up rows interleaved
 cudaError_t launch_convert(cudaStream_t st, int sdt_api, const void* src, size_t n, int ddt,
-                           void* dst);
+                           void* dst, int glu_I = 0, int cols = 0);
 // out[i] = sum_s p[s*stride + i]
 cudaError_t launch_reduce_partials(cudaStream_t st, const float* p, int S, size_t stride, size_t n,
                                    float* out);
@@ -167,8 +168,20 @@ struct Tc5Args {
   // weights of a later GEMM to pull into L2 while this one waits / drains (decode only)
   const void* pf_ptr;
   size_t pf_bytes;
+  // grouped (mixture-of-experts) GEMM, g_experts > 0: A is the expert-sorted activation matrix
+  // [M, K]; W stacks g_experts matrices of [N, K]; the token tiles (g_tile rows each, device
+  // lists written by moe_sort_kernel) say which rows meet which expert.  S must be 1.
+  int g_experts;
+  int g_tile;            // rows per token tile the sort used: 32 / 64 / 128 / 256
+  int g_max_tiles;       // capacity of the tile lists
+  const int* g_tile_expert;
+  const int* g_tile_row0;
+  const int* g_tile_rows;
+  const int* g_n_tiles;  // [1] on the device
 };
 enum { TC5_EPI_PARTIAL = 0, TC5_EPI_SWIGLU = 1, TC5_EPI_GELU = 2 };
+// token-tile rows for a grouped GEMM averaging `rows_per_expert` rows per expert
+int tc5_group_tile(int rows_per_expert);
 bool tc5_supported(int M, int N, int K);
 int tc5_splits(int M, int N, int K, int sm_count);
 // *S_out = slices actually written (<= a.S)
@@ -228,7 +241,7 @@ cudaError_t launch_attn_decode_sk(cudaStream_t st, const AttnArgs& a, int* ticke
 // (moe.go:63-103).  x fp32 [T,H]; R fp32 [E,H].
 cudaError_t launch_moe_router(cudaStream_t st, const float* x, const float* R, int T, int H, int E,
                               int k, int* topk_idx, float* topk_w);
-// Group the T*k (token,slot) pairs by expert into 64-row tiles.
+// Group the T*k (token,slot) pairs by expert into `tile`-row tiles.
 struct MoeSortBufs {
   int* counts;       // [E]
   int* offsets;      // [E+1]
@@ -242,8 +255,12 @@ struct MoeSortBufs {
   int* n_tiles;      // [1]
 };
 cudaError_t launch_moe_sort(cudaStream_t st, const int* topk_idx, int T, int k, int E,
-                            const MoeSortBufs& b, int max_tiles);
-// g[row, j] = silu(h[row, j]) * h[row, I + j] with the fp32 sigmoid of moe.go:203-212
+                            const MoeSortBufs& b, int max_tiles, int tile);
+// xs[row, :] = x[a_rows[row], :]  (bf16 rows of H elements)
+cudaError_t launch_moe_gather(cudaStream_t st, int rows, int H, const void* x, const int* a_rows,
+                              void* xs);
+// g[row, j] = silu(h[row, 2j]) * h[row, 2j + 1] (gate / up interleaved at load) with the fp32
+// sigmoid of moe.go:203-212
 cudaError_t launch_moe_glu(cudaStream_t st, int odt, int rows, int I, const float* h, void* g);
 // y[t,:] = sum_s w[t,s] * Y[pair_row[t*k+s], :]   (moe.go:116-118, slot order = descending prob)
 cudaError_t launch_moe_combine(cudaStream_t st, int T, int k, int H, const float* Y,

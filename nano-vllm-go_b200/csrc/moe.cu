@@ -101,7 +101,7 @@ cudaError_t launch_moe_router(cudaStream_t st, const float* x, const float* R, i
 // not depend on it.
 __global__ void __launch_bounds__(1024)
 moe_sort_kernel(const int* __restrict__ topk_idx, int n_pairs, int k, int E, MoeSortBufs b,
-                int max_tiles) {
+                int max_tiles, int tile) {
   pdl_launch_dependents();
   pdl_wait();
   __shared__ int cnt[MOE_MAX_E];
@@ -116,10 +116,10 @@ moe_sort_kernel(const int* __restrict__ topk_idx, int n_pairs, int k, int E, Moe
       off[e] = run;
       b.counts[e] = cnt[e];
       b.offsets[e] = run;
-      for (int r = 0; r < cnt[e] && nt < max_tiles; r += 64) {
+      for (int r = 0; r < cnt[e] && nt < max_tiles; r += tile) {
         b.tile_expert[nt] = e;
         b.tile_row0[nt] = run + r;
-        b.tile_rows[nt] = min(64, cnt[e] - r);
+        b.tile_rows[nt] = min(tile, cnt[e] - r);
         nt++;
       }
       run += cnt[e];
@@ -141,14 +141,43 @@ moe_sort_kernel(const int* __restrict__ topk_idx, int n_pairs, int k, int E, Moe
 }
 
 cudaError_t launch_moe_sort(cudaStream_t st, const int* topk_idx, int T, int k, int E,
-                            const MoeSortBufs& b, int max_tiles) {
+                            const MoeSortBufs& b, int max_tiles, int tile) {
   if (T <= 0) return cudaSuccess;
-  if (E > MOE_MAX_E) return cudaErrorInvalidValue;
-  (void)launch_k(moe_sort_kernel, dim3(1), dim3(1024), 0, st, topk_idx, T * k, k, E, b, max_tiles);
+  if (E > MOE_MAX_E || tile <= 0) return cudaErrorInvalidValue;
+  (void)launch_k(moe_sort_kernel, dim3(1), dim3(1024), 0, st, topk_idx, T * k, k, E, b, max_tiles,
+                 tile);
   return cudaGetLastError();
 }
 
-// moe.go:203-212: sigmoid with an fp32 divide, gate = first half, up = second half
+// xs[row, :] = x[a_rows[row], :] — the expert-sorted copy of the normed activations that the
+// grouped tensor-core GEMM reads with plain 2-D TMA boxes (bf16, H % 8 == 0)
+__global__ void moe_gather_kernel(size_t nvec, int vpr, const uint4* __restrict__ x,
+                                  const int* __restrict__ a_rows, uint4* __restrict__ xs) {
+  pdl_launch_dependents();
+  pdl_wait();
+  for (size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec;
+       v += (size_t)gridDim.x * blockDim.x) {
+    const size_t row = v / vpr;
+    const int j = (int)(v - row * vpr);
+    xs[v] = x[(size_t)a_rows[row] * vpr + j];
+  }
+}
+
+cudaError_t launch_moe_gather(cudaStream_t st, int rows, int H, const void* x, const int* a_rows,
+                              void* xs) {
+  if (rows <= 0) return cudaSuccess;
+  if (H % 8) return cudaErrorInvalidValue;
+  const int vpr = H / 8;
+  const size_t nvec = (size_t)rows * vpr;
+  const int blocks = (int)min((size_t)148 * 8, (nvec + 255) / 256);
+  (void)launch_k(moe_gather_kernel, dim3(blocks), dim3(256), 0, st, nvec, vpr, (const uint4*)x,
+                 a_rows, (uint4*)xs);
+  return cudaGetLastError();
+}
+
+// moe.go:203-212: sigmoid with an fp32 divide; gate j = proj[j], up j = proj[I + j].  The
+// expert input weights are repacked at load with gate / up rows interleaved (weights.cu), so
+// h[row, 2j] is gate j and h[row, 2j + 1] is up j.
 template <typename OT>
 __global__ void moe_glu_kernel(size_t nvec, int I, const float* __restrict__ h,
                                OT* __restrict__ g) {
@@ -159,13 +188,15 @@ __global__ void moe_glu_kernel(size_t nvec, int I, const float* __restrict__ h,
        v += (size_t)gridDim.x * blockDim.x) {
     const size_t row = v / vpr;
     const int j = (int)(v % vpr) * 8;
-    float a[8], u[8], o[8];
-    load8(h + row * 2 * I + j, a);
-    load8(h + row * 2 * I + I + j, u);
+    float lo[8], hi[8], o[8];
+    load8(h + row * 2 * I + 2 * j, lo);
+    load8(h + row * 2 * I + 2 * j + 8, hi);
 #pragma unroll
     for (int i = 0; i < 8; i++) {
-      const float sig = 1.0f / (1.0f + expf(-a[i]));
-      o[i] = a[i] * sig * u[i];
+      const float a = i < 4 ? lo[2 * i] : hi[2 * i - 8];
+      const float u = i < 4 ? lo[2 * i + 1] : hi[2 * i - 7];
+      const float sig = 1.0f / (1.0f + expf(-a));
+      o[i] = a * sig * u;
     }
     store8(g + row * I + j, o);
   }

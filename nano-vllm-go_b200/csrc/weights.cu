@@ -182,7 +182,8 @@ extern "C" int nvllm_set_weight(nvllm_handle* h, int id, int layer, int dtype, c
       e = launch_transpose_convert(h->stream, dtype, src, o.ld_src, o.K, o.N, ddt, o.dst, o.ld_dst,
                                    o.row_mul, o.row_add);
     else
-      e = launch_convert(h->stream, dtype, src, o.N < 0 ? (size_t)numel : (size_t)o.N, ddt, o.dst);
+      e = launch_convert(h->stream, dtype, src, o.N < 0 ? (size_t)numel : (size_t)o.N, ddt, o.dst,
+                         id == NVLLM_W_MOE_INPUT ? Fg : 0, H);
   }
   // row-parallel output biases are added once: ranks other than 0 hold zeros
   if (e == cudaSuccess && h->rank != 0 && (id == NVLLM_W_O_BIAS || id == NVLLM_W_FFN_B2))

@@ -162,6 +162,23 @@ def test_bf16_long_context_split_kv(name):
     _greedy_parity(name, C.PREC_BF16, prompt_len=700, steps=6, table=TINY_HD)
 
 
+MOE_WIDE = {
+    # grouped tensor-core expert GEMMs: several 128-row weight tiles per expert, experts with
+    # more rows than one token tile (600 x 4 / 8 = 300 rows per expert on average), N not a
+    # multiple of 128 (2 I = 192)
+    "granite_wide": lambda: C.tiny_granite(hidden=256, num_heads=4, num_kv_heads=2, head_dim=64,
+                                           ffn_dim=128, num_experts=8, num_experts_per_tok=4),
+    "granite_odd": lambda: C.tiny_granite(hidden=192, num_heads=6, num_kv_heads=2, head_dim=32,
+                                          ffn_dim=96, num_experts=6, num_experts_per_tok=3),
+}
+
+
+@pytest.mark.parametrize("name", list(MOE_WIDE))
+@pytest.mark.parametrize("prompt_len", [40, 600])
+def test_bf16_moe_grouped_tensor_core_gemm(name, prompt_len):
+    _greedy_parity(name, C.PREC_BF16, prompt_len=prompt_len, steps=6, table=MOE_WIDE)
+
+
 @pytest.mark.parametrize("name", ["gpt2", "llama"])
 def test_context_crossing_block_boundaries(name):
     """Prompt of 250 tokens, decode across position 256 (second KV block)."""
