@@ -13,6 +13,8 @@
 //    group, KV split).  The query heads that share a kv head are the M rows of the MMA,
 //    so each K/V byte is read once per group.  HBM-bound: 3-4 cp.async stages keep
 //    >= 48 KB per SM in flight.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "kernels.h"
 #include "tma.cuh"
@@ -54,6 +56,11 @@ __device__ __forceinline__ void mma16816(float (&d)[4], uint32_t a0, uint32_t a1
       "{%0,%1,%2,%3};"
       : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ void st_shared16(uint32_t addr, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
 }
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
@@ -262,22 +269,34 @@ attn_prefill_mma_kernel(AttnArgs a) {
 // ------------------------------------------------------------------ decode
 // split partial record (shared with attention.cu's combine kernel): [hd] unnormalised
 // accumulator, then m (in score units, already multiplied by scale), l
+//
+// One CTA = (sequence, `kpc` consecutive kv heads [or one 16-row chunk of a big head group], KV
+// split).  The fixed cost of a CTA (launch, first-tile latency, Q build, warp merge) is ~5 us
+// against ~1 us per 128-key tile, so when the step has more (sequence, kv head) pairs than
+// resident CTA slots the launcher packs kpc heads into one CTA: the K/V tile ring runs straight
+// through the head boundaries and the grid fits one wave.
 template <int HD, int BN, int STAGES>
-__global__ void __launch_bounds__(128)
-attn_decode_mma_kernel(AttnArgs a, int G, int chunks, Trace tr) {
+__global__ void __launch_bounds__(128, (HD == 64 && BN == 64) ? 4 : 2)
+attn_decode_mma_kernel(AttnArgs a, int G, int chunks, int kpc, Trace tr) {
   const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
   pdl_launch_dependents();
   constexpr int TILE_BYTES = BN * HD * 2;
   constexpr int WK = BN / 4;  // keys per warp per tile
+  constexpr int RS = HD + 2;
   extern __shared__ __align__(128) uint8_t smem[];
-  const uint32_t sQ = smem_addr(smem);  // [16][HD]
-  const uint32_t sK = sQ + 16 * HD * 2;
+  const uint32_t sQ = smem_addr(smem);  // [kpc][16][HD]
+  const uint32_t sK = sQ + kpc * 16 * HD * 2;
   const uint32_t sV = sK + STAGES * TILE_BYTES;
+  // warp-merge scratch [4][min(16, G)][HD + 2] fp32: its own region when heads are packed (the ring is
+  // still streaming the next head), aliased on the drained ring otherwise
+  float* red = reinterpret_cast<float*>(
+      smem + kpc * 16 * HD * 2 + (kpc > 1 ? 2 * STAGES * TILE_BYTES : 0));
+  bf16* s_newkv = reinterpret_cast<bf16*>(smem + a.newkv_off);  // [kpc][2][HD]
   const int seq = blockIdx.x;
-  const int kvh = blockIdx.y / chunks, chunk = blockIdx.y % chunks;
+  const int kvh0 = (blockIdx.y / chunks) * kpc, chunk = blockIdx.y % chunks;
   const int split = blockIdx.z;
-  const int h0 = kvh * G + chunk * 16;           // first query head of this CTA
-  const int rows = min(16, G - chunk * 16);      // valid query heads
+  const int rows = min(16, G - chunk * 16);      // valid query heads per kv head
+  const int rrows = min(16, G);                  // rows of the warp-merge scratch
   const int len = a.seq_len[seq];                // step state: stable before the wait
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t = lane & 3;
@@ -289,110 +308,255 @@ attn_decode_mma_kernel(AttnArgs a, int G, int chunks, Trace tr) {
   const int tps = (tiles_total + a.n_splits - 1) / a.n_splits;
   const int tile_begin = split * tps;
   const int n_tiles = max(0, min(tps, tiles_total - tile_begin));
+  const int F = n_tiles * kpc;  // flat (head, tile) work list
 
-  auto issue_kv = [&](int j, int stage) {
+  auto issue_kv = [&](int f, int stage) {
+    if (a.ablate == 2) return;
+    const int hh = f / n_tiles, j = f - hh * n_tiles;
     const int k0 = (tile_begin + j) * BN;
     const int nk = min(BN, len - k0);
-    const size_t base = (((size_t)bt[k0 / KV_BLOCK] * a.nkv + kvh) * KV_BLOCK + (k0 % KV_BLOCK)) * HD;
+    const size_t base =
+        (((size_t)bt[k0 / KV_BLOCK] * a.nkv + kvh0 + hh) * KV_BLOCK + (k0 % KV_BLOCK)) * HD;
     load_tile<HD, 128>(sK + stage * TILE_BYTES, kpool + base, BN, nk, HD);
     load_tile<HD, 128>(sV + stage * TILE_BYTES, vpool + base, BN, nk, HD);
   };
-  // The only K/V row the previous kernel (RoPE + KV append) writes for this sequence is
-  // position len - 1: tiles that end before it were written by earlier steps, so their
-  // loads start BEFORE the dependency resolves (the HBM stream overlaps the RoPE kernel).
-  auto tile_is_old = [&](int j) { return (tile_begin + j + 1) * BN <= len - 1; };
+  // The only K/V row the previous kernel writes for this sequence is position len - 1: tiles
+  // that end before it were written by earlier steps, so their loads start BEFORE the
+  // dependency resolves.
+  auto tile_is_old = [&](int f) { return (tile_begin + f % n_tiles + 1) * BN <= len - 1; };
 #pragma unroll
   for (int s = 0; s < STAGES - 1; s++) {
-    if (s < n_tiles && tile_is_old(s)) issue_kv(s, s);
+    if (s < F && tile_is_old(s)) issue_kv(s, s);
     cp_async_commit();
   }
+  // fused mode: this CTA's key range ends with the token being decoded, whose K / V row does
+  // not exist in the pool yet — it is built below and patched into the last tile of each head
+  const bool fused = a.qkv_p != nullptr;
+  const bool has_new = fused && n_tiles > 0 && tile_begin + n_tiles == tiles_total;
   pdl_wait();
   const unsigned long long t_wait = tr.buf ? gtime() : 0ull;
-  load_tile<HD, 128>(sQ, (const bf16*)a.q + (size_t)seq * a.nh * HD + (size_t)h0 * HD, 16, rows, HD);
+  if (fused) {  // the remaining tiles stream while the prologue below builds Q / K / V
 #pragma unroll
-  for (int s = 0; s < STAGES - 1; s++)
-    if (s < n_tiles && !tile_is_old(s)) issue_kv(s, s);
+    for (int s = 0; s < STAGES - 1; s++)
+      if (s < F && !tile_is_old(s)) issue_kv(s, s);
+  }
+  if (!fused) {
+    for (int hh = 0; hh < kpc; hh++)
+      load_tile<HD, 128>(sQ + hh * 16 * HD * 2,
+                         (const bf16*)a.q + (size_t)seq * a.nh * HD +
+                             (size_t)((kvh0 + hh) * G + chunk * 16) * HD,
+                         16, rows, HD);
+  } else {
+    // split-K sum + bias, rotate_half RoPE at position len - 1 (rope.go:153-205), bf16: what
+    // rope_kv_kernel does for a decode token, for this CTA's query heads and its kv heads
+    constexpr int HALF = HD / 2, VPH = HALF / 8;
+    const int pos = len - 1;
+    const float* rowp = a.qkv_p + (size_t)seq * a.qkv_ld;
+    const int q_items = 16 * VPH, kv_items = has_new ? 2 * VPH : 0;
+    const int per_head = q_items + kv_items;
+    for (int it0 = threadIdx.x; it0 < per_head * kpc; it0 += 128) {
+      const int hh = it0 / per_head, it = it0 - hh * per_head;
+      const int kvh = kvh0 + hh;
+      const bool is_q = it < q_items;
+      const int r = is_q ? it / VPH : 0;
+      const int which = is_q ? 0 : (it - q_items) / VPH;  // 0 = K, 1 = V
+      const int j = (is_q ? it % VPH : (it - q_items) % VPH) * 8;
+      uint4 lo = make_uint4(0, 0, 0, 0), hi = lo;
+      if (!is_q || r < rows) {
+        const int col = (is_q ? kvh * G + chunk * 16 + r : a.nh + which * a.nkv + kvh) * HD + j;
+        float x[8], y[8], c[8], sn[8];
+        const bool rot = a.cosT != nullptr && (is_q || which == 0);
+        if (rot) {  // issued first: independent of the partial sums
+          load8(a.cosT + (size_t)pos * HALF + j, c);
+          load8(a.sinT + (size_t)pos * HALF + j, sn);
+        }
+        if (a.qkv_S <= 8) {
+          // every slice of both halves in flight at once: one L2 round trip, not 2 S / 4
+          float px[8][8], py[8][8];
+#pragma unroll
+          for (int q = 0; q < 8; q++)
+            if (q < a.qkv_S) {
+              load8(rowp + (size_t)q * a.qkv_stride + col, px[q]);
+              load8(rowp + (size_t)q * a.qkv_stride + col + HALF, py[q]);
+            }
+#pragma unroll
+          for (int i = 0; i < 8; i++) x[i] = y[i] = 0.f;
+#pragma unroll
+          for (int q = 0; q < 8; q++)
+            if (q < a.qkv_S) {
+#pragma unroll
+              for (int i = 0; i < 8; i++) {
+                x[i] += px[q][i];
+                y[i] += py[q][i];
+              }
+            }
+        } else {
+          sum_partials8(rowp + col, a.qkv_S, a.qkv_stride, x);
+          sum_partials8(rowp + col + HALF, a.qkv_S, a.qkv_stride, y);
+        }
+        if (a.qkv_bias) {
+          float bb[8];
+          load8(a.qkv_bias + col, bb);
+#pragma unroll
+          for (int i = 0; i < 8; i++) x[i] += bb[i];
+          load8(a.qkv_bias + col + HALF, bb);
+#pragma unroll
+          for (int i = 0; i < 8; i++) y[i] += bb[i];
+        }
+        if (rot) {
+#pragma unroll
+          for (int i = 0; i < 8; i++) {
+            const float ra = x[i] * c[i] - y[i] * sn[i];
+            const float rb = y[i] * c[i] + x[i] * sn[i];
+            x[i] = ra;
+            y[i] = rb;
+          }
+        }
+        lo = make_uint4(pack_bf16(x[0], x[1]), pack_bf16(x[2], x[3]), pack_bf16(x[4], x[5]),
+                        pack_bf16(x[6], x[7]));
+        hi = make_uint4(pack_bf16(y[0], y[1]), pack_bf16(y[2], y[3]), pack_bf16(y[4], y[5]),
+                        pack_bf16(y[6], y[7]));
+      }
+      if (is_q) {
+        const uint32_t q = sQ + hh * 16 * HD * 2;
+        st_shared16(q + swz<HD>(r, j / 8), lo);
+        st_shared16(q + swz<HD>(r, (j + HALF) / 8), hi);
+      } else {
+        bf16* nk = s_newkv + ((size_t)hh * 2 + which) * HD;
+        *reinterpret_cast<uint4*>(nk + j) = lo;
+        *reinterpret_cast<uint4*>(nk + j + HALF) = hi;
+        if (chunk == 0) {  // one CTA per (sequence, kv head) appends to the paged pool
+          bf16* pool = which ? (bf16*)a.vpool : (bf16*)a.kpool;
+          bf16* dst = pool + (((size_t)bt[pos / KV_BLOCK] * a.nkv + kvh) * KV_BLOCK + (pos % KV_BLOCK)) * HD + j;
+          *reinterpret_cast<uint4*>(dst) = lo;
+          *reinterpret_cast<uint4*>(dst + HALF) = hi;
+        }
+      }
+    }
+  }
+  if (!fused) {
+#pragma unroll
+    for (int s = 0; s < STAGES - 1; s++)
+      if (s < F && !tile_is_old(s)) issue_kv(s, s);
+  }
   cp_async_commit();
 
   uint32_t qf[HD / 16][4];
   float o[HD / 8][4];
-#pragma unroll
-  for (int dn = 0; dn < HD / 8; dn++)
-#pragma unroll
-    for (int i = 0; i < 4; i++) o[dn][i] = 0.f;
-  float m[2] = {-INFINITY, -INFINITY}, l[2] = {0.f, 0.f};
+  float m[2], l[2];
   const int limit[2] = {len - 1, len - 1};
   const float scale_log2 = a.scale * 1.4426950408889634f;
+  auto reset_head = [&]() {
+#pragma unroll
+    for (int dn = 0; dn < HD / 8; dn++)
+#pragma unroll
+      for (int i = 0; i < 4; i++) o[dn][i] = 0.f;
+    m[0] = m[1] = -INFINITY;
+    l[0] = l[1] = 0.f;
+  };
+  // merge the 4 warps (each covered different keys) through shared memory and write head
+  // group hh's output (or its split record)
+  auto finish_head = [&](int hh) {
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      l[i] += __shfl_xor_sync(0xffffffffu, l[i], 1);
+      l[i] += __shfl_xor_sync(0xffffffffu, l[i], 2);
+    }
+    if (kpc == 1) {
+      cp_async_wait<0>();
+      __syncthreads();  // the ring is drained: `red` aliases it
+    }
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      if (g + 8 * i >= rrows) continue;  // padding rows of the 16-row MMA tile
+      float* rr = red + ((size_t)warp * rrows + g + 8 * i) * RS;
+#pragma unroll
+      for (int dn = 0; dn < HD / 8; dn++) {
+        rr[dn * 8 + 2 * t] = o[dn][2 * i];
+        rr[dn * 8 + 2 * t + 1] = o[dn][2 * i + 1];
+      }
+      if (t == 0) {
+        rr[HD] = m[i];
+        rr[HD + 1] = l[i];
+      }
+    }
+    __syncthreads();
+    const int h0 = (kvh0 + hh) * G + chunk * 16;
+    for (int idx = threadIdx.x; idx < rows * HD; idx += 128) {
+      const int r = idx / HD, d = idx % HD;
+      float mn = -INFINITY;
+#pragma unroll
+      for (int w = 0; w < 4; w++) mn = fmaxf(mn, red[((size_t)w * rrows + r) * RS + HD]);
+      float lt = 0.f, at = 0.f;
+#pragma unroll
+      for (int w = 0; w < 4; w++) {
+        const float* rr = red + ((size_t)w * rrows + r) * RS;
+        const float c = (rr[HD] == -INFINITY) ? 0.f : exp2f((rr[HD] - mn) * scale_log2);
+        lt += rr[HD + 1] * c;
+        at += rr[d] * c;
+      }
+      const int h = h0 + r;
+      if (a.n_splits == 1) {
+        ((bf16*)a.out)[(size_t)seq * a.nh * HD + (size_t)h * HD + d] = __float2bfloat16_rn(at / lt);
+      } else {
+        float* rec = a.ws + (((size_t)seq * a.nh + h) * a.n_splits + split) * (HD + 2);
+        rec[d] = at;
+        if (d == 0) {
+          rec[HD] = (mn == -INFINITY) ? -INFINITY : mn * a.scale;  // combine kernel works in exp()
+          rec[HD + 1] = lt;
+        }
+      }
+    }
+  };
 
-  for (int j = 0; j < n_tiles; j++) {
-    const int stage = j % STAGES;
-    if (j == 0) cp_async_wait<0>();  // Q and the post-wait tiles are in the newest group
+  reset_head();
+  const unsigned long long t_prol = tr.buf ? gtime() : 0ull;
+  unsigned long long t_first = 0, t_fin0 = 0;
+  for (int f = 0; f < F; f++) {
+    const int stage = f % STAGES;
+    const int hh = f / n_tiles, j = f - hh * n_tiles;
+    if (f == 0) cp_async_wait<0>();  // Q and the post-wait tiles are in the newest group
     else cp_async_wait<STAGES - 2>();
     __syncthreads();
-    if (j + STAGES - 1 < n_tiles) issue_kv(j + STAGES - 1, (j + STAGES - 1) % STAGES);
+    if (tr.buf && f == 0) t_first = gtime();
+    if (f + STAGES - 1 < F) issue_kv(f + STAGES - 1, (f + STAGES - 1) % STAGES);
     cp_async_commit();
     if (j == 0) {
       const int mi = lane >> 3, lr = lane & 7;
+      const uint32_t q = sQ + hh * 16 * HD * 2;
 #pragma unroll
       for (int ks = 0; ks < HD / 16; ks++)
-        ldsm_x4(sQ + swz<HD>(lr + (mi & 1) * 8, ks * 2 + (mi >> 1)), qf[ks][0], qf[ks][1], qf[ks][2],
+        ldsm_x4(q + swz<HD>(lr + (mi & 1) * 8, ks * 2 + (mi >> 1)), qf[ks][0], qf[ks][1], qf[ks][2],
                 qf[ks][3]);
+    }
+    if (has_new && j == n_tiles - 1) {
+      // the tile just landed with whatever the pool held at position len - 1: overwrite that
+      // row with the K / V built in the prologue
+      const int row = len - 1 - (tile_begin + j) * BN;
+      if (threadIdx.x < 2 * (HD / 8)) {
+        const int which = threadIdx.x / (HD / 8), c = threadIdx.x % (HD / 8);
+        st_shared16((which ? sV : sK) + stage * TILE_BYTES + swz<HD>(row, c),
+                    *reinterpret_cast<const uint4*>(s_newkv + ((size_t)hh * 2 + which) * HD + c * 8));
+      }
+      __syncthreads();
     }
     const int k0 = (tile_begin + j) * BN;
     const bool need_mask = k0 + BN > len;
-    attn_block<HD, WK / 8>(qf, sK + stage * TILE_BYTES, sV + stage * TILE_BYTES, warp * WK,
-                           k0 + warp * WK, limit, need_mask, scale_log2, m, l, o);
+    if (a.ablate != 1)
+      attn_block<HD, WK / 8>(qf, sK + stage * TILE_BYTES, sV + stage * TILE_BYTES, warp * WK,
+                             k0 + warp * WK, limit, need_mask, scale_log2, m, l, o);
+    if (j == n_tiles - 1) {
+      if (tr.buf && hh == 0) t_fin0 = gtime();
+      finish_head(hh);
+      reset_head();
+    }
   }
+  if (n_tiles == 0) finish_head(0);  // empty split: (0, -inf, 0) records
   cp_async_wait<0>();
-#pragma unroll
-  for (int i = 0; i < 2; i++) {
-    l[i] += __shfl_xor_sync(0xffffffffu, l[i], 1);
-    l[i] += __shfl_xor_sync(0xffffffffu, l[i], 2);
-  }
-  // merge the 4 warps (each covered different keys) through shared memory
-  __syncthreads();  // pipeline buffers are free now
-  float* red = reinterpret_cast<float*>(smem + 16 * HD * 2);  // [4][16][HD + 2]
-  constexpr int RS = HD + 2;
-#pragma unroll
-  for (int i = 0; i < 2; i++) {
-    float* rr = red + ((size_t)warp * 16 + g + 8 * i) * RS;
-#pragma unroll
-    for (int dn = 0; dn < HD / 8; dn++) {
-      rr[dn * 8 + 2 * t] = o[dn][2 * i];
-      rr[dn * 8 + 2 * t + 1] = o[dn][2 * i + 1];
-    }
-    if (t == 0) {
-      rr[HD] = m[i];
-      rr[HD + 1] = l[i];
-    }
-  }
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < rows * HD; idx += 128) {
-    const int r = idx / HD, d = idx % HD;
-    float mn = -INFINITY;
-#pragma unroll
-    for (int w = 0; w < 4; w++) mn = fmaxf(mn, red[((size_t)w * 16 + r) * RS + HD]);
-    float lt = 0.f, at = 0.f;
-#pragma unroll
-    for (int w = 0; w < 4; w++) {
-      const float* rr = red + ((size_t)w * 16 + r) * RS;
-      const float c = (rr[HD] == -INFINITY) ? 0.f : exp2f((rr[HD] - mn) * scale_log2);
-      lt += rr[HD + 1] * c;
-      at += rr[d] * c;
-    }
-    const int h = h0 + r;
-    if (a.n_splits == 1) {
-      ((bf16*)a.out)[(size_t)seq * a.nh * HD + (size_t)h * HD + d] = __float2bfloat16_rn(at / lt);
-    } else {
-      float* rec = a.ws + (((size_t)seq * a.nh + h) * a.n_splits + split) * (HD + 2);
-      rec[d] = at;
-      if (d == 0) {
-        rec[HD] = (mn == -INFINITY) ? -INFINITY : mn * a.scale;  // combine kernel works in exp()
-        rec[HD + 1] = lt;
-      }
-    }
-  }
-  if (threadIdx.x == 0) trace_rec(tr, t_entry, t_wait, 0);
+  if (threadIdx.x == 0 && tr.buf)
+    trace_rec(tr, t_entry, t_wait,
+              (((t_prol - t_wait) & 0x1fffff) << 42) | (((t_first - t_wait) & 0x1fffff) << 21) |
+                  ((t_fin0 - t_wait) & 0x1fffff));
 }
 
 // ------------------------------------------------------------------ launchers
@@ -415,21 +579,54 @@ cudaError_t launch_attn_prefill_mma(cudaStream_t st, const AttnArgs& a) {
 }
 
 template <int HD, int BN, int STAGES>
-static cudaError_t decode_launch(cudaStream_t st, const AttnArgs& a, int G, int chunks) {
+static cudaError_t decode_launch(cudaStream_t st, AttnArgs a, int G, int chunks) {
   constexpr size_t pipe = (size_t)2 * STAGES * BN * HD * 2;
-  constexpr size_t red = (size_t)4 * 16 * (HD + 2) * 4;
-  constexpr size_t smem = 16 * HD * 2 + (pipe > red ? pipe : red);
-  cudaError_t e = cudaFuncSetAttribute(attn_decode_mma_kernel<HD, BN, STAGES>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
-  (void)launch_k(attn_decode_mma_kernel<HD, BN, STAGES>, dim3(dim3(a.n_seqs, a.nkv * chunks, a.n_splits)), dim3(128), smem, st, a, G, chunks, next_trace(4));
+  const size_t red = (size_t)4 * (G < 16 ? G : 16) * (HD + 2) * 4;
+  constexpr size_t smem_cap = 113 * 1024;  // two CTAs per SM
+  // pack kpc kv heads per CTA while the grid still covers ~1.6 CTAs per SM (one wave of the
+  // 2-per-SM residency) — only for small head groups, unsplit contexts
+  int kpc = 1;
+  if (chunks == 1 && a.n_splits == 1) {
+    int sm = a.sm_count > 0 ? a.sm_count : 148;
+    while (kpc < 4 && a.nkv % (kpc * 2) == 0 &&
+           (long)a.n_seqs * (a.nkv / (kpc * 2)) * 10 >= (long)sm * 16 &&
+           (size_t)(kpc * 2) * (16 * HD * 2 + 2 * HD * 2) + pipe + red <= smem_cap)
+      kpc *= 2;
+  }
+  static const int kpc_env = getenv("NVLLM_ATTN_KPC") ? atoi(getenv("NVLLM_ATTN_KPC")) : 0;
+  if (kpc_env > 0 && chunks == 1 && a.n_splits == 1 && a.nkv % kpc_env == 0) kpc = kpc_env;
+  const size_t q_bytes = (size_t)kpc * 16 * HD * 2;
+  const size_t body = kpc > 1 ? pipe + red : (pipe > red ? pipe : red);
+  a.newkv_off = (int)(q_bytes + body);
+  const size_t smem = q_bytes + body + (size_t)kpc * 2 * HD * 2;
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    cudaError_t e = cudaFuncSetAttribute(attn_decode_mma_kernel<HD, BN, STAGES>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    smem_set = smem;
+  }
+  (void)launch_k(attn_decode_mma_kernel<HD, BN, STAGES>,
+                 dim3(a.n_seqs, (a.nkv / kpc) * chunks, a.n_splits), dim3(128), smem, st, a, G,
+                 chunks, kpc, next_trace(4));
   return cudaGetLastError();
 }
-int attn_decode_mma_tile(int hd) { return hd == 64 ? 128 : 64; }
-cudaError_t launch_attn_decode_mma(cudaStream_t st, const AttnArgs& a) {
-  if (a.n_seqs <= 0) return cudaSuccess;
+int attn_decode_mma_tile(int hd) {
+  static const int bn_env = getenv("NVLLM_ATTN_BN") ? atoi(getenv("NVLLM_ATTN_BN")) : 0;
+  return hd == 64 ? (bn_env ? 64 : 128) : 64;
+}
+cudaError_t launch_attn_decode_mma(cudaStream_t st, const AttnArgs& a_in) {
+  if (a_in.n_seqs <= 0) return cudaSuccess;
+  static const int abl = getenv("NVLLM_ATTN_ABL") ? atoi(getenv("NVLLM_ATTN_ABL")) : 0;
+  AttnArgs a = a_in;
+  a.ablate = abl;
   const int G = a.nh / a.nkv, chunks = (G + 15) / 16;
-  if (a.hd == 64) return decode_launch<64, 128, 3>(st, a, G, chunks);
+  static const int bn_env = getenv("NVLLM_ATTN_BN") ? atoi(getenv("NVLLM_ATTN_BN")) : 0;
+  if (a.hd == 64) {
+    if (bn_env == 64) return decode_launch<64, 64, 3>(st, a, G, chunks);
+    if (bn_env == 644) return decode_launch<64, 64, 4>(st, a, G, chunks);
+    return decode_launch<64, 128, 3>(st, a, G, chunks);
+  }
   return decode_launch<128, 64, 3>(st, a, G, chunks);
 }
 

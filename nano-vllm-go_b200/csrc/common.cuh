@@ -193,4 +193,38 @@ __device__ __forceinline__ void trace_rec(const Trace& t, unsigned long long t0,
 __host__ __device__ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
+// sum of S split-K slices of 8 consecutive floats, slices `stride` apart; the loads of four
+// slices are issued together (one L2 round trip per group instead of one per slice)
+__device__ __forceinline__ void sum_partials8(const float* __restrict__ p, int S, size_t stride,
+                                              float (&acc)[8]) {
+#pragma unroll
+  for (int j = 0; j < 8; j++) acc[j] = 0.f;
+  int s = 0;
+  for (; s + 8 <= S; s += 8) {
+    float a[8][8];
+#pragma unroll
+    for (int q = 0; q < 8; q++) load8(p + (size_t)(s + q) * stride, a[q]);
+#pragma unroll
+    for (int q = 0; q < 8; q++)
+#pragma unroll
+      for (int j = 0; j < 8; j++) acc[j] += a[q][j];
+  }
+  for (; s + 4 <= S; s += 4) {
+    float a[8], b[8], c[8], d[8];
+    load8(p + (size_t)s * stride, a);
+    load8(p + (size_t)(s + 1) * stride, b);
+    load8(p + (size_t)(s + 2) * stride, c);
+    load8(p + (size_t)(s + 3) * stride, d);
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[j] = (((acc[j] + a[j]) + b[j]) + c[j]) + d[j];
+  }
+  for (; s < S; s++) {
+    float a[8];
+    load8(p + (size_t)s * stride, a);
+#pragma unroll
+    for (int j = 0; j < 8; j++) acc[j] += a[j];
+  }
+}
+
+
 }  // namespace nvllm

@@ -358,7 +358,13 @@ int forward_step(nvllm_handle* h) {
       return rc;
     void* kp = (char*)h->kpool + (size_t)l * kv_layer_bytes;
     void* vp = (char*)h->vpool + (size_t)l * kv_layer_bytes;
-    {
+    const bool fuse_rope = !is_prefill && attn_decode_fuses_rope(h->adt, h->kvdt, h->hd);
+    if (fuse_rope) {
+      at.qkv_p = qkv.p; at.qkv_S = qkv.S; at.qkv_stride = qkv.stride; at.qkv_ld = h->qkv_cols;
+      at.qkv_bias = lw.bqkv;
+      at.cosT = h->use_rope ? h->cosT : nullptr;
+      at.sinT = h->use_rope ? h->sinT : nullptr;
+    } else {
       ProfScope ps(h, NVLLM_K_ROPE_KV,
                    (double)T * h->qkv_cols * 4 * qkv.S + (double)T * h->q_cols * asz +
                        2.0 * T * h->kv_cols * kvsz, 0);

@@ -211,6 +211,19 @@ struct AttnArgs {
   const int* seq_len;  // [n_seqs] tokens incl. the new one
   int n_splits;
   float* ws;           // [n_seqs*nh*n_splits*(hd+2)] split partials
+  // decode with RoPE + KV append fused in (attention_mma.cu), qkv_p != null: the kernel builds
+  // Q and the new K / V row (position seq_len - 1) itself from the QKV GEMM's split-K partials
+  // [S][n_seqs][qkv_ld] (columns [Q heads | K heads | V heads]) — `q` is not read and the
+  // rope_kv kernel is not launched
+  const float* qkv_p;
+  int qkv_S;
+  size_t qkv_stride;
+  int qkv_ld;
+  const float* qkv_bias;  // [qkv_ld] or null
+  const float* cosT;      // [max_pos, hd/2] or null (no RoPE)
+  const float* sinT;
+  int newkv_off;          // set by the launcher: smem offset of the new K / V rows
+  int ablate;             // timing experiments only (NVLLM_ATTN_ABL): 1 = no math, 2 = no K/V loads
   // stream-K decode (attention_mma.cu): ticket per (seq, kv head, head chunk), zero between
   // kernels; total_tiles = host LOWER bound of the key tiles in the step (caps the grid)
   int* tickets;
@@ -227,6 +240,7 @@ int attn_decode_splits(int qdt, int kvdt, int n_seqs, int nh, int nkv, int hd, i
                        int sm_count);
 cudaError_t launch_attn_prefill(cudaStream_t st, const AttnArgs& a);
 cudaError_t launch_attn_decode(cudaStream_t st, const AttnArgs& a);
+bool attn_decode_fuses_rope(int qdt, int kvdt, int hd);
 // attention_mma.cu (bf16, hd 64 / 128)
 bool attn_mma_supported(int qdt, int kvdt, int hd);
 int attn_decode_mma_tile(int hd);

@@ -58,6 +58,11 @@ for sq in seqs:
         d = (r[:, 6].astype(np.int64) - np.maximum(r[:, 5], r[:, 4]).astype(np.int64)) / 1e3
         extra = " per-CTA dur p10/50/90/max: " + "/".join(f"{np.percentile(d, q):.1f}" for q in (10, 50, 90, 100))
         extra += f" SMs used {len(set(int(x) for x in r[:,3]))}"
+        a_ = ((ex >> np.uint64(42)) & np.uint64(0x1fffff)).astype(np.int64)
+        b_ = ((ex >> np.uint64(21)) & np.uint64(0x1fffff)).astype(np.int64)
+        c_ = (ex & np.uint64(0x1fffff)).astype(np.int64)
+        extra += (f" | after wait: prologue_done {np.median(a_)/1e3:.2f} first_tile {np.median(b_)/1e3:.2f} "
+                  f"head0_tiles_done {np.median(c_)/1e3:.2f}")
     if kid == 2:
         extra = (f" per-CTA median: loads_done {np.median((ex >> np.uint64(32)).astype(np.int64))/1e3:.2f} "
                  f"reduce_done {np.median((ex & np.uint64(0xffffffff)).astype(np.int64))/1e3:.2f} "
