@@ -292,9 +292,8 @@ def main():
     ap.add_argument("--no-profile", action="store_true")
     args = ap.parse_args()
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    D = nvllm_pkg.sub("dist")
+    rank, world, local_rank = D.env_ranks()
     spec = dict(CONFIGS[args.config])
     for k, v in (("model", args.model), ("batch", args.batch), ("prompt_len", args.prompt_len),
                  ("decode_steps", args.decode_steps)):
@@ -306,8 +305,7 @@ def main():
     if args.config == 4 and cfg.max_seq_len < need_pos:
         from dataclasses import replace
         cfg = replace(cfg, max_seq_len=need_pos + 31)
-    tp = world if (spec["tp"] and world > 1) else 1
-    replicas = 1 if tp > 1 else world
+    tp, replicas = D.plan(world, spec["tp"])
     config = {"workload": f"{cfg.name} bf16 weights/fp32 accumulate, {spec['label']} "
                           f"(BASELINE.json configs[{args.config - 1}])",
               "global_batch": spec["batch"] * replicas, "prompt_len": spec["prompt_len"],
@@ -358,13 +356,11 @@ def main():
 
     # replicas draw disjoint request sets; the ranks of a tensor-parallel group share one
     job = Job(cfg, spec["batch"], spec["prompt_len"], spec["decode_steps"],
-              seed0=4321 + (0 if tp > 1 else 1000 * rank), shared_prefix=spec["shared_prefix"])
+              seed0=D.request_seed(4321, rank, tp), shared_prefix=spec["shared_prefix"])
     keep = [] if (rank == 0 and not args.no_cpu_baseline) else None
     tp_id = None
     if tp > 1:
-        box = [nvllm_pkg.sub("lib").tp_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(box, src=0)
-        tp_id = box[0]
+        tp_id = D.share_tp_id(dist, rank, nvllm_pkg.sub("lib").tp_unique_id)
     run = make_runner(cfg, job, device, keep, tp_size=tp, tp_rank=rank if tp > 1 else 0, tp_id=tp_id)
     mem = run.memory_info()
 
@@ -388,11 +384,8 @@ def main():
     ms = run.timer_stop()
     clocks = sampler.stop()
     barrier()
-    if dist is not None:
-        t = torch.tensor([ms], device=f"cuda:{device}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
-    value = replicas * job.tokens_per_step * args.steps / (ms / 1e3)
+    ms = D.reduce_max(dist, ms, f"cuda:{device}")
+    value = D.aggregate_throughput(job.tokens_per_step, replicas, args.steps, ms)
 
     # ---- e2e leg: host buffers through nvllm_run every step
     job.run_e2e(run)  # warm (staging buffers sized)
@@ -405,11 +398,8 @@ def main():
         d2h += b
     torch.cuda.synchronize(device)
     e2e_s = time.perf_counter() - t0
-    if dist is not None:
-        t = torch.tensor([e2e_s], device=f"cuda:{device}")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e = replicas * job.tokens_per_step * args.steps / e2e_s
+    e2e_s = D.reduce_max(dist, e2e_s, f"cuda:{device}")
+    e2e = D.aggregate_throughput(job.tokens_per_step, replicas, args.steps, e2e_s * 1e3)
 
     # ---- separate profiled pass: per-kernel-class time, phase split, roofline
     peaks = load_peaks()
