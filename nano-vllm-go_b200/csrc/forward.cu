@@ -272,12 +272,19 @@ static int tp_reduce_pending(nvllm_handle* h, Pending* p1, Pending* p2, int T) {
   {
     const double n = (double)T * h->H * 4;
     ProfScope ps(h, NVLLM_K_COMM, n * (a->S + (b ? b->S : 0) + 1) + 2.0 * n, 0);
-    LAUNCH(h, launch_tp_partial(h->stream, T, h->H, a->p, a->S, a->stride, a->m, a->bias,
-                                b ? b->p : nullptr, b ? b->S : 0, b ? b->stride : 0,
-                                b ? b->m : 0.f, b ? b->bias : nullptr, w.tp_buf));
-    int rc = tp_all_reduce_f32(h, w.tp_buf, (size_t)T * h->H);
-    if (rc) return rc;
-    h->launches++;
+    if (tp_p2p_fits(h, (size_t)T * h->H)) {
+      // one kernel: partial sums + all-reduce over NVLink peer memory (tp.cu)
+      LAUNCH(h, launch_tp_allreduce_p2p(h, T, h->H, a->p, a->S, a->stride, a->m, a->bias,
+                                        b ? b->p : nullptr, b ? b->S : 0, b ? b->stride : 0,
+                                        b ? b->m : 0.f, b ? b->bias : nullptr, w.tp_buf));
+    } else {
+      LAUNCH(h, launch_tp_partial(h->stream, T, h->H, a->p, a->S, a->stride, a->m, a->bias,
+                                  b ? b->p : nullptr, b ? b->S : 0, b ? b->stride : 0,
+                                  b ? b->m : 0.f, b ? b->bias : nullptr, w.tp_buf));
+      int rc = tp_all_reduce_f32(h, w.tp_buf, (size_t)T * h->H);
+      if (rc) return rc;
+      h->launches++;
+    }
   }
   if (p1) *p1 = Pending();
   if (p2) *p2 = Pending();

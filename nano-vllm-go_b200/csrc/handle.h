@@ -100,6 +100,12 @@ struct nvllm_handle {
   int Vl = 0;        // LM-head rows per rank (slot width of the gathered logits), multiple of 8
   int Vl_valid = 0;  // rows of this rank's slice that exist (last rank may be short)
   void* nccl = nullptr;  // ncclComm_t
+  // NVLink peer-memory all-reduce (tp.cu): this rank's region, the peers' mapped regions
+  float* p2p_peer[8] = {nullptr};  // [rank] base pointers (own entry = p2p_own)
+  float* p2p_own = nullptr;
+  size_t p2p_cap = 0;              // floats per data buffer
+  uint32_t p2p_epoch = 0;
+  bool p2p_ok = false;
   // weights
   void *wte = nullptr, *wpe = nullptr, *lm_head = nullptr;
   bool lm_head_owned = false;
@@ -164,6 +170,12 @@ int tp_unique_id(uint8_t out_id[128]);
 int tp_init(nvllm_handle* h, const uint8_t* id);  // ncclCommInitRank(tp, id, rank)
 void tp_destroy(nvllm_handle* h);
 int tp_all_reduce_f32(nvllm_handle* h, float* buf, size_t count);           // in place, sum
+// peer-memory path: true when the fused partial-sum + all-reduce kernel can take T x H floats
+bool tp_p2p_fits(const nvllm_handle* h, size_t count);
+cudaError_t launch_tp_allreduce_p2p(nvllm_handle* h, int T, int H, const float* p1, int S1,
+                                    size_t stride1, float m1, const float* bias1, const float* p2,
+                                    int S2, size_t stride2, float m2, const float* bias2,
+                                    float* out);
 int tp_all_gather_f32(nvllm_handle* h, float* buf, size_t count_per_rank);  // in place, slot = rank
 
 #define NV_CHECK(h, expr)                                                                   \

@@ -21,14 +21,18 @@ def _n_gpus():
     return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
 
-def _launch(tp, case, prec, timeout=600):
+def _launch(tp, case, prec, timeout=600, p2p=True, two_shot=False):
+    """p2p: the fused partial-sum + all-reduce kernel over NVLink peer memory (default);
+    False forces the NCCL all-reduce path (NVLLM_TP_P2P=0)."""
     with tempfile.TemporaryDirectory() as td:
         id_file = os.path.join(td, "tp_id")
         procs = []
+        env = dict(os.environ, NVLLM_TP_P2P="1" if p2p else "0", NVLLM_TP_DEBUG="1",
+                   NVLLM_TP_TWOSHOT="1" if two_shot else "0")
         for r in range(tp):
             procs.append(subprocess.Popen(
                 [sys.executable, os.path.join(HERE, "tp_worker.py"), str(r), str(tp), id_file, case,
-                 str(prec)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+                 str(prec)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env))
         outs = []
         try:
             for p in procs:
@@ -40,6 +44,8 @@ def _launch(tp, case, prec, timeout=600):
                     p.kill()
         for r, (p, out) in enumerate(zip(procs, outs)):
             assert p.returncode == 0 and "TP_OK" in out, f"rank {r} failed:\n{out[-3000:]}"
+            if p2p:
+                assert "peer-memory all-reduce enabled" in out, f"rank {r} fell back to NCCL:\n{out[-2000:]}"
     return outs
 
 
@@ -50,6 +56,21 @@ def test_tp2_matches_oracle(case, prec):
     if _n_gpus() < 2:
         pytest.skip("needs 2 GPUs")
     _launch(2, case, prec)
+
+
+@pytest.mark.parametrize("case,prec", [("falcon", C.PREC_FP32), ("llama", C.PREC_BF16)])
+def test_tp2_nccl_path_matches_oracle(case, prec):
+    if _n_gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    _launch(2, case, prec, p2p=False)
+
+
+@pytest.mark.parametrize("case,prec", [("falcon", C.PREC_FP32), ("llama", C.PREC_BF16)])
+def test_tp2_two_shot_peer_kernel_matches_oracle(case, prec):
+    """The reduce-scatter + all-gather kernel over peer memory (opt-in: NVLLM_TP_TWOSHOT=1)."""
+    if _n_gpus() < 2:
+        pytest.skip("needs 2 GPUs")
+    _launch(2, case, prec, two_shot=True)
 
 
 @pytest.mark.parametrize("case,prec", [("falcon", C.PREC_BF16), ("llama", C.PREC_FP32)])
