@@ -5,6 +5,7 @@
 #include <cuda_fp16.h>
 
 #include "common.cuh"
+#include "moe_route.cuh"
 #include "kernels.h"
 
 namespace nvllm {
@@ -92,7 +93,20 @@ __global__ void norm_kernel(NormArgs a, Trace tr) {
     load8(xr + i, v);
     if (a.p1) {
       float acc[8];
-      sum_partials8(a.p1 + (size_t)r * H + i, a.S1, a.stride1, acc);
+      if (a.comb_rows) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[j] = 0.f;
+        for (int s = 0; s < a.comb_k; s++) {
+          const int prow = a.comb_rows[(size_t)r * a.comb_k + s];
+          const float cw = a.comb_w[(size_t)r * a.comb_k + s];
+          float pv[8];
+          load8(a.p1 + (size_t)prow * H + i, pv);
+#pragma unroll
+          for (int j = 0; j < 8; j++) acc[j] += cw * pv[j];
+        }
+      } else {
+        sum_partials8(a.p1 + (size_t)r * H + i, a.S1, a.stride1, acc);
+      }
       if (a.bias1) {
         float p[8];
         if (i == i0) {
@@ -176,6 +190,12 @@ __global__ void norm_kernel(NormArgs a, Trace tr) {
     }
     store8(yr + i, o);
     if (a.y_f32) store8(a.y_f32 + (size_t)orow * H + i, o);
+    if (a.router) store8(row + i, o);  // each thread overwrites only what it alone reads
+  }
+  if (a.router) {
+    __shared__ float probs[MOE_MAX_E];
+    __syncthreads();
+    moe_route_row(row, a.router, H, a.E, a.topk, probs, (size_t)orow, a.topk_idx, a.topk_w);
   }
   if (threadIdx.x == 0 && tr.buf)
     trace_rec(tr, t_entry, t_wait, ((t_loads - t_wait) << 32) | (t_red - t_wait));

@@ -169,6 +169,18 @@ struct Pending {  // a GEMM result still to be added to the residual stream
   size_t stride = 0;
   float m = 1.f;
   const float* bias = nullptr;
+  // mixture-of-experts: p holds the expert outputs by sorted row; the addend of token r is
+  // sum_s comb_w[r, s] * p[comb_rows[r, s], :]  (fused into the consuming norm kernel)
+  const int* comb_rows = nullptr;
+  const float* comb_w = nullptr;
+  int comb_k = 0;
+};
+
+struct RouterArgs {  // expert routing fused into the FFN norm of a MoE layer
+  const float* R = nullptr;
+  int E = 0, k = 0;
+  int* topk_idx = nullptr;
+  float* topk_w = nullptr;
 };
 
 #define LAUNCH(h, expr)                                                                       \
@@ -238,14 +250,23 @@ static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int 
 }
 
 static int run_norm(nvllm_handle* h, float* x, Pending* p1, Pending* p2, const float* w,
-                    const float* b, void* y, float* y_f32, const int* row_idx, int n_rows) {
+                    const float* b, void* y, float* y_f32, const int* row_idx, int n_rows,
+                    const RouterArgs* route = nullptr) {
   NormArgs a{};
   a.x = x;
   double bytes = (double)n_rows * h->H * (4 + dt_size(h->adt));
   if (p1 && p1->p) {
     a.p1 = p1->p; a.S1 = p1->S; a.stride1 = p1->stride; a.m1 = p1->m; a.bias1 = p1->bias;
-    bytes += (double)n_rows * h->H * 4 * (p1->S + 1);
+    a.comb_rows = p1->comb_rows; a.comb_w = p1->comb_w; a.comb_k = p1->comb_k;
+    bytes += (double)n_rows * h->H * 4 * ((p1->comb_rows ? p1->comb_k : p1->S) + 1);
   }
+  if (route && route->R) {
+    a.router = route->R; a.E = route->E; a.topk = route->k;
+    a.topk_idx = route->topk_idx; a.topk_w = route->topk_w;
+    bytes += (double)route->E * h->H * 4;
+  }
+  if (p2 && p2->p && p2->comb_rows)
+    return set_err(h, NVLLM_ERR_INVALID, "MoE layers in a parallel block are not supported");
   if (p2 && p2->p) {
     a.p2 = p2->p; a.S2 = p2->S; a.stride2 = p2->stride; a.m2 = p2->m; a.bias2 = p2->bias;
     bytes += (double)n_rows * h->H * 4 * p2->S;
@@ -401,8 +422,13 @@ int forward_step(nvllm_handle* h) {
       ffn_out = w.ws_c;  // FFN reads the same normed input (generic_model.go:395-418)
     } else {
       if ((rc = tp_reduce_pending(h, &p1, nullptr, T))) return rc;
-      if ((rc = run_norm(h, w.x, &p1, nullptr, lw.ffn_norm_w, lw.ffn_norm_b, w.xn,
-                         h->moe ? w.xn_f32 : nullptr, nullptr, T)))
+      RouterArgs ra;
+      if (h->moe) {
+        ra.R = lw.router; ra.E = h->E; ra.k = h->topk;
+        ra.topk_idx = w.topk_idx; ra.topk_w = w.topk_w;
+      }
+      if ((rc = run_norm(h, w.x, &p1, nullptr, lw.ffn_norm_w, lw.ffn_norm_b, w.xn, nullptr, nullptr,
+                         T, &ra)))
         return rc;
     }
     Pending& pf = h->parallel ? p2 : p1;
@@ -413,15 +439,20 @@ int forward_step(nvllm_handle* h) {
       const bool tc = h->adt == DT_BF16 && h->wdt == DT_BF16 && tc5_supported(P, 2 * I, H) &&
                       tc5_supported(P, H, I) && (I % 8) == 0;
       const int tile = tc ? tc5_group_tile((P + h->E - 1) / h->E) : 64;
+      // the routing itself (softmax, top-k) ran inside the FFN norm kernel above
+      const bool sg = tc && moe_sort_gather_fits(T, k, h->E, H);
       {
-        ProfScope ps(h, NVLLM_K_MOE_ROUTE, (double)T * H * 4 + (double)h->E * H * 4, 2.0 * T * H * h->E);
-        LAUNCH(h, launch_moe_router(st, w.xn_f32, lw.router, T, H, h->E, k, w.topk_idx, w.topk_w));
-        LAUNCH(h, launch_moe_sort(st, w.topk_idx, T, k, h->E, w.sort, w.max_tiles, tile));
+        ProfScope ps(h, NVLLM_K_MOE_ROUTE, (double)P * 4 * 4 + (sg ? (double)P * H * 2 * 2 : 0.0), 0);
+        if (sg)
+          LAUNCH(h, launch_moe_sort_gather(st, w.topk_idx, T, k, h->E, w.sort, w.max_tiles, tile, H,
+                                           w.xn, w.moe_xs));
+        else
+          LAUNCH(h, launch_moe_sort(st, w.topk_idx, T, k, h->E, w.sort, w.max_tiles, tile));
       }
       const double wsz = dt_size(h->wdt);
       const int e_touched = std::min(h->E, P);
       if (tc) {
-        {
+        if (!sg) {
           ProfScope ps(h, NVLLM_K_MOE_MISC, (double)P * H * 2 * 2, 0);
           LAUNCH(h, launch_moe_gather(st, P, H, w.xn, w.sort.a_rows, w.moe_xs));
         }
@@ -477,11 +508,9 @@ int forward_step(nvllm_handle* h) {
           LAUNCH(h, launch_gemm_simt(st, g2));
         }
       }
-      {
-        ProfScope ps(h, NVLLM_K_MOE_MISC, (double)P * H * 4 + (double)T * H * 4, 0);
-        LAUNCH(h, launch_moe_combine(st, T, k, H, w.moe_Y, w.sort.pair_row, w.topk_w, w.moe_y));
-      }
-      pf.p = w.moe_y; pf.S = 1; pf.stride = 0; pf.bias = nullptr;
+      // the weighted combine (moe.go:116-118) happens inside the norm kernel that consumes pf
+      pf.p = w.moe_Y; pf.S = 1; pf.stride = 0; pf.bias = nullptr;
+      pf.comb_rows = w.sort.pair_row; pf.comb_w = w.topk_w; pf.comb_k = k;
     } else {
       Pending h1;
       if ((rc = run_gemm(h, w.xn, H, lw.w1, T, h->w1_cols, H, 1.f, w.ws_a, w.ws_a_floats,

@@ -49,6 +49,19 @@ struct NormArgs {
   const int* row_idx;  // optional gather: output row i reads x row row_idx[i]
   int n_rows;
   int H;
+  // mixture-of-experts fusions (moe.cu holds the stand-alone kernels)
+  //  * comb_rows != null: the first addend is the weighted combine of the expert outputs,
+  //    sum_s comb_w[r, s] * p1[comb_rows[r, s], :] in slot order (moe.go:116-118), instead of a
+  //    split-K sum (S1 / stride1 unused)
+  const int* comb_rows;   // [*, comb_k] row of p1 holding (token r, slot s)
+  const float* comb_w;    // [*, comb_k]
+  int comb_k;
+  //  * router != null: route the normed row (fp32, before rounding) — softmax over all E
+  //    experts, top-k, renormalise (moe.go:63-103) — and write topk_idx / topk_w [n_rows, k]
+  const float* router;    // [E, H] fp32
+  int E, topk;
+  int* topk_idx;
+  float* topk_w;
 };
 cudaError_t launch_norm(cudaStream_t st, const NormArgs& a);
 
@@ -270,6 +283,11 @@ struct MoeSortBufs {
 };
 cudaError_t launch_moe_sort(cudaStream_t st, const int* topk_idx, int T, int k, int E,
                             const MoeSortBufs& b, int max_tiles, int tile);
+// sort + gather in one launch for decode-sized batches (moe_sort_gather_fits)
+bool moe_sort_gather_fits(int T, int k, int E, int H);
+cudaError_t launch_moe_sort_gather(cudaStream_t st, const int* topk_idx, int T, int k, int E,
+                                   const MoeSortBufs& b, int max_tiles, int tile, int H,
+                                   const void* x, void* xs);
 // xs[row, :] = x[a_rows[row], :]  (bf16 rows of H elements)
 cudaError_t launch_moe_gather(cudaStream_t st, int rows, int H, const void* x, const int* a_rows,
                               void* xs);

@@ -2,17 +2,16 @@
 // router (matmul + softmax over ALL experts + top-k + renormalise, moe.go:63-103), grouping
 // of the (token, slot) pairs by expert into 64-row tiles, the GLU between the two expert
 // GEMMs (moe.go:203-212) and the weighted combine (moe.go:116-118).
+#include <algorithm>
+
 #include "common.cuh"
 #include "kernels.h"
+#include "moe_route.cuh"
 
 namespace nvllm {
 
-constexpr int MOE_MAX_E = 256;
-
-// One CTA (4 warps) per token.  Warp w computes the logits of experts w, w+4, ...;
-// warp 0 then does softmax and k rounds of first-max selection (ties -> lower index, which
-// is what a stable descending sort gives; the reference's sort.Slice is unstable, ties have
-// measure zero with random-init weights).
+// One CTA (4 warps) per token: the stand-alone router (fp32 parity mode and callers that did
+// not fuse it into the norm).
 __global__ void __launch_bounds__(128)
 moe_router_kernel(const float* __restrict__ x, const float* __restrict__ R, int H, int E, int k,
                   int* __restrict__ topk_idx, float* __restrict__ topk_w) {
@@ -20,72 +19,7 @@ moe_router_kernel(const float* __restrict__ x, const float* __restrict__ R, int 
   pdl_wait();
   __shared__ float probs[MOE_MAX_E];
   const int t = blockIdx.x;
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const float* xr = x + (size_t)t * H;
-  for (int e = warp; e < E; e += 4) {
-    const float* rr = R + (size_t)e * H;
-    float acc = 0.f;
-    for (int i = lane * 8; i < H; i += 256) {
-      float a[8], b[8];
-      load8(xr + i, a);
-      load8(rr + i, b);
-#pragma unroll
-      for (int j = 0; j < 8; j++) acc = fmaf(a[j], b[j], acc);
-    }
-    acc = warp_sum(acc);
-    if (lane == 0) probs[e] = acc;
-  }
-  __syncthreads();
-  if (warp != 0) return;
-  // tensor.go:128-155 softmax over all E
-  float mx = -INFINITY;
-  for (int e = lane; e < E; e += 32) mx = fmaxf(mx, probs[e]);
-  mx = warp_max(mx);
-  float sum = 0.f;
-  for (int e = lane; e < E; e += 32) {
-    float p = expf(probs[e] - mx);
-    probs[e] = p;
-    sum += p;
-  }
-  sum = warp_sum(sum);
-  __syncwarp();
-  for (int e = lane; e < E; e += 32) probs[e] = probs[e] / sum;
-  __syncwarp();
-  // top-k by repeated first-max
-  float sel_p = 0.f;  // lane s keeps the s-th selection (k <= 32)
-  int sel_i = 0;
-  float ksum = 0.f;
-  for (int s = 0; s < k; s++) {
-    float bv = -1.f;
-    int bi = 0x7fffffff;
-    for (int e = lane; e < E; e += 32) {
-      float p = probs[e];
-      if (p > bv) {
-        bv = p;
-        bi = e;
-      }
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (ov > bv || (ov == bv && oi < bi)) {
-        bv = ov;
-        bi = oi;
-      }
-    }
-    if (lane == s) {
-      sel_p = bv;
-      sel_i = bi;
-    }
-    ksum += bv;  // moe.go:98-103: sum in descending order
-    if (lane == 0) probs[bi] = -2.f;
-    __syncwarp();
-  }
-  if (lane < k) {
-    topk_idx[(size_t)t * k + lane] = sel_i;
-    topk_w[(size_t)t * k + lane] = sel_p / ksum;
-  }
+  moe_route_row(x + (size_t)t * H, R, H, E, k, probs, (size_t)t, topk_idx, topk_w);
 }
 
 cudaError_t launch_moe_router(cudaStream_t st, const float* x, const float* R, int T, int H, int E,
@@ -172,6 +106,105 @@ cudaError_t launch_moe_gather(cudaStream_t st, int rows, int H, const void* x, c
   const int blocks = (int)min((size_t)148 * 8, (nvec + 255) / 256);
   (void)launch_k(moe_gather_kernel, dim3(blocks), dim3(256), 0, st, nvec, vpr, (const uint4*)x,
                  a_rows, (uint4*)xs);
+  return cudaGetLastError();
+}
+
+// Decode-sized batches (<= MOE_SG_MAX_P pairs, <= MOE_SG_MAX_E experts): sort and gather in ONE
+// launch.  Every CTA recomputes the same stable counting sort of the pairs in shared memory
+// (row of pair p = offset of its expert + number of earlier pairs routed to that expert —
+// deterministic, so all CTAs agree), CTA 0 publishes the lists the grouped GEMMs and the
+// combine read, and each CTA copies its share of the sorted activation rows.
+constexpr int MOE_SG_MAX_P = 4096, MOE_SG_MAX_E = 64;
+__global__ void __launch_bounds__(1024)
+moe_sort_gather_kernel(const int* __restrict__ topk_idx, int n_pairs, int k, int E, MoeSortBufs b,
+                       int max_tiles, int tile, int vpr, const uint4* __restrict__ x,
+                       uint4* __restrict__ xs) {
+  pdl_launch_dependents();
+  __shared__ int s_cnt[MOE_SG_MAX_E];
+  __shared__ int s_off[MOE_SG_MAX_E + 1];
+  __shared__ int s_base[MOE_SG_MAX_E];
+  __shared__ int s_wcnt[32][MOE_SG_MAX_E];
+  __shared__ int s_inv[MOE_SG_MAX_P];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < MOE_SG_MAX_E) s_cnt[tid] = s_base[tid] = 0;
+  pdl_wait();
+  __syncthreads();
+  for (int p = tid; p < n_pairs; p += 1024) atomicAdd(&s_cnt[topk_idx[p]], 1);
+  __syncthreads();
+  if (tid == 0) {
+    int run = 0, nt = 0;
+    const bool pub = blockIdx.x == 0;
+    for (int e = 0; e < E; e++) {
+      s_off[e] = run;
+      if (pub) {
+        b.counts[e] = s_cnt[e];
+        b.offsets[e] = run;
+        for (int r = 0; r < s_cnt[e] && nt < max_tiles; r += tile) {
+          b.tile_expert[nt] = e;
+          b.tile_row0[nt] = run + r;
+          b.tile_rows[nt] = min(tile, s_cnt[e] - r);
+          nt++;
+        }
+      }
+      run += s_cnt[e];
+    }
+    s_off[E] = run;
+    if (pub) {
+      b.offsets[E] = run;
+      *b.n_tiles = nt;
+    }
+  }
+  for (int c0 = 0; c0 < n_pairs; c0 += 1024) {
+    for (int i = tid; i < 32 * MOE_SG_MAX_E; i += 1024) (&s_wcnt[0][0])[i] = 0;
+    __syncthreads();
+    const int p = c0 + tid;
+    const int e = p < n_pairs ? topk_idx[p] : -1;
+    const unsigned same = __match_any_sync(0xffffffffu, e);
+    const int rank = __popc(same & ((1u << lane) - 1));
+    if (e >= 0 && rank == 0) s_wcnt[warp][e] = __popc(same);
+    __syncthreads();
+    if (tid < E) {  // exclusive prefix over the warps, continuing from the earlier chunks
+      int run = s_base[tid];
+      for (int w = 0; w < 32; w++) {
+        const int n = s_wcnt[w][tid];
+        s_wcnt[w][tid] = run;
+        run += n;
+      }
+      s_base[tid] = run;
+    }
+    __syncthreads();
+    if (e >= 0) {
+      const int row = s_off[e] + s_wcnt[warp][e] + rank;
+      s_inv[row] = p;
+      if (blockIdx.x == 0) {
+        b.sorted_pair[row] = p;
+        b.pair_row[p] = row;
+        b.a_rows[row] = p / k;
+      }
+    }
+    __syncthreads();
+  }
+  const int rpc = (n_pairs + gridDim.x - 1) / gridDim.x;
+  const int r0 = blockIdx.x * rpc;
+  for (int idx = tid; idx < rpc * vpr; idx += 1024) {
+    const int r = r0 + idx / vpr, j = idx % vpr;
+    if (r < n_pairs) xs[(size_t)r * vpr + j] = x[(size_t)(s_inv[r] / k) * vpr + j];
+  }
+}
+
+bool moe_sort_gather_fits(int T, int k, int E, int H) {
+  return (long)T * k <= MOE_SG_MAX_P && E <= MOE_SG_MAX_E && (H % 8) == 0;
+}
+cudaError_t launch_moe_sort_gather(cudaStream_t st, const int* topk_idx, int T, int k, int E,
+                                   const MoeSortBufs& b, int max_tiles, int tile, int H,
+                                   const void* x, void* xs) {
+  if (T <= 0) return cudaSuccess;
+  if (!moe_sort_gather_fits(T, k, E, H) || tile <= 0) return cudaErrorInvalidValue;
+  const int vpr = H / 8;
+  const long work = (long)T * k * vpr;
+  const int grid = (int)std::max(1L, std::min(148L, work / 2048));
+  (void)launch_k(moe_sort_gather_kernel, dim3(grid), dim3(1024), 0, st, topk_idx, T * k, k, E, b,
+                 max_tiles, tile, vpr, (const uint4*)x, (uint4*)xs);
   return cudaGetLastError();
 }
 

@@ -389,8 +389,10 @@ def test_profile_reports_every_kernel_class():
         run.set_profile(True)
         run.run_flat([prompt], True, [0], [[0]], [0.0])
         prof = run.get_profile()
+        # (the router runs inside the FFN norm; sort + gather are one "moe_route" launch at this
+        # size and the weighted combine is part of the next norm: no "moe_misc" launches)
         for k in ("embed", "norm", "gemm_tc5", "rope_kv", "attn_prefill", "moe_route", "moe_gemm",
-                  "moe_misc", "sample"):
+                  "sample"):
             assert k in prof and prof[k]["ms"] > 0 and prof[k]["bytes"] > 0, k
         assert prof["gemm_tc5"]["launches"] == 2 * cfg.num_layers
         run.set_profile(False)
