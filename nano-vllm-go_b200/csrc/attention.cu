@@ -408,7 +408,10 @@ cudaError_t launch_attn_decode(cudaStream_t st, const AttnArgs& a) {
   if (attn_mma_supported(a.qdt, a.kvdt, a.hd) && a.tickets && use_sk)
     return launch_attn_decode_sk(st, a, a.tickets, a.sm_count, a.total_tiles);
   if (attn_mma_supported(a.qdt, a.kvdt, a.hd)) {
-    cudaError_t e = launch_attn_decode_mma(st, a);
+    // small head groups: TMA-fed, keys-as-M-rows kernel (attention_dec.cu); Falcon's 71-head
+    // MQA group keeps the 16-query-row kernel
+    cudaError_t e = attn_decode_t_supported(a) ? launch_attn_decode_t(st, a)
+                                               : launch_attn_decode_mma(st, a);
     if (e != cudaSuccess || a.n_splits == 1) return e;
     (void)launch_k(attn_combine_kernel<bf16>, dim3(dim3(a.n_seqs, a.nh)), dim3(min(128, a.hd)), 0, st, a);
     return cudaGetLastError();

@@ -1,0 +1,494 @@
+// attention_dec.cu — bf16 paged decode attention for small query-head groups
+// (G = n_heads / n_kv_heads <= 8: GPT-2 MHA, Llama / Granite GQA), sm_100a.
+//
+// Same semantics as attention_mma.cu's decode kernel (reference attention.go:354-421: scores =
+// (q.k)*scale, keys after the query masked, softmax, P.V; q head h uses kv head h / G) and the
+// same fused prologue (split-K sum of the QKV GEMM partials + bias, rotate_half RoPE
+// rope.go:153-205, K/V append through the block table).  What differs is how the stream is fed
+// and which way round the MMAs sit — the decode step's attention is a pure HBM stream and the
+// older kernel was issue-bound at ~900 instructions per warp per 128-key tile:
+//
+//  * K/V tiles arrive by TMA (one elected lane of a dedicated producer warp issues 2*HD/64
+//    bulk tensor copies per tile, SWIZZLE_128B, completion on an mbarrier) — no per-thread
+//    cp.async address arithmetic; the consumer warps never issue a load.  full/empty mbarrier
+//    ring, no __syncthreads per tile, so the four consumer warps drift freely.
+//  * "keys are the M rows": S^T[key][head] = K[key][d] . Q^T[d][head] with the K tile as the
+//    ldmatrix-fed A operand and the (<= 8, zero-padded) query heads as the 8 columns of the
+//    m16n8k16 B operand held in registers; O^T[d][head] = V^T[d][key] . P^T[key][head] with V
+//    through ldmatrix.trans and P^T turned from accumulator layout into a B fragment by
+//    movmatrix.  Per 16 keys x 64 dims: 4 + 4 ldmatrix.x4, 4 + 4 mma, 2 movmatrix — a 16-row
+//    query tile with 4 real rows would need twice the MMAs and 4x the accumulator registers.
+//  * the row maximum is a 3-shuffle reduction over the 8 key lanes; row sums stay per-thread
+//    partials until the head is finished.
+#include <stdlib.h>
+
+#include "common.cuh"
+#include "kernels.h"
+#include "mma.cuh"
+#include "tma.cuh"
+
+namespace nvllm {
+
+constexpr int DT_CONSUMERS = 4;                       // consumer warps
+constexpr int DT_THREADS = (DT_CONSUMERS + 1) * 32;   // + the TMA producer warp
+
+__device__ __forceinline__ void consumer_bar() {
+  asm volatile("bar.sync 1, %0;" ::"n"(DT_CONSUMERS * 32) : "memory");
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+// 16-byte chunk c of key row r in a TMA-written tile: HD/64 panels of [BN][128 B], SWIZZLE_128B
+template <int BN>
+__device__ __forceinline__ uint32_t tile_off_t(int r, int c) {
+  return (uint32_t)((c >> 3) * (BN * 128) + r * 128 + (((c & 7) ^ (r & 7)) << 4));
+}
+
+template <int HD>
+struct DecSmem {
+  static constexpr int QROW = HD * 2 + 16;  // padded query row: conflict-free 32-bit reads
+  static constexpr int Q_BYTES = 8 * QROW;  // per packed kv head
+  static constexpr int RS = HD + 2;
+  static constexpr int RED_BYTES = DT_CONSUMERS * 8 * RS * 4;
+};
+
+template <int HD, int BN, int STAGES>
+__global__ void __launch_bounds__(DT_THREADS, (HD == 64 && BN == 64 && STAGES <= 4) ? 3 : 2)
+attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
+                     AttnArgs a, int G, int kpc, Trace tr) {
+  const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
+  pdl_launch_dependents();
+  using SM = DecSmem<HD>;
+  constexpr int PANELS = HD / 64;
+  constexpr uint32_t TILE_BYTES = BN * HD * 2;
+  constexpr int WK = BN / DT_CONSUMERS;  // keys per consumer warp per tile
+  constexpr int MT = WK / 16;
+  constexpr int RS = SM::RS;
+  static_assert(WK % 16 == 0, "tile too small for the consumer warps");
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw = smem_u32(smem_raw);
+  const uint32_t sK = (raw + 1023u) & ~1023u;  // SWIZZLE_128B panels need 1024 B alignment
+  uint8_t* smem = smem_raw + (sK - raw);
+  const uint32_t sV = sK + STAGES * TILE_BYTES;
+  uint8_t* p_after = smem + 2 * STAGES * TILE_BYTES;
+  float* red = reinterpret_cast<float*>(p_after);                       // [4][8][HD + 2]
+  uint8_t* q_gen = p_after + SM::RED_BYTES;                             // [kpc][8][QROW]
+  const uint32_t sQ = sK + 2 * STAGES * TILE_BYTES + SM::RED_BYTES;
+  bf16* s_newkv = reinterpret_cast<bf16*>(q_gen + kpc * SM::Q_BYTES);   // [kpc][2][HD]
+  const uint32_t bars = sQ + kpc * SM::Q_BYTES + kpc * 2 * HD * 2;      // full[STAGES], empty[STAGES]
+
+  const int seq = blockIdx.x;
+  const int kvh0 = blockIdx.y * kpc;
+  const int split = blockIdx.z;
+  const int len = a.seq_len[seq];  // step state: stable before the wait
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int* bt = a.block_tables + (size_t)seq * a.max_blocks;
+  // this split's key range, in whole tiles
+  const int tiles_total = (len + BN - 1) / BN;
+  const int tps = (tiles_total + a.n_splits - 1) / a.n_splits;
+  const int tile_begin = split * tps;
+  const int n_tiles = max(0, min(tps, tiles_total - tile_begin));
+  const int F = n_tiles * kpc;  // flat (head, tile) work list
+  const bool fused = a.qkv_p != nullptr;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; s++) {
+      mbar_init(bars + 8 * s, 1);
+      mbar_init(bars + 8 * (STAGES + s), DT_CONSUMERS);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  if (warp == DT_CONSUMERS) {
+    // ------------------------------------------------------------ producer warp
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&tmK) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&tmV) : "memory");
+    }
+    // Rows past the sequence end hold whatever the pool block holds (zeros or finite stale
+    // values): their scores are masked to -inf, so they contribute exactly 0.  The only row
+    // the previous kernel (rope_kv, unfused mode) writes is position len - 1: tiles that end
+    // before it were written by earlier steps and are requested BEFORE the dependency
+    // resolves.  Fused mode patches that row in shared memory, so nothing here depends on the
+    // previous kernel at all.
+    bool waited = fused;
+    for (int f = 0; f < F; f++) {
+      const int stage = f % STAGES;
+      const int hh = f / n_tiles, j = f - hh * n_tiles;
+      const int k0 = (tile_begin + j) * BN;
+      if (!waited && k0 + BN > len - 1) {
+        pdl_wait();
+        waited = true;
+      }
+      if (f >= STAGES) mbar_wait(bars + 8 * (STAGES + stage), ((f / STAGES) - 1) & 1);
+      const int blk = bt[k0 / KV_BLOCK];
+      const int row = (blk * a.nkv + kvh0 + hh) * KV_BLOCK + (k0 % KV_BLOCK);
+      const uint32_t full = bars + 8 * stage;
+      if (elect_one()) {
+        mbar_expect_tx(full, 2 * TILE_BYTES);
+#pragma unroll
+        for (int p = 0; p < PANELS; p++) {
+          tma_load_2d(sK + stage * TILE_BYTES + p * (BN * 128), &tmK, full, p * 64, row);
+          tma_load_2d(sV + stage * TILE_BYTES + p * (BN * 128), &tmV, full, p * 64, row);
+        }
+      }
+      __syncwarp();
+    }
+    if (!waited) pdl_wait();
+    return;
+  }
+
+  // -------------------------------------------------------------- consumer warps
+  const int g = lane >> 2, t = lane & 3;
+  const int mi = lane >> 3, lr = lane & 7;
+  const bool has_new = fused && n_tiles > 0 && tile_begin + n_tiles == tiles_total;
+  pdl_wait();
+  const unsigned long long t_wait = tr.buf ? gtime() : 0ull;
+  if (!fused) {
+    // Q rows (bf16, written by rope_kv) -> padded shared rows; heads >= G are zero
+    constexpr int CPR = HD / 8;
+    for (int i = threadIdx.x; i < kpc * 8 * CPR; i += DT_CONSUMERS * 32) {
+      const int hh = i / (8 * CPR), r = (i / CPR) % 8, c = i % CPR;
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (r < G)
+        v = *reinterpret_cast<const uint4*>((const bf16*)a.q + (size_t)seq * a.nh * HD +
+                                            (size_t)((kvh0 + hh) * G + r) * HD + c * 8);
+      *reinterpret_cast<uint4*>(q_gen + hh * SM::Q_BYTES + r * SM::QROW + c * 16) = v;
+    }
+  } else {
+    // split-K sum + bias, rotate_half RoPE at position len - 1, bf16: what rope_kv_kernel does
+    // for a decode token, for this CTA's query heads and its kv heads
+    constexpr int HALF = HD / 2, VPH = HALF / 4;  // 4-float items keep the prologue's registers low
+    const int pos = len - 1;
+    const float* rowp = a.qkv_p + (size_t)seq * a.qkv_ld;
+    const int q_items = 8 * VPH, kv_items = has_new ? 2 * VPH : 0;
+    const int per_head = q_items + kv_items;
+    for (int it0 = threadIdx.x; it0 < per_head * kpc; it0 += DT_CONSUMERS * 32) {
+      const int hh = it0 / per_head, it = it0 - hh * per_head;
+      const int kvh = kvh0 + hh;
+      const bool is_q = it < q_items;
+      const int r = is_q ? it / VPH : 0;
+      const int which = is_q ? 0 : (it - q_items) / VPH;  // 0 = K, 1 = V
+      const int j = (is_q ? it % VPH : (it - q_items) % VPH) * 4;
+      uint2 lo = make_uint2(0, 0), hi = lo;
+      if (!is_q || r < G) {
+        const int col = (is_q ? kvh * G + r : a.nh + which * a.nkv + kvh) * HD + j;
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f), y = x, c = x, sn = x;
+        const bool rot = a.cosT != nullptr && (is_q || which == 0);
+        if (rot) {  // issued first: independent of the partial sums
+          c = __ldg(reinterpret_cast<const float4*>(a.cosT + (size_t)pos * HALF + j));
+          sn = __ldg(reinterpret_cast<const float4*>(a.sinT + (size_t)pos * HALF + j));
+        }
+        for (int q0 = 0; q0 < a.qkv_S; q0 += 8) {
+          // up to 8 slices of both halves in flight at once: one L2 round trip
+          float4 px[8], py[8];
+#pragma unroll
+          for (int q = 0; q < 8; q++)
+            if (q0 + q < a.qkv_S) {
+              const float* pp = rowp + (size_t)(q0 + q) * a.qkv_stride + col;
+              px[q] = *reinterpret_cast<const float4*>(pp);
+              py[q] = *reinterpret_cast<const float4*>(pp + HALF);
+            }
+#pragma unroll
+          for (int q = 0; q < 8; q++)
+            if (q0 + q < a.qkv_S) {
+              x.x += px[q].x; x.y += px[q].y; x.z += px[q].z; x.w += px[q].w;
+              y.x += py[q].x; y.y += py[q].y; y.z += py[q].z; y.w += py[q].w;
+            }
+        }
+        if (a.qkv_bias) {
+          const float4 bx = __ldg(reinterpret_cast<const float4*>(a.qkv_bias + col));
+          const float4 by = __ldg(reinterpret_cast<const float4*>(a.qkv_bias + col + HALF));
+          x.x += bx.x; x.y += bx.y; x.z += bx.z; x.w += bx.w;
+          y.x += by.x; y.y += by.y; y.z += by.z; y.w += by.w;
+        }
+        if (rot) {
+          const float4 x0 = x, y0 = y;
+          x.x = x0.x * c.x - y0.x * sn.x; y.x = y0.x * c.x + x0.x * sn.x;
+          x.y = x0.y * c.y - y0.y * sn.y; y.y = y0.y * c.y + x0.y * sn.y;
+          x.z = x0.z * c.z - y0.z * sn.z; y.z = y0.z * c.z + x0.z * sn.z;
+          x.w = x0.w * c.w - y0.w * sn.w; y.w = y0.w * c.w + x0.w * sn.w;
+        }
+        lo = make_uint2(pack_bf16(x.x, x.y), pack_bf16(x.z, x.w));
+        hi = make_uint2(pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
+      }
+      if (is_q) {
+        uint8_t* qr = q_gen + hh * SM::Q_BYTES + r * SM::QROW;
+        *reinterpret_cast<uint2*>(qr + j * 2) = lo;
+        *reinterpret_cast<uint2*>(qr + (j + HALF) * 2) = hi;
+      } else {
+        bf16* nk = s_newkv + ((size_t)hh * 2 + which) * HD;
+        *reinterpret_cast<uint2*>(nk + j) = lo;
+        *reinterpret_cast<uint2*>(nk + j + HALF) = hi;
+        // this CTA covers the end of the sequence: it appends the row to the paged pool
+        bf16* pool = which ? (bf16*)a.vpool : (bf16*)a.kpool;
+        bf16* dst = pool + (((size_t)bt[pos / KV_BLOCK] * a.nkv + kvh) * KV_BLOCK + (pos % KV_BLOCK)) * HD + j;
+        *reinterpret_cast<uint2*>(dst) = lo;
+        *reinterpret_cast<uint2*>(dst + HALF) = hi;
+      }
+    }
+  }
+  consumer_bar();  // Q and the new K / V rows are visible to the four warps
+  const unsigned long long t_prol = tr.buf ? gtime() : 0ull;
+  unsigned long long t_first = 0, t_fin0 = 0;
+
+  uint32_t qb[HD / 16][2];
+  float o[HD / 16][4];
+  float m[2], l[2];
+  const float scale_log2 = a.scale * 1.4426950408889634f;
+  const int limit = len - 1;
+
+  for (int f = 0; f < F; f++) {
+    const int stage = f % STAGES;
+    const int hh = f / n_tiles, j = f - hh * n_tiles;
+    if (j == 0) {
+      const uint32_t q = sQ + hh * SM::Q_BYTES + g * SM::QROW + t * 4;
+#pragma unroll
+      for (int ks = 0; ks < HD / 16; ks++) {
+        qb[ks][0] = lds32(q + ks * 32);
+        qb[ks][1] = lds32(q + ks * 32 + 16);
+      }
+#pragma unroll
+      for (int dt = 0; dt < HD / 16; dt++)
+#pragma unroll
+        for (int i = 0; i < 4; i++) o[dt][i] = 0.f;
+      m[0] = m[1] = -INFINITY;
+      l[0] = l[1] = 0.f;
+    }
+    mbar_wait(bars + 8 * stage, (f / STAGES) & 1);
+    if (tr.buf && f == 0) t_first = gtime();
+    const uint32_t tK = sK + stage * TILE_BYTES, tV = sV + stage * TILE_BYTES;
+    const int k0 = (tile_begin + j) * BN;
+    const int key0 = warp * WK;
+    bool patched = false;
+    if (has_new && j == n_tiles - 1) {
+      // the tile landed with whatever the pool held at position len - 1: the warp that owns
+      // that key row overwrites it with the K / V built in the prologue
+      const int row = len - 1 - k0;
+      if (row >= key0 && row < key0 + WK) {
+        for (int i = lane; i < 2 * (HD / 8); i += 32) {
+          const int which = i / (HD / 8), c = i % (HD / 8);
+          st_shared16((which ? tV : tK) + tile_off_t<BN>(row, c),
+                      *reinterpret_cast<const uint4*>(s_newkv + ((size_t)hh * 2 + which) * HD + c * 8));
+        }
+        __syncwarp();
+        patched = true;
+      }
+    }
+    // ---- S^T = K . Q^T for this warp's WK keys
+    float s[MT][4];
+#pragma unroll
+    for (int mt = 0; mt < MT; mt++) {
+#pragma unroll
+      for (int i = 0; i < 4; i++) s[mt][i] = 0.f;
+#pragma unroll
+      for (int ks = 0; ks < HD / 16; ks++) {
+        uint32_t a0, a1, a2, a3;
+        ldsm_x4(tK + tile_off_t<BN>(key0 + mt * 16 + lr + (mi & 1) * 8, ks * 2 + (mi >> 1)), a0, a1,
+                a2, a3);
+        mma16816(s[mt], a0, a1, a2, a3, qb[ks][0], qb[ks][1]);
+      }
+    }
+    if (k0 + BN > len) {
+#pragma unroll
+      for (int mt = 0; mt < MT; mt++) {
+        const int kp = k0 + key0 + mt * 16 + g;
+        if (kp > limit) s[mt][0] = s[mt][1] = -INFINITY;
+        if (kp + 8 > limit) s[mt][2] = s[mt][3] = -INFINITY;
+      }
+    }
+    // ---- online softmax: this thread holds heads 2t (e = 0) and 2t + 1 (e = 1)
+    float corr[2], mu[2];
+#pragma unroll
+    for (int e = 0; e < 2; e++) {
+      float mx = -INFINITY;
+#pragma unroll
+      for (int mt = 0; mt < MT; mt++) mx = fmaxf(mx, fmaxf(s[mt][e], s[mt][2 + e]));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+      mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+      const float m_new = fmaxf(m[e], mx);
+      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;
+      corr[e] = exp2f((m[e] - m_use) * scale_log2);  // m = -inf => 0
+      m[e] = m_new;
+      mu[e] = m_use * scale_log2;
+      float rs = 0.f;
+#pragma unroll
+      for (int mt = 0; mt < MT; mt++) {
+        const float p0 = exp2f(fmaf(s[mt][e], scale_log2, -mu[e]));
+        const float p1 = exp2f(fmaf(s[mt][2 + e], scale_log2, -mu[e]));
+        s[mt][e] = p0;
+        s[mt][2 + e] = p1;
+        rs += p0 + p1;
+      }
+      l[e] = l[e] * corr[e] + rs;  // per-thread partial; the key lanes are reduced at the end
+    }
+#pragma unroll
+    for (int dt = 0; dt < HD / 16; dt++) {
+      o[dt][0] *= corr[0];
+      o[dt][1] *= corr[1];
+      o[dt][2] *= corr[0];
+      o[dt][3] *= corr[1];
+    }
+    // ---- O^T += V^T . P^T
+#pragma unroll
+    for (int mt = 0; mt < MT; mt++) {
+      const uint32_t b0 = movmatrix_t(pack_bf16(s[mt][0], s[mt][1]));
+      const uint32_t b1 = movmatrix_t(pack_bf16(s[mt][2], s[mt][3]));
+#pragma unroll
+      for (int dt = 0; dt < HD / 16; dt++) {
+        uint32_t a0, a1, a2, a3;
+        ldsm_x4_t(tV + tile_off_t<BN>(key0 + mt * 16 + lr + (mi >> 1) * 8, dt * 2 + (mi & 1)), a0, a1,
+                  a2, a3);
+        mma16816(o[dt], a0, a1, a2, a3, b0, b1);
+      }
+    }
+    // ---- release the stage
+    if (patched) asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+    if (lane == 0) mbar_arrive(bars + 8 * (STAGES + stage));
+
+    if (j == n_tiles - 1) {
+      if (tr.buf && hh == 0) t_fin0 = gtime();
+      // ---- merge the 4 warps (each covered different keys) and write head group hh
+#pragma unroll
+      for (int e = 0; e < 2; e++) {
+        l[e] += __shfl_xor_sync(0xffffffffu, l[e], 4);
+        l[e] += __shfl_xor_sync(0xffffffffu, l[e], 8);
+        l[e] += __shfl_xor_sync(0xffffffffu, l[e], 16);
+      }
+#pragma unroll
+      for (int e = 0; e < 2; e++) {
+        const int r = 2 * t + e;
+        if (r >= G) continue;
+        float* rr = red + ((size_t)warp * 8 + r) * RS;
+#pragma unroll
+        for (int dt = 0; dt < HD / 16; dt++) {
+          rr[dt * 16 + g] = o[dt][e];
+          rr[dt * 16 + 8 + g] = o[dt][2 + e];
+        }
+        if (g == 0) {
+          rr[HD] = m[e];
+          rr[HD + 1] = l[e];
+        }
+      }
+      consumer_bar();
+      const int h0 = (kvh0 + hh) * G;
+      for (int idx = threadIdx.x; idx < G * HD; idx += DT_CONSUMERS * 32) {
+        const int r = idx / HD, d = idx % HD;
+        float mn = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < DT_CONSUMERS; w++) mn = fmaxf(mn, red[((size_t)w * 8 + r) * RS + HD]);
+        float lt = 0.f, at = 0.f;
+#pragma unroll
+        for (int w = 0; w < DT_CONSUMERS; w++) {
+          const float* rr = red + ((size_t)w * 8 + r) * RS;
+          const float c = (rr[HD] == -INFINITY) ? 0.f : exp2f((rr[HD] - mn) * scale_log2);
+          lt += rr[HD + 1] * c;
+          at += rr[d] * c;
+        }
+        const int h = h0 + r;
+        if (a.n_splits == 1) {
+          ((bf16*)a.out)[(size_t)seq * a.nh * HD + (size_t)h * HD + d] = __float2bfloat16_rn(at / lt);
+        } else {
+          float* rec = a.ws + (((size_t)seq * a.nh + h) * a.n_splits + split) * (HD + 2);
+          rec[d] = at;
+          if (d == 0) {
+            rec[HD] = (mn == -INFINITY) ? -INFINITY : mn * a.scale;  // combine kernel works in exp()
+            rec[HD + 1] = lt;
+          }
+        }
+      }
+      if (hh + 1 < kpc) consumer_bar();  // `red` is rewritten by the next head
+    }
+  }
+  if (n_tiles == 0) {  // empty split: (0, -inf, 0) records
+    for (int idx = threadIdx.x; idx < kpc * G * HD; idx += DT_CONSUMERS * 32) {
+      const int h = kvh0 * G + idx / HD, d = idx % HD;
+      float* rec = a.ws + (((size_t)seq * a.nh + h) * a.n_splits + split) * (HD + 2);
+      rec[d] = 0.f;
+      if (d == 0) {
+        rec[HD] = -INFINITY;
+        rec[HD + 1] = 0.f;
+      }
+    }
+  }
+  if (threadIdx.x == 0 && tr.buf)
+    trace_rec(tr, t_entry, t_wait,
+              (((t_prol - t_wait) & 0x1fffff) << 42) | (((t_first - t_wait) & 0x1fffff) << 21) |
+                  ((t_fin0 - t_wait) & 0x1fffff));
+}
+
+// ------------------------------------------------------------------ launcher
+bool attn_decode_t_supported(const AttnArgs& a) {
+  static const int off = getenv("NVLLM_ATTN_T") ? atoi(getenv("NVLLM_ATTN_T")) == 0 : 0;
+  if (off) return false;
+  return attn_mma_supported(a.qdt, a.kvdt, a.hd) && a.nkv > 0 && a.nh % a.nkv == 0 &&
+         a.nh / a.nkv <= 8 && a.pool_blocks > 0;
+}
+
+template <int HD, int BN, int STAGES>
+static cudaError_t decode_t_launch(cudaStream_t st, const AttnArgs& a, int G, int kpc) {
+  using SM = DecSmem<HD>;
+  const size_t smem = 1024 + (size_t)2 * STAGES * BN * HD * 2 + SM::RED_BYTES +
+                      (size_t)kpc * SM::Q_BYTES + (size_t)kpc * 2 * HD * 2 + 16 * STAGES;
+  const int pool_rows = a.pool_blocks * a.nkv * KV_BLOCK;
+  const TmaDesc* tk = tma_map_cached(a.kpool, pool_rows, HD, BN);
+  const TmaDesc* tv = tma_map_cached(a.vpool, pool_rows, HD, BN);
+  if (!tk || !tv) return cudaErrorInvalidValue;
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    cudaError_t e = cudaFuncSetAttribute(attn_decode_t_kernel<HD, BN, STAGES>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    smem_set = smem;
+  }
+  (void)launch_k(attn_decode_t_kernel<HD, BN, STAGES>, dim3(a.n_seqs, a.nkv / kpc, a.n_splits),
+                 dim3(DT_THREADS), smem, st, *reinterpret_cast<const CUtensorMap*>(tk),
+                 *reinterpret_cast<const CUtensorMap*>(tv), a, G, kpc, next_trace(4));
+  return cudaGetLastError();
+}
+
+// Shape of the launch: `cfg` = 100 * BN-code + 10 * stages + kpc can be forced for experiments
+// with NVLLM_ATTN_T_CFG (e.g. 1231 = 128-key tiles, 3 stages, 1 kv head per CTA).
+cudaError_t launch_attn_decode_t(cudaStream_t st, const AttnArgs& a) {
+  if (a.n_seqs <= 0) return cudaSuccess;
+  const int G = a.nh / a.nkv;
+  static const int cfg_env = getenv("NVLLM_ATTN_T_CFG") ? atoi(getenv("NVLLM_ATTN_T_CFG")) : 0;
+  // The fixed cost of a CTA (launch, prologue, first-tile latency, warp merge) is ~4 us against
+  // ~0.6 us per 64-key tile: when the step has more (sequence, kv head) pairs than resident
+  // CTA slots, pack kpc heads per CTA (the TMA ring runs straight through the head boundary)
+  // while the grid still covers ~1.6 CTAs per SM — measured on cfg2 (512 pairs): 1 head/CTA
+  // 1141 us/step, 2 heads/CTA 1112 us/step.
+  int bn = 64, kpc = 1;
+  if (a.n_splits == 1) {
+    const int sm = a.sm_count > 0 ? a.sm_count : 148;
+    while (kpc < 4 && a.nkv % (kpc * 2) == 0 &&
+           (long)a.n_seqs * (a.nkv / (kpc * 2)) * 10 >= (long)sm * 16)
+      kpc *= 2;
+  }
+  int stages = a.hd == 64 ? (kpc > 1 ? 6 : 4) : 3;
+  if (cfg_env > 0) {
+    bn = cfg_env / 100 >= 12 ? 128 : 64;
+    stages = (cfg_env / 10) % 10;
+    kpc = cfg_env % 10;
+  }
+  if (kpc < 1 || a.nkv % kpc != 0 || a.n_splits > 1) kpc = 1;
+  if (a.hd == 64) {
+    if (bn == 128) {
+      if (stages == 2) return decode_t_launch<64, 128, 2>(st, a, G, kpc);
+      return decode_t_launch<64, 128, 3>(st, a, G, kpc);
+    }
+    if (stages == 3) return decode_t_launch<64, 64, 3>(st, a, G, kpc);
+    if (stages == 6) return decode_t_launch<64, 64, 6>(st, a, G, kpc);
+    return decode_t_launch<64, 64, 4>(st, a, G, kpc);
+  }
+  if (stages == 2) return decode_t_launch<128, 64, 2>(st, a, G, kpc);
+  return decode_t_launch<128, 64, 3>(st, a, G, kpc);
+}
+
+}  // namespace nvllm

@@ -350,6 +350,8 @@ int forward_step(nvllm_handle* h) {
   at.tile_seq = d + L.tile_seq; at.tile_q0 = d + L.tile_q0; at.n_qtiles = L.n_qtiles;
   at.seq_len = d + L.seq_len;
   at.ws = w.attn_ws;
+  at.pool_blocks = h->num_blocks;
+  at.sm_count = h->sm_count;
   if (!is_prefill) {
     static const bool use_sk = [] {
       const char* e = getenv("NVLLM_ATTN_SK");

@@ -259,6 +259,9 @@ bool attn_mma_supported(int qdt, int kvdt, int hd);
 int attn_decode_mma_tile(int hd);
 cudaError_t launch_attn_prefill_mma(cudaStream_t st, const AttnArgs& a);
 cudaError_t launch_attn_decode_mma(cudaStream_t st, const AttnArgs& a);
+// attention_dec.cu: decode kernel for query-head groups of <= 8 (needs AttnArgs::pool_blocks)
+bool attn_decode_t_supported(const AttnArgs& a);
+cudaError_t launch_attn_decode_t(cudaStream_t st, const AttnArgs& a);
 size_t attn_decode_sk_ws_floats(int hd, int sm_count);
 cudaError_t launch_attn_decode_sk(cudaStream_t st, const AttnArgs& a, int* tickets, int sm_count,
                                   long long total_tiles_hint);
