@@ -146,87 +146,107 @@ attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_const
   const int g = lane >> 2, t = lane & 3;
   const int mi = lane >> 3, lr = lane & 7;
   const bool has_new = fused && n_tiles > 0 && tile_begin + n_tiles == tiles_total;
+  // Fused prologue = split-K sum + bias, rotate_half RoPE at position len - 1, bf16: what
+  // rope_kv_kernel does for a decode token, for this CTA's query heads and its kv heads.  One
+  // item = 4 + 4 floats (x at column j, its rotation partner at j + HD/2) of one real query
+  // head row or of the new K / V row.  Everything that does not depend on the QKV GEMM — item
+  // geometry, cos / sin, bias, the pool slot, the zero padding rows — is done BEFORE the
+  // dependency resolves; after it there is one round trip for the partial slices.
+  constexpr int HALF = HD / 2, VPH = HALF / 4;
+  constexpr int NT = DT_CONSUMERS * 32;
+  const int pos = len - 1;
+  const int q_items = G * VPH, kv_items = has_new ? 2 * VPH : 0;
+  const int per_head = q_items + kv_items;
+  const int n_items = fused ? per_head * kpc : 0;
+  struct Item {
+    int hh, r, which, j, col;
+    bool is_q, rot;
+    float4 c, sn, bx, by;
+  };
+  auto prep = [&](int it0) {
+    Item I;
+    I.hh = it0 / per_head;
+    const int it = it0 - I.hh * per_head;
+    I.is_q = it < q_items;
+    I.r = I.is_q ? it / VPH : 0;
+    I.which = I.is_q ? 0 : (it - q_items) / VPH;  // 0 = K, 1 = V
+    I.j = (I.is_q ? it % VPH : (it - q_items) % VPH) * 4;
+    const int kvh = kvh0 + I.hh;
+    I.col = (I.is_q ? kvh * G + I.r : a.nh + I.which * a.nkv + kvh) * HD + I.j;
+    I.rot = a.cosT != nullptr && (I.is_q || I.which == 0);
+    I.c = I.sn = I.bx = I.by = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (I.rot) {
+      I.c = __ldg(reinterpret_cast<const float4*>(a.cosT + (size_t)pos * HALF + I.j));
+      I.sn = __ldg(reinterpret_cast<const float4*>(a.sinT + (size_t)pos * HALF + I.j));
+    }
+    if (a.qkv_bias) {
+      I.bx = __ldg(reinterpret_cast<const float4*>(a.qkv_bias + I.col));
+      I.by = __ldg(reinterpret_cast<const float4*>(a.qkv_bias + I.col + HALF));
+    }
+    return I;
+  };
+  Item first;
+  if ((int)threadIdx.x < n_items) first = prep(threadIdx.x);
+  const int new_blk = has_new ? bt[pos / KV_BLOCK] : 0;
+  // query rows >= G are MMA padding: zero
+  for (int i = threadIdx.x; i < kpc * (8 - G) * (HD / 8); i += NT) {
+    const int hh = i / ((8 - G) * (HD / 8)), rem = i % ((8 - G) * (HD / 8));
+    const int r = G + rem / (HD / 8), c = rem % (HD / 8);
+    *reinterpret_cast<uint4*>(q_gen + hh * SM::Q_BYTES + r * SM::QROW + c * 16) = make_uint4(0, 0, 0, 0);
+  }
   pdl_wait();
   const unsigned long long t_wait = tr.buf ? gtime() : 0ull;
   if (!fused) {
-    // Q rows (bf16, written by rope_kv) -> padded shared rows; heads >= G are zero
+    // Q rows (bf16, written by rope_kv) -> padded shared rows
     constexpr int CPR = HD / 8;
-    for (int i = threadIdx.x; i < kpc * 8 * CPR; i += DT_CONSUMERS * 32) {
-      const int hh = i / (8 * CPR), r = (i / CPR) % 8, c = i % CPR;
-      uint4 v = make_uint4(0, 0, 0, 0);
-      if (r < G)
-        v = *reinterpret_cast<const uint4*>((const bf16*)a.q + (size_t)seq * a.nh * HD +
-                                            (size_t)((kvh0 + hh) * G + r) * HD + c * 8);
-      *reinterpret_cast<uint4*>(q_gen + hh * SM::Q_BYTES + r * SM::QROW + c * 16) = v;
+    for (int i = threadIdx.x; i < kpc * G * CPR; i += NT) {
+      const int hh = i / (G * CPR), r = (i / CPR) % G, c = i % CPR;
+      *reinterpret_cast<uint4*>(q_gen + hh * SM::Q_BYTES + r * SM::QROW + c * 16) =
+          *reinterpret_cast<const uint4*>((const bf16*)a.q + (size_t)seq * a.nh * HD +
+                                          (size_t)((kvh0 + hh) * G + r) * HD + c * 8);
     }
   } else {
-    // split-K sum + bias, rotate_half RoPE at position len - 1, bf16: what rope_kv_kernel does
-    // for a decode token, for this CTA's query heads and its kv heads
-    constexpr int HALF = HD / 2, VPH = HALF / 4;  // 4-float items keep the prologue's registers low
-    const int pos = len - 1;
     const float* rowp = a.qkv_p + (size_t)seq * a.qkv_ld;
-    const int q_items = 8 * VPH, kv_items = has_new ? 2 * VPH : 0;
-    const int per_head = q_items + kv_items;
-    for (int it0 = threadIdx.x; it0 < per_head * kpc; it0 += DT_CONSUMERS * 32) {
-      const int hh = it0 / per_head, it = it0 - hh * per_head;
-      const int kvh = kvh0 + hh;
-      const bool is_q = it < q_items;
-      const int r = is_q ? it / VPH : 0;
-      const int which = is_q ? 0 : (it - q_items) / VPH;  // 0 = K, 1 = V
-      const int j = (is_q ? it % VPH : (it - q_items) % VPH) * 4;
-      uint2 lo = make_uint2(0, 0), hi = lo;
-      if (!is_q || r < G) {
-        const int col = (is_q ? kvh * G + r : a.nh + which * a.nkv + kvh) * HD + j;
-        float4 x = make_float4(0.f, 0.f, 0.f, 0.f), y = x, c = x, sn = x;
-        const bool rot = a.cosT != nullptr && (is_q || which == 0);
-        if (rot) {  // issued first: independent of the partial sums
-          c = __ldg(reinterpret_cast<const float4*>(a.cosT + (size_t)pos * HALF + j));
-          sn = __ldg(reinterpret_cast<const float4*>(a.sinT + (size_t)pos * HALF + j));
-        }
-        for (int q0 = 0; q0 < a.qkv_S; q0 += 8) {
-          // up to 8 slices of both halves in flight at once: one L2 round trip
-          float4 px[8], py[8];
+    for (int it0 = threadIdx.x; it0 < n_items; it0 += NT) {
+      const Item I = it0 == (int)threadIdx.x ? first : prep(it0);
+      float4 x = I.bx, y = I.by;
+      for (int q0 = 0; q0 < a.qkv_S; q0 += 8) {
+        // up to 8 slices of both halves in flight at once: one L2 round trip
+        float4 px[8], py[8];
 #pragma unroll
-          for (int q = 0; q < 8; q++)
-            if (q0 + q < a.qkv_S) {
-              const float* pp = rowp + (size_t)(q0 + q) * a.qkv_stride + col;
-              px[q] = *reinterpret_cast<const float4*>(pp);
-              py[q] = *reinterpret_cast<const float4*>(pp + HALF);
-            }
+        for (int q = 0; q < 8; q++)
+          if (q0 + q < a.qkv_S) {
+            const float* pp = rowp + (size_t)(q0 + q) * a.qkv_stride + I.col;
+            px[q] = *reinterpret_cast<const float4*>(pp);
+            py[q] = *reinterpret_cast<const float4*>(pp + HALF);
+          }
 #pragma unroll
-          for (int q = 0; q < 8; q++)
-            if (q0 + q < a.qkv_S) {
-              x.x += px[q].x; x.y += px[q].y; x.z += px[q].z; x.w += px[q].w;
-              y.x += py[q].x; y.y += py[q].y; y.z += py[q].z; y.w += py[q].w;
-            }
-        }
-        if (a.qkv_bias) {
-          const float4 bx = __ldg(reinterpret_cast<const float4*>(a.qkv_bias + col));
-          const float4 by = __ldg(reinterpret_cast<const float4*>(a.qkv_bias + col + HALF));
-          x.x += bx.x; x.y += bx.y; x.z += bx.z; x.w += bx.w;
-          y.x += by.x; y.y += by.y; y.z += by.z; y.w += by.w;
-        }
-        if (rot) {
-          const float4 x0 = x, y0 = y;
-          x.x = x0.x * c.x - y0.x * sn.x; y.x = y0.x * c.x + x0.x * sn.x;
-          x.y = x0.y * c.y - y0.y * sn.y; y.y = y0.y * c.y + x0.y * sn.y;
-          x.z = x0.z * c.z - y0.z * sn.z; y.z = y0.z * c.z + x0.z * sn.z;
-          x.w = x0.w * c.w - y0.w * sn.w; y.w = y0.w * c.w + x0.w * sn.w;
-        }
-        lo = make_uint2(pack_bf16(x.x, x.y), pack_bf16(x.z, x.w));
-        hi = make_uint2(pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
+        for (int q = 0; q < 8; q++)
+          if (q0 + q < a.qkv_S) {
+            x.x += px[q].x; x.y += px[q].y; x.z += px[q].z; x.w += px[q].w;
+            y.x += py[q].x; y.y += py[q].y; y.z += py[q].z; y.w += py[q].w;
+          }
       }
-      if (is_q) {
-        uint8_t* qr = q_gen + hh * SM::Q_BYTES + r * SM::QROW;
-        *reinterpret_cast<uint2*>(qr + j * 2) = lo;
-        *reinterpret_cast<uint2*>(qr + (j + HALF) * 2) = hi;
+      if (I.rot) {
+        const float4 x0 = x, y0 = y, c = I.c, sn = I.sn;
+        x.x = x0.x * c.x - y0.x * sn.x; y.x = y0.x * c.x + x0.x * sn.x;
+        x.y = x0.y * c.y - y0.y * sn.y; y.y = y0.y * c.y + x0.y * sn.y;
+        x.z = x0.z * c.z - y0.z * sn.z; y.z = y0.z * c.z + x0.z * sn.z;
+        x.w = x0.w * c.w - y0.w * sn.w; y.w = y0.w * c.w + x0.w * sn.w;
+      }
+      const uint2 lo = make_uint2(pack_bf16(x.x, x.y), pack_bf16(x.z, x.w));
+      const uint2 hi = make_uint2(pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
+      if (I.is_q) {
+        uint8_t* qr = q_gen + I.hh * SM::Q_BYTES + I.r * SM::QROW;
+        *reinterpret_cast<uint2*>(qr + I.j * 2) = lo;
+        *reinterpret_cast<uint2*>(qr + (I.j + HALF) * 2) = hi;
       } else {
-        bf16* nk = s_newkv + ((size_t)hh * 2 + which) * HD;
-        *reinterpret_cast<uint2*>(nk + j) = lo;
-        *reinterpret_cast<uint2*>(nk + j + HALF) = hi;
+        bf16* nk = s_newkv + ((size_t)I.hh * 2 + I.which) * HD;
+        *reinterpret_cast<uint2*>(nk + I.j) = lo;
+        *reinterpret_cast<uint2*>(nk + I.j + HALF) = hi;
         // this CTA covers the end of the sequence: it appends the row to the paged pool
-        bf16* pool = which ? (bf16*)a.vpool : (bf16*)a.kpool;
-        bf16* dst = pool + (((size_t)bt[pos / KV_BLOCK] * a.nkv + kvh) * KV_BLOCK + (pos % KV_BLOCK)) * HD + j;
+        bf16* pool = I.which ? (bf16*)a.vpool : (bf16*)a.kpool;
+        bf16* dst = pool + (((size_t)new_blk * a.nkv + kvh0 + I.hh) * KV_BLOCK + (pos % KV_BLOCK)) * HD + I.j;
         *reinterpret_cast<uint2*>(dst) = lo;
         *reinterpret_cast<uint2*>(dst + HALF) = hi;
       }

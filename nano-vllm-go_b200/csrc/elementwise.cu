@@ -61,7 +61,7 @@ cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int*
 //   x <- x + m1 * (sum_s p1[s] + bias1) + m2 * (sum_s p2[s] + bias2);  y = norm(x)
 // The updated row is staged in shared memory so x is read once and written once.
 template <typename YT>
-__global__ void norm_kernel(NormArgs a, Trace tr) {
+__global__ void __launch_bounds__(512) norm_kernel(NormArgs a, Trace tr) {
   const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
   pdl_launch_dependents();
   extern __shared__ float row[];
@@ -96,13 +96,27 @@ __global__ void norm_kernel(NormArgs a, Trace tr) {
       if (a.comb_rows) {
 #pragma unroll
         for (int j = 0; j < 8; j++) acc[j] = 0.f;
-        for (int s = 0; s < a.comb_k; s++) {
-          const int prow = a.comb_rows[(size_t)r * a.comb_k + s];
-          const float cw = a.comb_w[(size_t)r * a.comb_k + s];
-          float pv[8];
-          load8(a.p1 + (size_t)prow * H + i, pv);
+        // slot order (moe.go:116-118), four slots at a time: the index / weight loads of all
+        // four first, then all four row loads, then the ordered accumulation — two L2 round
+        // trips per four slots instead of two per slot
+        for (int s0 = 0; s0 < a.comb_k; s0 += 4) {
+          int prow[4];
+          float cw[4], pv[4][8];
 #pragma unroll
-          for (int j = 0; j < 8; j++) acc[j] += cw * pv[j];
+          for (int q = 0; q < 4; q++)
+            if (s0 + q < a.comb_k) {
+              prow[q] = a.comb_rows[(size_t)r * a.comb_k + s0 + q];
+              cw[q] = a.comb_w[(size_t)r * a.comb_k + s0 + q];
+            }
+#pragma unroll
+          for (int q = 0; q < 4; q++)
+            if (s0 + q < a.comb_k) load8(a.p1 + (size_t)prow[q] * H + i, pv[q]);
+#pragma unroll
+          for (int q = 0; q < 4; q++)
+            if (s0 + q < a.comb_k) {
+#pragma unroll
+              for (int j = 0; j < 8; j++) acc[j] += cw[q] * pv[q][j];
+            }
         }
       } else {
         sum_partials8(a.p1 + (size_t)r * H + i, a.S1, a.stride1, acc);
@@ -204,6 +218,8 @@ __global__ void norm_kernel(NormArgs a, Trace tr) {
 cudaError_t launch_norm(cudaStream_t st, const NormArgs& a) {
   if (a.n_rows <= 0) return cudaSuccess;
   int threads = min(512, max(64, ((a.H / 8 + 31) / 32) * 32));
+  // fused router: 16 warps so that each takes two experts of a 32-expert layer in one pass
+  if (a.router) threads = 512;
   size_t smem = (size_t)a.H * sizeof(float);
   if (a.ydt == DT_F32)
     (void)launch_k(norm_kernel<float>, dim3(a.n_rows), dim3(threads), smem, st, a, next_trace(2));

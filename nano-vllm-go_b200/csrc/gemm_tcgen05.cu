@@ -623,7 +623,15 @@ cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int* S_out) {
   if (a.epi == TC5_EPI_PARTIAL && a.out_capacity && (size_t)S * a.split_stride > a.out_capacity) return cudaErrorInvalidValue;
   switch (bt) {
     case 32: return launch_bt<32, 10>(st, a, tw, ta, S);
-    case 64: return launch_bt<64, 8>(st, a, tw, ta, S);
+    case 64: {
+      // ring depth experiment: a shallower ring (<= ~110 KB) lets the NEXT kernel's CTAs
+      // become resident (and prefetch) while this one drains
+      static const int st64 = getenv("NVLLM_TC5_ST64") ? atoi(getenv("NVLLM_TC5_ST64")) : 8;
+      if (st64 == 4) return launch_bt<64, 4>(st, a, tw, ta, S);
+      if (st64 == 5) return launch_bt<64, 5>(st, a, tw, ta, S);
+      if (st64 == 6) return launch_bt<64, 6>(st, a, tw, ta, S);
+      return launch_bt<64, 8>(st, a, tw, ta, S);
+    }
     case 128: return launch_bt<128, 6>(st, a, tw, ta, S);
     default: return launch_bt<256, 4>(st, a, tw, ta, S);
   }

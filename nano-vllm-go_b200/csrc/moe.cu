@@ -131,27 +131,56 @@ moe_sort_gather_kernel(const int* __restrict__ topk_idx, int n_pairs, int k, int
   __syncthreads();
   for (int p = tid; p < n_pairs; p += 1024) atomicAdd(&s_cnt[topk_idx[p]], 1);
   __syncthreads();
-  if (tid == 0) {
-    int run = 0, nt = 0;
+  if (warp == 0) {
+    // expert offsets and the tile list by warp scans (E <= 64: lane holds experts lane and
+    // lane + 32) — the serial loop over the experts cost ~2 us on the single publishing thread
     const bool pub = blockIdx.x == 0;
-    for (int e = 0; e < E; e++) {
-      s_off[e] = run;
-      if (pub) {
-        b.counts[e] = s_cnt[e];
-        b.offsets[e] = run;
-        for (int r = 0; r < s_cnt[e] && nt < max_tiles; r += tile) {
-          b.tile_expert[nt] = e;
-          b.tile_row0[nt] = run + r;
-          b.tile_rows[nt] = min(tile, s_cnt[e] - r);
-          nt++;
+    const int e0 = lane, e1 = lane + 32;
+    const int c0 = e0 < E ? s_cnt[e0] : 0, c1 = e1 < E ? s_cnt[e1] : 0;
+    const int t0 = (c0 + tile - 1) / tile, t1 = (c1 + tile - 1) / tile;
+    int ic0 = c0, ic1 = c1, it0 = t0, it1 = t1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int a0 = __shfl_up_sync(0xffffffffu, ic0, o), a1 = __shfl_up_sync(0xffffffffu, ic1, o);
+      const int b0 = __shfl_up_sync(0xffffffffu, it0, o), b1 = __shfl_up_sync(0xffffffffu, it1, o);
+      if (lane >= o) {
+        ic0 += a0;
+        ic1 += a1;
+        it0 += b0;
+        it1 += b1;
+      }
+    }
+    const int tot_c0 = __shfl_sync(0xffffffffu, ic0, 31), tot_t0 = __shfl_sync(0xffffffffu, it0, 31);
+    const int tot_c = tot_c0 + __shfl_sync(0xffffffffu, ic1, 31);
+    const int tot_t = tot_t0 + __shfl_sync(0xffffffffu, it1, 31);
+    const int off0 = ic0 - c0, off1 = tot_c0 + ic1 - c1;
+    const int tb0 = it0 - t0, tb1 = tot_t0 + it1 - t1;
+    if (e0 < E) s_off[e0] = off0;
+    if (e1 < E) s_off[e1] = off1;
+    if (lane == 0) s_off[E] = tot_c;
+    if (pub) {
+      if (e0 < E) {
+        b.counts[e0] = c0;
+        b.offsets[e0] = off0;
+        for (int r = 0; r < t0 && tb0 + r < max_tiles; r++) {
+          b.tile_expert[tb0 + r] = e0;
+          b.tile_row0[tb0 + r] = off0 + r * tile;
+          b.tile_rows[tb0 + r] = min(tile, c0 - r * tile);
         }
       }
-      run += s_cnt[e];
-    }
-    s_off[E] = run;
-    if (pub) {
-      b.offsets[E] = run;
-      *b.n_tiles = nt;
+      if (e1 < E) {
+        b.counts[e1] = c1;
+        b.offsets[e1] = off1;
+        for (int r = 0; r < t1 && tb1 + r < max_tiles; r++) {
+          b.tile_expert[tb1 + r] = e1;
+          b.tile_row0[tb1 + r] = off1 + r * tile;
+          b.tile_rows[tb1 + r] = min(tile, c1 - r * tile);
+        }
+      }
+      if (lane == 0) {
+        b.offsets[E] = tot_c;
+        *b.n_tiles = min(tot_t, max_tiles);
+      }
     }
   }
   for (int c0 = 0; c0 < n_pairs; c0 += 1024) {

@@ -18,18 +18,47 @@ __device__ __forceinline__ void moe_route_row(const float* y, const float* __res
                                               int* __restrict__ topk_idx,
                                               float* __restrict__ topk_w) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  for (int e = warp; e < E; e += nw) {
-    const float* rr = R + (size_t)e * H;
-    float acc = 0.f;
-    for (int i = lane * 8; i < H; i += 256) {
-      float a[8], b[8];
-      load8(y + i, a);
-      load8(rr + i, b);
+  // Two experts per pass with the k loop unrolled four deep: up to 8 independent 32-byte loads
+  // of R per lane in flight, so the E / nw passes cost one L2 round trip each instead of one
+  // per 256 columns per expert (measured 10 us per row CTA with the rolled loop at E = 32).
+  // The per-expert accumulation order (ascending i, then the warp tree) is unchanged.
+  for (int e = warp; e < E; e += 2 * nw) {
+    const int e2 = e + nw;
+    const bool two = e2 < E;
+    const float* r1 = R + (size_t)e * H;
+    const float* r2 = R + (size_t)(two ? e2 : e) * H;
+    float acc1 = 0.f, acc2 = 0.f;
+    for (int i0 = lane * 8; i0 < H; i0 += 1024) {
+      float b1[4][8], b2[4][8];
 #pragma unroll
-      for (int j = 0; j < 8; j++) acc = fmaf(a[j], b[j], acc);
+      for (int u = 0; u < 4; u++) {
+        const int i = i0 + u * 256;
+        if (i < H) {
+          load8(r1 + i, b1[u]);
+          if (two) load8(r2 + i, b2[u]);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int i = i0 + u * 256;
+        if (i < H) {
+          float a[8];
+          load8(y + i, a);
+#pragma unroll
+          for (int j = 0; j < 8; j++) acc1 = fmaf(a[j], b1[u][j], acc1);
+          if (two) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc2 = fmaf(a[j], b2[u][j], acc2);
+          }
+        }
+      }
     }
-    acc = warp_sum(acc);
-    if (lane == 0) probs[e] = acc;
+    acc1 = warp_sum(acc1);
+    acc2 = warp_sum(acc2);
+    if (lane == 0) {
+      probs[e] = acc1;
+      if (two) probs[e2] = acc2;
+    }
   }
   __syncthreads();
   if (warp != 0) return;
