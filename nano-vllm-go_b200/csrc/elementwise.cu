@@ -218,8 +218,10 @@ __global__ void __launch_bounds__(512) norm_kernel(NormArgs a, Trace tr) {
 cudaError_t launch_norm(cudaStream_t st, const NormArgs& a) {
   if (a.n_rows <= 0) return cudaSuccess;
   int threads = min(512, max(64, ((a.H / 8 + 31) / 32) * 32));
-  // fused router: 16 warps so that each takes two experts of a 32-expert layer in one pass
-  if (a.router) threads = 512;
+  // fused router, decode-sized batches (latency-bound: fewer row CTAs than two waves): 16 warps
+  // so that each takes two experts of a 32-expert layer in one pass; prefill keeps the
+  // occupancy of the narrow CTA (measured: 512 threads cost cfg3 prefill 35 -> 44 ms)
+  if (a.router && a.n_rows <= 1024) threads = 512;
   size_t smem = (size_t)a.H * sizeof(float);
   if (a.ydt == DT_F32)
     (void)launch_k(norm_kernel<float>, dim3(a.n_rows), dim3(threads), smem, st, a, next_trace(2));
