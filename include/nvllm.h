@@ -270,7 +270,13 @@ int nvllm_timer_record(nvllm_handle* h, int which);
 int nvllm_timer_elapsed(nvllm_handle* h, float* ms);
 
 /* SetSamplingParamsWithRepetition (tensor_model_runner.go:35-52):
- * repetition_penalty 1.0 disables; top_k 0 disables; top_p 1.0 disables. */
+ * repetition_penalty 1.0 disables; top_k 0 disables; top_p 1.0 disables.
+ * With any of them enabled, rows with temperature > 0 are drawn by SampleWithHistory
+ * (sampling.go:33-217: penalty over the sequence's token_ids with the x3 weight of the last
+ * ten, temperature, softmax, top-k, top-p, renormalise, inverse CDF with the step's uniform);
+ * rows with temperature <= 0 stay greedy.  The history comes from nvllm_run's token_ids, so
+ * nvllm_run_resident returns NVLLM_ERR_STATE after such a step.  Invalid values
+ * (top_p <= 0, top_k < 0, repetition_penalty <= 0) return NVLLM_ERR_INVALID. */
 int nvllm_set_sampling(nvllm_handle* h, float top_p, int top_k, float repetition_penalty);
 int nvllm_set_seed(nvllm_handle* h, uint64_t seed);
 

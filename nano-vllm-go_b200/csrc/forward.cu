@@ -575,6 +575,13 @@ int forward_step(nvllm_handle* h) {
     ProfScope ps(h, NVLLM_K_SAMPLE, (double)n * h->V * 4, 0);
     LAUNCH(h, launch_sample(st, logits, h->ldl, h->V, n, d_temp, d_uni, w.out_tokens, w.amax,
                             w.amax_ticket, vsplit));
+    if (h->filters_active() && h->hist_n == n) {
+      // TensorModelRunner's sampler (tensor_model_runner.go:92-94): the rows with
+      // temperature > 0 are redrawn with the repetition penalty / top-k / top-p applied
+      LAUNCH(h, launch_sample_filtered(st, logits, h->ldl, h->V, n, vsplit, d_temp, d_uni,
+                                       h->d_hist + (n + 1), h->d_hist, h->top_p, h->top_k,
+                                       h->rep_penalty, h->d_probs, w.out_tokens));
+    }
   }
   h->ws.logits_final = logits;
   return NVLLM_OK;

@@ -129,6 +129,14 @@ struct nvllm_handle {
   // sampling
   float top_p = 1.f, rep_penalty = 1.f;
   int top_k = 0;
+  // SampleWithHistory filters (sampling.cu): the step's flattened token history
+  // [cu_hist (n + 1) | tokens] and the per-row probability scratch, grown on demand
+  int32_t* d_hist = nullptr;
+  size_t hist_words = 0;
+  int hist_n = 0;           // sequences of the uploaded history (0 = none for this step)
+  float* d_probs = nullptr;
+  size_t probs_floats = 0;
+  bool filters_active() const { return rep_penalty != 1.f || top_k > 0 || top_p < 1.f; }
   uint64_t seed = 0, rng_counter = 0;
   int graphs_enabled = 1;
   int use_tc5 = 1;

@@ -85,6 +85,14 @@ cudaError_t launch_rope_kv(cudaStream_t st, int qdt, int kvdt, int T, int nh, in
 // vsplit > 0: the logits are vocabulary slices gathered rank-major, [V / vsplit][n][vsplit]
 // (tensor-parallel LM head); logit v of row s lives at (v / vsplit) * n * vsplit + s * vsplit +
 // v % vsplit.  vsplit = 0: plain [n, ldl].
+// sampling.cu: SampleWithHistory (sampling.go:33-217) for the rows with temperature > 0 —
+// repetition penalty over hist[cu_hist[s] .. cu_hist[s+1]), temperature, softmax, top-k, top-p,
+// renormalise, inverse-CDF draw with uniforms[s]; probs = [n, V] scratch.  Overwrites
+// out_tokens[s] of those rows only.
+cudaError_t launch_sample_filtered(cudaStream_t st, const float* logits, int ldl, int V, int n,
+                                   int vsplit, const float* temperature, const float* uniforms,
+                                   const int* hist, const int* cu_hist, float top_p, int top_k,
+                                   float rep, float* probs, int* out_tokens);
 cudaError_t launch_sample(cudaStream_t st, const float* logits, int ldl, int V, int n,
                           const float* temperature, const float* uniforms, int* out_tokens,
                           unsigned long long* amax = nullptr, int* ticket = nullptr, int vsplit = 0);

@@ -273,6 +273,8 @@ int nvllm_destroy(nvllm_handle* h) {
   F(h->vpool);
   F(h->d_stage);
   F(h->d_stage2);
+  F(h->d_hist);
+  F(h->d_probs);
   for (auto& r : h->prof_open) {
     cudaEventDestroy(r.e0);
     cudaEventDestroy(r.e1);
@@ -307,6 +309,8 @@ int nvllm_memory_info(const nvllm_handle* h, uint64_t* weight_bytes, uint64_t* k
 
 int nvllm_set_sampling(nvllm_handle* h, float top_p, int top_k, float repetition_penalty) {
   if (!h) return NVLLM_ERR_INVALID;
+  if (!(top_p > 0.f) || top_k < 0 || !(repetition_penalty > 0.f))
+    return set_err(h, NVLLM_ERR_INVALID, "sampling: need top_p > 0, top_k >= 0, repetition_penalty > 0");
   h->top_p = top_p;
   h->top_k = top_k;
   h->rep_penalty = repetition_penalty;

@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <vector>
 
 #include "common.cuh"
 #include "handle.h"
@@ -184,6 +185,43 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
   s[L.cu_q + n] = row;
 
   cudaStream_t st = h->stream;
+  // SampleWithHistory filters need every sequence's full token history on the device
+  // (previousTokens = seq.TokenIDs, tensor_model_runner.go:94)
+  h->hist_n = 0;
+  if (h->filters_active()) {
+    bool any = false;
+    for (int i = 0; i < n && !any; i++) any = temperature && temperature[i] > 0.f;
+    if (any) {
+      const size_t total = (size_t)(cu_seqlens[n] - cu_seqlens[0]);
+      const size_t words = (size_t)(n + 1) + total;
+      if (words > h->hist_words) {
+        NV_CHECK(h, cudaStreamSynchronize(st));
+        if (h->d_hist) cudaFree(h->d_hist);
+        h->d_hist = nullptr;
+        h->hist_words = 0;
+        NV_CHECK(h, cudaMalloc((void**)&h->d_hist, words * 2 * 4));
+        h->hist_words = words * 2;
+      }
+      const size_t pf = (size_t)n * h->V;
+      if (pf > h->probs_floats) {
+        NV_CHECK(h, cudaStreamSynchronize(st));
+        if (h->d_probs) cudaFree(h->d_probs);
+        h->d_probs = nullptr;
+        h->probs_floats = 0;
+        NV_CHECK(h, cudaMalloc((void**)&h->d_probs, pf * 4));
+        h->probs_floats = pf;
+      }
+      // offsets relative to the first token, then the tokens themselves (the caller's buffers
+      // are pageable: these copies are staged by the driver before the call returns)
+      std::vector<int32_t> cu(n + 1);
+      for (int i = 0; i <= n; i++) cu[i] = cu_seqlens[i] - cu_seqlens[0];
+      NV_CHECK(h, cudaMemcpyAsync(h->d_hist, cu.data(), (size_t)(n + 1) * 4, cudaMemcpyHostToDevice, st));
+      NV_CHECK(h, cudaMemcpyAsync(h->d_hist + (n + 1), token_ids + cu_seqlens[0], total * 4,
+                                  cudaMemcpyHostToDevice, st));
+      NV_CHECK(h, cudaStreamSynchronize(st));  // `cu` is a stack temporary
+      h->hist_n = n;
+    }
+  }
   NV_CHECK(h, cudaMemcpyAsync(h->d_stage, h->h_stage, L.words * 4, cudaMemcpyHostToDevice, st));
   NV_CHECK(h, cudaEventRecord(h->ev0, st));
   h->launches = 0;
@@ -228,6 +266,9 @@ extern "C" int nvllm_run_resident(nvllm_handle* h, nvllm_run_stats* stats) {
   if (!h) return NVLLM_ERR_INVALID;
   if (!h->resident_ok)
     return set_err(h, NVLLM_ERR_STATE, "nvllm_run_resident needs a preceding nvllm_run");
+  if (h->hist_n)
+    return set_err(h, NVLLM_ERR_STATE,
+                   "repetition penalty / top-k / top-p need the token history: use nvllm_run");
   NV_CHECK(h, cudaSetDevice(h->dev));
   StepLayout& L = h->lay;
   const int n = L.n;

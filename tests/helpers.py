@@ -60,3 +60,33 @@ def rel_err(a, b):
     a = np.asarray(a, dtype=np.float64)
     b = np.asarray(b, dtype=np.float64)
     return float(np.abs(a - b).max() / max(np.abs(b).max(), 1e-30))
+
+
+def ref_filter_probs(logits, history, temp, top_p, top_k, rep):
+    """numpy float64 restatement of the filter pipeline — only used to measure how far a draw
+    is from a CDF step / a filter cut (the token itself is checked against the C oracle)."""
+    lc = logits.astype(np.float64).copy()
+    if rep != 1.0 and len(history):
+        cnt = {}
+        for i, t in enumerate(history):
+            cnt[t] = cnt.get(t, 0) + (3 if i >= len(history) - 10 else 1)
+        for t, c in cnt.items():
+            lc[t] = lc[t] / (rep * c) if lc[t] > 0 else lc[t] * (rep * c)
+    if temp > 0 and temp != 1.0:
+        lc /= temp
+    p = np.exp(lc - lc.max())
+    p /= p.sum()
+    order = np.lexsort((np.arange(p.size), -p))
+    if 0 < top_k < p.size:
+        keep = order[:top_k]
+        q = np.zeros_like(p)
+        q[keep] = p[keep]
+        p = q
+        order = np.lexsort((np.arange(p.size), -p))
+    if top_p < 1.0:
+        cum = np.cumsum(p[order])
+        cut = int(np.searchsorted(cum, top_p, side="left")) + 1
+        q = np.zeros_like(p)
+        q[order[:cut]] = p[order[:cut]]
+        p = q
+    return p / p.sum()

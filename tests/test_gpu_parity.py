@@ -11,7 +11,7 @@ Gates (BASELINE.json north_star / SURVEY.md §8d):
 import numpy as np
 import pytest
 
-from helpers import C, W, E, TINY, TINY_HD, make_oracle, oracle_mod, rel_err
+from helpers import C, W, E, TINY, TINY_HD, make_oracle, oracle_mod, rel_err, ref_filter_probs
 import nvllm_pkg
 
 pytestmark = pytest.mark.gpu
@@ -297,6 +297,59 @@ def test_temperature_sampling_with_injected_uniforms():
             assert abs(cdf[toks[i]] - cdf[ref]) < 1e-3 or toks[i] == ref
             exact += int(toks[i] == ref)
         assert exact >= 4
+    finally:
+        run.close()
+
+
+@pytest.mark.parametrize("top_p,top_k,rep", [(1.0, 0, 1.2), (1.0, 40, 1.0), (0.9, 0, 1.0),
+                                              (0.85, 50, 1.2), (0.5, 5, 1.5)])
+def test_sample_with_history_filters(top_p, top_k, rep):
+    """sampling.go:33-217 SampleWithHistory on the device: repetition penalty over the token
+    history (x3 for the last ten), temperature, top-k, top-p, renormalise, inverse-CDF draw —
+    rand.Float32() replaced by injected uniforms.  Tokens must equal the oracle's; where u
+    lands within fp32 rounding of a CDF step the neighbouring kept token is accepted."""
+    O = oracle_mod()
+    cfg = TINY["gpt2"]()
+    run = _runner(cfg, C.PREC_FP32)
+    try:
+        run.set_sampling_params(1.0, top_p=top_p, top_k=top_k, repetition_penalty=rep)
+        rng = np.random.default_rng(7)
+        prompts = []
+        for i in range(8):
+            pr = W.random_prompt(cfg.vocab_size, 14 + 3 * i, 90 + i).tolist()
+            pr[-3] = pr[2]  # a repeat inside the last ten tokens (weight 3 + 1)
+            pr[5] = pr[1]
+            prompts.append(pr)
+        temps = [0.7, 1.0, 1.3, 0.0, 2.0, 0.5, 1.0, 0.9]
+        us = [float(u) for u in rng.uniform(0.02, 0.98, size=8)]
+        bts = [[i] for i in range(8)]
+        toks, logits = run.run_flat(prompts, True, [0] * 8, bts, temps, us, want_logits=True)
+        exact = 0
+        for i in range(8):
+            if temps[i] == 0.0:
+                assert toks[i] == O.argmax(logits[i])  # greedy rows are not filtered
+                continue
+            ref = O.sample(logits[i], prompts[i], temps[i], top_p=top_p, top_k=top_k,
+                           rep_penalty=rep, u=us[i])
+            p = ref_filter_probs(logits[i], prompts[i], temps[i], top_p, top_k, rep)
+            assert p[toks[i]] > 0, f"row {i}: token {toks[i]} was filtered out by the reference"
+            if toks[i] != ref:
+                cdf = np.cumsum(p)
+                assert abs(cdf[toks[i]] - cdf[ref]) < 1e-3 or abs(cdf[min(toks[i], ref)] - us[i]) < 1e-3, \
+                    f"row {i}: token {toks[i]} != oracle {ref}"
+            exact += int(toks[i] == ref)
+        assert exact >= 6
+        # decode step: the history is the whole sequence so far
+        seqs = [pr + [int(t)] for pr, t in zip(prompts, toks)]
+        toks2, logits2 = run.run_flat(seqs, False, None, bts, temps, us, want_logits=True)
+        same = sum(int(toks2[i] == O.sample(logits2[i], seqs[i], temps[i], top_p=top_p, top_k=top_k,
+                                            rep_penalty=rep, u=us[i]))
+                   for i in range(8) if temps[i] > 0)
+        assert same >= 6
+        # the device-resident loop has no host-side history: it must refuse, not ignore the knobs
+        L = nvllm_pkg.sub("lib")
+        with pytest.raises(L.NvllmError):
+            run.run_resident()
     finally:
         run.close()
 
