@@ -170,6 +170,7 @@ struct Trace {
   unsigned long long* buf;
   int seq, kid;
 };
+bool trace_active();       // a device timeline is being recorded: kernel arguments carry its buffer
 Trace next_trace(int kid);  // {nullptr} unless tracing is on (host side, gemm_tcgen05.cu)
 __device__ __forceinline__ unsigned long long gtime() {
   unsigned long long t;

@@ -547,6 +547,7 @@ void trace_set(unsigned long long* buf) {
   g_trace_buf = buf;
   g_trace_seq = 0;
 }
+bool trace_active() { return g_trace_buf != nullptr; }
 Trace next_trace(int kid) {
   Trace t{g_trace_buf, 0, kid};
   if (g_trace_buf) t.seq = g_trace_seq++;

@@ -148,6 +148,17 @@ struct nvllm_handle {
   bool resident_ok = false;  // the last step's state is on the device (nvllm_run_resident)
   nvllm::StepLayout run_lay;  // layout of the last nvllm_run (nvllm_rerun replays it)
   bool run_lay_ok = false;
+  // CUDA graph of one device-resident decode step (advance + forward pass), replayed while
+  // the launch shape stays the same (run.cu)
+  cudaGraphExec_t step_graph = nullptr;
+  struct GraphSig {
+    const int32_t* d = nullptr;
+    int n = 0, max_blocks = 0, n_splits = 0;
+    bool operator==(const GraphSig& o) const {
+      return d == o.d && n == o.n && max_blocks == o.max_blocks && n_splits == o.n_splits;
+    }
+  } graph_sig;
+  int graph_launches = 0;
   int32_t* d_stage2 = nullptr;  // decode layout derived on the device from a prefill step
   size_t stage2_words = 0;
   // per-kernel-class profile (nvllm_set_profile / nvllm_get_profile)

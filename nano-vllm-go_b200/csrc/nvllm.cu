@@ -272,6 +272,10 @@ int nvllm_destroy(nvllm_handle* h) {
   F(h->kpool);
   F(h->vpool);
   F(h->d_stage);
+  if (h->step_graph) {
+    cudaGraphExecDestroy(h->step_graph);
+    h->step_graph = nullptr;  // free_workspace below would destroy it again
+  }
   F(h->d_stage2);
   F(h->d_hist);
   F(h->d_probs);

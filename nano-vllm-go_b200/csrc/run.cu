@@ -306,14 +306,61 @@ extern "C" int nvllm_run_resident(nvllm_handle* h, nvllm_run_stats* stats) {
     L = D;
   } else {
     int32_t* d = L.d;
-    cudaError_t e = launch_advance(st, n, h->ws.out_tokens, d + L.tokens, d + L.positions,
-                                   d + L.slots, d + L.seq_len, d + L.block_tables, L.max_blocks,
-                                   L.max_blocks * KV_BLOCK);
-    h->launches++;
-    if (e != cudaSuccess) return set_err(h, NVLLM_ERR_CUDA, "advance: %s", cudaGetErrorString(e));
     L.max_len += 1;
     L.sum_len += n;
     L.attn_pairs = (double)L.sum_len;
+    auto advance = [&]() -> int {
+      cudaError_t e = launch_advance(st, n, h->ws.out_tokens, d + L.tokens, d + L.positions,
+                                     d + L.slots, d + L.seq_len, d + L.block_tables, L.max_blocks,
+                                     L.max_blocks * KV_BLOCK);
+      h->launches++;
+      if (e != cudaSuccess) return set_err(h, NVLLM_ERR_CUDA, "advance: %s", cudaGetErrorString(e));
+      return NVLLM_OK;
+    };
+    // Steady-state decode: every kernel argument of the step is a device pointer or a constant
+    // of the launch shape (the step state itself lives in device memory and is advanced by a
+    // kernel), so the ~100 launches of advance + forward pass are captured once — programmatic
+    // dependent-launch edges included — and replayed with one cudaGraphLaunch until the shape
+    // changes (batch, block-table width, KV split count).
+    const bool graph_ok = h->graphs_enabled && !h->profile && !trace_active() && h->tp == 1 &&
+                          h->skip_mask == 0 && h->ws.T_cap >= n && h->ws.n_cap >= n;
+    if (graph_ok) {
+      nvllm_handle::GraphSig sig;
+      sig.d = d;
+      sig.n = n;
+      sig.max_blocks = L.max_blocks;
+      sig.n_splits = attn_decode_splits(h->adt, h->kvdt, n, h->nh, h->nkv, h->hd, L.max_len,
+                                        h->sm_count);
+      if (!h->step_graph || !(sig == h->graph_sig)) {
+        if (h->step_graph) cudaGraphExecDestroy(h->step_graph);
+        h->step_graph = nullptr;
+        NV_CHECK(h, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        rc = advance();
+        if (!rc) rc = forward_step(h);
+        cudaGraph_t g = nullptr;
+        cudaError_t e = cudaStreamEndCapture(st, &g);
+        if (rc) {
+          if (g) cudaGraphDestroy(g);
+          return rc;
+        }
+        if (e != cudaSuccess) return set_err(h, NVLLM_ERR_CUDA, "graph capture: %s", cudaGetErrorString(e));
+        e = cudaGraphInstantiate(&h->step_graph, g, 0);
+        cudaGraphDestroy(g);
+        if (e != cudaSuccess) {
+          h->step_graph = nullptr;
+          return set_err(h, NVLLM_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(e));
+        }
+        h->graph_sig = sig;
+        h->graph_launches = h->launches;
+      }
+      NV_CHECK(h, cudaGraphLaunch(h->step_graph, st));
+      h->launches = h->graph_launches;
+      NV_CHECK(h, cudaEventRecord(h->ev1, st));
+      fill_stats(h, stats, n, 0, 0, false);
+      if (stats) stats->used_graph = 1;
+      return NVLLM_OK;
+    }
+    if ((rc = advance())) return rc;
   }
   if ((rc = forward_step(h))) return rc;
   NV_CHECK(h, cudaEventRecord(h->ev1, st));

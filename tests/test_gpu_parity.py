@@ -410,6 +410,7 @@ def test_resident_decode_matches_stepwise():
         # again, resident
         seqs = [list(p) for p in prompts]
         out, _ = run.run_flat(seqs, True, [0] * 5, bts, [0.0] * 5)
+        first_out = out.copy()
         for s, t in zip(seqs, out):
             s.append(int(t))
         out, _ = run.run_flat(seqs, False, None, bts, [0.0] * 5)
@@ -418,6 +419,19 @@ def test_resident_decode_matches_stepwise():
             run.run_resident()
             got, _ = run.sync(5)
             np.testing.assert_array_equal(got, ref[i])
+            # steady-state decode steps replay one captured CUDA graph
+            assert run.last_stats.used_graph == 1
+        # the same loop with graphs off launches kernel by kernel and gives the same tokens
+        run.set_graphs(False)
+        seqs = [list(p) + [int(t)] for p, t in zip(prompts, first_out)]
+        out, _ = run.run_flat(seqs, False, None, bts, [0.0] * 5)
+        np.testing.assert_array_equal(out, ref[0])
+        for i in range(1, 4):
+            run.run_resident()
+            got, _ = run.sync(5)
+            np.testing.assert_array_equal(got, ref[i])
+            assert run.last_stats.used_graph == 0
+        run.set_graphs(True)
         # resident straight after a prefill step (decode state derived on the device), twice:
         # the second time from nvllm_rerun's replay of the staged prefill
         first, _ = run.run_flat([list(p) for p in prompts], True, [0] * 5, bts, [0.0] * 5)

@@ -13,6 +13,7 @@ dsteps = int(sys.argv[4]) if len(sys.argv) > 4 else 256
 cfg = C.PRESETS[model]()
 job = bench.Job(cfg, batch, plen, dsteps, 4321)
 run = bench.make_runner(cfg, job, 0)
+run.set_graphs(bool(int(os.environ.get('NVLLM_GRAPHS', '1'))))
 job.stage(run)
 for _ in range(2):
     job.run_resident(run)
