@@ -19,10 +19,7 @@ namespace nvllm {
 // ------------------------------------------------------------------ workspace
 void free_workspace(nvllm_handle* h) {
   Workspace& w = h->ws;
-  if (h->step_graph) {  // the captured decode step holds these pointers
-    cudaGraphExecDestroy(h->step_graph);
-    h->step_graph = nullptr;
-  }
+  h->drop_graphs();  // the captured decode steps hold these pointers
   void* ptrs[] = {w.tp_buf, w.x, w.xn, w.xn_f32, w.ws_a, w.ws_b, w.ws_c, w.q, w.attn_out, w.hbuf, w.xn_last,
                   w.logits_p, w.logits, w.attn_ws, w.attn_tickets, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
                   w.sort.counts, w.sort.offsets, w.sort.cursor, w.sort.sorted_pair, w.sort.pair_row,

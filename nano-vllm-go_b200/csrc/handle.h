@@ -150,15 +150,22 @@ struct nvllm_handle {
   bool run_lay_ok = false;
   // CUDA graph of one device-resident decode step (advance + forward pass), replayed while
   // the launch shape stays the same (run.cu)
-  cudaGraphExec_t step_graph = nullptr;
+  // slot 0: nvllm_run_resident (advance + forward pass), slot 1: nvllm_run decode step
+  cudaGraphExec_t step_graph[2] = {nullptr, nullptr};
   struct GraphSig {
     const int32_t* d = nullptr;
     int n = 0, max_blocks = 0, n_splits = 0;
     bool operator==(const GraphSig& o) const {
       return d == o.d && n == o.n && max_blocks == o.max_blocks && n_splits == o.n_splits;
     }
-  } graph_sig;
-  int graph_launches = 0;
+  } graph_sig[2];
+  int graph_launches[2] = {0, 0};
+  void drop_graphs() {
+    for (auto& g : step_graph) {
+      if (g) cudaGraphExecDestroy(g);
+      g = nullptr;
+    }
+  }
   int32_t* d_stage2 = nullptr;  // decode layout derived on the device from a prefill step
   size_t stage2_words = 0;
   // per-kernel-class profile (nvllm_set_profile / nvllm_get_profile)

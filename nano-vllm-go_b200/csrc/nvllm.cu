@@ -272,10 +272,7 @@ int nvllm_destroy(nvllm_handle* h) {
   F(h->kpool);
   F(h->vpool);
   F(h->d_stage);
-  if (h->step_graph) {
-    cudaGraphExecDestroy(h->step_graph);
-    h->step_graph = nullptr;  // free_workspace below would destroy it again
-  }
+  h->drop_graphs();
   F(h->d_stage2);
   F(h->d_hist);
   F(h->d_probs);

@@ -80,6 +80,54 @@ static void fill_stats(nvllm_handle* h, nvllm_run_stats* stats, int T, uint64_t 
   stats->d2h_bytes = d2h;
 }
 
+// ---- CUDA graph replay of a decode step.  Every kernel argument of a decode step is a device
+// pointer or a constant of the launch shape (the step state itself lives in device memory), so
+// the ~100 launches are captured once — programmatic dependent-launch edges included — and
+// replayed with one cudaGraphLaunch until the shape changes (staging buffer, batch,
+// block-table width, KV split count).  slot 0 = nvllm_run_resident (`pre` launches the advance
+// kernel), slot 1 = nvllm_run's decode step (`pre` does nothing; the H2D copy stays outside).
+static bool graph_usable(const nvllm_handle* h, int n) {
+  return h->graphs_enabled && !h->profile && !trace_active() && h->tp == 1 && h->skip_mask == 0 &&
+         h->hist_n == 0 && h->ws.T_cap >= n && h->ws.n_cap >= n;
+}
+template <typename Pre>
+static int graphed_step(nvllm_handle* h, int slot, Pre pre, bool* used) {
+  const StepLayout& L = h->lay;
+  cudaStream_t st = h->stream;
+  nvllm_handle::GraphSig sig;
+  sig.d = L.d;
+  sig.n = L.n;
+  sig.max_blocks = L.max_blocks;
+  sig.n_splits = attn_decode_splits(h->adt, h->kvdt, L.n, h->nh, h->nkv, h->hd, L.max_len,
+                                    h->sm_count);
+  if (!h->step_graph[slot] || !(sig == h->graph_sig[slot])) {
+    if (h->step_graph[slot]) cudaGraphExecDestroy(h->step_graph[slot]);
+    h->step_graph[slot] = nullptr;
+    NV_CHECK(h, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    int rc = pre();
+    if (!rc) rc = forward_step(h);
+    cudaGraph_t g = nullptr;
+    cudaError_t e = cudaStreamEndCapture(st, &g);
+    if (rc) {
+      if (g) cudaGraphDestroy(g);
+      return rc;
+    }
+    if (e != cudaSuccess) return set_err(h, NVLLM_ERR_CUDA, "graph capture: %s", cudaGetErrorString(e));
+    e = cudaGraphInstantiate(&h->step_graph[slot], g, 0);
+    cudaGraphDestroy(g);
+    if (e != cudaSuccess) {
+      h->step_graph[slot] = nullptr;
+      return set_err(h, NVLLM_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(e));
+    }
+    h->graph_sig[slot] = sig;
+    h->graph_launches[slot] = h->launches;
+  }
+  NV_CHECK(h, cudaGraphLaunch(h->step_graph[slot], st));
+  h->launches = h->graph_launches[slot];
+  *used = true;
+  return NVLLM_OK;
+}
+
 extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* token_ids,
                          const int32_t* cu_seqlens, const int32_t* num_cached,
                          const int32_t* block_tables, const int32_t* cu_blocks,
@@ -225,7 +273,12 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
   NV_CHECK(h, cudaMemcpyAsync(h->d_stage, h->h_stage, L.words * 4, cudaMemcpyHostToDevice, st));
   NV_CHECK(h, cudaEventRecord(h->ev0, st));
   h->launches = 0;
-  if ((rc = forward_step(h))) return rc;
+  bool used_graph = false;
+  if (!is_prefill && graph_usable(h, n)) {
+    if ((rc = graphed_step(h, 1, [] { return (int)NVLLM_OK; }, &used_graph))) return rc;
+  } else if ((rc = forward_step(h))) {
+    return rc;
+  }
   NV_CHECK(h, cudaEventRecord(h->ev1, st));
   NV_CHECK(h, cudaMemcpyAsync(h->h_out, h->ws.out_tokens, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
   uint64_t d2h = (uint64_t)n * 4;
@@ -255,6 +308,7 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
   h->run_lay = L;
   h->run_lay_ok = true;
   fill_stats(h, stats, T, L.words * 4, d2h, true);
+  if (stats) stats->used_graph = used_graph ? 1 : 0;
   return NVLLM_OK;
 }
 
@@ -317,44 +371,9 @@ extern "C" int nvllm_run_resident(nvllm_handle* h, nvllm_run_stats* stats) {
       if (e != cudaSuccess) return set_err(h, NVLLM_ERR_CUDA, "advance: %s", cudaGetErrorString(e));
       return NVLLM_OK;
     };
-    // Steady-state decode: every kernel argument of the step is a device pointer or a constant
-    // of the launch shape (the step state itself lives in device memory and is advanced by a
-    // kernel), so the ~100 launches of advance + forward pass are captured once — programmatic
-    // dependent-launch edges included — and replayed with one cudaGraphLaunch until the shape
-    // changes (batch, block-table width, KV split count).
-    const bool graph_ok = h->graphs_enabled && !h->profile && !trace_active() && h->tp == 1 &&
-                          h->skip_mask == 0 && h->ws.T_cap >= n && h->ws.n_cap >= n;
-    if (graph_ok) {
-      nvllm_handle::GraphSig sig;
-      sig.d = d;
-      sig.n = n;
-      sig.max_blocks = L.max_blocks;
-      sig.n_splits = attn_decode_splits(h->adt, h->kvdt, n, h->nh, h->nkv, h->hd, L.max_len,
-                                        h->sm_count);
-      if (!h->step_graph || !(sig == h->graph_sig)) {
-        if (h->step_graph) cudaGraphExecDestroy(h->step_graph);
-        h->step_graph = nullptr;
-        NV_CHECK(h, cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        rc = advance();
-        if (!rc) rc = forward_step(h);
-        cudaGraph_t g = nullptr;
-        cudaError_t e = cudaStreamEndCapture(st, &g);
-        if (rc) {
-          if (g) cudaGraphDestroy(g);
-          return rc;
-        }
-        if (e != cudaSuccess) return set_err(h, NVLLM_ERR_CUDA, "graph capture: %s", cudaGetErrorString(e));
-        e = cudaGraphInstantiate(&h->step_graph, g, 0);
-        cudaGraphDestroy(g);
-        if (e != cudaSuccess) {
-          h->step_graph = nullptr;
-          return set_err(h, NVLLM_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(e));
-        }
-        h->graph_sig = sig;
-        h->graph_launches = h->launches;
-      }
-      NV_CHECK(h, cudaGraphLaunch(h->step_graph, st));
-      h->launches = h->graph_launches;
+    if (graph_usable(h, n)) {
+      bool used = false;
+      if ((rc = graphed_step(h, 0, advance, &used))) return rc;
       NV_CHECK(h, cudaEventRecord(h->ev1, st));
       fill_stats(h, stats, n, 0, 0, false);
       if (stats) stats->used_graph = 1;
