@@ -283,6 +283,15 @@ int nvllm_set_seed(nvllm_handle* h, uint64_t seed);
 /* Enable/disable CUDA-graph replay of decode steps (default on). */
 int nvllm_set_graphs(nvllm_handle* h, int enabled);
 
+/* Speculative next decode step (default on; needs graphs on, greedy rows, tp_size 1): at the
+ * end of nvllm_run the library issues the step the engine will most likely ask for next — the
+ * same sequences one token longer (llm_engine.go:62-70 loops Step over an unchanged batch) — so
+ * the GPU does not idle during the host's turnaround.  The next nvllm_run that asks for exactly
+ * that step (same lengths + 1, last token = the one returned, same block tables) only waits
+ * for it and copies nothing to the device; any other call restages everything as usual.
+ * After one miss the next call does not speculate. */
+int nvllm_set_speculation(nvllm_handle* h, int enabled);
+
 /* GetVocabSize / GetModelConfig (purego/generic_runner.go:184-196). */
 int nvllm_get_config(const nvllm_handle* h, nvllm_config* out);
 

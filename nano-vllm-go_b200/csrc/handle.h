@@ -166,6 +166,13 @@ struct nvllm_handle {
       g = nullptr;
     }
   }
+  // Speculative next decode step (run.cu): issued at the end of nvllm_run so that the GPU is
+  // not idle while the host turns the sampled tokens around; consumed by the next nvllm_run /
+  // nvllm_run_resident when it asks for exactly that step, overwritten otherwise
+  int spec_enabled = 1;
+  bool spec_pending = false;
+  int spec_skip = 0;  // calls that do not speculate (set after a miss)
+  std::vector<int32_t> spec_len, spec_nb, spec_bt;  // per-sequence lengths / block tables of the last call
   int32_t* d_stage2 = nullptr;  // decode layout derived on the device from a prefill step
   size_t stage2_words = 0;
   // per-kernel-class profile (nvllm_set_profile / nvllm_get_profile)

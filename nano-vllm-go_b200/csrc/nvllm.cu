@@ -329,6 +329,12 @@ int nvllm_set_graphs(nvllm_handle* h, int enabled) {
   return NVLLM_OK;
 }
 
+int nvllm_set_speculation(nvllm_handle* h, int enabled) {
+  if (!h) return NVLLM_ERR_INVALID;
+  h->spec_enabled = enabled;
+  return NVLLM_OK;
+}
+
 int nvllm_tp_unique_id(uint8_t out_id[128]) {
   if (!out_id) return set_err(nullptr, NVLLM_ERR_INVALID, "null argument");
   return tp_unique_id(out_id);

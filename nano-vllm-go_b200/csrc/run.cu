@@ -128,6 +128,58 @@ static int graphed_step(nvllm_handle* h, int slot, Pre pre, bool* used) {
   return NVLLM_OK;
 }
 
+// ---- speculative next step.  ModelRunner.Run is synchronous (the engine needs the tokens to
+// schedule the next step), so between two calls the GPU would idle for the host's turnaround
+// (sync, Go/cgo, staging, launch: ~100 us of a ~1.1 ms cfg2 step).  A decode batch is almost
+// always followed by the same batch one token longer, so nvllm_run ends by issuing exactly that
+// step on the device (what nvllm_run_resident does).  The next call either asks for it — same
+// sequences, one token longer, last token = the one just returned, same block tables, greedy —
+// and only has to wait for it, or asks for something else and restages everything as usual.
+// A speculative step that is thrown away has only written K/V at the next position of each
+// sequence, a slot nothing reads before its owner writes it.
+static int resident_step(nvllm_handle* h, nvllm_run_stats* stats);
+static void remember_call(nvllm_handle* h, int n, const int32_t* cu_seqlens, const int32_t* block_tables,
+                          const int32_t* cu_blocks) {
+  h->spec_len.resize(n);
+  h->spec_nb.resize(n);
+  for (int i = 0; i < n; i++) {
+    h->spec_len[i] = cu_seqlens[i + 1] - cu_seqlens[i];
+    h->spec_nb[i] = cu_blocks[i + 1] - cu_blocks[i];
+  }
+  h->spec_bt.assign(block_tables + cu_blocks[0], block_tables + cu_blocks[n]);
+}
+static void try_speculate(nvllm_handle* h, int n, const float* temperature) {
+  h->spec_pending = false;
+  if (!h->spec_enabled || !graph_usable(h, n)) return;
+  if (h->spec_skip > 0) {
+    h->spec_skip--;
+    return;
+  }
+  for (int i = 0; i < n; i++) {
+    if (temperature && temperature[i] > 0.f) return;  // a draw needs the next call's uniform
+    if (h->spec_len[i] >= h->spec_nb[i] * KV_BLOCK) return;  // next position needs a new block
+    if (h->use_rope && h->spec_len[i] + 1 > h->cfg.max_seq_len) return;
+  }
+  const int saved = h->launches;
+  if (resident_step(h, nullptr) == NVLLM_OK) h->spec_pending = true;
+  h->launches = saved;
+}
+static bool speculation_hit(const nvllm_handle* h, int n, int is_prefill, const int32_t* token_ids,
+                            const int32_t* cu_seqlens, const int32_t* block_tables,
+                            const int32_t* cu_blocks, const float* temperature) {
+  if (is_prefill || n != (int)h->spec_len.size() || h->filters_active()) return false;
+  size_t o = 0;
+  for (int i = 0; i < n; i++) {
+    const int len = cu_seqlens[i + 1] - cu_seqlens[i], nb = cu_blocks[i + 1] - cu_blocks[i];
+    if (len != h->spec_len[i] + 1 || nb != h->spec_nb[i]) return false;
+    if (token_ids[cu_seqlens[i + 1] - 1] != h->h_out[i]) return false;
+    if (temperature && temperature[i] > 0.f) return false;
+    if (memcmp(block_tables + cu_blocks[i], h->spec_bt.data() + o, (size_t)nb * 4) != 0) return false;
+    o += nb;
+  }
+  return true;
+}
+
 extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* token_ids,
                          const int32_t* cu_seqlens, const int32_t* num_cached,
                          const int32_t* block_tables, const int32_t* cu_blocks,
@@ -141,6 +193,32 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
   if (n == 0) return NVLLM_OK;
   NV_CHECK(h, cudaSetDevice(h->dev));
   const nvllm_config& c = h->cfg;
+  if (h->spec_pending) {
+    h->spec_pending = false;
+    if (speculation_hit(h, n, is_prefill, token_ids, cu_seqlens, block_tables, cu_blocks, temperature)) {
+      // the requested step is already running (or done): collect it
+      cudaStream_t st = h->stream;
+      NV_CHECK(h, cudaMemcpyAsync(h->h_out, h->ws.out_tokens, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+      uint64_t d2h = (uint64_t)n * 4;
+      if (out_logits) {
+        NV_CHECK(h, cudaMemcpy2DAsync(out_logits, (size_t)h->V * 4, h->ws.logits_final,
+                                      (size_t)h->ldl * 4, (size_t)h->V * 4, n, cudaMemcpyDeviceToHost, st));
+        d2h += (uint64_t)n * h->V * 4;
+      }
+      cudaError_t e = cudaStreamSynchronize(st);
+      if (e != cudaSuccess)
+        return set_err(h, NVLLM_ERR_CUDA, "forward pass failed: %s", cudaGetErrorString(e));
+      memcpy(out_tokens, h->h_out, (size_t)n * 4);
+      h->run_lay = h->lay;
+      h->run_lay_ok = true;
+      fill_stats(h, stats, n, 0, d2h, true);
+      if (stats) stats->used_graph = h->step_graph[0] != nullptr;
+      remember_call(h, n, cu_seqlens, block_tables, cu_blocks);
+      try_speculate(h, n, temperature);
+      return NVLLM_OK;
+    }
+    h->spec_skip = 1;  // missed: the caller is not stepping one batch; back off once
+  }
   h->resident_ok = false;
   h->run_lay_ok = false;
 
@@ -309,6 +387,8 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
   h->run_lay_ok = true;
   fill_stats(h, stats, T, L.words * 4, d2h, true);
   if (stats) stats->used_graph = used_graph ? 1 : 0;
+  remember_call(h, n, cu_seqlens, block_tables, cu_blocks);
+  try_speculate(h, n, temperature);
   return NVLLM_OK;
 }
 
@@ -316,8 +396,7 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
 // sampled tokens become the inputs, positions advance by one, KV slots come from the block
 // tables already resident.  No host<->device copy, no host sync.  Works after a decode step
 // (state advanced in place) and after a prefill step (decode state derived by a kernel).
-extern "C" int nvllm_run_resident(nvllm_handle* h, nvllm_run_stats* stats) {
-  if (!h) return NVLLM_ERR_INVALID;
+static int resident_step(nvllm_handle* h, nvllm_run_stats* stats) {
   if (!h->resident_ok)
     return set_err(h, NVLLM_ERR_STATE, "nvllm_run_resident needs a preceding nvllm_run");
   if (h->hist_n)
@@ -387,6 +466,17 @@ extern "C" int nvllm_run_resident(nvllm_handle* h, nvllm_run_stats* stats) {
   return NVLLM_OK;
 }
 
+extern "C" int nvllm_run_resident(nvllm_handle* h, nvllm_run_stats* stats) {
+  if (!h) return NVLLM_ERR_INVALID;
+  if (h->spec_pending) {  // the step asked for is the one already in flight
+    h->spec_pending = false;
+    fill_stats(h, stats, h->lay.n, 0, 0, false);
+    if (stats) stats->used_graph = h->step_graph[0] != nullptr;
+    return NVLLM_OK;
+  }
+  return resident_step(h, stats);
+}
+
 // Re-execute the last nvllm_run step from its staged device inputs.
 extern "C" int nvllm_rerun(nvllm_handle* h, nvllm_run_stats* stats) {
   if (!h) return NVLLM_ERR_INVALID;
@@ -397,6 +487,7 @@ extern "C" int nvllm_rerun(nvllm_handle* h, nvllm_run_stats* stats) {
                    "nvllm_rerun replays prefill steps only (a decode step's staged state is "
                    "advanced in place by nvllm_run_resident)");
   h->lay = h->run_lay;
+  h->spec_pending = false;
   NV_CHECK(h, cudaEventRecord(h->ev0, h->stream));
   h->launches = 0;
   int rc = forward_step(h);
@@ -416,7 +507,10 @@ extern "C" int nvllm_sync(nvllm_handle* h, int32_t* out_tokens, int n, float* la
     return set_err(h, NVLLM_ERR_CUDA, "stream failed: %s", cudaGetErrorString(e));
   if (out_tokens && n > 0) {
     if (n > h->lay.n) n = h->lay.n;
-    NV_CHECK(h, cudaMemcpy(out_tokens, h->ws.out_tokens, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    if (h->spec_pending)  // ws.out_tokens already holds the speculative step's tokens
+      memcpy(out_tokens, h->h_out, (size_t)n * 4);
+    else
+      NV_CHECK(h, cudaMemcpy(out_tokens, h->ws.out_tokens, (size_t)n * 4, cudaMemcpyDeviceToHost));
   }
   if (last_step_ms) {
     float ms = 0.f;

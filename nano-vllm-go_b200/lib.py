@@ -81,6 +81,7 @@ SIGNATURES = {
                                           ctypes.c_float]),
     "nvllm_set_seed": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint64]),
     "nvllm_set_graphs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
+    "nvllm_set_speculation": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int]),
     "nvllm_get_config": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(C.CConfig)]),
     "nvllm_memory_info": (ctypes.c_int, [ctypes.c_void_p, _u64p, _u64p, _u64p]),
     "nvllm_op_matmul": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,

@@ -192,6 +192,9 @@ class CudaModelRunner:
     def set_graphs(self, enabled: bool):
         L.check(self._lib.nvllm_set_graphs(self._h, int(enabled)), self._h)
 
+    def set_speculation(self, enabled: bool):
+        L.check(self._lib.nvllm_set_speculation(self._h, int(enabled)), self._h)
+
     def clear_cache(self, seq_id: int) -> None:  # state is addressed by block tables only
         return None
 

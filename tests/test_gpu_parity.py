@@ -448,6 +448,51 @@ def test_resident_decode_matches_stepwise():
         run.close()
 
 
+def test_speculative_next_step_hits_and_misses():
+    """nvllm_run ends by issuing the step the engine asks for next; a call that matches it copies
+    nothing to the device and must return what a non-speculating runner returns, a call that
+    does not match (another token, another batch) must be unaffected by the discarded step."""
+    cfg = TINY["llama"]()
+    prompts = [W.random_prompt(cfg.vocab_size, 18 + 7 * i, 300 + i).tolist() for i in range(4)]
+    bts = [_blocks(len(p) + 20, first=2 * i) for i, p in enumerate(prompts)]
+
+    def drive(spec, force_at=None):
+        run = _runner(cfg, C.PREC_FP32)
+        try:
+            run.set_speculation(spec)
+            seqs = [list(p) for p in prompts]
+            out, _ = run.run_flat(seqs, True, [0] * 4, bts, [0.0] * 4)
+            toks, hits, logs = [out.copy()], 0, []
+            for step in range(10):
+                for i, (s, t) in enumerate(zip(seqs, out)):
+                    # a forced token differs from what the device predicted: a miss
+                    s.append(7 if (force_at == step and i == 1) else int(t))
+                if step == 6:  # another batch in between (the first two sequences only): a miss
+                    o2, _ = run.run_flat(seqs[:2], False, None, bts[:2], [0.0] * 2)
+                    logs.append(o2.copy())
+                    for s, t in zip(seqs[:2], o2):
+                        s.append(int(t))
+                out, lg = run.run_flat(seqs, False, None, bts, [0.0] * 4, want_logits=True)
+                hits += int(run.last_stats.h2d_bytes == 0)
+                toks.append(out.copy())
+                logs.append(lg.copy())
+            return toks, hits, logs
+        finally:
+            run.close()
+
+    for force_at in (None, 3):
+        ref_t, ref_h, ref_l = drive(False, force_at)
+        got_t, got_h, got_l = drive(True, force_at)
+        assert ref_h == 0
+        # steps 0..9: every step hits except the forced one, the one after the interleaved
+        # batch, and the one call after each miss that does not speculate
+        assert got_h >= 5, got_h
+        for a, b in zip(ref_t, got_t):
+            np.testing.assert_array_equal(a, b)
+        for a, b in zip(ref_l, got_l):
+            np.testing.assert_array_equal(a, b)  # same kernels, same order: bit-identical
+
+
 def test_profile_reports_every_kernel_class():
     cfg = TINY["granite"]()
     run = _runner(cfg, C.PREC_BF16)
