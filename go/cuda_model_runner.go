@@ -238,6 +238,16 @@ func (r *CudaModelRunner) SetSamplingParamsWithRepetition(temperature, topP floa
 	C.nvllm_set_sampling(r.h, C.float(topP), C.int(topK), C.float(rep))
 }
 
+// SetSpeculation toggles the library's speculative next decode step (include/nvllm.h:
+// nvllm_set_speculation; on by default).  Not part of the reference's method set.
+func (r *CudaModelRunner) SetSpeculation(on bool) {
+	v := 0
+	if on {
+		v = 1
+	}
+	C.nvllm_set_speculation(r.h, C.int(v))
+}
+
 // ClearCache / ClearAllCaches (tensor_model_runner.go:100-111): KV state lives in the paged
 // pool and is addressed only through BlockTable, so there is nothing to free per sequence.
 func (r *CudaModelRunner) ClearCache(seqID int64) {}

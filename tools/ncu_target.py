@@ -13,6 +13,8 @@ steps = int(sys.argv[4]) if len(sys.argv) > 4 else 3
 cfg = C.PRESETS[model]()
 job = bench.Job(cfg, batch, plen, steps, 4321)
 run = bench.make_runner(cfg, job, 0)
+# ncu serialises and replays kernels: capture-free launches keep -k / -s / -c counting simple
+run.set_graphs(bool(int(os.environ.get('NVLLM_GRAPHS', '0'))))
 job.stage(run)
 for _ in range(steps):
     run.run_resident()
