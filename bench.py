@@ -468,7 +468,15 @@ def main():
             ach = e["bytes"] / e["launches"] / (per * 1e6)
             peak = peaks["hbm_gbs"]
             roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s"}
-        roofline.update({"frac": ach / peak, "traffic": None, "kernel": f"{phase}.{name}",
+        traffic = None
+        try:  # per-launch DRAM bytes of the dominant kernel from the committed ncu --set full capture
+            tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+            ent = tr.get(f"{phase}.{name}")
+            if ent and ent.get("workload", "").split()[0] == cfg.name.lower():
+                traffic = ent["dram_bytes_per_launch"]
+        except (OSError, ValueError, KeyError):
+            traffic = None
+        roofline.update({"frac": ach / peak, "traffic": traffic, "kernel": f"{phase}.{name}",
                          "avg_launch_us": per * 1e3, "launches": e["launches"],
                          "peak_source": peaks["source"],
                          "share_of_step": e["ms"] / sum(x["ms"] for p in (prof_prefill, prof_decode)
