@@ -54,19 +54,30 @@ struct DecSmem {
   static constexpr int RED_BYTES = DT_CONSUMERS * 8 * RS * 4;
 };
 
-template <int HD, int BN, int STAGES>
+// KPC = kv heads per CTA (1, 2, 4).  The four consumer warps split into KPC groups of
+// WPH = 4 / KPC warps; group i owns head i of the CTA for the whole kernel, its warps split each
+// 64-key tile of that head between them.  The tiles of the KPC heads are interleaved in the
+// ring, so the groups stream concurrently and never wait for each other: no CTA-wide barrier
+// after the prologue, a WPH-warp merge per head (none at all for KPC = 4).
+template <int HD, int BN, int STAGES, int KPC>
 __global__ void __launch_bounds__(DT_THREADS, (HD == 64 && BN == 64 && STAGES <= 4) ? 3 : 2)
 attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
-                     AttnArgs a, int G, int kpc, Trace tr) {
+                     AttnArgs a, int G, Trace tr) {
+  constexpr int kpc = KPC;
+  constexpr int WPH = DT_CONSUMERS / KPC;  // warps per head
   const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
   pdl_launch_dependents();
   using SM = DecSmem<HD>;
   constexpr int PANELS = HD / 64;
   constexpr uint32_t TILE_BYTES = BN * HD * 2;
-  constexpr int WK = BN / DT_CONSUMERS;  // keys per consumer warp per tile
+  constexpr int WK = BN / WPH;  // keys per consumer warp per tile
   constexpr int MT = WK / 16;
   constexpr int RS = SM::RS;
   static_assert(WK % 16 == 0, "tile too small for the consumer warps");
+  // tile f = j * KPC + head sits in stage f % STAGES: with STAGES a multiple of KPC a stage only
+  // ever holds tiles of ONE head, so exactly one warp group waits on / releases its barriers
+  // (a group that skipped a phase of a barrier would see a stale parity as "complete")
+  static_assert(STAGES % KPC == 0, "each ring stage must belong to one head group");
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw = smem_u32(smem_raw);
@@ -97,7 +108,7 @@ attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_const
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; s++) {
       mbar_init(bars + 8 * s, 1);
-      mbar_init(bars + 8 * (STAGES + s), DT_CONSUMERS);
+      mbar_init(bars + 8 * (STAGES + s), WPH);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -118,7 +129,7 @@ attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_const
     bool waited = fused;
     for (int f = 0; f < F; f++) {
       const int stage = f % STAGES;
-      const int hh = f / n_tiles, j = f - hh * n_tiles;
+      const int hh = f % KPC, j = f / KPC;  // heads interleaved tile by tile
       const int k0 = (tile_begin + j) * BN;
       if (!waited && k0 + BN > len - 1) {
         pdl_wait();
@@ -262,28 +273,29 @@ attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_const
   const float scale_log2 = a.scale * 1.4426950408889634f;
   const int limit = len - 1;
 
-  for (int f = 0; f < F; f++) {
-    const int stage = f % STAGES;
-    const int hh = f / n_tiles, j = f - hh * n_tiles;
-    if (j == 0) {
-      const uint32_t q = sQ + hh * SM::Q_BYTES + g * SM::QROW + t * 4;
+  const int hh = warp / WPH, wi = warp % WPH;  // this warp's head and its slot in the group
+  {
+    const uint32_t q = sQ + hh * SM::Q_BYTES + g * SM::QROW + t * 4;
 #pragma unroll
-      for (int ks = 0; ks < HD / 16; ks++) {
-        qb[ks][0] = lds32(q + ks * 32);
-        qb[ks][1] = lds32(q + ks * 32 + 16);
-      }
-#pragma unroll
-      for (int dt = 0; dt < HD / 16; dt++)
-#pragma unroll
-        for (int i = 0; i < 4; i++) o[dt][i] = 0.f;
-      m[0] = m[1] = -INFINITY;
-      l[0] = l[1] = 0.f;
+    for (int ks = 0; ks < HD / 16; ks++) {
+      qb[ks][0] = lds32(q + ks * 32);
+      qb[ks][1] = lds32(q + ks * 32 + 16);
     }
+#pragma unroll
+    for (int dt = 0; dt < HD / 16; dt++)
+#pragma unroll
+      for (int i = 0; i < 4; i++) o[dt][i] = 0.f;
+    m[0] = m[1] = -INFINITY;
+    l[0] = l[1] = 0.f;
+  }
+  for (int j = 0; j < n_tiles; j++) {
+    const int f = j * KPC + hh;
+    const int stage = f % STAGES;
     mbar_wait(bars + 8 * stage, (f / STAGES) & 1);
-    if (tr.buf && f == 0) t_first = gtime();
+    if (tr.buf && j == 0) t_first = gtime();
     const uint32_t tK = sK + stage * TILE_BYTES, tV = sV + stage * TILE_BYTES;
     const int k0 = (tile_begin + j) * BN;
-    const int key0 = warp * WK;
+    const int key0 = wi * WK;
     bool patched = false;
     if (has_new && j == n_tiles - 1) {
       // the tile landed with whatever the pool held at position len - 1: the warp that owns
@@ -372,15 +384,32 @@ attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_const
     __syncwarp();
     if (lane == 0) mbar_arrive(bars + 8 * (STAGES + stage));
 
-    if (j == n_tiles - 1) {
-      if (tr.buf && hh == 0) t_fin0 = gtime();
-      // ---- merge the 4 warps (each covered different keys) and write head group hh
+  }
+  if (n_tiles > 0) {
+    if (tr.buf && hh == 0) t_fin0 = gtime();
+    // ---- finish this group's head: row sums over the 8 key lanes, then either write straight
+    // from the registers (one warp per head) or merge the group's WPH warps through `red`
+#pragma unroll
+    for (int e = 0; e < 2; e++) {
+      l[e] += __shfl_xor_sync(0xffffffffu, l[e], 4);
+      l[e] += __shfl_xor_sync(0xffffffffu, l[e], 8);
+      l[e] += __shfl_xor_sync(0xffffffffu, l[e], 16);
+    }
+    const int h0 = (kvh0 + hh) * G;
+    if constexpr (WPH == 1) {
 #pragma unroll
       for (int e = 0; e < 2; e++) {
-        l[e] += __shfl_xor_sync(0xffffffffu, l[e], 4);
-        l[e] += __shfl_xor_sync(0xffffffffu, l[e], 8);
-        l[e] += __shfl_xor_sync(0xffffffffu, l[e], 16);
+        const int r = 2 * t + e;
+        if (r >= G) continue;
+        const float inv = 1.f / l[e];
+        bf16* op = (bf16*)a.out + (size_t)seq * a.nh * HD + (size_t)(h0 + r) * HD;
+#pragma unroll
+        for (int dt = 0; dt < HD / 16; dt++) {
+          op[dt * 16 + g] = __float2bfloat16_rn(o[dt][e] * inv);
+          op[dt * 16 + 8 + g] = __float2bfloat16_rn(o[dt][2 + e] * inv);
+        }
       }
+    } else {
 #pragma unroll
       for (int e = 0; e < 2; e++) {
         const int r = 2 * t + e;
@@ -396,17 +425,23 @@ attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_const
           rr[HD + 1] = l[e];
         }
       }
-      consumer_bar();
-      const int h0 = (kvh0 + hh) * G;
-      for (int idx = threadIdx.x; idx < G * HD; idx += DT_CONSUMERS * 32) {
+      // immediate barrier ids: a register id would make ptxas reserve all 16 named barriers
+      if constexpr (WPH == DT_CONSUMERS) {
+        consumer_bar();
+      } else {
+        if (hh == 0) asm volatile("bar.sync 2, 64;" ::: "memory");
+        else asm volatile("bar.sync 3, 64;" ::: "memory");
+      }
+      const int w0 = hh * WPH;
+      for (int idx = threadIdx.x - w0 * 32; idx < G * HD; idx += WPH * 32) {
         const int r = idx / HD, d = idx % HD;
         float mn = -INFINITY;
 #pragma unroll
-        for (int w = 0; w < DT_CONSUMERS; w++) mn = fmaxf(mn, red[((size_t)w * 8 + r) * RS + HD]);
+        for (int w = 0; w < WPH; w++) mn = fmaxf(mn, red[((size_t)(w0 + w) * 8 + r) * RS + HD]);
         float lt = 0.f, at = 0.f;
 #pragma unroll
-        for (int w = 0; w < DT_CONSUMERS; w++) {
-          const float* rr = red + ((size_t)w * 8 + r) * RS;
+        for (int w = 0; w < WPH; w++) {
+          const float* rr = red + ((size_t)(w0 + w) * 8 + r) * RS;
           const float c = (rr[HD] == -INFINITY) ? 0.f : exp2f((rr[HD] - mn) * scale_log2);
           lt += rr[HD + 1] * c;
           at += rr[d] * c;
@@ -423,7 +458,6 @@ attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_const
           }
         }
       }
-      if (hh + 1 < kpc) consumer_bar();  // `red` is rewritten by the next head
     }
   }
   if (n_tiles == 0) {  // empty split: (0, -inf, 0) records
@@ -451,64 +485,59 @@ bool attn_decode_t_supported(const AttnArgs& a) {
          a.nh / a.nkv <= 8 && a.pool_blocks > 0;
 }
 
-template <int HD, int BN, int STAGES>
-static cudaError_t decode_t_launch(cudaStream_t st, const AttnArgs& a, int G, int kpc) {
+template <int HD, int BN, int STAGES, int KPC>
+static cudaError_t decode_t_launch(cudaStream_t st, const AttnArgs& a, int G) {
   using SM = DecSmem<HD>;
+  constexpr int kpc = KPC;
   const size_t smem = 1024 + (size_t)2 * STAGES * BN * HD * 2 + SM::RED_BYTES +
                       (size_t)kpc * SM::Q_BYTES + (size_t)kpc * 2 * HD * 2 + 16 * STAGES;
   const int pool_rows = a.pool_blocks * a.nkv * KV_BLOCK;
   const TmaDesc* tk = tma_map_cached(a.kpool, pool_rows, HD, BN);
   const TmaDesc* tv = tma_map_cached(a.vpool, pool_rows, HD, BN);
   if (!tk || !tv) return cudaErrorInvalidValue;
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
-    cudaError_t e = cudaFuncSetAttribute(attn_decode_t_kernel<HD, BN, STAGES>,
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t e = cudaFuncSetAttribute(attn_decode_t_kernel<HD, BN, STAGES, KPC>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    smem_set = smem;
+    attr_set = true;
   }
-  (void)launch_k(attn_decode_t_kernel<HD, BN, STAGES>, dim3(a.n_seqs, a.nkv / kpc, a.n_splits),
+  (void)launch_k(attn_decode_t_kernel<HD, BN, STAGES, KPC>, dim3(a.n_seqs, a.nkv / kpc, a.n_splits),
                  dim3(DT_THREADS), smem, st, *reinterpret_cast<const CUtensorMap*>(tk),
-                 *reinterpret_cast<const CUtensorMap*>(tv), a, G, kpc, next_trace(4));
+                 *reinterpret_cast<const CUtensorMap*>(tv), a, G, next_trace(4));
   return cudaGetLastError();
 }
 
-// Shape of the launch: `cfg` = 100 * BN-code + 10 * stages + kpc can be forced for experiments
-// with NVLLM_ATTN_T_CFG (e.g. 1231 = 128-key tiles, 3 stages, 1 kv head per CTA).
+// kv heads per CTA can be forced with NVLLM_ATTN_T_KPC (1, 2, 4) for experiments.
 cudaError_t launch_attn_decode_t(cudaStream_t st, const AttnArgs& a) {
   if (a.n_seqs <= 0) return cudaSuccess;
   const int G = a.nh / a.nkv;
-  static const int cfg_env = getenv("NVLLM_ATTN_T_CFG") ? atoi(getenv("NVLLM_ATTN_T_CFG")) : 0;
-  // The fixed cost of a CTA (launch, prologue, first-tile latency, warp merge) is ~4 us against
-  // ~0.6 us per 64-key tile: when the step has more (sequence, kv head) pairs than resident
-  // CTA slots, pack kpc heads per CTA (the TMA ring runs straight through the head boundary)
-  // while the grid still covers ~1.6 CTAs per SM — measured on cfg2 (512 pairs): 1 head/CTA
-  // 1141 us/step, 2 heads/CTA 1112 us/step.
-  int bn = 64, kpc = 1;
+  // read per launch (not cached): the parity tests switch it between runners
+  const char* kpc_s = getenv("NVLLM_ATTN_T_KPC");
+  const int kpc_env = kpc_s ? atoi(kpc_s) : 0;
+  // The fixed cost of a CTA (launch, prologue, first-tile latency) is ~4 us against ~0.6 us
+  // per 64-key tile: when the step has more (sequence, kv head) pairs than resident CTA slots,
+  // pack 2 heads per CTA while the grid still covers ~1.6 CTAs per SM.  (4 heads per CTA with
+  // one stage per head measured slower — cfg3 1810 vs 1775 us/step, cfg2 1231 vs 1088 — and is
+  // only reachable through the knob.)
+  int kpc = 1;
   if (a.n_splits == 1) {
     const int sm = a.sm_count > 0 ? a.sm_count : 148;
-    while (kpc < 4 && a.nkv % (kpc * 2) == 0 &&
+    while (kpc < 2 && a.nkv % (kpc * 2) == 0 &&
            (long)a.n_seqs * (a.nkv / (kpc * 2)) * 10 >= (long)sm * 16)
       kpc *= 2;
+    if ((kpc_env == 1 || kpc_env == 2 || kpc_env == 4) && a.nkv % kpc_env == 0) kpc = kpc_env;
   }
-  int stages = a.hd == 64 ? (kpc > 1 ? 6 : 4) : 3;
-  if (cfg_env > 0) {
-    bn = cfg_env / 100 >= 12 ? 128 : 64;
-    stages = (cfg_env / 10) % 10;
-    kpc = cfg_env % 10;
-  }
-  if (kpc < 1 || a.nkv % kpc != 0 || a.n_splits > 1) kpc = 1;
   if (a.hd == 64) {
-    if (bn == 128) {
-      if (stages == 2) return decode_t_launch<64, 128, 2>(st, a, G, kpc);
-      return decode_t_launch<64, 128, 3>(st, a, G, kpc);
-    }
-    if (stages == 3) return decode_t_launch<64, 64, 3>(st, a, G, kpc);
-    if (stages == 6) return decode_t_launch<64, 64, 6>(st, a, G, kpc);
-    return decode_t_launch<64, 64, 4>(st, a, G, kpc);
+    // 4 heads: one 16 KB stage per head (3 CTAs / SM, 12 head streams per SM in flight)
+    if (kpc == 4) return decode_t_launch<64, 64, 4, 4>(st, a, G);
+    if (kpc == 2) return decode_t_launch<64, 64, 6, 2>(st, a, G);
+    if (a.n_splits > 1) return decode_t_launch<64, 64, 6, 1>(st, a, G);
+    return decode_t_launch<64, 64, 4, 1>(st, a, G);
   }
-  if (stages == 2) return decode_t_launch<128, 64, 2>(st, a, G, kpc);
-  return decode_t_launch<128, 64, 3>(st, a, G, kpc);
+  // head dim 128: 32 KB stages; at most 2 heads per CTA
+  if (kpc >= 2) return decode_t_launch<128, 64, 2, 2>(st, a, G);
+  return decode_t_launch<128, 64, 3, 1>(st, a, G);
 }
 
 }  // namespace nvllm

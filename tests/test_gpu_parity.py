@@ -162,6 +162,23 @@ def test_bf16_long_context_split_kv(name):
     _greedy_parity(name, C.PREC_BF16, prompt_len=700, steps=6, table=TINY_HD)
 
 
+PACKED = {
+    # four kv heads so that 1, 2 or 4 of them can share a decode-attention CTA
+    "llama_kv4_hd64": lambda: C.tiny_llama(hidden=512, num_heads=8, num_kv_heads=4, head_dim=64),
+    "llama_kv4_hd128": lambda: C.tiny_llama(hidden=512, num_heads=4, num_kv_heads=4, head_dim=128),
+}
+
+
+@pytest.mark.parametrize("name", list(PACKED))
+@pytest.mark.parametrize("kpc", [1, 2, 4])
+def test_decode_attention_heads_per_cta(name, kpc, monkeypatch):
+    """attention_dec.cu packs 1, 2 or 4 kv heads per CTA (4, 2 or 1 warps per head, tiles of the
+    heads interleaved in the TMA ring); big batches pick 2 or 4 on their own, here the knob
+    forces each variant.  300-token prompt: two KV blocks, the appended row crosses tiles."""
+    monkeypatch.setenv("NVLLM_ATTN_T_KPC", str(kpc))
+    _greedy_parity(name, C.PREC_BF16, prompt_len=300, steps=8, table=PACKED)
+
+
 MOE_WIDE = {
     # grouped tensor-core expert GEMMs: several 128-row weight tiles per expert, experts with
     # more rows than one token tile (600 x 4 / 8 = 300 rows per expert on average), N not a
