@@ -388,9 +388,16 @@ def test_error_paths_return_codes_not_aborts():
         with pytest.raises(L.NvllmError) as e:  # block id outside the pool
             run.run_flat([[1] * 10], True, [0], [[9999]], [0.0])
         assert e.value.code == L.ERR_RANGE
-        # the handle is still usable after errors
+        for bad in ((0.0, 0, 1.0), (1.0, -1, 1.0), (1.0, 0, 0.0)):  # top_p, top_k, penalty
+            with pytest.raises(L.NvllmError) as e:
+                run.set_sampling_params(1.0, top_p=bad[0], top_k=bad[1], repetition_penalty=bad[2])
+            assert e.value.code == L.ERR_INVALID
+        # the handle is still usable after errors (and after a speculative step was thrown away
+        # by the failing calls above)
         toks, _ = run.run_flat([[1, 2, 3]], True, [0], [[0]], [0.0])
         assert 0 <= toks[0] < cfg.vocab_size
+        toks2, _ = run.run_flat([[1, 2, 3, int(toks[0])]], False, None, [[0]], [0.0])
+        assert 0 <= toks2[0] < cfg.vocab_size
     finally:
         run.close()
 
