@@ -503,7 +503,12 @@ int tc5_splits(int M, int N, int K, int sm_count) {
   if (tiles >= 2L * sm_count) return 1;
   int best = 1;
   double best_cost = 1e30;
-  for (int s = 1; s <= 16 && s <= nkb; s++) {
+  // The consumer of the partials sums up to 8 slices with one batch of loads (sum_partials8); a
+  // 9th slice costs it a second L2 round trip, more than the GEMM gains from the finer split
+  // (cfg2 decode, W2 GEMM K = 8192: S = 9 -> 1105 us/step, capped at 8 -> 1079; 6 -> 1099).
+  // NVLLM_TC5_SMAX overrides the cap.
+  static const int smax = getenv("NVLLM_TC5_SMAX") ? atoi(getenv("NVLLM_TC5_SMAX")) : 8;
+  for (int s = 1; s <= smax && s <= nkb; s++) {
     const int kbps = ceil_div(nkb, s);
     if (s > 1 && kbps < 2) break;
     const int s_eff = ceil_div(nkb, kbps);
