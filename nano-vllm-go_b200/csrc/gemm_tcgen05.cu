@@ -101,6 +101,10 @@ struct Tc5Sched {
   const int* g_rows;
   const int* g_ntiles;
   int g_N;
+  // decode-sized grouped GEMMs: raw weight base / bytes per weight row / expert count for the
+  // speculative L2 prefetch before the dependency resolves (null = off)
+  const uint8_t* g_wbase;
+  int g_row_bytes, g_E;
 };
 // rot: CTAs working on the same k range start at different k-blocks (and wrap), so that at any
 // instant they pull DIFFERENT activation tiles out of L2 — otherwise every CTA of a skinny
@@ -223,6 +227,25 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
         if (++kb == t.nkb) {
           kb = 0;
           u += grid;
+        }
+      }
+    }
+    // (1a') grouped mode cannot know its experts before the sort kernel has run, but a decode
+    // batch routes a handful of rows to EVERY expert: one token tile per expert, in expert
+    // order, so unit u multiplies expert u / n_tiles.  Pull that guess into L2 now (a wrong
+    // guess only costs bandwidth); the real TMA loads after the wait then hit L2.
+    if (grouped && sc.g_wbase && (prefetch & 1)) {
+      for (int u = blockIdx.x; u < sc.g_E * sc.n_tiles; u += grid) {
+        const int nt = u % sc.n_tiles, e = u / sc.n_tiles;
+        const int rows = min(TC_BN, sc.g_N - nt * TC_BN);
+        const uint8_t* base = sc.g_wbase + ((size_t)e * sc.g_N + (size_t)nt * TC_BN) * sc.g_row_bytes;
+        const uint32_t bytes = (uint32_t)rows * sc.g_row_bytes;
+        constexpr uint32_t PIECE = 8192;
+        for (uint32_t o = lane * PIECE; o < bytes; o += 32 * PIECE) {
+          const uint32_t sz = (bytes - o < PIECE ? bytes - o : PIECE) & ~15u;
+          if (sz)
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(base + o), "r"(sz)
+                         : "memory");
         }
       }
     }
@@ -590,6 +613,12 @@ static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* t
     sc.g_rows = a.g_tile_rows;
     sc.g_ntiles = a.g_n_tiles;
     sc.g_N = a.N;
+    // average rows per expert within one token tile: the one-tile-per-expert guess is plausible
+    if (a.M <= (long)BT * a.g_experts && (((size_t)a.K * 2) % 16) == 0) {
+      sc.g_wbase = (const uint8_t*)a.W;
+      sc.g_row_bytes = a.K * 2;
+      sc.g_E = a.g_experts;
+    }
     m_tiles = min(a.g_max_tiles, a.M / BT + a.g_experts);  // upper bound; the kernel reads the count
   }
   sc.units = sc.n_tiles * m_tiles * sc.S;
