@@ -88,15 +88,13 @@ __device__ __forceinline__ void moe_route_row(const float* y, const float* __res
         bi = e;
       }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-      int oi = __shfl_xor_sync(0xffffffffu, bi, o);
-      if (ov > bv || (ov == bv && oi < bi)) {
-        bv = ov;
-        bi = oi;
-      }
-    }
+    // warp arg-max in two redux operations instead of five shuffle rounds: probabilities are
+    // >= 0, so their bit patterns order like the values (+1 keeps a genuine 0.0 above the -1 of
+    // a lane with no candidate); ties go to the lower expert index
+    const unsigned key = bv < 0.f ? 0u : __float_as_uint(bv) + 1u;
+    const unsigned kmax = __reduce_max_sync(0xffffffffu, key);
+    bi = (int)__reduce_min_sync(0xffffffffu, key == kmax ? (unsigned)bi : 0x7fffffffu);
+    bv = kmax ? __uint_as_float(kmax - 1u) : -1.f;
     if (lane == s) {
       sel_p = bv;
       sel_i = bi;
