@@ -248,7 +248,8 @@ def make_runner(cfg, job, device, keep_host=None, tp_size=1, tp_rank=0, tp_id=No
     max_T = max(len(g) for g in job.prefill_steps) * job.P
     return R.CudaModelRunner(cfg, gen(), precision=C.PREC_BF16, num_kv_blocks=job.num_blocks,
                              device=device, max_num_seqs=job.n, max_batched_tokens=max_T,
-                             weight_dtype=C.DT_BF16, tp_size=tp_size, tp_rank=tp_rank, tp_id=tp_id)
+                             weight_dtype=C.DT_BF16, tp_size=tp_size, tp_rank=tp_rank, tp_id=tp_id,
+                             sampling=None)  # greedy rows: the job is BASELINE's greedy decode
 
 
 def cpu_oracle_sample(cfg, weights, budget_s, prompt_tokens=None):

@@ -13,8 +13,10 @@
 //
 // plus the extras of TensorModelRunner (tensor_model_runner.go:35-52,100-111) and
 // GenericModelRunner (purego/generic_runner.go:184-196).  The image this library was built
-// in has no Go toolchain, so this file is shipped uncompiled; nano-vllm-go_b200/runner.py is
-// the same shim over ctypes and is what the tests exercise.
+// in has no Go toolchain, so this file is shipped UNCOMPILED (INTEGRATION.md says so);
+// nano-vllm-go_b200/runner.py is the same shim over ctypes and is what the GPU tests exercise.
+// tests/test_go_shim.py statically checks every selector used below (model.X, b.X.Y, mc.X,
+// tensor.X, engineCfg.X, s.X, C.X) against the reference's Go declarations and include/nvllm.h.
 package nanovllm
 
 /*
@@ -35,7 +37,11 @@ import (
 type CudaModelRunner struct {
 	h           *C.nvllm_handle
 	cfg         *tensor.ModelConfig
-	temperature float32 // <= 0: greedy argmax (cmd/ask/main.go:389-402)
+	// sampling defaults of NewTensorModelRunner (tensor_model_runner.go:27-31 ->
+	// tensor.DefaultSamplingParams, sampling.go:17-24): temperature 1.0, repetition penalty 1.2.
+	// temperature <= 0 selects the greedy first-max rule of cmd/ask/main.go:389-402 (deviation:
+	// the reference runner treats 0 as "no temperature scaling" and still draws).
+	temperature float32
 
 	// reusable flattening buffers (no Go pointer is retained by the library)
 	tok, cuSeq, cached, bt, cuBt, out []C.int32_t
@@ -99,9 +105,14 @@ func NewCudaModelRunner(modelDir string, engineCfg *Config, device int, bf16 boo
 	if rc := C.nvllm_create(&cc, nil, &h); rc != 0 {
 		return nil, lastError(nil)
 	}
-	r := &CudaModelRunner{h: h, cfg: mc}
+	r := &CudaModelRunner{h: h, cfg: mc, temperature: 1.0}
+	if rc := C.nvllm_set_sampling(h, C.float(1.0), C.int(0), C.float(1.2)); rc != 0 {
+		e := lastError(h)
+		C.nvllm_destroy(h)
+		return nil, e
+	}
 	set := func(id C.int, layer int, t *tensor.Tensor) error {
-		if t == nil {
+		if t == nil || len(t.Data) == 0 {
 			return nil // optional tensors (biases) are simply not sent
 		}
 		if rc := C.nvllm_set_weight(h, id, C.int(layer), C.NVLLM_DT_F32,
@@ -159,9 +170,15 @@ func (r *CudaModelRunner) setBlock(set func(C.int, int, *tensor.Tensor) error, l
 	case *tensor.MultiQueryAttention:
 		es = append(es, set(C.NVLLM_W_Q, l, a.QWeight), set(C.NVLLM_W_KV, l, a.KVWeight), set(C.NVLLM_W_O, l, a.OutWeight),
 			set(C.NVLLM_W_Q_BIAS, l, a.QBias), set(C.NVLLM_W_O_BIAS, l, a.OutBias))
+		if a.KVBias != nil { // [K | V] halves (mqa.go:20,120-125): the library keeps K and V biases apart
+			hd := a.HeadDim
+			es = append(es,
+				set(C.NVLLM_W_K_BIAS, l, &tensor.Tensor{Data: a.KVBias.Data[:hd], Shape: []int{hd}}),
+				set(C.NVLLM_W_V_BIAS, l, &tensor.Tensor{Data: a.KVBias.Data[hd : 2*hd], Shape: []int{hd}}))
+		}
 	}
 	if b.MoE != nil {
-		es = append(es, set(C.NVLLM_W_MOE_ROUTER, l, b.MoE.RouterWeight), set(C.NVLLM_W_MOE_INPUT, l, b.MoE.InputLinear),
+		es = append(es, set(C.NVLLM_W_MOE_ROUTER, l, b.MoE.Router), set(C.NVLLM_W_MOE_INPUT, l, b.MoE.InputLinear),
 			set(C.NVLLM_W_MOE_OUTPUT, l, b.MoE.OutputLinear))
 	} else if b.FFN != nil {
 		es = append(es, set(C.NVLLM_W_FFN_W1, l, b.FFN.W1), set(C.NVLLM_W_FFN_W2, l, b.FFN.W2),
@@ -206,8 +223,8 @@ func (r *CudaModelRunner) Run(seqs []*Sequence, isPrefill bool) ([]int, error) {
 	}
 	// cgo may move this goroutine between OS threads between calls; every entry point of the
 	// library does cudaSetDevice itself, so no thread pinning is needed here.
-	rc := C.nvllm_run(r.h, C.int(n), prefill, &r.tok[0], &r.cuSeq[0], &r.cached[0], &r.bt[0], &r.cuBt[0],
-		&r.temp[0], nil, &r.out[0], nil, nil)
+	rc := C.nvllm_run(r.h, C.int(n), prefill, i32ptr(r.tok), i32ptr(r.cuSeq), i32ptr(r.cached), i32ptr(r.bt),
+		i32ptr(r.cuBt), &r.temp[0], nil, &r.out[0], nil, nil)
 	if rc != 0 {
 		return nil, lastError(r.h)
 	}
@@ -216,6 +233,15 @@ func (r *CudaModelRunner) Run(seqs []*Sequence, isPrefill bool) ([]int, error) {
 		res[i] = int(r.out[i])
 	}
 	return res, nil
+}
+
+// i32ptr is &s[0] that tolerates an empty slice (a sequence without blocks or tokens is
+// rejected by the library with NVLLM_ERR_INVALID instead of a Go panic here).
+func i32ptr(s []C.int32_t) *C.int32_t {
+	if len(s) == 0 {
+		return nil
+	}
+	return &s[0]
 }
 
 // Close implements ModelRunner.Close (model_runner.go:15).

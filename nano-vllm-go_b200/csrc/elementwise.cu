@@ -640,18 +640,23 @@ cudaError_t launch_sample(cudaStream_t st, const float* logits, int ldl, int V, 
 __global__ void advance_kernel(int n, const int* __restrict__ sampled, int* tokens, int* positions,
                                int* slots, int* seq_len, const int* __restrict__ block_tables,
                                int max_blocks, int max_pos) {
-  pdl_wait();  // step prologue: later kernels may read the step state before their own wait
-  pdl_launch_dependents();
+  // Step prologue: later kernels read the step state BEFORE their own griddepcontrol.wait, so
+  // the dependents are released only after this kernel's writes (the embedding kernel that
+  // follows additionally waits for this grid's completion before it releases its own).
+  pdl_wait();
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  tokens[i] = sampled[i];
-  int pos = positions[i] + 1;
-  if (pos >= max_pos) pos = max_pos - 1;  // caller bounds n_steps; never index past the table
-  int bi = pos / KV_BLOCK;
-  if (bi >= max_blocks) bi = max_blocks - 1;
-  positions[i] = pos;
-  seq_len[i] = pos + 1;
-  slots[i] = block_tables[(size_t)i * max_blocks + bi] * KV_BLOCK + pos % KV_BLOCK;
+  if (i < n) {
+    tokens[i] = sampled[i];
+    int pos = positions[i] + 1;
+    if (pos >= max_pos) pos = max_pos - 1;  // the host bounds every sequence; never index past the table
+    int bi = pos / KV_BLOCK;
+    if (bi >= max_blocks) bi = max_blocks - 1;
+    positions[i] = pos;
+    seq_len[i] = pos + 1;
+    slots[i] = block_tables[(size_t)i * max_blocks + bi] * KV_BLOCK + pos % KV_BLOCK;
+  }
+  __threadfence();
+  pdl_launch_dependents();
 }
 
 cudaError_t launch_advance(cudaStream_t st, int n, const int* sampled, int* tokens, int* positions,
@@ -791,8 +796,8 @@ __global__ void make_decode_state_kernel(int n, int mb, const int* __restrict__ 
                                          const int* __restrict__ src_uni, int* tokens,
                                          int* positions, int* slots, int* cu_q, int* seq_start,
                                          int* seq_len, int* last_row, int* bt, int* temp, int* uni) {
-  pdl_wait();  // step prologue: later kernels may read the step state before their own wait
-  pdl_launch_dependents();
+  // step prologue: dependents are released after the writes below (see advance_kernel)
+  pdl_wait();
   const int i = blockIdx.x;
   for (int b = threadIdx.x; b < mb; b += blockDim.x) bt[(size_t)i * mb + b] = src_bt[(size_t)i * mb + b];
   if (threadIdx.x == 0) {
@@ -810,6 +815,9 @@ __global__ void make_decode_state_kernel(int n, int mb, const int* __restrict__ 
     temp[i] = src_temp[i];
     uni[i] = src_uni[i];
   }
+  __threadfence();
+  __syncthreads();
+  pdl_launch_dependents();
 }
 cudaError_t launch_make_decode_state(cudaStream_t st, int n, int mb, const int* sampled,
                                      const int* src_seq_len, const int* src_bt, const int* src_temp,

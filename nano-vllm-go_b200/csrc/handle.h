@@ -160,6 +160,9 @@ struct nvllm_handle {
     }
   } graph_sig[2];
   int graph_launches[2] = {0, 0};
+  // where the captured step leaves its summed logits (forward_step picks the buffer per launch
+  // shape; a replay does not run the host code that records it)
+  const float* graph_logits[2] = {nullptr, nullptr};
   void drop_graphs() {
     for (auto& g : step_graph) {
       if (g) cudaGraphExecDestroy(g);
@@ -171,8 +174,13 @@ struct nvllm_handle {
   // nvllm_run_resident when it asks for exactly that step, overwritten otherwise
   int spec_enabled = 1;
   bool spec_pending = false;
+  bool spec_used_graph = false;  // the in-flight speculative step replayed a graph
   int spec_skip = 0;  // calls that do not speculate (set after a miss)
   std::vector<int32_t> spec_len, spec_nb, spec_bt;  // per-sequence lengths / block tables of the last call
+  // device-resident decode state as the host knows it: context length (incl. the token the last
+  // step appended) and block-table extent of every sequence — nvllm_run_resident refuses to step
+  // a sequence past its own table (the padded entries of a ragged batch are not its blocks)
+  std::vector<int32_t> res_len, res_nb;
   int32_t* d_stage2 = nullptr;  // decode layout derived on the device from a prefill step
   size_t stage2_words = 0;
   // per-kernel-class profile (nvllm_set_profile / nvllm_get_profile)

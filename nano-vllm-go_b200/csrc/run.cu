@@ -121,9 +121,11 @@ static int graphed_step(nvllm_handle* h, int slot, Pre pre, bool* used) {
     }
     h->graph_sig[slot] = sig;
     h->graph_launches[slot] = h->launches;
+    h->graph_logits[slot] = h->ws.logits_final;
   }
   NV_CHECK(h, cudaGraphLaunch(h->step_graph[slot], st));
   h->launches = h->graph_launches[slot];
+  h->ws.logits_final = h->graph_logits[slot];
   *used = true;
   return NVLLM_OK;
 }
@@ -137,7 +139,7 @@ static int graphed_step(nvllm_handle* h, int slot, Pre pre, bool* used) {
 // and only has to wait for it, or asks for something else and restages everything as usual.
 // A speculative step that is thrown away has only written K/V at the next position of each
 // sequence, a slot nothing reads before its owner writes it.
-static int resident_step(nvllm_handle* h, nvllm_run_stats* stats);
+static int resident_step(nvllm_handle* h, nvllm_run_stats* stats, bool* used_graph = nullptr);
 static void remember_call(nvllm_handle* h, int n, const int32_t* cu_seqlens, const int32_t* block_tables,
                           const int32_t* cu_blocks) {
   h->spec_len.resize(n);
@@ -147,6 +149,8 @@ static void remember_call(nvllm_handle* h, int n, const int32_t* cu_seqlens, con
     h->spec_nb[i] = cu_blocks[i + 1] - cu_blocks[i];
   }
   h->spec_bt.assign(block_tables + cu_blocks[0], block_tables + cu_blocks[n]);
+  h->res_len = h->spec_len;
+  h->res_nb = h->spec_nb;
 }
 static void try_speculate(nvllm_handle* h, int n, const float* temperature) {
   h->spec_pending = false;
@@ -160,8 +164,21 @@ static void try_speculate(nvllm_handle* h, int n, const float* temperature) {
     if (h->spec_len[i] >= h->spec_nb[i] * KV_BLOCK) return;  // next position needs a new block
     if (h->use_rope && h->spec_len[i] + 1 > h->cfg.max_seq_len) return;
   }
+  // a failed speculative step must leave no trace: layout, per-sequence extents and the
+  // caller-visible error string are restored
   const int saved = h->launches;
-  if (resident_step(h, nullptr) == NVLLM_OK) h->spec_pending = true;
+  const StepLayout lay0 = h->lay;
+  const std::vector<int32_t> len0 = h->res_len;
+  const std::string err0 = h->err;
+  h->spec_used_graph = false;
+  if (resident_step(h, nullptr, &h->spec_used_graph) == NVLLM_OK) {
+    h->spec_pending = true;
+  } else {
+    h->lay = lay0;
+    h->res_len = len0;
+    h->err = err0;
+    h->resident_ok = false;  // the device state may be half advanced: restage on the next call
+  }
   h->launches = saved;
 }
 static bool speculation_hit(const nvllm_handle* h, int n, int is_prefill, const int32_t* token_ids,
@@ -212,7 +229,7 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
       h->run_lay = h->lay;
       h->run_lay_ok = true;
       fill_stats(h, stats, n, 0, d2h, true);
-      if (stats) stats->used_graph = h->step_graph[0] != nullptr;
+      if (stats) stats->used_graph = h->spec_used_graph ? 1 : 0;
       remember_call(h, n, cu_seqlens, block_tables, cu_blocks);
       try_speculate(h, n, temperature);
       return NVLLM_OK;
@@ -396,7 +413,7 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
 // sampled tokens become the inputs, positions advance by one, KV slots come from the block
 // tables already resident.  No host<->device copy, no host sync.  Works after a decode step
 // (state advanced in place) and after a prefill step (decode state derived by a kernel).
-static int resident_step(nvllm_handle* h, nvllm_run_stats* stats) {
+static int resident_step(nvllm_handle* h, nvllm_run_stats* stats, bool* used_graph) {
   if (!h->resident_ok)
     return set_err(h, NVLLM_ERR_STATE, "nvllm_run_resident needs a preceding nvllm_run");
   if (h->hist_n)
@@ -407,6 +424,15 @@ static int resident_step(nvllm_handle* h, nvllm_run_stats* stats) {
   const int n = L.n;
   if (L.max_len + 1 > L.max_blocks * KV_BLOCK || (h->use_rope && L.max_len + 1 > h->cfg.max_seq_len))
     return set_err(h, NVLLM_ERR_RANGE, "resident decode ran past the block tables / max_seq_len");
+  // ragged batches: every sequence against ITS OWN table (entries past it are padding)
+  if ((int)h->res_len.size() != n || (int)h->res_nb.size() != n)
+    return set_err(h, NVLLM_ERR_STATE, "nvllm_run_resident: no per-sequence state for this batch");
+  for (int i = 0; i < n; i++)
+    if (h->res_len[i] + 1 > h->res_nb[i] * KV_BLOCK)
+      return set_err(h, NVLLM_ERR_RANGE,
+                     "resident decode: sequence %d would grow to %d tokens, its block table holds %d",
+                     i, h->res_len[i] + 1, h->res_nb[i] * KV_BLOCK);
+  for (int i = 0; i < n; i++) h->res_len[i] += 1;
   cudaStream_t st = h->stream;
   int rc;
   NV_CHECK(h, cudaEventRecord(h->ev0, st));
@@ -456,6 +482,7 @@ static int resident_step(nvllm_handle* h, nvllm_run_stats* stats) {
       NV_CHECK(h, cudaEventRecord(h->ev1, st));
       fill_stats(h, stats, n, 0, 0, false);
       if (stats) stats->used_graph = 1;
+      if (used_graph) *used_graph = true;
       return NVLLM_OK;
     }
     if ((rc = advance())) return rc;
@@ -471,7 +498,7 @@ extern "C" int nvllm_run_resident(nvllm_handle* h, nvllm_run_stats* stats) {
   if (h->spec_pending) {  // the step asked for is the one already in flight
     h->spec_pending = false;
     fill_stats(h, stats, h->lay.n, 0, 0, false);
-    if (stats) stats->used_graph = h->step_graph[0] != nullptr;
+    if (stats) stats->used_graph = h->spec_used_graph ? 1 : 0;
     return NVLLM_OK;
   }
   return resident_step(h, stats);
@@ -488,6 +515,8 @@ extern "C" int nvllm_rerun(nvllm_handle* h, nvllm_run_stats* stats) {
                    "advanced in place by nvllm_run_resident)");
   h->lay = h->run_lay;
   h->spec_pending = false;
+  h->res_len = h->spec_len;  // the device state is the replayed step's again
+  h->res_nb = h->spec_nb;
   NV_CHECK(h, cudaEventRecord(h->ev0, h->stream));
   h->launches = 0;
   int rc = forward_step(h);

@@ -32,12 +32,17 @@ from . import config as C
 from . import lib as L
 
 
+# NewTensorModelRunner -> tensor.DefaultSamplingParams() (tensor_model_runner.go:27-31,
+# sampling.go:17-24); the Go shim applies the same values in NewCudaModelRunner
+DEFAULT_SAMPLING = dict(temperature=1.0, top_p=1.0, top_k=0, repetition_penalty=1.2)
+
+
 class CudaModelRunner:
     def __init__(self, cfg: C.ModelConfig, weights: Iterable[Tuple[int, int, np.ndarray]],
                  precision: int = C.PREC_BF16, num_kv_blocks: int = -1, device: int = 0,
                  max_num_seqs: int = 512, max_batched_tokens: int = 16384,
                  weight_dtype: Optional[int] = None, tp_size: int = 1, tp_rank: int = 0,
-                 tp_id: Optional[bytes] = None):
+                 tp_id: Optional[bytes] = None, sampling: Optional[dict] = DEFAULT_SAMPLING):
         """Replaces NewTensorModelRunner(modelDir) (tensor_model_runner.go:21-32): instead of a
         directory, takes the tensors in the layouts LoadModel leaves them in
         (generic_loader.go:184-265), as (weight_id, layer, ndarray) triples.
@@ -47,7 +52,12 @@ class CudaModelRunner:
 
         tp_size > 1: this runner is rank tp_rank of a tensor-parallel group (one runner per GPU,
         every rank handed the same FULL tensors and the same Run calls); tp_id is the 128-byte
-        group id from tp_unique_id(), created on one rank and distributed by the host code."""
+        group id from tp_unique_id(), created on one rank and distributed by the host code.
+
+        sampling: the runner-wide sampling parameters Run() draws with; the default is the
+        reference runner's (temperature 1.0, repetition penalty 1.2: every row is drawn by the
+        device-side SampleWithHistory).  None = greedy first-max rows, no filters (what the
+        parity tests and the benchmark use: the reference's draw uses an unseeded global RNG)."""
         self._lib = L.load()
         self.cfg = cfg
         self.precision = precision
@@ -68,9 +78,15 @@ class CudaModelRunner:
         except Exception:
             self.close()
             raise
-        # tensor.DefaultSamplingParams (sampling.go:18-25) has temperature 1.0; cmd/ask runs chat
-        # models greedy (main.go:79-85).  temperature <= 0 => greedy.
+        # temperature <= 0 => greedy first-max (cmd/ask/main.go:389-402); deviation from the
+        # reference runner, where 0 means "no temperature scaling" and the row is still drawn
         self.temperature = 0.0
+        if sampling is not None:
+            try:
+                self.set_sampling_params(**sampling)
+            except Exception:
+                self.close()
+                raise
         self.last_stats = L.RunStats()
         self.last_logits: Optional[np.ndarray] = None
 

@@ -22,7 +22,8 @@ TOL = {C.PREC_FP32: 1e-4, C.PREC_BF16: 2e-2}
 def _runner(cfg, prec, seed=1234, **kw):
     R = nvllm_pkg.sub("runner")
     return R.CudaModelRunner(cfg, W.random_weights(cfg, seed, round_bf16=(prec == C.PREC_BF16)),
-                             precision=prec, num_kv_blocks=kw.pop("num_kv_blocks", 32), **kw)
+                             precision=prec, num_kv_blocks=kw.pop("num_kv_blocks", 32),
+                             sampling=kw.pop("sampling", None), **kw)
 
 
 def _blocks(n_tokens, first=0):
@@ -102,13 +103,26 @@ def test_argmax_bit_exact_with_ties():
 
 
 # ------------------------------------------------------------------ whole forward pass
-def _greedy_parity(name, prec, prompt_len, steps, table=None):
+# Prompt seeds of the strict (free-running, identical-token) cases: the first seed >= 4321 whose
+# oracle top-2 margin is >= 2 % of max|logit| on every compared step, for fp32 and bf16-rounded
+# weights alike (tests/golden/find_margin_seeds.py prints this table).  Random-init logits are
+# nearly flat; on other seeds a near-tie lets a correct bf16 run pick the runner-up.
+STRICT_SEEDS = {"gpt2": 4322, "llama": 4321, "granite": 4321, "falcon": 4391, "gpt2_hd64": 4321,
+                "llama_hd64": 4321, "llama_hd128": 4321, "granite_hd64": 4321, "falcon_g18": 4323}
+
+
+def _greedy_parity(name, prec, prompt_len, steps, table=None, strict_seed=None):
+    """strict_seed given: FREE-RUNNING — the device's own tokens are fed back, every one of them
+    must equal the oracle's (north_star: identical greedy tokens), logits within the gate at every
+    step.  Otherwise (kernel-variant coverage on prompts whose margins were not screened): the
+    oracle's token is fed back, logits within the gate, and a token may differ only where the
+    oracle's own top-2 margin is inside the measured numerical error (reported, never > 2)."""
     cfg = (table or TINY)[name]()
     bf16 = prec == C.PREC_BF16
     orc = make_oracle(cfg, round_bf16=bf16)
     run = _runner(cfg, prec)
     try:
-        prompt = W.random_prompt(cfg.vocab_size, prompt_len, 4321)
+        prompt = W.random_prompt(cfg.vocab_size, prompt_len, strict_seed or 4321)
         ref_toks, ref_logits = orc.greedy(prompt, steps)
         toks = list(int(t) for t in prompt)
         bt = _blocks(prompt_len + steps)
@@ -122,16 +136,21 @@ def _greedy_parity(name, prec, prompt_len, steps, table=None):
             assert err <= TOL[prec], f"{name} step {i}: rel err {err}"
             # the device argmax must be the first-max of the device logits, bit-exact
             assert int(out[0]) == oracle_mod().argmax(logits[0])
+            if strict_seed is not None:
+                assert int(out[0]) == int(ref_toks[i]), \
+                    f"{name} step {i}: token {out[0]} != oracle {ref_toks[i]} (free-running)"
+                toks.append(int(out[0]))
+                continue
             if int(out[0]) != int(ref_toks[i]):
-                # fp32 mode: never.  bf16 mode: only when the oracle's own top-2 margin is inside
-                # the numerical tolerance (random-init logits are nearly flat, so near-ties exist)
                 margin = float(ref_logits[i][ref_toks[i]] - ref_logits[i][out[0]])
                 scale = float(np.abs(ref_logits[i]).max())
                 assert prec == C.PREC_BF16 and margin <= 2 * err * scale + 1e-6, \
                     f"{name} step {i}: token {out[0]} != {ref_toks[i]} (margin {margin}, err {err})"
                 flips += 1
-            toks.append(int(ref_toks[i]))  # teacher-forced with the oracle's token
+            toks.append(int(ref_toks[i]))
         assert flips <= 2, f"{name}: {flips} near-tie flips in {steps} steps"
+        if flips:
+            print(f"{name}: {flips} near-tie token(s) inside the numerical error")
         return worst
     finally:
         run.close()
@@ -139,20 +158,23 @@ def _greedy_parity(name, prec, prompt_len, steps, table=None):
 
 @pytest.mark.parametrize("name", list(TINY))
 def test_fp32_logits_and_greedy_tokens(name):
-    _greedy_parity(name, C.PREC_FP32, prompt_len=40, steps=32)
+    _greedy_parity(name, C.PREC_FP32, prompt_len=40, steps=32, strict_seed=STRICT_SEEDS[name])
 
 
 @pytest.mark.parametrize("name", list(TINY))
 def test_bf16_logits_and_greedy_tokens(name):
-    _greedy_parity(name, C.PREC_BF16, prompt_len=40, steps=32)
+    """north_star: <= 2e-2 and identical greedy tokens for the first 32 steps, free-running."""
+    _greedy_parity(name, C.PREC_BF16, prompt_len=40, steps=32, strict_seed=STRICT_SEEDS[name])
 
 
 @pytest.mark.parametrize("name", list(TINY_HD))
 @pytest.mark.parametrize("prec", [C.PREC_FP32, C.PREC_BF16])
 def test_head_dim_64_128_families(name, prec):
     """head_dim 64 / 128: bf16 mode runs the tensor-core attention kernels (prefill tiles of 64
-    queries, decode with the query-head group as MMA rows, MQA group of 18 heads in 2 chunks)."""
-    _greedy_parity(name, prec, prompt_len=100, steps=12, table=TINY_HD)
+    queries, decode with the query-head group as MMA rows, MQA group of 18 heads in 2 chunks).
+    Free-running, identical tokens."""
+    _greedy_parity(name, prec, prompt_len=100, steps=12, table=TINY_HD,
+                   strict_seed=STRICT_SEEDS[name])
 
 
 @pytest.mark.parametrize("name", ["llama_hd64", "llama_hd128", "falcon_g18"])
@@ -290,30 +312,48 @@ def test_fully_cached_prompt_still_yields_logits():
         run.close()
 
 
+def _safe_uniform(p, target):
+    """A uniform whose inverse-CDF draw from the distribution p is unambiguous: the midpoint of
+    a CDF bin at least 4e-4 wide, nearest to `target` — >= 2e-4 away from every CDF step, far
+    outside what fp32 summation order can move (the oracle test uses the same exclusion,
+    tests/test_oracle.py)."""
+    cdf = np.cumsum(p.astype(np.float64))
+    lo = np.concatenate([[0.0], cdf[:-1]])
+    ok = np.nonzero((cdf - lo) >= 4e-4)[0]
+    assert len(ok), "distribution too flat for an unambiguous draw"
+    mid = 0.5 * (lo[ok] + cdf[ok])
+    j = int(np.argmin(np.abs(mid - target)))
+    return float(np.float32(mid[j])), int(ok[j])
+
+
 def test_temperature_sampling_with_injected_uniforms():
-    """sampling.go:70-74,105-128,196-217 with rand.Float32() replaced by a given uniform."""
+    """sampling.go:70-74,105-128,196-217 with rand.Float32() replaced by a given uniform: index
+    work, so the drawn tokens must EQUAL the oracle's.  A first greedy pass yields the logits, the
+    uniforms are then placed mid-bin of each row's CDF."""
     O = oracle_mod()
     cfg = TINY["gpt2"]()
     run = _runner(cfg, C.PREC_FP32)
     try:
         prompts = [W.random_prompt(cfg.vocab_size, 12 + i, 50 + i).tolist() for i in range(6)]
         temps = [0.7, 1.0, 1.3, 0.0, 2.0, 0.5]
-        us = [0.01, 0.35, 0.62, 0.5, 0.93, 0.999]
+        targets = [0.01, 0.35, 0.62, 0.5, 0.93, 0.999]
         bts = [[i] for i in range(6)]
-        toks, logits = run.run_flat(prompts, True, [0] * 6, bts, temps, us, want_logits=True)
-        exact = 0
+        _t, logits0 = run.run_flat(prompts, True, [0] * 6, bts, [0.0] * 6, want_logits=True)
+        us, expect = [], []
         for i in range(6):
             if temps[i] == 0.0:
-                assert toks[i] == O.argmax(logits[i])
+                us.append(0.5)
+                expect.append(O.argmax(logits0[i]))
                 continue
-            ref = O.sample(logits[i], None, temps[i], u=us[i])
-            # identical up to fp32 summation order of the CDF: allow the neighbouring index when
-            # u lands within rounding of a CDF step
-            p = np.exp((logits[i] / temps[i]).astype(np.float64))
-            cdf = np.cumsum(p / p.sum())
-            assert abs(cdf[toks[i]] - cdf[ref]) < 1e-3 or toks[i] == ref
-            exact += int(toks[i] == ref)
-        assert exact >= 4
+            u, tok = _safe_uniform(ref_filter_probs(logits0[i], [], temps[i], 1.0, 0, 1.0), targets[i])
+            us.append(u)
+            expect.append(tok)
+        toks, logits = run.run_flat(prompts, True, [0] * 6, bts, temps, us, want_logits=True)
+        np.testing.assert_array_equal(logits, logits0)  # same step, same kernels: bit-identical
+        for i in range(6):
+            ref = O.argmax(logits[i]) if temps[i] == 0.0 else O.sample(logits[i], None, temps[i], u=us[i])
+            assert ref == expect[i], f"row {i}: oracle {ref} vs float64 restatement {expect[i]}"
+            assert int(toks[i]) == ref, f"row {i}: device drew {toks[i]}, oracle {ref}"
     finally:
         run.close()
 
@@ -323,8 +363,8 @@ def test_temperature_sampling_with_injected_uniforms():
 def test_sample_with_history_filters(top_p, top_k, rep):
     """sampling.go:33-217 SampleWithHistory on the device: repetition penalty over the token
     history (x3 for the last ten), temperature, top-k, top-p, renormalise, inverse-CDF draw —
-    rand.Float32() replaced by injected uniforms.  Tokens must equal the oracle's; where u
-    lands within fp32 rounding of a CDF step the neighbouring kept token is accepted."""
+    rand.Float32() replaced by injected uniforms placed mid-bin of the filtered CDF.  Tokens
+    must EQUAL the oracle's on the prefill step and on the decode step after it."""
     O = oracle_mod()
     cfg = TINY["gpt2"]()
     run = _runner(cfg, C.PREC_FP32)
@@ -338,31 +378,34 @@ def test_sample_with_history_filters(top_p, top_k, rep):
             pr[5] = pr[1]
             prompts.append(pr)
         temps = [0.7, 1.0, 1.3, 0.0, 2.0, 0.5, 1.0, 0.9]
-        us = [float(u) for u in rng.uniform(0.02, 0.98, size=8)]
+        targets = [float(u) for u in rng.uniform(0.02, 0.98, size=8)]
         bts = [[i] for i in range(8)]
-        toks, logits = run.run_flat(prompts, True, [0] * 8, bts, temps, us, want_logits=True)
-        exact = 0
-        for i in range(8):
-            if temps[i] == 0.0:
-                assert toks[i] == O.argmax(logits[i])  # greedy rows are not filtered
-                continue
-            ref = O.sample(logits[i], prompts[i], temps[i], top_p=top_p, top_k=top_k,
-                           rep_penalty=rep, u=us[i])
-            p = ref_filter_probs(logits[i], prompts[i], temps[i], top_p, top_k, rep)
-            assert p[toks[i]] > 0, f"row {i}: token {toks[i]} was filtered out by the reference"
-            if toks[i] != ref:
-                cdf = np.cumsum(p)
-                assert abs(cdf[toks[i]] - cdf[ref]) < 1e-3 or abs(cdf[min(toks[i], ref)] - us[i]) < 1e-3, \
-                    f"row {i}: token {toks[i]} != oracle {ref}"
-            exact += int(toks[i] == ref)
-        assert exact >= 6
+
+        def step(seqs, prefill):
+            # pass 1 (greedy rows) for the logits, pass 2 with uniforms placed mid-bin
+            nc = [0] * 8 if prefill else None
+            _t, lg0 = run.run_flat(seqs, prefill, nc, bts, [0.0] * 8, want_logits=True)
+            us = []
+            for i in range(8):
+                if temps[i] == 0.0:
+                    us.append(0.5)
+                    continue
+                p = ref_filter_probs(lg0[i], seqs[i], temps[i], top_p, top_k, rep)
+                us.append(_safe_uniform(p, targets[i])[0])
+            toks, lg = run.run_flat(seqs, prefill, nc, bts, temps, us, want_logits=True)
+            np.testing.assert_array_equal(lg, lg0)
+            for i in range(8):
+                if temps[i] == 0.0:
+                    assert toks[i] == O.argmax(lg[i])  # greedy rows are not filtered
+                    continue
+                ref = O.sample(lg[i], seqs[i], temps[i], top_p=top_p, top_k=top_k, rep_penalty=rep,
+                               u=us[i])
+                assert int(toks[i]) == ref, f"row {i}: device drew {toks[i]}, oracle {ref} (u={us[i]})"
+            return toks
+
+        toks = step(prompts, True)
         # decode step: the history is the whole sequence so far
-        seqs = [pr + [int(t)] for pr, t in zip(prompts, toks)]
-        toks2, logits2 = run.run_flat(seqs, False, None, bts, temps, us, want_logits=True)
-        same = sum(int(toks2[i] == O.sample(logits2[i], seqs[i], temps[i], top_p=top_p, top_k=top_k,
-                                            rep_penalty=rep, u=us[i]))
-                   for i in range(8) if temps[i] > 0)
-        assert same >= 6
+        step([pr + [int(t)] for pr, t in zip(prompts, toks)], False)
         # the device-resident loop has no host-side history: it must refuse, not ignore the knobs
         L = nvllm_pkg.sub("lib")
         with pytest.raises(L.NvllmError):
@@ -408,7 +451,7 @@ def test_missing_weight_is_reported():
     cfg = TINY["llama"]()
     ws = [w for w in W.random_weights(cfg) if not (w[0] == C.W_O and w[1] == 1)]
     with pytest.raises(L.NvllmError) as e:
-        R.CudaModelRunner(cfg, ws, precision=C.PREC_FP32, num_kv_blocks=4)
+        R.CudaModelRunner(cfg, ws, precision=C.PREC_FP32, num_kv_blocks=4, sampling=None)
     assert e.value.code == L.ERR_INVALID and "NVLLM_W_O" in str(e.value)
 
 
@@ -534,3 +577,106 @@ def test_profile_reports_every_kernel_class():
         run.set_profile(False)
     finally:
         run.close()
+
+
+def test_resident_ragged_batch_stops_at_each_sequences_own_table():
+    """in a ragged batch the shorter table is padded with block 0 on the device; the
+    resident loop must refuse to step a sequence past ITS OWN table (NVLLM_ERR_RANGE) instead of
+    appending its K/V into pool block 0, which here belongs to the other sequence."""
+    L = nvllm_pkg.sub("lib")
+    cfg = TINY["llama"]()
+    pa = W.random_prompt(cfg.vocab_size, 250, 901).tolist()   # one block: positions 0..255
+    pb = W.random_prompt(cfg.vocab_size, 40, 902).tolist()    # owns pool block 0
+    steps = 12
+
+    def stepwise():
+        run = _runner(cfg, C.PREC_FP32)
+        try:
+            run.set_speculation(False)
+            seqs, bts = [list(pa), list(pb)], [[5, 6], [0, 1]]
+            out, _ = run.run_flat(seqs, True, [0, 0], bts, [0.0, 0.0])
+            toks = [out.copy()]
+            for _ in range(steps):
+                for s_, t in zip(seqs, out):
+                    s_.append(int(t))
+                out, _ = run.run_flat(seqs, False, None, bts, [0.0, 0.0])
+                toks.append(out.copy())
+            return toks
+        finally:
+            run.close()
+
+    ref = stepwise()
+    run = _runner(cfg, C.PREC_FP32)
+    try:
+        run.set_speculation(False)
+        seqs = [list(pa), list(pb)]
+        out, _ = run.run_flat(seqs, True, [0, 0], [[5], [0, 1]], [0.0, 0.0])
+        np.testing.assert_array_equal(out, ref[0])
+        for s_, t in zip(seqs, out):
+            s_.append(int(t))
+        # 250-token context + 6 appended tokens fill block 5 exactly
+        for i in range(1, 7):
+            run.run_resident()
+            got, _ = run.sync(2)
+            np.testing.assert_array_equal(got, ref[i])
+            for s_, t in zip(seqs, got):
+                s_.append(int(t))
+        with pytest.raises(L.NvllmError) as e:
+            run.run_resident()
+        assert e.value.code == L.ERR_RANGE and "sequence 0" in str(e.value)
+        # the engine allocates the next block and carries on: nothing of sequence 1 was damaged
+        for i in range(7, steps + 1):
+            out, _ = run.run_flat(seqs, False, None, [[5, 6], [0, 1]], [0.0, 0.0])
+            np.testing.assert_array_equal(out, ref[i])
+            for s_, t in zip(seqs, out):
+                s_.append(int(t))
+    finally:
+        run.close()
+
+
+@pytest.mark.parametrize("batch", [1, 64])
+def test_resident_and_speculative_loops_1000_steps(batch):
+    """the device-resident loop (advance_kernel -> forward pass, captured in
+    a CUDA graph, every kernel released by programmatic dependent launch) against stepping
+    through nvllm_run with speculation off, token for token over 1000 steps; then the same loop
+    through nvllm_run with the speculative next step on."""
+    cfg = TINY["llama"]()
+    steps = 1000
+    prompts = [W.random_prompt(cfg.vocab_size, 8 + (i % 13), 7000 + i).tolist() for i in range(batch)]
+    nb = (8 + 12 + steps + 2 + 255) // 256
+    bts = [list(range(i * nb, (i + 1) * nb)) for i in range(batch)]
+    zeros = [0.0] * batch
+
+    def drive(mode):
+        run = _runner(cfg, C.PREC_FP32, num_kv_blocks=batch * nb)
+        try:
+            run.set_speculation(mode == "spec")
+            seqs = [list(p) for p in prompts]
+            out, _ = run.run_flat(seqs, True, [0] * batch, bts, zeros)
+            hist = [out.copy()]
+            for s_, t in zip(seqs, out):
+                s_.append(int(t))
+            out, _ = run.run_flat(seqs, False, None, bts, zeros)
+            hist.append(out.copy())
+            hits = 0
+            for _ in range(steps - 1):
+                if mode == "resident":
+                    run.run_resident()
+                    out, _ = run.sync(batch)
+                else:
+                    for s_, t in zip(seqs, out):
+                        s_.append(int(t))
+                    out, _ = run.run_flat(seqs, False, None, bts, zeros)
+                    hits += int(run.last_stats.h2d_bytes == 0)
+                hist.append(out.copy())
+            return np.stack(hist), hits
+        finally:
+            run.close()
+
+    ref, _ = drive("stepwise")
+    got, _ = drive("resident")
+    np.testing.assert_array_equal(got, ref)
+    got, hits = drive("spec")
+    np.testing.assert_array_equal(got, ref)
+    # every step hits except the ones that need a new KV block's first position staged by the host
+    assert hits >= steps - 16, hits

@@ -45,7 +45,8 @@ def main():
     cfg = CASES[case]()
     bf16 = prec == C.PREC_BF16
     run = R.CudaModelRunner(cfg, W.random_weights(cfg, 1234, round_bf16=bf16), precision=prec,
-                            num_kv_blocks=16, device=rank, tp_size=tp, tp_rank=rank, tp_id=tid)
+                            num_kv_blocks=16, device=rank, tp_size=tp, tp_rank=rank, tp_id=tid,
+                            sampling=None)
     orc = make_oracle(cfg, round_bf16=bf16)
     O = oracle_mod()
     # two sequences of different length in one ragged batch, crossing a KV block boundary
