@@ -149,6 +149,21 @@ class OracleModel:
             logits = self.forward([nt], cache)
         return np.array(toks, dtype=np.int32), np.stack(logs)
 
+    def greedy_batch(self, prompts, steps: int, threads: int | None = None):
+        """greedy() for independent sequences, one host thread each (ctypes releases the GIL;
+        oracle_forward only reads the model).  The first sequence runs alone: a tied LM head is
+        materialised lazily by the first forward call (generic_loader.go:255-259 transposes the
+        embedding once), which must not race.  Returns ([tokens], [logits])."""
+        from concurrent.futures import ThreadPoolExecutor
+        if not len(prompts):
+            return [], []
+        res = [self.greedy(prompts[0], steps)]
+        if len(prompts) > 1:
+            nt = max(1, min(len(prompts) - 1, threads or os.cpu_count() or 1))
+            with ThreadPoolExecutor(max_workers=nt) as ex:
+                res += list(ex.map(lambda p: self.greedy(p, steps), prompts[1:]))
+        return [r[0] for r in res], [r[1] for r in res]
+
     def __del__(self):
         try:
             lib().oracle_destroy(self._p)

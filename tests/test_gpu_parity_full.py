@@ -15,8 +15,6 @@
     device token may differ from it only where the oracle's own top-2 margin is inside the
     measured error (counted and printed).
 """
-import os
-from concurrent.futures import ThreadPoolExecutor
 from dataclasses import replace
 
 import numpy as np
@@ -66,10 +64,8 @@ def test_cfg1_gpt2_small_full_size_free_running(prec, steps):
 
 # ------------------------------------------------------------------ configs[1..4], full width
 def _oracle_batch(orc, prompts, steps):
-    """Per-sequence greedy runs of the oracle, one host thread each (ctypes drops the GIL)."""
-    with ThreadPoolExecutor(max_workers=max(1, min(len(prompts), os.cpu_count() or 1))) as ex:
-        res = list(ex.map(lambda p: orc.greedy(p, steps), prompts))
-    return [r[0] for r in res], [r[1] for r in res]
+    """Per-sequence greedy runs of the oracle, one host thread each."""
+    return orc.greedy_batch(prompts, steps)
 
 
 def _batch_parity(cfg, prec, prompts, steps, tables, num_cached=None, num_kv_blocks=None):
