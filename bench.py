@@ -254,7 +254,8 @@ def make_runner(cfg, job, device, keep_host=None, tp_size=1, tp_rank=0, tp_id=No
 
 def cpu_oracle_sample(cfg, weights, budget_s, prompt_tokens=None):
     """Time the restated reference (1 thread): prefill `p` tokens + decode `d` tokens of one
-    sequence, sized to ~budget_s after a 2-token calibration."""
+    sequence, sized to ~budget_s after a 2-token calibration.  The last-token logits of every
+    step and the greedy tokens are kept so that the GPU can be checked on the same prompt."""
     from oracle import oracle as O
     m = O.OracleModel(cfg, weights)
     prompt = W.random_prompt(cfg.vocab_size, 64, 4321)
@@ -268,13 +269,37 @@ def cpu_oracle_sample(cfg, weights, budget_s, prompt_tokens=None):
     t0 = time.perf_counter()
     logits = m.forward(prompt[:p], cache)
     t_prefill = time.perf_counter() - t0
+    step_logits, step_tokens = [], []
     t0 = time.perf_counter()
     for _ in range(d):
         nt = O.argmax(logits)
+        step_logits.append(np.array(logits, dtype=np.float32, copy=True))
+        step_tokens.append(int(nt))
         logits = m.forward([nt], cache)
     t_decode = time.perf_counter() - t0
     return {"tokens": p + d, "seconds": t_prefill + t_decode, "prefill_tokens": p,
-            "decode_tokens": d, "prefill_tok_s": p / t_prefill, "decode_tok_s": d / t_decode}, m
+            "decode_tokens": d, "prefill_tok_s": p / t_prefill, "decode_tok_s": d / t_decode,
+            "prompt": [int(t) for t in prompt[:p]], "logits": step_logits,
+            "greedy": step_tokens}, m
+
+
+def gpu_parity(run, ref):
+    """The same prompt through nvllm_run (bf16 weights, the library's production kernels at the
+    full model size): free-running greedy, last-token logits of every step against the oracle's.
+    Gate (BASELINE.json north_star, bf16 mode): max|dlogit| / max|logit| <= 2e-2 per step and
+    identical greedy tokens."""
+    toks = list(ref["prompt"])
+    worst, equal, steps = 0.0, True, len(ref["greedy"])
+    for i in range(steps):
+        out, logits = run.run_flat([toks], i == 0, [0], [[0]], [0.0], want_logits=True)
+        r = ref["logits"][i]
+        worst = max(worst, float(np.abs(logits[0] - r).max() / np.abs(r).max()))
+        equal = equal and int(out[0]) == ref["greedy"][i]
+        toks.append(int(out[0]))
+    return {"max_rel_err": worst, "tolerance": 2e-2, "tokens_equal": bool(equal), "steps": steps,
+            "prompt_tokens": len(ref["prompt"]), "within_tolerance": bool(worst <= 2e-2),
+            "against": "oracle/nvllm_oracle.c on the same bf16-rounded weights and prompt "
+                       "(full-size model, free-running greedy)"}
 
 
 def main():
@@ -424,15 +449,20 @@ def main():
     peaks = load_peaks()
     kernels, roofline, phases = {}, None, {}
     if not args.no_profile:
+        # tp == 1: device timeline (mode 2) — launches stay back to back with their PDL edges and
+        # each is charged the time from its predecessor's last exit to its own, so the classes
+        # add up to the phase's device time.  tp > 1: CUDA events around every launch (mode 1),
+        # the only instrument that sees the NCCL calls; serialised, an upper bound.
+        prof_mode = 2 if tp == 1 else 1
         job.stage(run)
-        run.set_profile(True)
+        run.set_profile(prof_mode)
         run.rerun()
         prof_prefill = run.get_profile()
-        run.set_profile(True)
+        run.set_profile(prof_mode)
         for _ in range(job.D):
             run.run_resident()
         prof_decode = run.get_profile()
-        run.set_profile(False)
+        run.set_profile(0)
         # un-instrumented phase times
         job.stage(run)
         run.sync()
@@ -448,14 +478,31 @@ def main():
                   "prefill_tok_s": job.n * job.P / (t_prefill / 1e3),
                   "prefill_computed_tok_s": new_tok / (t_prefill / 1e3),
                   "prefix_cached_tokens": int(job.num_cached.sum()),
-                  "decode_tok_s": job.n * job.D / (t_decode / 1e3) if job.D else None}
+                  "decode_tok_s": job.n * job.D / (t_decode / 1e3) if job.D else None,
+                  "decode_us_per_step": 1e3 * t_decode / job.D if job.D else None,
+                  # whole-phase roofline fractions on ALGORITHMIC work: prefill
+                  # flops against the sustained bf16 tensor peak, decode bytes (weights + K/V +
+                  # logits + one pass over each activation) against the measured HBM peak
+                  "prefill_frac_of_tensor_peak":
+                      sum(e["flops"] for e in prof_prefill.values()) / (t_prefill * 1e9) /
+                      peaks["bf16_tflops_sustained"],
+                  "decode_frac_of_hbm_peak":
+                      (sum(e["bytes"] for e in prof_decode.values()) / (t_decode * 1e6) /
+                       peaks["hbm_gbs"]) if job.D else None,
+                  "profile_instrument": "device timeline (globaltimer, PDL intact)"
+                                        if prof_mode == 2 else "CUDA events per launch (serialised)",
+                  # the profiled pass's own total next to the un-instrumented phase time
+                  "profiled_prefill_ms": sum(e["ms"] for e in prof_prefill.values()),
+                  "profiled_decode_ms": sum(e["ms"] for e in prof_decode.values())}
         best = None
         for phase, prof in (("prefill", prof_prefill), ("decode", prof_decode)):
             for name, e in prof.items():
                 gbs = e["bytes"] / (e["ms"] * 1e6) if e["ms"] > 0 else 0.0
                 tfs = e["flops"] / (e["ms"] * 1e9) if e["ms"] > 0 else 0.0
                 kernels[f"{phase}.{name}"] = {"ms": round(e["ms"], 3), "launches": e["launches"],
-                                              "GB/s": round(gbs, 1), "TFLOP/s": round(tfs, 2)}
+                                              "GB/s": round(gbs, 1), "TFLOP/s": round(tfs, 2),
+                                              "alg_MB_per_launch": round(e["bytes"] / e["launches"] / 1e6, 3),
+                                              "impl_MB_per_launch": round(e["impl_bytes"] / e["launches"] / 1e6, 3)}
                 if best is None or e["ms"] > best[2]["ms"]:
                     best = (phase, name, e)
         phase, name, e = best
@@ -479,14 +526,20 @@ def main():
             traffic = None
         roofline.update({"frac": ach / peak, "traffic": traffic, "kernel": f"{phase}.{name}",
                          "avg_launch_us": per * 1e3, "launches": e["launches"],
+                         "algorithmic_bytes_per_launch": e["bytes"] / e["launches"],
+                         "implementation_bytes_per_launch": e["impl_bytes"] / e["launches"],
+                         "instrument": phases["profile_instrument"],
                          "peak_source": peaks["source"],
                          "share_of_step": e["ms"] / sum(x["ms"] for p in (prof_prefill, prof_decode)
                                                         for x in p.values())})
 
-    cpu = None
+    cpu, parity = None, None
     if rank == 0 and keep is not None:
-        run.close()
         r, _m = cpu_oracle_sample(cfg, keep, args.cpu_budget_s)
+        del _m
+        if tp == 1:
+            parity = gpu_parity(run, r)
+        run.close()
         cpu = {"value": r["tokens"] / r["seconds"], "unit": "tokens/s", "cores": 1, "kind": "port",
                "sample": f"1 sequence, {r['prefill_tokens']}-token prefill + {r['decode_tokens']} decode "
                          f"steps, full-size {cfg.name} (bf16-rounded weights as fp32)",
@@ -502,6 +555,7 @@ def main():
                         "speculative_next_step": {"value": e2e_spec, "unit": "tokens/s",
                                                   "h2d_bytes_per_step": h2d_spec // args.steps}},
                 "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
+                "parity": parity,
                 "phases": phases, "kernels": kernels, "memory": mem}
         print(json.dumps(line))
     if dist is not None:

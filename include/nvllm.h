@@ -220,10 +220,16 @@ int nvllm_run_resident(nvllm_handle* h, nvllm_run_stats* stats);
  * with every input already in HBM. */
 int nvllm_rerun(nvllm_handle* h, nvllm_run_stats* stats);
 
-/* Per-kernel-class device timing.  While enabled every launch is bracketed by CUDA events on
- * the compute stream (slower: use a separate pass from the headline timing); bytes / flops
- * are the ALGORITHMIC figures of each launch.  nvllm_set_profile resets the
- * counters; nvllm_get_profile synchronises and fills out[NVLLM_K_COUNT]. */
+/* Per-kernel-class device timing.  mode 1: every launch is bracketed by CUDA events on the
+ * compute stream (serialises the chain: an upper bound; the only mode that times the NCCL calls
+ * of a tensor-parallel step).  mode 2: device timeline — every kernel records the first entry /
+ * dependency release / last exit of its CTAs in %globaltimer ns while the launches stay back to
+ * back with their programmatic-dependent-launch edges; a launch is charged the time from its
+ * predecessor's last exit to its own, so the classes add up to the window's device time (CUDA
+ * graph replay is off while profiling; up to 2^18 launches per window).  mode 0: off.
+ * `bytes` / `flops` are the ALGORITHMIC figures of each launch, `impl_bytes` what this
+ * implementation moves on top.  nvllm_set_profile resets the counters;
+ * nvllm_get_profile synchronises and fills out[NVLLM_K_COUNT]. */
 enum nvllm_kernel_class {
   NVLLM_K_EMBED = 0,
   NVLLM_K_NORM = 1,
@@ -244,11 +250,12 @@ enum nvllm_kernel_class {
 };
 typedef struct nvllm_profile_entry {
   double ms;
-  double bytes;
+  double bytes;       /* algorithmic bytes (weights, K/V, logits, one pass over activations) */
   double flops;
   int64_t launches;
+  double impl_bytes;  /* extra bytes of this implementation (split-K partials, staging) */
 } nvllm_profile_entry;
-int nvllm_set_profile(nvllm_handle* h, int enabled);
+int nvllm_set_profile(nvllm_handle* h, int mode);
 int nvllm_get_profile(nvllm_handle* h, nvllm_profile_entry* out);
 
 /* Diagnostics: device timeline of the instrumented kernels (GEMM, norm, RoPE+KV, decode

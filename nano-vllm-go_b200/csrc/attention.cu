@@ -329,7 +329,8 @@ attn_decode_kernel(AttnArgs a) {
 }
 
 template <typename QT>
-__global__ void attn_combine_kernel(AttnArgs a) {
+__global__ void attn_combine_kernel(AttnArgs a, Trace tr) {
+  TRACE_ENTRY(tr);
   pdl_launch_dependents();
   pdl_wait();
   const int seq = blockIdx.x, h = blockIdx.y, HD = a.hd;
@@ -347,6 +348,7 @@ __global__ void attn_combine_kernel(AttnArgs a) {
     }
     ((QT*)a.out)[(size_t)seq * a.nh * HD + h * HD + d] = from_f32<QT>(at / lt);
   }
+  TRACE_EXIT(tr);
 }
 
 template <typename QT, typename KT, int HD>
@@ -368,7 +370,7 @@ static cudaError_t decode_dispatch_gc(cudaStream_t st, const AttnArgs& a) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   if (a.n_splits > 1) {
-    (void)launch_k(attn_combine_kernel<QT>, dim3(dim3(a.n_seqs, a.nh)), dim3(min(128, a.hd)), 0, st, a);
+    (void)launch_k(attn_combine_kernel<QT>, dim3(dim3(a.n_seqs, a.nh)), dim3(min(128, a.hd)), 0, st, a, next_trace(14));
     e = cudaGetLastError();
   }
   return e;
@@ -413,7 +415,7 @@ cudaError_t launch_attn_decode(cudaStream_t st, const AttnArgs& a) {
     cudaError_t e = attn_decode_t_supported(a) ? launch_attn_decode_t(st, a)
                                                : launch_attn_decode_mma(st, a);
     if (e != cudaSuccess || a.n_splits == 1) return e;
-    (void)launch_k(attn_combine_kernel<bf16>, dim3(dim3(a.n_seqs, a.nh)), dim3(min(128, a.hd)), 0, st, a);
+    (void)launch_k(attn_combine_kernel<bf16>, dim3(dim3(a.n_seqs, a.nh)), dim3(min(128, a.hd)), 0, st, a, next_trace(14));
     return cudaGetLastError();
   }
   if (a.qdt == DT_F32 && a.kvdt == DT_F32) return decode_dispatch<float, float>(st, a);

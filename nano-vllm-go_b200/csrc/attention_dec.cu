@@ -65,7 +65,7 @@ attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_const
                      AttnArgs a, int G, Trace tr) {
   constexpr int kpc = KPC;
   constexpr int WPH = DT_CONSUMERS / KPC;  // warps per head
-  const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
+  const unsigned long long t_entry = trace_on(tr) ? gtime() : 0ull;
   pdl_launch_dependents();
   using SM = DecSmem<HD>;
   constexpr int PANELS = HD / 64;
@@ -206,7 +206,7 @@ attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_const
     *reinterpret_cast<uint4*>(q_gen + hh * SM::Q_BYTES + r * SM::QROW + c * 16) = make_uint4(0, 0, 0, 0);
   }
   pdl_wait();
-  const unsigned long long t_wait = tr.buf ? gtime() : 0ull;
+  const unsigned long long t_wait = trace_on(tr) ? gtime() : 0ull;
   if (!fused) {
     // Q rows (bf16, written by rope_kv) -> padded shared rows
     constexpr int CPR = HD / 8;
@@ -471,7 +471,7 @@ attn_decode_t_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_const
       }
     }
   }
-  if (threadIdx.x == 0 && tr.buf)
+  if (threadIdx.x == 0 && trace_on(tr))
     trace_rec(tr, t_entry, t_wait,
               (((t_prol - t_wait) & 0x1fffff) << 42) | (((t_first - t_wait) & 0x1fffff) << 21) |
                   ((t_fin0 - t_wait) & 0x1fffff));

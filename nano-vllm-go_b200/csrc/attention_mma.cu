@@ -131,7 +131,8 @@ __device__ __forceinline__ void load_tile(uint32_t dst, const bf16* src, int row
 // ------------------------------------------------------------------ prefill
 template <int HD>
 __global__ void __launch_bounds__(128)
-attn_prefill_mma_kernel(AttnArgs a) {
+attn_prefill_mma_kernel(AttnArgs a, Trace tr) {
+  TRACE_ENTRY(tr);
   pdl_launch_dependents();
   pdl_wait();
   constexpr int BM = 64, BN = 64;
@@ -213,6 +214,7 @@ attn_prefill_mma_kernel(AttnArgs a) {
       *reinterpret_cast<__nv_bfloat162*>(op + dn * 8) =
           __floats2bfloat162_rn(o[dn][2 * i] * inv, o[dn][2 * i + 1] * inv);
   }
+  TRACE_EXIT(tr);
 }
 
 // ------------------------------------------------------------------ decode
@@ -227,7 +229,7 @@ attn_prefill_mma_kernel(AttnArgs a) {
 template <int HD, int BN, int STAGES>
 __global__ void __launch_bounds__(128, (HD == 64 && BN == 64) ? 4 : 2)
 attn_decode_mma_kernel(AttnArgs a, int G, int chunks, int kpc, Trace tr) {
-  const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
+  const unsigned long long t_entry = trace_on(tr) ? gtime() : 0ull;
   pdl_launch_dependents();
   constexpr int TILE_BYTES = BN * HD * 2;
   constexpr int WK = BN / 4;  // keys per warp per tile
@@ -283,7 +285,7 @@ attn_decode_mma_kernel(AttnArgs a, int G, int chunks, int kpc, Trace tr) {
   const bool fused = a.qkv_p != nullptr;
   const bool has_new = fused && n_tiles > 0 && tile_begin + n_tiles == tiles_total;
   pdl_wait();
-  const unsigned long long t_wait = tr.buf ? gtime() : 0ull;
+  const unsigned long long t_wait = trace_on(tr) ? gtime() : 0ull;
   if (fused) {  // the remaining tiles stream while the prologue below builds Q / K / V
 #pragma unroll
     for (int s = 0; s < STAGES - 1; s++)
@@ -502,7 +504,7 @@ attn_decode_mma_kernel(AttnArgs a, int G, int chunks, int kpc, Trace tr) {
   }
   if (n_tiles == 0) finish_head(0);  // empty split: (0, -inf, 0) records
   cp_async_wait<0>();
-  if (threadIdx.x == 0 && tr.buf)
+  if (threadIdx.x == 0 && trace_on(tr))
     trace_rec(tr, t_entry, t_wait,
               (((t_prol - t_wait) & 0x1fffff) << 42) | (((t_first - t_wait) & 0x1fffff) << 21) |
                   ((t_fin0 - t_wait) & 0x1fffff));
@@ -519,7 +521,7 @@ static cudaError_t prefill_launch(cudaStream_t st, const AttnArgs& a) {
   cudaError_t e = cudaFuncSetAttribute(attn_prefill_mma_kernel<HD>,
                                        cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  (void)launch_k(attn_prefill_mma_kernel<HD>, dim3(dim3(a.n_qtiles, a.nh)), dim3(128), smem, st, a);
+  (void)launch_k(attn_prefill_mma_kernel<HD>, dim3(dim3(a.n_qtiles, a.nh)), dim3(128), smem, st, a, next_trace(13));
   return cudaGetLastError();
 }
 cudaError_t launch_attn_prefill_mma(cudaStream_t st, const AttnArgs& a) {
@@ -605,7 +607,7 @@ __global__ void __launch_bounds__(128)
 attn_decode_sk_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
                       AttnArgs a, int G, int chunks, int red_rows, int* __restrict__ tickets,
                       Trace tr) {
-  const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
+  const unsigned long long t_entry = trace_on(tr) ? gtime() : 0ull;
   pdl_launch_dependents();
   constexpr int PANELS = HD / 64;
   constexpr uint32_t TILE_BYTES = BN * HD * 2;
@@ -742,7 +744,7 @@ attn_decode_sk_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_cons
     }
   }
   pdl_wait();
-  const unsigned long long t_wait = tr.buf ? gtime() : 0ull;
+  const unsigned long long t_wait = trace_on(tr) ? gtime() : 0ull;
   int seg_issue = -1;  // index of the segment the issue cursor is in
 #pragma unroll
   for (int s = 0; s < STAGES - 1; s++) {

@@ -166,19 +166,31 @@ static inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 blo
 // ---- device timeline trace (diagnostics; nvllm_trace_begin / nvllm_trace_end) -----------
 // Record = 8 x u64: launch seq, kernel id, CTA, SM, t_entry, t_after_wait, t_exit, extra
 // (ns of %globaltimer).  buf[0] = records written, buf[1] = capacity; records start at buf+8.
+// `agg` (nvllm_set_profile mode 2) is the per-LAUNCH summary the timeline profile is built from:
+// agg[4 seq + {0,1,2}] = {min t_entry, min t_after_wait, max t_exit} over the launch's CTAs.
 struct Trace {
   unsigned long long* buf;
   int seq, kid;
+  unsigned long long* agg;
 };
 bool trace_active();       // a device timeline is being recorded: kernel arguments carry its buffer
 Trace next_trace(int kid);  // {nullptr} unless tracing is on (host side, gemm_tcgen05.cu)
+int trace_seq();            // launches traced so far (host side)
+void trace_agg_set(unsigned long long* agg, int capacity);
 __device__ __forceinline__ unsigned long long gtime() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
+__device__ __forceinline__ bool trace_on(const Trace& t) { return t.buf != nullptr || t.agg != nullptr; }
 __device__ __forceinline__ void trace_rec(const Trace& t, unsigned long long t0,
                                           unsigned long long t1, unsigned long long extra) {
+  if (t.agg) {
+    unsigned long long* a = t.agg + 4 * (size_t)t.seq;
+    atomicMin(a, t0);
+    if (t1) atomicMin(a + 1, t1);
+    atomicMax(a + 2, gtime());
+  }
   if (!t.buf) return;
   const unsigned long long t2 = gtime();
   const unsigned long long slot = atomicAdd(t.buf, 1ull);
@@ -190,6 +202,12 @@ __device__ __forceinline__ void trace_rec(const Trace& t, unsigned long long t0,
   r[2] = blockIdx.x + (unsigned long long)gridDim.x * (blockIdx.y + (unsigned long long)gridDim.y * blockIdx.z);
   r[3] = sm; r[4] = t0; r[5] = t1; r[6] = t2; r[7] = extra;
 }
+// kernels whose only trace points are entry and exit
+#define TRACE_ENTRY(tr) const unsigned long long _tr_entry = trace_on(tr) ? gtime() : 0ull
+#define TRACE_EXIT(tr)                                                              \
+  do {                                                                              \
+    if (threadIdx.x == 0 && threadIdx.y == 0 && trace_on(tr)) trace_rec(tr, _tr_entry, 0ull, 0ull); \
+  } while (0)
 
 __host__ __device__ static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 static inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }

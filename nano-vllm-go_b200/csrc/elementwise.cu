@@ -15,7 +15,8 @@ namespace nvllm {
 template <typename WT>
 __global__ void embed_kernel(const int* __restrict__ tokens, const int* __restrict__ positions,
                              const WT* __restrict__ wte, const WT* __restrict__ wpe, int max_pos,
-                             float mult, float* __restrict__ x, int H) {
+                             float mult, float* __restrict__ x, int H, Trace tr) {
+  TRACE_ENTRY(tr);
   pdl_wait();  // step prologue: later kernels may read the step state before their own wait
   pdl_launch_dependents();
   const int t = blockIdx.x;
@@ -39,6 +40,7 @@ __global__ void embed_kernel(const int* __restrict__ tokens, const int* __restri
     }
     store8(x + (size_t)t * H + i, v);
   }
+  TRACE_EXIT(tr);
 }
 
 cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int* positions,
@@ -48,10 +50,10 @@ cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int*
   int threads = min(256, max(32, ((H / 8 + 31) / 32) * 32));
   if (wdt == DT_F32)
     (void)launch_k(embed_kernel<float>, dim3(T), dim3(threads), 0, st, tokens, positions, (const float*)wte,
-                                               (const float*)wpe, max_pos, mult, x, H);
+                                               (const float*)wpe, max_pos, mult, x, H, next_trace(5));
   else
     (void)launch_k(embed_kernel<bf16>, dim3(T), dim3(threads), 0, st, tokens, positions, (const bf16*)wte,
-                                              (const bf16*)wpe, max_pos, mult, x, H);
+                                              (const bf16*)wpe, max_pos, mult, x, H, next_trace(5));
   return cudaGetLastError();
 }
 
@@ -62,7 +64,7 @@ cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int*
 // The updated row is staged in shared memory so x is read once and written once.
 template <typename YT>
 __global__ void __launch_bounds__(512) norm_kernel(NormArgs a, Trace tr) {
-  const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
+  const unsigned long long t_entry = trace_on(tr) ? gtime() : 0ull;
   pdl_launch_dependents();
   extern __shared__ float row[];
   __shared__ float red[32];
@@ -82,7 +84,7 @@ __global__ void __launch_bounds__(512) norm_kernel(NormArgs a, Trace tr) {
     if (a.p2 && a.bias2) load8(a.bias2 + i0, bias2_0);
   }
   pdl_wait();
-  const unsigned long long t_wait = tr.buf ? gtime() : 0ull;
+  const unsigned long long t_wait = trace_on(tr) ? gtime() : 0ull;
   const int orow = blockIdx.x;
   const int r = a.row_idx ? a.row_idx[orow] : orow;
   float* xr = a.x + (size_t)r * H;
@@ -211,7 +213,7 @@ __global__ void __launch_bounds__(512) norm_kernel(NormArgs a, Trace tr) {
     __syncthreads();
     moe_route_row(row, a.router, H, a.E, a.topk, probs, (size_t)orow, a.topk_idx, a.topk_w);
   }
-  if (threadIdx.x == 0 && tr.buf)
+  if (threadIdx.x == 0 && trace_on(tr))
     trace_rec(tr, t_entry, t_wait, ((t_loads - t_wait) << 32) | (t_red - t_wait));
 }
 
@@ -233,7 +235,8 @@ cudaError_t launch_norm(cudaStream_t st, const NormArgs& a) {
 // ---------------------------------------------------------------- activations
 template <typename OT>
 __global__ void act_kernel(int T, int F, const float* __restrict__ h, int S, size_t stride,
-                           const float* __restrict__ bias, int swiglu, OT* __restrict__ out) {
+                           const float* __restrict__ bias, int swiglu, OT* __restrict__ out, Trace tr) {
+  TRACE_ENTRY(tr);
   pdl_launch_dependents();
   pdl_wait();
   const int ld = swiglu ? 2 * F : F;
@@ -284,6 +287,7 @@ __global__ void act_kernel(int T, int F, const float* __restrict__ h, int S, siz
     }
     store8(out + (size_t)t * F + j, o);
   }
+  TRACE_EXIT(tr);
 }
 
 cudaError_t launch_act(cudaStream_t st, int odt, int T, int F, const float* h, int S, size_t stride,
@@ -293,9 +297,9 @@ cudaError_t launch_act(cudaStream_t st, int odt, int T, int F, const float* h, i
   int threads = 256;
   int blocks = (int)min((size_t)148 * 16, (nvec + threads - 1) / threads);
   if (odt == DT_F32)
-    (void)launch_k(act_kernel<float>, dim3(blocks), dim3(threads), 0, st, T, F, h, S, stride, bias, swiglu, (float*)out);
+    (void)launch_k(act_kernel<float>, dim3(blocks), dim3(threads), 0, st, T, F, h, S, stride, bias, swiglu, (float*)out, next_trace(6));
   else
-    (void)launch_k(act_kernel<bf16>, dim3(blocks), dim3(threads), 0, st, T, F, h, S, stride, bias, swiglu, (bf16*)out);
+    (void)launch_k(act_kernel<bf16>, dim3(blocks), dim3(threads), 0, st, T, F, h, S, stride, bias, swiglu, (bf16*)out, next_trace(6));
   return cudaGetLastError();
 }
 
@@ -309,7 +313,7 @@ __global__ void rope_kv_kernel(int nh, int nkv, int hd, const float* __restrict_
                                const float* __restrict__ cosT, const float* __restrict__ sinT,
                                QT* __restrict__ q_out, KT* __restrict__ kpool,
                                KT* __restrict__ vpool, Trace tr) {
-  const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
+  const unsigned long long t_entry = trace_on(tr) ? gtime() : 0ull;
   pdl_launch_dependents();
   const int t = blockIdx.x;
   const int half = hd / 2;
@@ -332,7 +336,7 @@ __global__ void rope_kv_kernel(int nh, int nkv, int hd, const float* __restrict_
     load8(sinT + (size_t)pos * half + j, s0v);
   }
   pdl_wait();
-  const unsigned long long t_wait = tr.buf ? gtime() : 0ull;
+  const unsigned long long t_wait = trace_on(tr) ? gtime() : 0ull;
   for (int it = blockIdx.y * blockDim.x + threadIdx.x; it < items; it += gridDim.y * blockDim.x) {
     const int head = it / vph;
     const int j = (it % vph) * 8;
@@ -514,7 +518,8 @@ __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
                               const float* __restrict__ temperature,
                               const float* __restrict__ uniforms, int* __restrict__ out_tokens,
                               unsigned long long* __restrict__ amax, int* __restrict__ ticket,
-                              int vsplit) {
+                              int vsplit, Trace tr) {
+  TRACE_ENTRY(tr);
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float red[32];
@@ -525,6 +530,7 @@ __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
   if (vsplit > 0) {
     sample_split_rows(logits, V, gridDim.x, vsplit, temperature, uniforms, out_tokens, red, amred,
                       scan, &winner);
+    TRACE_EXIT(tr);
     return;
   }
   const float* l = logits + (size_t)s * ldl;
@@ -581,6 +587,7 @@ __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
         }
       }
     }
+    TRACE_EXIT(tr);
     return;
   }
   if (blockIdx.y != 0) return;
@@ -624,6 +631,7 @@ __global__ void sample_kernel(const float* __restrict__ logits, int ldl, int V,
   }
   __syncthreads();
   if (threadIdx.x == 0) out_tokens[s] = winner;
+  TRACE_EXIT(tr);
 }
 
 cudaError_t launch_sample(cudaStream_t st, const float* logits, int ldl, int V, int n,
@@ -633,13 +641,14 @@ cudaError_t launch_sample(cudaStream_t st, const float* logits, int ldl, int V, 
   // ~8K logits per CTA keeps >= 2 waves of CTAs in flight for a large vocabulary
   const int chunks = (amax && ticket && vsplit == 0) ? max(1, min(64, V / 8192)) : 1;
   (void)launch_k(sample_kernel, dim3(n, chunks), dim3(chunks > 1 ? 256 : 1024), 0, st, logits, ldl,
-                 V, temperature, uniforms, out_tokens, amax, ticket, vsplit);
+                 V, temperature, uniforms, out_tokens, amax, ticket, vsplit, next_trace(7));
   return cudaGetLastError();
 }
 
 __global__ void advance_kernel(int n, const int* __restrict__ sampled, int* tokens, int* positions,
                                int* slots, int* seq_len, const int* __restrict__ block_tables,
-                               int max_blocks, int max_pos) {
+                               int max_blocks, int max_pos, Trace tr) {
+  TRACE_ENTRY(tr);
   // Step prologue: later kernels read the step state BEFORE their own griddepcontrol.wait, so
   // the dependents are released only after this kernel's writes (the embedding kernel that
   // follows additionally waits for this grid's completion before it releases its own).
@@ -657,6 +666,7 @@ __global__ void advance_kernel(int n, const int* __restrict__ sampled, int* toke
   }
   __threadfence();
   pdl_launch_dependents();
+  TRACE_EXIT(tr);
 }
 
 cudaError_t launch_advance(cudaStream_t st, int n, const int* sampled, int* tokens, int* positions,
@@ -664,7 +674,7 @@ cudaError_t launch_advance(cudaStream_t st, int n, const int* sampled, int* toke
                            int max_pos) {
   if (n <= 0) return cudaSuccess;
   (void)launch_k(advance_kernel, dim3((n + 127) / 128), dim3(128), 0, st, n, sampled, tokens, positions, slots, seq_len,
-                                                 block_tables, max_blocks, max_pos);
+                                                 block_tables, max_blocks, max_pos, next_trace(8));
   return cudaGetLastError();
 }
 
@@ -769,7 +779,8 @@ cudaError_t launch_fill(cudaStream_t st, float* p, size_t n, float v) {
 
 // out[i] = sum_s p[s*stride + i]   (split-K partials of the LM head -> logits)
 __global__ void reduce_partials_kernel(const float* __restrict__ p, int S, size_t stride, size_t n,
-                                       float* __restrict__ out) {
+                                       float* __restrict__ out, Trace tr) {
+  TRACE_ENTRY(tr);
   pdl_launch_dependents();
   pdl_wait();
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
@@ -778,12 +789,13 @@ __global__ void reduce_partials_kernel(const float* __restrict__ p, int S, size_
     for (int s = 0; s < S; s++) acc += p[(size_t)s * stride + i];
     out[i] = acc;
   }
+  TRACE_EXIT(tr);
 }
 cudaError_t launch_reduce_partials(cudaStream_t st, const float* p, int S, size_t stride, size_t n,
                                    float* out) {
   if (n == 0) return cudaSuccess;
   int blocks = (int)min((size_t)148 * 8, (n + 255) / 256);
-  (void)launch_k(reduce_partials_kernel, dim3(blocks), dim3(256), 0, st, p, S, stride, n, out);
+  (void)launch_k(reduce_partials_kernel, dim3(blocks), dim3(256), 0, st, p, S, stride, n, out, next_trace(10));
   return cudaGetLastError();
 }
 
@@ -795,7 +807,9 @@ __global__ void make_decode_state_kernel(int n, int mb, const int* __restrict__ 
                                          const int* __restrict__ src_temp,
                                          const int* __restrict__ src_uni, int* tokens,
                                          int* positions, int* slots, int* cu_q, int* seq_start,
-                                         int* seq_len, int* last_row, int* bt, int* temp, int* uni) {
+                                         int* seq_len, int* last_row, int* bt, int* temp, int* uni,
+                                         Trace tr) {
+  TRACE_ENTRY(tr);
   // step prologue: dependents are released after the writes below (see advance_kernel)
   pdl_wait();
   const int i = blockIdx.x;
@@ -818,6 +832,7 @@ __global__ void make_decode_state_kernel(int n, int mb, const int* __restrict__ 
   __threadfence();
   __syncthreads();
   pdl_launch_dependents();
+  TRACE_EXIT(tr);
 }
 cudaError_t launch_make_decode_state(cudaStream_t st, int n, int mb, const int* sampled,
                                      const int* src_seq_len, const int* src_bt, const int* src_temp,
@@ -827,7 +842,7 @@ cudaError_t launch_make_decode_state(cudaStream_t st, int n, int mb, const int* 
   if (n <= 0) return cudaSuccess;
   (void)launch_k(make_decode_state_kernel, dim3(n), dim3(64), 0, st, n, mb, sampled, src_seq_len, src_bt, src_temp, src_uni,
                                              tokens, positions, slots, cu_q, seq_start, seq_len,
-                                             last_row, bt, temp, uni);
+                                             last_row, bt, temp, uni, next_trace(8));
   return cudaGetLastError();
 }
 

@@ -10,6 +10,7 @@
 #include <string.h>
 
 #include <algorithm>
+#include <vector>
 
 #include "common.cuh"
 #include "handle.h"
@@ -130,29 +131,86 @@ static cudaEvent_t prof_event(nvllm_handle* h) {
   cudaEventCreate(&e);
   return e;
 }
+// Two instruments behind nvllm_set_profile:
+//  mode 1  CUDA events around every launch.  Serialises the chain (no programmatic-dependent-
+//          launch overlap, no graph replay): per-launch times are an upper bound.  The only mode
+//          that sees the NCCL calls of a tensor-parallel step.
+//  mode 2  device timeline: every kernel records min(entry) / min(dependency released) /
+//          max(exit) of its CTAs in %globaltimer ns (Trace::agg); launches stay back to back on
+//          the stream with their PDL edges, exactly as in a real step.  A launch is charged the
+//          time between its predecessor's last exit and its own last exit, so the classes add up
+//          to the device time of the profiled window.
+// `bytes` are ALGORITHMIC bytes only (weights, K/V, logits, one pass over each activation the
+// reference's dataflow has); `impl` are the extra bytes of this implementation (split-K
+// partials, staged activations).
 struct ProfScope {
   nvllm_handle* h;
   int idx = -1;
-  ProfScope(nvllm_handle* hh, int cls, double bytes, double flops) : h(hh) {
+  ProfScope(nvllm_handle* hh, int cls, double bytes, double flops, double impl = 0.0) : h(hh) {
     h->cur_cls = cls;
     if (!h->profile) return;
-    nvllm_handle::ProfRec r{cls, bytes, flops, prof_event(h), prof_event(h)};
-    cudaEventRecord(r.e0, h->stream);
+    nvllm_handle::ProfRec r{cls, bytes, flops, nullptr, nullptr, impl, 0, 0};
+    if (h->profile == 2) {
+      r.seq0 = trace_seq();
+    } else {
+      r.e0 = prof_event(h);
+      r.e1 = prof_event(h);
+      cudaEventRecord(r.e0, h->stream);
+    }
     idx = (int)h->prof_open.size();
     h->prof_open.push_back(r);
   }
   ~ProfScope() {
-    if (idx >= 0) cudaEventRecord(h->prof_open[idx].e1, h->stream);
+    if (idx < 0) return;
+    if (h->profile == 2) h->prof_open[idx].seq1 = trace_seq();
+    else cudaEventRecord(h->prof_open[idx].e1, h->stream);
   }
 };
+constexpr int PROF_AGG_CAP = 1 << 18;  // launches per profiled window (32 B each)
+static int prof_agg_reset(nvllm_handle* h) {
+  std::vector<unsigned long long> init((size_t)PROF_AGG_CAP * 4);
+  for (size_t i = 0; i < init.size(); i += 4) {
+    init[i] = init[i + 1] = ~0ull;
+    init[i + 2] = init[i + 3] = 0ull;
+  }
+  NV_CHECK(h, cudaMemcpy(h->prof_agg, init.data(), init.size() * 8, cudaMemcpyHostToDevice));
+  trace_agg_set(h->prof_agg, PROF_AGG_CAP);
+  return NVLLM_OK;
+}
 int prof_collect(nvllm_handle* h) {
   if (h->prof_open.empty()) return NVLLM_OK;
   NV_CHECK(h, cudaStreamSynchronize(h->stream));
+  if (h->profile == 2) {
+    const int nseq = std::min(trace_seq(), PROF_AGG_CAP);
+    std::vector<unsigned long long> agg((size_t)nseq * 4);
+    if (nseq) NV_CHECK(h, cudaMemcpy(agg.data(), h->prof_agg, agg.size() * 8, cudaMemcpyDeviceToHost));
+    unsigned long long prev_exit = 0;
+    for (auto& r : h->prof_open) {
+      unsigned long long first = ~0ull, exit = 0;
+      for (int sq = r.seq0; sq < r.seq1 && sq < nseq; sq++) {
+        const unsigned long long* a = &agg[(size_t)sq * 4];
+        if (a[2] == 0) continue;  // the launch had no traced CTA
+        first = std::min(first, a[1] != ~0ull ? a[1] : a[0]);
+        exit = std::max(exit, a[2]);
+      }
+      h->prof[r.cls].bytes += r.bytes;
+      h->prof[r.cls].impl_bytes += r.impl;
+      h->prof[r.cls].flops += r.flops;
+      h->prof[r.cls].launches += 1;
+      if (exit == 0) continue;  // un-instrumented kernel: its time goes to the next record
+      const unsigned long long start = prev_exit ? prev_exit : first;
+      if (exit > start) h->prof[r.cls].ms += (double)(exit - start) * 1e-6;
+      prev_exit = std::max(prev_exit, exit);
+    }
+    h->prof_open.clear();
+    return prof_agg_reset(h);
+  }
   for (auto& r : h->prof_open) {
     float ms = 0.f;
     if (cudaEventElapsedTime(&ms, r.e0, r.e1) == cudaSuccess) {
       h->prof[r.cls].ms += ms;
       h->prof[r.cls].bytes += r.bytes;
+      h->prof[r.cls].impl_bytes += r.impl;
       h->prof[r.cls].flops += r.flops;
       h->prof[r.cls].launches += 1;
     }
@@ -201,17 +259,20 @@ struct RouterArgs {  // expert routing fused into the FFN norm of a MoE layer
 static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int M, int N, int K,
                     float alpha, float* out, size_t cap, int ldo, Pending* res, int epi = 0,
                     void* epi_out = nullptr, int epi_ld = 0, const float* epi_bias = nullptr,
-                    const void* pf_ptr = nullptr, size_t pf_bytes = 0) {
+                    const void* pf_ptr = nullptr, size_t pf_bytes = 0, double alg_out = 0.0) {
   res->p = out;
   res->stride = (size_t)M * ldo;
   const double flops = 2.0 * M * N * K;
-  const double io = (double)N * K * dt_size(h->wdt) + (double)M * K * dt_size(h->adt);
+  // algorithmic: the weights once (+ the logits the LM head must produce, alg_out);
+  // implementation: the staged activations and the fp32 split-K partials
+  const double io = (double)N * K * dt_size(h->wdt) + alg_out;
+  const double a_in = (double)M * K * dt_size(h->adt) - alg_out;
   if (M <= 8) {
     GemmArgs g{};
     g.A = A; g.adt = h->adt; g.lda = lda; g.W = W; g.wdt = h->wdt;
     g.M = M; g.N = N; g.K = K; g.out = out; g.ldo = ldo; g.split_stride = res->stride;
     g.alpha = alpha; g.out_capacity = cap;
-    ProfScope ps(h, NVLLM_K_GEMV, io + 4.0 * gemv_splits(M, N, K) * M * N, flops);
+    ProfScope ps(h, NVLLM_K_GEMV, io, flops, a_in + 4.0 * gemv_splits(M, N, K) * M * N);
     LAUNCH(h, launch_gemv(h->stream, g));
     res->S = g.S;
     return NVLLM_OK;
@@ -230,13 +291,13 @@ static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int 
       t.S = 1;
       t.epi = epi; t.epi_out = epi_out; t.epi_ld = epi_ld; t.epi_bias = epi_bias;
       const double obytes = (double)M * epi_ld * 2;
-      ProfScope ps(h, NVLLM_K_GEMM_TC5, io + obytes, flops);
+      ProfScope ps(h, NVLLM_K_GEMM_TC5, io, flops, a_in + obytes);
       LAUNCH(h, launch_gemm_tc5(h->stream, t, nullptr));
       res->S = 0;
       return NVLLM_OK;
     }
     while (t.S > 1 && (size_t)t.S * M * ldo > cap) t.S--;
-    ProfScope ps(h, NVLLM_K_GEMM_TC5, io + 4.0 * t.S * M * N, flops);
+    ProfScope ps(h, NVLLM_K_GEMM_TC5, io, flops, a_in + 4.0 * t.S * M * N);
     LAUNCH(h, launch_gemm_tc5(h->stream, t, &res->S));
     return NVLLM_OK;
   }
@@ -244,7 +305,7 @@ static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int 
   g.A = A; g.adt = h->adt; g.lda = lda; g.W = W; g.wdt = h->wdt;
   g.M = M; g.N = N; g.K = K; g.out = out; g.ldo = ldo; g.split_stride = res->stride;
   g.alpha = alpha; g.out_capacity = cap;
-  ProfScope ps(h, NVLLM_K_GEMM_SIMT, io + 4.0 * M * N, flops);
+  ProfScope ps(h, NVLLM_K_GEMM_SIMT, io, flops, a_in + 4.0 * M * N);
   LAUNCH(h, launch_gemm_simt(h->stream, g));
   res->S = g.S;
   return NVLLM_OK;
@@ -255,11 +316,13 @@ static int run_norm(nvllm_handle* h, float* x, Pending* p1, Pending* p2, const f
                     const RouterArgs* route = nullptr) {
   NormArgs a{};
   a.x = x;
-  double bytes = (double)n_rows * h->H * (4 + dt_size(h->adt));
+  // algorithmic: x in, y out, and (when a GEMM result is pending) that result once + x back
+  double bytes = (double)n_rows * h->H * (4 + dt_size(h->adt)), impl = 0.0;
   if (p1 && p1->p) {
     a.p1 = p1->p; a.S1 = p1->S; a.stride1 = p1->stride; a.m1 = p1->m; a.bias1 = p1->bias;
     a.comb_rows = p1->comb_rows; a.comb_w = p1->comb_w; a.comb_k = p1->comb_k;
-    bytes += (double)n_rows * h->H * 4 * ((p1->comb_rows ? p1->comb_k : p1->S) + 1);
+    bytes += (double)n_rows * h->H * 4 * 2;
+    impl += (double)n_rows * h->H * 4 * ((p1->comb_rows ? p1->comb_k : p1->S) - 1);
   }
   if (route && route->R) {
     a.router = route->R; a.E = route->E; a.topk = route->k;
@@ -270,11 +333,12 @@ static int run_norm(nvllm_handle* h, float* x, Pending* p1, Pending* p2, const f
     return set_err(h, NVLLM_ERR_INVALID, "MoE layers in a parallel block are not supported");
   if (p2 && p2->p) {
     a.p2 = p2->p; a.S2 = p2->S; a.stride2 = p2->stride; a.m2 = p2->m; a.bias2 = p2->bias;
-    bytes += (double)n_rows * h->H * 4 * p2->S;
+    bytes += (double)n_rows * h->H * 4;
+    impl += (double)n_rows * h->H * 4 * (p2->S - 1);
   }
   a.w = w; a.b = b; a.eps = h->cfg.norm_eps; a.y = y; a.ydt = h->adt; a.y_f32 = y_f32;
   a.row_idx = row_idx; a.n_rows = n_rows; a.H = h->H;
-  ProfScope ps(h, NVLLM_K_NORM, bytes, 0);
+  ProfScope ps(h, NVLLM_K_NORM, bytes, 0, impl);
   LAUNCH(h, launch_norm(h->stream, a));
   if (p1) *p1 = Pending();
   if (p2) *p2 = Pending();
@@ -375,7 +439,9 @@ int forward_step(nvllm_handle* h) {
   }
   const double qo_bytes = 2.0 * T * h->q_cols * asz;
   const double attn_flops = 4.0 * h->nh * h->hd * L.attn_pairs;
-  const double attn_bytes = 2.0 * L.sum_len * h->nkv * h->hd * kvsz + qo_bytes;
+  // algorithmic: every K/V row of the contexts once (+ the new rows appended by a fused decode
+  // prologue); implementation: Q / O staging (and the QKV partials a fused prologue sums)
+  const double attn_bytes = 2.0 * L.sum_len * h->nkv * h->hd * kvsz;
 
   for (int l = 0; l < h->L; l++) {
     const LayerW& lw = h->layers[l];
@@ -397,8 +463,8 @@ int forward_step(nvllm_handle* h) {
       at.sinT = h->use_rope ? h->sinT : nullptr;
     } else {
       ProfScope ps(h, NVLLM_K_ROPE_KV,
-                   (double)T * h->qkv_cols * 4 * qkv.S + (double)T * h->q_cols * asz +
-                       2.0 * T * h->kv_cols * kvsz, 0);
+                   (double)T * h->qkv_cols * 4 + (double)T * h->q_cols * asz +
+                       2.0 * T * h->kv_cols * kvsz, 0, (double)T * h->qkv_cols * 4 * (qkv.S - 1));
       LAUNCH(h, launch_rope_kv(st, h->adt, h->kvdt, T, h->nh, h->nkv, h->hd, qkv.p, qkv.S,
                                qkv.stride, lw.bqkv, d_pos, d_slots,
                                h->use_rope ? h->cosT : nullptr, h->use_rope ? h->sinT : nullptr, w.q,
@@ -407,10 +473,13 @@ int forward_step(nvllm_handle* h) {
     at.kpool = kp;
     at.vpool = vp;
     if (is_prefill) {
-      ProfScope ps(h, NVLLM_K_ATTN_PREFILL, attn_bytes, attn_flops);
+      ProfScope ps(h, NVLLM_K_ATTN_PREFILL, attn_bytes, attn_flops, qo_bytes);
       LAUNCH(h, launch_attn_prefill(st, at));
     } else {
-      ProfScope ps(h, NVLLM_K_ATTN_DECODE, attn_bytes, attn_flops);
+      ProfScope ps(h, NVLLM_K_ATTN_DECODE,
+                   attn_bytes + (fuse_rope ? 2.0 * T * h->kv_cols * kvsz : 0.0), attn_flops,
+                   fuse_rope ? (double)T * h->qkv_cols * 4 * qkv.S + (double)T * h->q_cols * asz
+                             : qo_bytes);
       LAUNCH(h, launch_attn_decode(st, at));
       if (at.n_splits > 1) h->launches++;
     }
@@ -466,9 +535,8 @@ int forward_step(nvllm_handle* h) {
         t.g_tile_expert = w.sort.tile_expert; t.g_tile_row0 = w.sort.tile_row0;
         t.g_tile_rows = w.sort.tile_rows; t.g_n_tiles = w.sort.n_tiles;
         {
-          ProfScope ps(h, NVLLM_K_MOE_GEMM,
-                       (double)e_touched * 2 * I * H * wsz + (double)P * H * asz + (double)P * I * asz,
-                       2.0 * P * 2 * I * H);
+          ProfScope ps(h, NVLLM_K_MOE_GEMM, (double)e_touched * 2 * I * H * wsz, 2.0 * P * 2 * I * H,
+                       (double)P * H * asz + (double)P * I * asz);
           LAUNCH(h, launch_gemm_tc5(st, t, nullptr));
         }
         Tc5Args t2 = t;
@@ -476,9 +544,8 @@ int forward_step(nvllm_handle* h) {
         t2.epi = TC5_EPI_PARTIAL; t2.epi_out = nullptr; t2.out = w.moe_Y; t2.ldo = H;
         t2.split_stride = 0; t2.out_capacity = 0;
         {
-          ProfScope ps(h, NVLLM_K_MOE_GEMM,
-                       (double)e_touched * H * I * wsz + (double)P * I * asz + (double)P * H * 4,
-                       2.0 * P * H * I);
+          ProfScope ps(h, NVLLM_K_MOE_GEMM, (double)e_touched * H * I * wsz, 2.0 * P * H * I,
+                       (double)P * I * asz + (double)P * H * 4);
           LAUNCH(h, launch_gemm_tc5(st, t2, nullptr));
         }
       } else {
@@ -521,7 +588,8 @@ int forward_step(nvllm_handle* h) {
                          lw.b1)))
         return rc;
       if (h1.S > 0) {
-        ProfScope ps(h, NVLLM_K_ACT, (double)T * h->w1_cols * 4 * h1.S + (double)T * h->F * asz, 0);
+        ProfScope ps(h, NVLLM_K_ACT, (double)T * h->w1_cols * 4 + (double)T * h->F * asz, 0,
+                     (double)T * h->w1_cols * 4 * (h1.S - 1));
         LAUNCH(h, launch_act(st, h->adt, T, h->F, h1.p, h1.S, h1.stride, lw.b1, h->swiglu ? 1 : 0,
                              w.hbuf));
       }
@@ -561,11 +629,12 @@ int forward_step(nvllm_handle* h) {
     vsplit = Vl;
   } else {
     if ((rc = run_gemm(h, w.xn_last, H, h->lm_head, n, h->V, H, alpha, w.logits_p,
-                       w.logits_p_floats, h->ldl, &lg)))
+                       w.logits_p_floats, h->ldl, &lg, 0, nullptr, 0, nullptr, nullptr, 0,
+                       (double)n * h->V * 4)))
       return rc;
     logits = lg.p;
     if (lg.S > 1) {
-      ProfScope ps(h, NVLLM_K_MISC, (double)n * h->ldl * 4 * (lg.S + 1), 0);
+      ProfScope ps(h, NVLLM_K_MISC, 0, 0, (double)n * h->ldl * 4 * (lg.S + 1));
       LAUNCH(h, launch_reduce_partials(st, lg.p, lg.S, lg.stride, (size_t)n * h->ldl, w.logits));
       logits = w.logits;
     }
@@ -595,9 +664,16 @@ using namespace nvllm;
 extern "C" int nvllm_set_profile(nvllm_handle* h, int enabled) {
   if (!h) return NVLLM_ERR_INVALID;
   NV_CHECK(h, cudaSetDevice(h->dev));
+  if (enabled < 0 || enabled > 2) return set_err(h, NVLLM_ERR_INVALID, "profile mode %d", enabled);
   int rc = prof_collect(h);
   if (rc) return rc;
   memset(h->prof, 0, sizeof h->prof);
+  if (h->profile == 2 && enabled != 2) trace_agg_set(nullptr, 0);
+  if (enabled == 2) {
+    if (!h->prof_agg) NV_CHECK(h, cudaMalloc((void**)&h->prof_agg, (size_t)PROF_AGG_CAP * 32));
+    h->profile = 2;
+    return prof_agg_reset(h);
+  }
   h->profile = enabled;
   return NVLLM_OK;
 }

@@ -38,7 +38,8 @@ int gemv_splits(int M, int N, int K) { return gemv_plan(M, N, K).S; }
 template <typename AT, typename WT, int M, int R>
 __global__ void __launch_bounds__(256)
 gemv_kernel(const AT* __restrict__ A, int lda, const WT* __restrict__ W, int N, int K, int KC,
-            float* __restrict__ out, int ldo, size_t split_stride, float alpha) {
+            float* __restrict__ out, int ldo, size_t split_stride, float alpha, Trace tr) {
+  TRACE_ENTRY(tr);
   pdl_launch_dependents();
   pdl_wait();
   extern __shared__ float a_s[];  // [M][KC]
@@ -92,6 +93,7 @@ gemv_kernel(const AT* __restrict__ A, int lda, const WT* __restrict__ W, int N, 
       if (lane == 0 && n0 + r < N)
         out[(size_t)blockIdx.y * split_stride + (size_t)m * ldo + n0 + r] = alpha * v;
     }
+  TRACE_EXIT(tr);
 }
 
 template <typename AT, typename WT, int M>
@@ -100,7 +102,8 @@ static cudaError_t gemv_dispatch_r(cudaStream_t st, const GemmArgs& g, const Gem
   size_t smem = (size_t)M * p.KC * sizeof(float);
 #define GV(RR)                                                                                     \
   (void)launch_k(gemv_kernel<AT, WT, M, RR>, dim3(grid), dim3(p.warps * 32), smem, st,                                     \
-      (const AT*)g.A, g.lda, (const WT*)g.W, g.N, g.K, p.KC, g.out, g.ldo, g.split_stride, g.alpha)
+      (const AT*)g.A, g.lda, (const WT*)g.W, g.N, g.K, p.KC, g.out, g.ldo, g.split_stride, g.alpha, \
+      next_trace(11))
   if (p.R == 4) GV(4);
   else if (p.R == 2) GV(2);
   else GV(1);
@@ -153,7 +156,8 @@ __device__ __forceinline__ void load4<bf16>(const bf16* p, float (&v)[4]) {
 
 template <typename AT, typename WT>
 __global__ void __launch_bounds__(256)
-gemm_simt_kernel(GemmArgs g) {
+gemm_simt_kernel(GemmArgs g, Trace tr) {
+  TRACE_ENTRY(tr);
   pdl_launch_dependents();
   pdl_wait();
   __shared__ float As[2][SBK][SBM + 4];
@@ -236,6 +240,7 @@ gemm_simt_kernel(GemmArgs g) {
       if (c < g.N) orow[c] = g.alpha * acc[i][j];
     }
   }
+  TRACE_EXIT(tr);
 }
 
 cudaError_t launch_gemm_simt(cudaStream_t st, GemmArgs& g) {
@@ -243,9 +248,9 @@ cudaError_t launch_gemm_simt(cudaStream_t st, GemmArgs& g) {
   g.S = 1;
   dim3 grid(g.tile_expert ? g.max_tiles : ceil_div(g.M, SBM), ceil_div(g.N, SBN));
   if (grid.x == 0 || grid.y == 0) return cudaSuccess;
-  if (g.adt == DT_F32 && g.wdt == DT_F32) (void)launch_k(gemm_simt_kernel<float, float>, dim3(grid), dim3(256), 0, st, g);
-  else if (g.adt == DT_F32 && g.wdt == DT_BF16) (void)launch_k(gemm_simt_kernel<float, bf16>, dim3(grid), dim3(256), 0, st, g);
-  else if (g.adt == DT_BF16 && g.wdt == DT_BF16) (void)launch_k(gemm_simt_kernel<bf16, bf16>, dim3(grid), dim3(256), 0, st, g);
+  if (g.adt == DT_F32 && g.wdt == DT_F32) (void)launch_k(gemm_simt_kernel<float, float>, dim3(grid), dim3(256), 0, st, g, next_trace(12));
+  else if (g.adt == DT_F32 && g.wdt == DT_BF16) (void)launch_k(gemm_simt_kernel<float, bf16>, dim3(grid), dim3(256), 0, st, g, next_trace(12));
+  else if (g.adt == DT_BF16 && g.wdt == DT_BF16) (void)launch_k(gemm_simt_kernel<bf16, bf16>, dim3(grid), dim3(256), 0, st, g, next_trace(12));
   else return cudaErrorInvalidValue;
   return cudaGetLastError();
 }

@@ -149,7 +149,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
                 float alpha, int w_reused, int epi, bf16* __restrict__ epi_out, int epi_ld,
                 const float* __restrict__ epi_bias, int prefetch, const uint8_t* __restrict__ pf_ptr,
                 unsigned long long pf_bytes, Trace tr) {
-  const unsigned long long t_entry = tr.buf ? gtime() : 0ull;
+  const unsigned long long t_entry = trace_on(tr) ? gtime() : 0ull;
   unsigned long long t_wait = 0;
   __shared__ unsigned long long tr_mma, tr_epi0, tr_epi1, tr_x[6];
   __shared__ __align__(16) uint8_t epi_stage[4][32 * 48];
@@ -265,7 +265,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       }
     }
     pdl_wait();
-    if (tr.buf) t_wait = gtime();
+    if (trace_on(tr)) t_wait = gtime();
     const int units = grouped ? *sc.g_ntiles * sc.n_tiles : sc.units;
     // (2) their activation tiles, then (3) the steady state
     int u = blockIdx.x, kb = 0, i = 0;
@@ -435,7 +435,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   }
   tc_fence_before();
   __syncthreads();
-  if (threadIdx.x == 0 && tr.buf) {
+  if (threadIdx.x == 0 && trace_on(tr)) {
     // extra: (last MMA commit issued, epilogue saw the accumulator, epilogue stores issued)
     // as 21-bit ns offsets from the dependency release
     const unsigned long long a = (tr_mma - t_wait) & 0x1fffff, b = (tr_epi0 - t_wait) & 0x1fffff,
@@ -443,6 +443,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     trace_rec(tr, t_entry, t_wait, (a << 42) | (b << 21) | c);
     Trace t2 = tr;
     t2.kid = 9;
+    t2.agg = nullptr;
     trace_rec(t2, tr_x[0] - t_wait, tr_x[1] - t_wait, ((tr_x[2] - t_wait) << 32) | (tr_x[3] - t_wait));
   }
   if (warp == 1) {
@@ -570,15 +571,26 @@ static int prefetch_flags() {
   return v;
 }
 static unsigned long long* g_trace_buf = nullptr;
+static unsigned long long* g_trace_agg = nullptr;
+static int g_trace_agg_cap = 0;
 static int g_trace_seq = 0;
 void trace_set(unsigned long long* buf) {
   g_trace_buf = buf;
   g_trace_seq = 0;
 }
-bool trace_active() { return g_trace_buf != nullptr; }
+void trace_agg_set(unsigned long long* agg, int capacity) {
+  g_trace_agg = agg;
+  g_trace_agg_cap = capacity;
+  g_trace_seq = 0;
+}
+bool trace_active() { return g_trace_buf != nullptr || g_trace_agg != nullptr; }
+int trace_seq() { return g_trace_seq; }
 Trace next_trace(int kid) {
-  Trace t{g_trace_buf, 0, kid};
-  if (g_trace_buf) t.seq = g_trace_seq++;
+  Trace t{g_trace_buf, 0, kid, nullptr};
+  if (g_trace_buf || g_trace_agg) {
+    t.seq = g_trace_seq++;
+    if (g_trace_agg && t.seq < g_trace_agg_cap) t.agg = g_trace_agg;
+  }
   return t;
 }
 static bool g_pdl = true;

@@ -188,8 +188,11 @@ struct nvllm_handle {
     int cls;
     double bytes, flops;
     cudaEvent_t e0, e1;
+    double impl;
+    int seq0, seq1;  // timeline mode: the traced launches issued inside the scope
   };
-  int profile = 0;
+  int profile = 0;  // 0 off, 1 events around every launch, 2 device timeline (forward.cu)
+  unsigned long long* prof_agg = nullptr;
   std::vector<ProfRec> prof_open;
   std::vector<cudaEvent_t> prof_pool;
   nvllm_profile_entry prof[NVLLM_K_COUNT] = {};

@@ -35,7 +35,8 @@ cudaError_t launch_moe_router(cudaStream_t st, const float* x, const float* R, i
 // not depend on it.
 __global__ void __launch_bounds__(1024)
 moe_sort_kernel(const int* __restrict__ topk_idx, int n_pairs, int k, int E, MoeSortBufs b,
-                int max_tiles, int tile) {
+                int max_tiles, int tile, Trace tr) {
+  TRACE_ENTRY(tr);
   pdl_launch_dependents();
   pdl_wait();
   __shared__ int cnt[MOE_MAX_E];
@@ -72,6 +73,7 @@ moe_sort_kernel(const int* __restrict__ topk_idx, int n_pairs, int k, int E, Moe
     b.pair_row[p] = row;
     b.a_rows[row] = p / k;
   }
+  TRACE_EXIT(tr);
 }
 
 cudaError_t launch_moe_sort(cudaStream_t st, const int* topk_idx, int T, int k, int E,
@@ -79,14 +81,16 @@ cudaError_t launch_moe_sort(cudaStream_t st, const int* topk_idx, int T, int k, 
   if (T <= 0) return cudaSuccess;
   if (E > MOE_MAX_E || tile <= 0) return cudaErrorInvalidValue;
   (void)launch_k(moe_sort_kernel, dim3(1), dim3(1024), 0, st, topk_idx, T * k, k, E, b, max_tiles,
-                 tile);
+                 tile, next_trace(15));
   return cudaGetLastError();
 }
 
 // xs[row, :] = x[a_rows[row], :] — the expert-sorted copy of the normed activations that the
 // grouped tensor-core GEMM reads with plain 2-D TMA boxes (bf16, H % 8 == 0)
 __global__ void moe_gather_kernel(size_t nvec, int vpr, const uint4* __restrict__ x,
-                                  const int* __restrict__ a_rows, uint4* __restrict__ xs) {
+                                  const int* __restrict__ a_rows, uint4* __restrict__ xs,
+                                  Trace tr) {
+  TRACE_ENTRY(tr);
   pdl_launch_dependents();
   pdl_wait();
   for (size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < nvec;
@@ -95,6 +99,7 @@ __global__ void moe_gather_kernel(size_t nvec, int vpr, const uint4* __restrict_
     const int j = (int)(v - row * vpr);
     xs[v] = x[(size_t)a_rows[row] * vpr + j];
   }
+  TRACE_EXIT(tr);
 }
 
 cudaError_t launch_moe_gather(cudaStream_t st, int rows, int H, const void* x, const int* a_rows,
@@ -105,7 +110,7 @@ cudaError_t launch_moe_gather(cudaStream_t st, int rows, int H, const void* x, c
   const size_t nvec = (size_t)rows * vpr;
   const int blocks = (int)min((size_t)148 * 8, (nvec + 255) / 256);
   (void)launch_k(moe_gather_kernel, dim3(blocks), dim3(256), 0, st, nvec, vpr, (const uint4*)x,
-                 a_rows, (uint4*)xs);
+                 a_rows, (uint4*)xs, next_trace(16));
   return cudaGetLastError();
 }
 
@@ -118,7 +123,8 @@ constexpr int MOE_SG_MAX_P = 4096, MOE_SG_MAX_E = 64;
 __global__ void __launch_bounds__(1024)
 moe_sort_gather_kernel(const int* __restrict__ topk_idx, int n_pairs, int k, int E, MoeSortBufs b,
                        int max_tiles, int tile, int vpr, const uint4* __restrict__ x,
-                       uint4* __restrict__ xs) {
+                       uint4* __restrict__ xs, Trace tr) {
+  TRACE_ENTRY(tr);
   pdl_launch_dependents();
   __shared__ int s_cnt[MOE_SG_MAX_E];
   __shared__ int s_off[MOE_SG_MAX_E + 1];
@@ -219,6 +225,7 @@ moe_sort_gather_kernel(const int* __restrict__ topk_idx, int n_pairs, int k, int
     const int r = r0 + idx / vpr, j = idx % vpr;
     if (r < n_pairs) xs[(size_t)r * vpr + j] = x[(size_t)(s_inv[r] / k) * vpr + j];
   }
+  TRACE_EXIT(tr);
 }
 
 bool moe_sort_gather_fits(int T, int k, int E, int H) {
@@ -233,7 +240,7 @@ cudaError_t launch_moe_sort_gather(cudaStream_t st, const int* topk_idx, int T, 
   const long work = (long)T * k * vpr;
   const int grid = (int)std::max(1L, std::min(148L, work / 2048));
   (void)launch_k(moe_sort_gather_kernel, dim3(grid), dim3(1024), 0, st, topk_idx, T * k, k, E, b,
-                 max_tiles, tile, vpr, (const uint4*)x, (uint4*)xs);
+                 max_tiles, tile, vpr, (const uint4*)x, (uint4*)xs, next_trace(17));
   return cudaGetLastError();
 }
 

@@ -277,10 +277,14 @@ int nvllm_destroy(nvllm_handle* h) {
   F(h->d_hist);
   F(h->d_probs);
   for (auto& r : h->prof_open) {
-    cudaEventDestroy(r.e0);
-    cudaEventDestroy(r.e1);
+    if (r.e0) cudaEventDestroy(r.e0);
+    if (r.e1) cudaEventDestroy(r.e1);
   }
   for (auto e : h->prof_pool) cudaEventDestroy(e);
+  if (h->prof_agg) {
+    if (h->profile == 2) nvllm::trace_agg_set(nullptr, 0);
+    cudaFree(h->prof_agg);
+  }
   if (h->h_stage) cudaFreeHost(h->h_stage);
   if (h->h_out) cudaFreeHost(h->h_out);
   if (h->h_logits) cudaFreeHost(h->h_logits);

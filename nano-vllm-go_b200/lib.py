@@ -38,7 +38,7 @@ class ProfileEntry(ctypes.Structure):
     """``struct nvllm_profile_entry``."""
 
     _fields_ = [("ms", ctypes.c_double), ("bytes", ctypes.c_double), ("flops", ctypes.c_double),
-                ("launches", ctypes.c_int64)]
+                ("launches", ctypes.c_int64), ("impl_bytes", ctypes.c_double)]
 
 
 KERNEL_CLASSES = ["embed", "norm", "gemm_tc5", "gemv", "gemm_simt", "rope_kv", "attn_prefill",

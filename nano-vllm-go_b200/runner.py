@@ -175,14 +175,16 @@ class CudaModelRunner:
         L.check(self._lib.nvllm_timer_elapsed(self._h, ctypes.byref(ms)), self._h)
         return ms.value
 
-    def set_profile(self, enabled: bool) -> None:
-        L.check(self._lib.nvllm_set_profile(self._h, int(enabled)), self._h)
+    def set_profile(self, mode) -> None:
+        """0 / False off, 1 / True CUDA events around every launch, 2 device timeline."""
+        L.check(self._lib.nvllm_set_profile(self._h, int(mode)), self._h)
 
     def get_profile(self) -> dict:
         """{class: {ms, bytes, flops, launches}} accumulated since set_profile(True)."""
         arr = (L.ProfileEntry * len(L.KERNEL_CLASSES))()
         L.check(self._lib.nvllm_get_profile(self._h, arr), self._h)
-        return {name: {"ms": e.ms, "bytes": e.bytes, "flops": e.flops, "launches": e.launches}
+        return {name: {"ms": e.ms, "bytes": e.bytes, "flops": e.flops, "launches": e.launches,
+                       "impl_bytes": e.impl_bytes}
                 for name, e in zip(L.KERNEL_CLASSES, arr) if e.launches}
 
     def sync(self, n: int = 0):
