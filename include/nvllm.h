@@ -168,6 +168,35 @@ int nvllm_create(const nvllm_config* cfg, const uint8_t* tp_id, nvllm_handle** o
 int nvllm_set_weight(nvllm_handle* h, int weight_id, int layer, int dtype,
                      const void* host_data, uint64_t numel);
 
+/* Checkpoint families the reference maps (purego/tensor/generic_loader.go:60-182). */
+enum nvllm_arch {
+  NVLLM_ARCH_GPT2 = 0,        /* GetGPT2Mapping: Conv1D [in,out] tensors, fused c_attn */
+  NVLLM_ARCH_FALCON = 1,      /* GetFalconMapping: fused query_key_value, parallel block */
+  NVLLM_ARCH_LLAMA = 2,       /* GetLlamaMapping: separate q/k/v, gate_proj + up_proj */
+  NVLLM_ARCH_GRANITE_MOE = 3  /* GetGraniteMoEMapping: router + stacked expert tensors */
+};
+
+/* Load every weight of the model straight from `model_dir` — model.safetensors, or the shards
+ * named by model.safetensors.index.json — instead of one nvllm_set_weight call per tensor.
+ * Replaces the weight half of tensor.LoadModelFromDirectory (generic_loader.go:1016-1163,
+ * 184-265): the files are mmap'ed, tensors go to the device in their file dtype (F32 / F16 /
+ * BF16; nothing is widened to fp32 on the host) and the loader's transposes, the GPT-2 /
+ * Falcon fused-QKV splits and the [gate | up] concatenation happen in the device-side repack.
+ * The handle's config (created from the same config.json the Go side parses with
+ * LoadModelConfig) says what to expect; call nvllm_finalize afterwards.  Tensor-parallel
+ * handles each read the full files and keep their shard.  bytes_read / tensors_loaded are
+ * optional. */
+int nvllm_load_safetensors(nvllm_handle* h, const char* model_dir, int arch,
+                           uint64_t* bytes_read, int32_t* tensors_loaded);
+
+/* Host-only checkpoint probe (no handle, no device): finds `name` the way the loader does
+ * ("transformer." retry, sharded index) and reports dtype (nvllm_dtype, -1 = unsupported),
+ * shape, byte size and the tensor's first 8 bytes.  NVLLM_ERR_INVALID when absent; the reason
+ * is in nvllm_last_error(NULL). */
+int nvllm_safetensors_find(const char* model_dir, const char* name, int32_t* dtype,
+                           int32_t* ndim, int64_t shape[8], uint64_t* nbytes,
+                           uint64_t* first_bytes);
+
 /* Pack weights (bf16 [out,in] K-major for TMA), build tensor maps, allocate
  * the paged KV pool [L][2][num_blocks][n_kv][256][hd] and workspaces. */
 int nvllm_finalize(nvllm_handle* h);

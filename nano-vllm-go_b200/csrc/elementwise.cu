@@ -767,6 +767,40 @@ cudaError_t launch_convert(cudaStream_t st, int sdt_api, const void* src, size_t
   return cudaGetLastError();
 }
 
+// dst[(n * row_mul + row_add) * ld_dst + k] = src[n * ld_src + k] for n < N rows, k < K: a row
+// range of a [out, in] (PyTorch / safetensors) linear taken as it lies — the device layout has
+// the same orientation, so loading is a strided copy + dtype conversion, no transpose
+template <typename ST, typename DT>
+__global__ void copy_rows_kernel(const ST* __restrict__ src, size_t ld_src, int N, int K,
+                                 DT* __restrict__ dst, int ld_dst, int row_mul, int row_add) {
+  const size_t total = (size_t)N * K;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const size_t n = i / K;
+    const int k = (int)(i - n * K);
+    dst[(n * row_mul + row_add) * ld_dst + k] = from_f32<DT>(src_to_f32<ST>(src[n * ld_src + k]));
+  }
+}
+cudaError_t launch_copy_rows(cudaStream_t st, int sdt_api, const void* src, size_t ld_src, int N,
+                             int K, int ddt, void* dst, int ld_dst, int row_mul, int row_add) {
+  if (N <= 0 || K <= 0) return cudaSuccess;
+  const size_t total = (size_t)N * K;
+  int blocks = (int)min((size_t)148 * 8, (total + 255) / 256);
+#define CR(ST, DT) \
+  copy_rows_kernel<ST, DT><<<blocks, 256, 0, st>>>((const ST*)src, ld_src, N, K, (DT*)dst, ld_dst, row_mul, row_add)
+  if (ddt == DT_F32) {
+    if (sdt_api == 0) CR(float, float);
+    else if (sdt_api == 1) CR(bf16, float);
+    else CR(__half, float);
+  } else {
+    if (sdt_api == 0) CR(float, bf16);
+    else if (sdt_api == 1) CR(bf16, bf16);
+    else CR(__half, bf16);
+  }
+#undef CR
+  return cudaGetLastError();
+}
+
 __global__ void fill_kernel(float* p, size_t n, float v) {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n;
        i += (size_t)gridDim.x * blockDim.x)

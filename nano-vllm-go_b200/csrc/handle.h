@@ -209,6 +209,17 @@ int prof_collect(nvllm_handle* h);
 
 int set_err(nvllm_handle* h, int code, const char* fmt, ...);
 
+// weights.cu: how the caller's buffer holds a tensor (nvllm_set_weight: all defaults)
+struct WeightSrc {
+  bool out_in = false;  // linears are [out, in] (PyTorch / safetensors) instead of [in, out]
+  size_t ld = 0;        // > 0: the tensor is columns [col0, col0 + width) of a [rows, ld] matrix
+  size_t col0 = 0;      //      (vectors: elements [col0, col0 + n) of a longer vector of ld)
+};
+// internal weight ids (never cross the C ABI): the two halves of a SwiGLU W1, each [H, F]
+enum { W_INT_FFN_GATE = 40, W_INT_FFN_UP = 41 };
+int set_weight_src(nvllm_handle* h, int id, int layer, int dtype, const void* host, uint64_t numel,
+                   const WeightSrc& src);
+
 // tp.cu — tensor-parallel group over NCCL (loaded with dlopen: no link-time dependency)
 int tp_unique_id(uint8_t out_id[128]);
 int tp_init(nvllm_handle* h, const uint8_t* id);  // ncclCommInitRank(tp, id, rank)

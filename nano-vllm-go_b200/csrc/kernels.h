@@ -119,6 +119,10 @@ cudaError_t launch_transpose_convert(cudaStream_t st, int sdt_api, const void* s
 // [2 glu_I, cols] matrix of the stack rewritten with gate / up rows interleaved
 cudaError_t launch_convert(cudaStream_t st, int sdt_api, const void* src, size_t n, int ddt,
                            void* dst, int glu_I = 0, int cols = 0);
+// dst[(n*row_mul + row_add), k] (dtype ddt) = src[n, k] for n < N, k < K (src rows ld_src apart)
+cudaError_t launch_copy_rows(cudaStream_t st, int sdt_api, const void* src, size_t ld_src, int N,
+                             int K, int ddt, void* dst, int ld_dst, int row_mul = 1,
+                             int row_add = 0);
 // out[i] = sum_s p[s*stride + i]
 cudaError_t launch_reduce_partials(cudaStream_t st, const float* p, int S, size_t stride, size_t n,
                                    float* out);

@@ -43,6 +43,16 @@ struct Repack {
 
 extern "C" int nvllm_set_weight(nvllm_handle* h, int id, int layer, int dtype, const void* host,
                                 uint64_t numel) {
+  return nvllm::set_weight_src(h, id, layer, dtype, host, numel, nvllm::WeightSrc());
+}
+
+// The one implementation behind nvllm_set_weight (reference post-load layout, [in, out]) and the
+// safetensors loader (safetensors.cu), which hands the tensors as the file holds them: PyTorch
+// linears are [out, in] — already the device orientation, so the "transpose" of the tables
+// below becomes a strided row copy — and fused tensors (GPT-2 c_attn [H, 3H], its bias) are
+// addressed as a column slice of a wider matrix (src.ld / src.col0).
+int nvllm::set_weight_src(nvllm_handle* h, int id, int layer, int dtype, const void* host,
+                          uint64_t numel, const WeightSrc& src) {
   if (!h) return NVLLM_ERR_INVALID;
   if (!host) return set_err(h, NVLLM_ERR_INVALID, "null weight pointer");
   if (dtype < 0 || dtype > 2) return set_err(h, NVLLM_ERR_INVALID, "bad dtype %d", dtype);
@@ -140,6 +150,12 @@ extern "C" int nvllm_set_weight(nvllm_handle* h, int id, int layer, int dtype, c
         tr(r, w->w1, f0, Fg, H, Fl, H);
       }
       break;
+    case W_INT_FFN_GATE:  // one half of a SwiGLU W1 (Llama gate_proj / up_proj): [H, F]
+    case W_INT_FFN_UP:
+      if (h->moe || !h->swiglu) return set_err(h, NVLLM_ERR_INVALID, "gate / up halves need a SwiGLU FFN");
+      expect = (size_t)H * Fg;
+      tr(r, w->w1, f0, Fg, H, Fl, H, 2, id == W_INT_FFN_UP ? 1 : 0);
+      break;
     case NVLLM_W_FFN_B1:
       if (h->moe || h->swiglu)  // transformer.go:50-66: the SwiGLU branch never adds B1
         return set_err(h, NVLLM_ERR_INVALID, "FFN_B1 only exists on the GELU branch");
@@ -166,24 +182,48 @@ extern "C" int nvllm_set_weight(nvllm_handle* h, int id, int layer, int dtype, c
       r.to_f32 = false; r.dst = w->moe_out; r.N = -1; expect = (size_t)h->E * H * Fg; break;
     default: return set_err(h, NVLLM_ERR_INVALID, "unknown weight id %d", id);
   }
-  if (numel != expect)
+  // `numel` is what the caller's buffer holds: the tensor itself, or the wider matrix it is a
+  // column slice of (src.ld > 0: [rows, src.ld] with this tensor at columns [col0, col0 + width))
+  uint64_t want = expect;
+  if (src.ld > 0) {
+    const size_t width = ops[0].transpose ? ops[0].ld_src : expect;  // natural row length
+    if (src.col0 + width > src.ld)
+      return set_err(h, NVLLM_ERR_INVALID, "weight %d: column slice [%zu, +%zu) outside ld %zu", id,
+                     src.col0, width, src.ld);
+    want = (expect / width) * src.ld;
+  }
+  if (numel != want)
     return set_err(h, NVLLM_ERR_INVALID, "weight %d (layer %d): numel %llu, expected %llu", id,
-                   layer, (unsigned long long)numel, (unsigned long long)expect);
+                   layer, (unsigned long long)numel, (unsigned long long)want);
   void* stage = nullptr;
   const size_t ssz = api_dt_size(dtype);
   int rc = stage_in(h, host, numel * ssz, &stage);
   if (rc) return rc;
   cudaError_t e = cudaSuccess;
   for (int i = 0; i < n_ops && e == cudaSuccess; i++) {
-    const Repack& o = ops[i];
-    const void* src = (const char*)stage + o.src_off * ssz;
+    Repack o = ops[i];
     const int ddt = o.to_f32 ? DT_F32 : h->wdt;
-    if (o.transpose)
-      e = launch_transpose_convert(h->stream, dtype, src, o.ld_src, o.K, o.N, ddt, o.dst, o.ld_dst,
-                                   o.row_mul, o.row_add);
-    else
-      e = launch_convert(h->stream, dtype, src, o.N < 0 ? (size_t)numel : (size_t)o.N, ddt, o.dst,
-                         id == NVLLM_W_MOE_INPUT ? Fg : 0, H);
+    if (o.transpose) {
+      // element (k, n) of the logical [in, out] slice: k < K input features, n < N outputs
+      const size_t r0 = o.src_off / o.ld_src, c0 = o.src_off % o.ld_src;
+      if (src.out_in) {
+        // the buffer is [out, in]: (k, n) lives at (c0 + n) * in_full + r0 + k — rows of the
+        // destination are contiguous runs of the source
+        const size_t in_full = (size_t)(expect / o.ld_src);
+        const void* sp = (const char*)stage + (c0 * in_full + r0) * ssz;
+        e = launch_copy_rows(h->stream, dtype, sp, in_full, o.N, o.K, ddt, o.dst, o.ld_dst,
+                             o.row_mul, o.row_add);
+      } else {
+        const size_t ld = src.ld > 0 ? src.ld : o.ld_src;
+        const void* sp = (const char*)stage + (r0 * ld + src.col0 + c0) * ssz;
+        e = launch_transpose_convert(h->stream, dtype, sp, ld, o.K, o.N, ddt, o.dst, o.ld_dst,
+                                     o.row_mul, o.row_add);
+      }
+      continue;
+    }
+    const void* sp = (const char*)stage + (o.src_off + src.col0) * ssz;
+    e = launch_convert(h->stream, dtype, sp, o.N < 0 ? (size_t)numel : (size_t)o.N, ddt, o.dst,
+                       id == NVLLM_W_MOE_INPUT ? Fg : 0, H);
   }
   // row-parallel output biases are added once: ranks other than 0 hold zeros
   if (e == cudaSuccess && h->rank != 0 && (id == NVLLM_W_O_BIAS || id == NVLLM_W_FFN_B2))
@@ -193,6 +233,11 @@ extern "C" int nvllm_set_weight(nvllm_handle* h, int id, int layer, int dtype, c
   if (e != cudaSuccess)
     return set_err(h, NVLLM_ERR_CUDA, "weight repack failed: %s", cudaGetErrorString(e));
   h->have[(size_t)(model_level ? 0 : layer + 1) * 64 + id] = 1;
+  // both halves of a SwiGLU W1 make the whole
+  if (id == W_INT_FFN_GATE || id == W_INT_FFN_UP) {
+    const size_t base = (size_t)(layer + 1) * 64;
+    if (h->have[base + W_INT_FFN_GATE] && h->have[base + W_INT_FFN_UP]) h->have[base + NVLLM_W_FFN_W1] = 1;
+  }
   return NVLLM_OK;
 }
 
