@@ -22,6 +22,8 @@ POS_LEARNED, POS_ROPE, POS_NONE = 0, 1, 2
 ACT_GELU, ACT_SWIGLU = 0, 1
 BLOCK_SEQUENTIAL, BLOCK_PARALLEL = 0, 1
 PREC_FP32, PREC_BF16 = 0, 1
+# enum nvllm_arch (checkpoint families of generic_loader.go:60-182)
+ARCH_GPT2, ARCH_FALCON, ARCH_LLAMA, ARCH_GRANITE_MOE = 0, 1, 2, 3
 DT_F32, DT_BF16, DT_F16 = 0, 1, 2
 
 # enum nvllm_weight_id

@@ -24,6 +24,7 @@ TensorModelRunner that are deliberate and visible at the boundary:
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Iterable, List, Optional, Sequence as Seq, Tuple
 
 import numpy as np
@@ -42,7 +43,8 @@ class CudaModelRunner:
                  precision: int = C.PREC_BF16, num_kv_blocks: int = -1, device: int = 0,
                  max_num_seqs: int = 512, max_batched_tokens: int = 16384,
                  weight_dtype: Optional[int] = None, tp_size: int = 1, tp_rank: int = 0,
-                 tp_id: Optional[bytes] = None, sampling: Optional[dict] = DEFAULT_SAMPLING):
+                 tp_id: Optional[bytes] = None, sampling: Optional[dict] = DEFAULT_SAMPLING,
+                 model_dir: Optional[str] = None, arch: Optional[int] = None):
         """Replaces NewTensorModelRunner(modelDir) (tensor_model_runner.go:21-32): instead of a
         directory, takes the tensors in the layouts LoadModel leaves them in
         (generic_loader.go:184-265), as (weight_id, layer, ndarray) triples.
@@ -57,7 +59,12 @@ class CudaModelRunner:
         sampling: the runner-wide sampling parameters Run() draws with; the default is the
         reference runner's (temperature 1.0, repetition penalty 1.2: every row is drawn by the
         device-side SampleWithHistory).  None = greedy first-max rows, no filters (what the
-        parity tests and the benchmark use: the reference's draw uses an unseeded global RNG)."""
+        parity tests and the benchmark use: the reference's draw uses an unseeded global RNG).
+
+        model_dir + arch (config.ARCH_*): what NewTensorModelRunner really takes — the library
+        reads model.safetensors / the sharded index itself (nvllm_load_safetensors: mmap, file
+        dtype kept, the loader's transposes and QKV splits done on the device); `weights` is
+        then ignored and may be None."""
         self._lib = L.load()
         self.cfg = cfg
         self.precision = precision
@@ -71,9 +78,16 @@ class CudaModelRunner:
                 raise ValueError("tp_size > 1 needs the 128-byte tp_id of the group")
             idbuf = (ctypes.c_uint8 * 128).from_buffer_copy(tp_id)
         L.check(self._lib.nvllm_create(ctypes.byref(cc), idbuf, ctypes.byref(self._h)))
+        self.loaded_bytes, self.loaded_tensors = 0, 0
         try:
-            for wid, layer, arr in weights:
-                self.set_weight(wid, layer, arr, weight_dtype)
+            if model_dir is not None:
+                nb, nt = ctypes.c_uint64(), ctypes.c_int32()
+                L.check(self._lib.nvllm_load_safetensors(self._h, os.fsencode(model_dir), int(arch),
+                                                         ctypes.byref(nb), ctypes.byref(nt)), self._h)
+                self.loaded_bytes, self.loaded_tensors = nb.value, nt.value
+            else:
+                for wid, layer, arr in weights:
+                    self.set_weight(wid, layer, arr, weight_dtype)
             L.check(self._lib.nvllm_finalize(self._h), self._h)
         except Exception:
             self.close()
