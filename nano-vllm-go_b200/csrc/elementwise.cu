@@ -15,10 +15,13 @@ namespace nvllm {
 template <typename WT>
 __global__ void embed_kernel(const int* __restrict__ tokens, const int* __restrict__ positions,
                              const WT* __restrict__ wte, const WT* __restrict__ wpe, int max_pos,
-                             float mult, float* __restrict__ x, int H, Trace tr) {
+                             float mult, float* __restrict__ x, int H, bf16* __restrict__ xb,
+                             float* __restrict__ ssq, Trace tr) {
   TRACE_ENTRY(tr);
   pdl_wait();  // step prologue: later kernels may read the step state before their own wait
   pdl_launch_dependents();
+  __shared__ float red[32];
+  float lsq = 0.f;
   const int t = blockIdx.x;
   const int tok = tokens[t];
   const int pos = positions[t];
@@ -39,21 +42,31 @@ __global__ void embed_kernel(const int* __restrict__ tokens, const int* __restri
       for (int j = 0; j < 8; j++) v[j] *= mult;
     }
     store8(x + (size_t)t * H + i, v);
+    if (xb) {
+      store8(xb + (size_t)t * H + i, v);
+#pragma unroll
+      for (int j = 0; j < 8; j++) lsq += v[j] * v[j];
+    }
+  }
+  if (xb) {
+    const float tot = block_sum(lsq, red);
+    if (threadIdx.x == 0) ssq[t] = tot;
   }
   TRACE_EXIT(tr);
 }
 
 cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int* positions,
                          const void* wte, const void* wpe, int max_pos, float mult, float* x, int T,
-                         int H) {
+                         int H, void* xb, float* ssq) {
   if (T <= 0) return cudaSuccess;
+  if ((xb == nullptr) != (ssq == nullptr)) return cudaErrorInvalidValue;
   int threads = min(256, max(32, ((H / 8 + 31) / 32) * 32));
   if (wdt == DT_F32)
     (void)launch_k(embed_kernel<float>, dim3(T), dim3(threads), 0, st, tokens, positions, (const float*)wte,
-                                               (const float*)wpe, max_pos, mult, x, H, next_trace(5));
+                                               (const float*)wpe, max_pos, mult, x, H, (bf16*)xb, ssq, next_trace(5));
   else
     (void)launch_k(embed_kernel<bf16>, dim3(T), dim3(threads), 0, st, tokens, positions, (const bf16*)wte,
-                                              (const bf16*)wpe, max_pos, mult, x, H, next_trace(5));
+                                              (const bf16*)wpe, max_pos, mult, x, H, (bf16*)xb, ssq, next_trace(5));
   return cudaGetLastError();
 }
 
@@ -77,7 +90,10 @@ __global__ void __launch_bounds__(512) norm_kernel(NormArgs a, Trace tr) {
   for (int j = 0; j < 8; j++) w0[j] = b0[j] = bias1_0[j] = bias2_0[j] = 0.f;
   if (i0 < H) {
     if (a.y) {
-      load8(a.w + i0, w0);
+      if (a.w) load8(a.w + i0, w0);
+      else
+#pragma unroll
+        for (int j = 0; j < 8; j++) w0[j] = 1.f;
       if (a.b) load8(a.b + i0, b0);
     }
     if (a.p1 && a.bias1) load8(a.bias1 + i0, bias1_0);
@@ -194,7 +210,10 @@ __global__ void __launch_bounds__(512) norm_kernel(NormArgs a, Trace tr) {
         bb[j] = b0[j];
       }
     } else {
-      load8(a.w + i, w);
+      if (a.w) load8(a.w + i, w);
+      else
+#pragma unroll
+        for (int j = 0; j < 8; j++) w[j] = 1.f;
       if (a.b) load8(a.b + i, bb);
     }
     if (a.b) {
@@ -798,6 +817,26 @@ cudaError_t launch_copy_rows(cudaStream_t st, int sdt_api, const void* src, size
     else CR(__half, bf16);
   }
 #undef CR
+  return cudaGetLastError();
+}
+
+__global__ void fold_cols_kernel(bf16* __restrict__ W, size_t n8, int K, const float* __restrict__ g) {
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8;
+       i += (size_t)gridDim.x * blockDim.x) {
+    const int k = (int)((i * 8) % K);
+    float w[8], s[8];
+    load8(W + i * 8, w);
+    load8(g + k, s);
+#pragma unroll
+    for (int j = 0; j < 8; j++) w[j] *= s[j];
+    store8(W + i * 8, w);
+  }
+}
+cudaError_t launch_fold_cols(cudaStream_t st, void* W, size_t rows, int K, const float* g) {
+  if (rows == 0) return cudaSuccess;
+  if (K % 8) return cudaErrorInvalidValue;
+  const size_t n8 = rows * (size_t)K / 8;
+  fold_cols_kernel<<<(int)min((size_t)148 * 16, (n8 + 255) / 256), 256, 0, st>>>((bf16*)W, n8, K, g);
   return cudaGetLastError();
 }
 

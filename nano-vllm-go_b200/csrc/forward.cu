@@ -17,12 +17,14 @@
 
 namespace nvllm {
 
+constexpr int RES_CTR_TILES = 4096;  // output tiles a split-K fused-residual GEMM may have
+
 // ------------------------------------------------------------------ workspace
 void free_workspace(nvllm_handle* h) {
   Workspace& w = h->ws;
   h->drop_graphs();  // the captured decode steps hold these pointers
   void* ptrs[] = {w.tp_buf, w.x, w.xn, w.xn_f32, w.ws_a, w.ws_b, w.ws_c, w.q, w.attn_out, w.hbuf, w.xn_last,
-                  w.logits_p, w.logits, w.attn_ws, w.attn_tickets, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
+                  w.xb, w.ssq, w.res_ctr, w.logits_p, w.logits, w.attn_ws, w.attn_tickets, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
                   w.sort.counts, w.sort.offsets, w.sort.cursor, w.sort.sorted_pair, w.sort.pair_row,
                   w.sort.a_rows, w.sort.tile_expert, w.sort.tile_row0, w.sort.tile_rows,
                   w.sort.n_tiles, w.moe_Y, w.moe_y, w.moe_xs};
@@ -75,6 +77,13 @@ int ensure_workspace(nvllm_handle* h, int T, int n) {
   WS(w.attn_out, (size_t)Tc * h->q_cols * asz);
   WS(w.hbuf, h->moe ? (size_t)Tc * h->topk * h->F * asz : (size_t)Tc * h->F * asz);
   WS(w.xn_last, nc * H * asz);
+  if (h->fold) {
+    WS(w.xb, Tc * H * 2);
+    WS(w.ssq, (size_t)ceil_div(h->H, 128) * Tc * 4);
+    WS(w.res_ctr, (size_t)4 * RES_CTR_TILES * 4);
+    if (cudaMemsetAsync(w.res_ctr, 0, (size_t)4 * RES_CTR_TILES * 4, h->stream) != cudaSuccess)
+      return set_err(h, NVLLM_ERR_CUDA, "memset(fused-residual counters) failed");
+  }
   if (h->tp > 1) WS(w.tp_buf, Tc * H * 4);
   // tp > 1: this rank's LM-head slice is Vl wide and the gathered logits are [tp][n][Vl]
   const size_t lcols = h->tp > 1 ? (size_t)h->Vl : (size_t)h->ldl;
@@ -235,6 +244,20 @@ struct Pending {  // a GEMM result still to be added to the residual stream
   int comb_k = 0;
 };
 
+// Folded RMSNorm, consumer side: the GEMM reads the un-normalised bf16 residual stream and scales
+// accumulator row m by 1 / sqrt(sum_p ssq[p][m] / H + eps)
+struct RowScale {
+  const float* ssq = nullptr;
+  int parts = 0;
+};
+// Folded RMSNorm, producer side: the GEMM's epilogue performs the residual update
+// x += m * (acc + bias) and leaves bf16(x) + the row sums of squares for the next consumer
+struct Resid {
+  float m = 1.f;
+  const float* bias = nullptr;
+  int site = 0;  // 0 = attention output projection, 1 = FFN down projection (counter sets)
+};
+
 struct RouterArgs {  // expert routing fused into the FFN norm of a MoE layer
   const float* R = nullptr;
   int E = 0, k = 0;
@@ -259,7 +282,8 @@ struct RouterArgs {  // expert routing fused into the FFN norm of a MoE layer
 static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int M, int N, int K,
                     float alpha, float* out, size_t cap, int ldo, Pending* res, int epi = 0,
                     void* epi_out = nullptr, int epi_ld = 0, const float* epi_bias = nullptr,
-                    const void* pf_ptr = nullptr, size_t pf_bytes = 0, double alg_out = 0.0) {
+                    const void* pf_ptr = nullptr, size_t pf_bytes = 0, double alg_out = 0.0,
+                    const RowScale* rs = nullptr, const Resid* rd = nullptr) {
   res->p = out;
   res->stride = (size_t)M * ldo;
   const double flops = 2.0 * M * N * K;
@@ -282,6 +306,27 @@ static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int 
     t.A = A; t.W = W; t.M = M; t.N = N; t.K = K; t.out = out; t.ldo = ldo;
     t.split_stride = res->stride; t.alpha = alpha; t.out_capacity = cap;
     t.S = tc5_splits(M, N, K, h->sm_count);
+    if (rs && rs->ssq) {
+      t.rs_ssq = rs->ssq; t.rs_parts = rs->parts; t.rs_ld = h->ws.T_cap;
+      t.rs_inv_h = 1.0f / (float)h->H; t.rs_eps = h->cfg.norm_eps;
+    }
+    if (rd) {
+      // x += m (A W^T + bias) inside the GEMM; nothing is left pending for a norm kernel
+      t.S = tc5_resid_splits(M, N, K, h->sm_count);
+      while (t.S > 1 && (size_t)t.S * M * ldo > cap) t.S--;
+      t.epi = TC5_EPI_RESID;
+      t.res_x = h->ws.x; t.res_xb = h->ws.xb; t.res_ssq = h->ws.ssq; t.res_ssq_ld = h->ws.T_cap;
+      t.res_bias = rd->bias; t.res_m = rd->m;
+      t.res_arrive = h->ws.res_ctr + (size_t)rd->site * 2 * RES_CTR_TILES;
+      t.res_done = t.res_arrive + RES_CTR_TILES;
+      const double xrw = (double)M * N * (4 + 4 + 2);
+      ProfScope ps(h, NVLLM_K_GEMM_TC5, io + (double)M * N * 4 * 2, flops,
+                   a_in + (double)M * N * 2 + (t.S > 1 ? 4.0 * t.S * M * N * 2 : 0.0));
+      (void)xrw;
+      LAUNCH(h, launch_gemm_tc5(h->stream, t, nullptr));
+      *res = Pending();
+      return NVLLM_OK;
+    }
     if (M <= 128) {  // weight-streaming regime: warm L2 with the next big matrix
       t.pf_ptr = pf_ptr;
       t.pf_bytes = pf_bytes;
@@ -309,6 +354,16 @@ static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int 
   LAUNCH(h, launch_gemm_simt(h->stream, g));
   res->S = g.S;
   return NVLLM_OK;
+}
+
+// can (M, N, K) with this activation stride take the tcgen05 path (and with it the folded-norm
+// epilogues)?
+static bool fold_gemm_ok(const nvllm_handle* h, int M, int N, int K, int lda) {
+  return h->fold && M > 8 && h->wdt == DT_BF16 && h->use_tc5 && lda == K && tc5_supported(M, N, K);
+}
+static bool resid_gemm_ok(const nvllm_handle* h, int M, int N, int K, int lda) {
+  if (!fold_gemm_ok(h, M, N, K, lda) || N != h->H) return false;
+  return tc5_resid_splits(M, N, K, h->sm_count) >= 1;  // S > 1 implies tiles < #SM <= RES_CTR_TILES
 }
 
 static int run_norm(nvllm_handle* h, float* x, Pending* p1, Pending* p2, const float* w,
@@ -398,8 +453,14 @@ int forward_step(nvllm_handle* h) {
   {
     ProfScope ps(h, NVLLM_K_EMBED, (double)T * H * (4 + dt_size(h->wdt)), 0);
     LAUNCH(h, launch_embed(st, h->wdt, d_tokens, d_pos, h->wte, h->wpe, c.max_seq_len,
-                           c.embedding_multiplier, w.x, T, H));
+                           c.embedding_multiplier, w.x, T, H, h->fold ? w.xb : nullptr,
+                           h->fold ? w.ssq : nullptr));
   }
+  // Folded RMSNorm (h->fold): while `xb_parts` > 0, w.xb holds bf16(x) of the CURRENT residual
+  // stream and w.ssq its row sums of squares in xb_parts column-tile slices — the next GEMM
+  // that would read a normed activation reads w.xb instead and the norm kernel is not launched.
+  int xb_parts = h->fold ? 1 : 0;
+  const int h_tiles = ceil_div(H, 128);
   // generic_model.go:359-365: res + rm * x when ResidualMultiplier != 0, else plain add
   const float m_res = (c.residual_multiplier != 0.f) ? c.residual_multiplier : 1.f;
   // generic_model.go:405-416 (parallel block): both multipliers or neither
@@ -447,12 +508,21 @@ int forward_step(nvllm_handle* h) {
     const LayerW& lw = h->layers[l];
     // ---- attention sub-block
     if ((rc = tp_reduce_pending(h, &p1, &p2, T))) return rc;
-    if ((rc = run_norm(h, w.x, &p1, &p2, lw.attn_norm_w, lw.attn_norm_b, w.xn, nullptr, nullptr, T)))
-      return rc;
     Pending qkv;
-    if ((rc = run_gemm(h, w.xn, H, lw.wqkv, T, h->qkv_cols, H, 1.f, w.ws_a, w.ws_a_floats,
-                       h->qkv_cols, &qkv)))
-      return rc;
+    if (xb_parts > 0 && fold_gemm_ok(h, T, h->qkv_cols, H, H)) {
+      RowScale rsc{w.ssq, xb_parts};
+      if ((rc = run_gemm(h, w.xb, H, lw.wqkv, T, h->qkv_cols, H, 1.f, w.ws_a, w.ws_a_floats,
+                         h->qkv_cols, &qkv, 0, nullptr, 0, nullptr, nullptr, 0, 0.0, &rsc)))
+        return rc;
+    } else {
+      if ((rc = run_norm(h, w.x, &p1, &p2, h->fold ? nullptr : lw.attn_norm_w, lw.attn_norm_b, w.xn,
+                         nullptr, nullptr, T)))
+        return rc;
+      if ((rc = run_gemm(h, w.xn, H, lw.wqkv, T, h->qkv_cols, H, 1.f, w.ws_a, w.ws_a_floats,
+                         h->qkv_cols, &qkv)))
+        return rc;
+    }
+    xb_parts = 0;
     void* kp = (char*)h->kpool + (size_t)l * kv_layer_bytes;
     void* vp = (char*)h->vpool + (size_t)l * kv_layer_bytes;
     const bool fuse_rope = !is_prefill && attn_decode_fuses_rope(h->adt, h->kvdt, h->hd);
@@ -483,11 +553,19 @@ int forward_step(nvllm_handle* h) {
       LAUNCH(h, launch_attn_decode(st, at));
       if (at.n_splits > 1) h->launches++;
     }
-    if ((rc = run_gemm(h, w.attn_out, h->q_cols, lw.wo, T, H, h->q_cols, 1.f, w.ws_b,
-                       w.ws_b_floats, H, &p1)))
-      return rc;
-    p1.bias = lw.bo;
-    p1.m = h->parallel ? (par_scaled ? c.attention_multiplier : 1.f) : m_res;
+    if (resid_gemm_ok(h, T, H, h->q_cols, h->q_cols)) {
+      Resid rd{m_res, lw.bo, 0};
+      if ((rc = run_gemm(h, w.attn_out, h->q_cols, lw.wo, T, H, h->q_cols, 1.f, w.ws_b,
+                         w.ws_b_floats, H, &p1, 0, nullptr, 0, nullptr, nullptr, 0, 0.0, nullptr, &rd)))
+        return rc;
+      xb_parts = h_tiles;
+    } else {
+      if ((rc = run_gemm(h, w.attn_out, h->q_cols, lw.wo, T, H, h->q_cols, 1.f, w.ws_b,
+                         w.ws_b_floats, H, &p1)))
+        return rc;
+      p1.bias = lw.bo;
+      p1.m = h->parallel ? (par_scaled ? c.attention_multiplier : 1.f) : m_res;
+    }
     // ---- feed-forward sub-block
     float* ffn_out = w.ws_b;
     if (h->parallel) {
@@ -499,9 +577,13 @@ int forward_step(nvllm_handle* h) {
         ra.R = lw.router; ra.E = h->E; ra.k = h->topk;
         ra.topk_idx = w.topk_idx; ra.topk_w = w.topk_w;
       }
-      if ((rc = run_norm(h, w.x, &p1, nullptr, lw.ffn_norm_w, lw.ffn_norm_b, w.xn, nullptr, nullptr,
-                         T, &ra)))
-        return rc;
+      const bool skip_norm = xb_parts > 0 && !h->moe && fold_gemm_ok(h, T, h->w1_cols, H, H);
+      if (!skip_norm) {
+        if ((rc = run_norm(h, w.x, &p1, nullptr, h->fold ? nullptr : lw.ffn_norm_w, lw.ffn_norm_b,
+                           w.xn, nullptr, nullptr, T, &ra)))
+          return rc;
+        xb_parts = 0;
+      }
     }
     Pending& pf = h->parallel ? p2 : p1;
     if (h->moe) {
@@ -583,21 +665,31 @@ int forward_step(nvllm_handle* h) {
       pf.comb_rows = w.sort.pair_row; pf.comb_w = w.topk_w; pf.comb_k = k;
     } else {
       Pending h1;
-      if ((rc = run_gemm(h, w.xn, H, lw.w1, T, h->w1_cols, H, 1.f, w.ws_a, w.ws_a_floats,
-                         h->w1_cols, &h1, h->swiglu ? TC5_EPI_SWIGLU : TC5_EPI_GELU, w.hbuf, h->F,
-                         lw.b1)))
+      RowScale rsc{xb_parts > 0 ? w.ssq : nullptr, xb_parts};
+      if ((rc = run_gemm(h, xb_parts > 0 ? w.xb : w.xn, H, lw.w1, T, h->w1_cols, H, 1.f, w.ws_a,
+                         w.ws_a_floats, h->w1_cols, &h1, h->swiglu ? TC5_EPI_SWIGLU : TC5_EPI_GELU,
+                         w.hbuf, h->F, lw.b1, nullptr, 0, 0.0, &rsc)))
         return rc;
+      xb_parts = 0;
       if (h1.S > 0) {
         ProfScope ps(h, NVLLM_K_ACT, (double)T * h->w1_cols * 4 + (double)T * h->F * asz, 0,
                      (double)T * h->w1_cols * 4 * (h1.S - 1));
         LAUNCH(h, launch_act(st, h->adt, T, h->F, h1.p, h1.S, h1.stride, lw.b1, h->swiglu ? 1 : 0,
                              w.hbuf));
       }
-      if ((rc = run_gemm(h, w.hbuf, h->F, lw.w2, T, H, h->F, 1.f, ffn_out, w.ws_b_floats, H, &pf)))
-        return rc;
-      pf.bias = lw.b2;
+      if (!h->parallel && resid_gemm_ok(h, T, H, h->F, h->F)) {
+        Resid rd{m_res, lw.b2, 1};
+        if ((rc = run_gemm(h, w.hbuf, h->F, lw.w2, T, H, h->F, 1.f, ffn_out, w.ws_b_floats, H, &pf, 0,
+                           nullptr, 0, nullptr, nullptr, 0, 0.0, nullptr, &rd)))
+          return rc;
+        xb_parts = h_tiles;
+      } else {
+        if ((rc = run_gemm(h, w.hbuf, h->F, lw.w2, T, H, h->F, 1.f, ffn_out, w.ws_b_floats, H, &pf)))
+          return rc;
+        pf.bias = lw.b2;
+      }
     }
-    pf.m = h->parallel ? (par_scaled ? c.residual_multiplier : 1.f) : m_res;
+    if (pf.p) pf.m = h->parallel ? (par_scaled ? c.residual_multiplier : 1.f) : m_res;
   }
   // final norm on the last token of each sequence only (the reference norms and projects all
   // T rows, generic_model.go:464-470, then keeps row T-1, :595-604)

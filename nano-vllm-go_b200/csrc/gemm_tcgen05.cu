@@ -106,6 +106,42 @@ struct Tc5Sched {
   const uint8_t* g_wbase;
   int g_row_bytes, g_E;
 };
+// the RMSNorm-fold arguments of Tc5Args (kernels.h), as the kernel takes them
+struct Tc5Fuse {
+  const float* rs_ssq;
+  int rs_parts, rs_ld;
+  float rs_inv_h, rs_eps;
+  float* x;
+  bf16* xb;
+  float* ssq;
+  int ssq_ld;
+  const float* bias;
+  float m;
+  unsigned* arrive;
+  unsigned* done;
+};
+__device__ __forceinline__ void named_bar(int id, int n) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// v[c] of every lane -> lane l gets sum over lanes of v[l]  (31 shuffles instead of 32 x 5)
+__device__ __forceinline__ float warp_transpose_sum(float (&v)[32], int lane) {
+#pragma unroll
+  for (int off = 16; off >= 1; off >>= 1) {
+    const bool up = (lane & off) != 0;
+#pragma unroll
+    for (int i = 0; i < off; i++) {
+      const float send = up ? v[i] : v[i + off];
+      const float keep = up ? v[i + off] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+    }
+  }
+  return v[0];
+}
 // rot: CTAs working on the same k range start at different k-blocks (and wrap), so that at any
 // instant they pull DIFFERENT activation tiles out of L2 — otherwise every CTA of a skinny
 // GEMM requests the same 8 KB A tile at the same time and the few L2 slices holding it pace
@@ -148,11 +184,14 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
                 int M, int N, Tc5Sched sc, float* __restrict__ out, int ldo, size_t split_stride,
                 float alpha, int w_reused, int epi, bf16* __restrict__ epi_out, int epi_ld,
                 const float* __restrict__ epi_bias, int prefetch, const uint8_t* __restrict__ pf_ptr,
-                unsigned long long pf_bytes, Trace tr) {
+                unsigned long long pf_bytes, Tc5Fuse fz, Trace tr) {
   const unsigned long long t_entry = trace_on(tr) ? gtime() : 0ull;
   unsigned long long t_wait = 0;
   __shared__ unsigned long long tr_mma, tr_epi0, tr_epi1, tr_x[6];
   __shared__ __align__(16) uint8_t epi_stage[4][32 * 48];
+  __shared__ float rstd_s[2][BT];       // row scales of the unit in flight (double-buffered)
+  __shared__ float ssq_s[2][4][32];     // RESID: per-warp row sums of squares of a 32-token chunk
+  __shared__ float ssq_rows[4][BT];     // RESID, S > 1: per-warp sums of this CTA's token rows
   constexpr uint32_t W_BYTES = TC_BN * TC_BK * 2;
   constexpr uint32_t A_BYTES = BT * TC_BK * 2;
   constexpr uint32_t STAGE_BYTES = W_BYTES + A_BYTES;
@@ -338,6 +377,25 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       const int n0 = t.n0, m0 = t.m0, split = t.split;
       const int M = t.m_end;  // rows past the tile's extent belong to the next expert / are padding
       const int buf = lu & 1;
+      const int et = threadIdx.x - 64;  // 0..127 over the four epilogue warps
+      const float* rs = nullptr;
+      if (fz.rs_ssq) {
+        // folded RMSNorm: 1 / sqrt(mean(x^2) + eps) per token row (tensor.go:211-224), from the
+        // per-column-tile sums the producing GEMM (or the embedding kernel) left; computed while
+        // the MMAs of this unit run
+        float* w = rstd_s[lu & 1];
+        for (int c = et; c < BT; c += 128) {
+          const int mm = m0 + c;
+          float ssum = 0.f;
+          if (mm < M) {
+#pragma unroll 8
+            for (int p = 0; p < fz.rs_parts; p++) ssum += __ldcg(fz.rs_ssq + (size_t)p * fz.rs_ld + mm);
+          }
+          w[c] = 1.0f / sqrtf(ssum * fz.rs_inv_h + fz.rs_eps);
+        }
+        named_bar(1, 128);
+        rs = w;
+      }
       mbar_wait(bar_tfull + 8 * buf, (lu >> 1) & 1);
       tc_fence_after();
       if (tr.buf && warp == 2 && lane == 0) tr_epi0 = gtime();
@@ -351,6 +409,10 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
           if (tr.buf && warp == 2 && lane == 0 && c0 == 0) tr_x[2] = gtime();
+          if (rs) {
+#pragma unroll
+            for (int c = 0; c < 32; c++) r[c] = __float_as_uint(__uint_as_float(r[c]) * rs[c0 + c]);
+          }
           if (n_ok) {
             float* op = obase + (size_t)(m0 + c0) * ldo;
             if (m0 + c0 + 32 <= M) {  // full chunk: straight-line stores, no per-row branch
@@ -379,6 +441,10 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
           if (m0 + c0 >= M) break;
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
+          if (rs) {
+#pragma unroll
+            for (int c = 0; c < 32; c++) r[c] = __float_as_uint(__uint_as_float(r[c]) * rs[c0 + c]);
+          }
 #pragma unroll
           for (int c = 0; c < 16; c++) {
             const float mine = __uint_as_float(odd ? r[c + 16] : r[c]);
@@ -401,6 +467,108 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
           }
           __syncwarp();
         }
+      } else if (epi == TC5_EPI_RESID) {
+        // residual update fused into the projection that feeds it (generic_model.go:359-365,
+        // 383-389: x = x + m * (proj + bias)), plus what the FOLDED RMSNorm of the next
+        // sub-block needs: the row rounded to bf16 and its sum of squares over this column tile
+        const float b = (fz.bias && n_ok) ? fz.bias[n] : 0.f;
+        const int nt = n0 / TC_BN;
+        if (sc.S == 1) {
+          int chunk = 0;
+#pragma unroll 1
+          for (int c0 = 0; c0 < BT; c0 += 32, chunk++) {
+            if (m0 + c0 >= M) break;
+            uint32_t r[32];
+            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
+            float sq[32];
+            const size_t base = (size_t)(m0 + c0) * N + n;
+            if (n_ok && m0 + c0 + 32 <= M) {
+              float xv[32];
+#pragma unroll
+              for (int c = 0; c < 32; c++) xv[c] = fz.x[base + (size_t)c * N];
+#pragma unroll
+              for (int c = 0; c < 32; c++) {
+                const float v = xv[c] + fz.m * (alpha * __uint_as_float(r[c]) + b);
+                fz.x[base + (size_t)c * N] = v;
+                fz.xb[base + (size_t)c * N] = __float2bfloat16_rn(v);
+                sq[c] = v * v;
+              }
+            } else {
+#pragma unroll
+              for (int c = 0; c < 32; c++) {
+                sq[c] = 0.f;
+                if (n_ok && m0 + c0 + c < M) {
+                  const float v = fz.x[base + (size_t)c * N] + fz.m * (alpha * __uint_as_float(r[c]) + b);
+                  fz.x[base + (size_t)c * N] = v;
+                  fz.xb[base + (size_t)c * N] = __float2bfloat16_rn(v);
+                  sq[c] = v * v;
+                }
+              }
+            }
+            const float tot = warp_transpose_sum(sq, lane);  // token c0 + lane over this warp's 32 columns
+            ssq_s[chunk & 1][q][lane] = tot;
+            named_bar(2, 128);
+            if (q == 0 && m0 + c0 + lane < M)
+              fz.ssq[(size_t)nt * fz.ssq_ld + m0 + c0 + lane] =
+                  ((ssq_s[chunk & 1][0][lane] + ssq_s[chunk & 1][1][lane]) + ssq_s[chunk & 1][2][lane]) +
+                  ssq_s[chunk & 1][3][lane];
+          }
+        } else {
+          // (1) this split's partial tile, as TC5_EPI_PARTIAL writes it
+          float* obase = out + (size_t)split * split_stride + n;
+#pragma unroll 1
+          for (int c0 = 0; c0 < BT; c0 += 32) {
+            if (m0 + c0 >= M) break;
+            uint32_t r[32];
+            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
+            if (n_ok) {
+              float* op = obase + (size_t)(m0 + c0) * ldo;
+#pragma unroll
+              for (int c = 0; c < 32; c++)
+                if (m0 + c0 + c < M) op[(size_t)c * ldo] = alpha * __uint_as_float(r[c]);
+            }
+          }
+          // (2) meet the other k-splits of this output tile (all resident: units <= #SM)
+          const int tile_id = (m0 / BT) * sc.n_tiles + nt;
+          __threadfence();
+          named_bar(2, 128);
+          if (et == 0) {
+            atomicAdd(fz.arrive + tile_id, 1u);
+            while (ld_acquire_u32(fz.arrive + tile_id) < (unsigned)sc.S) {
+            }
+          }
+          named_bar(2, 128);
+          // (3) reduce this split's share of the tile's token rows, slices in a fixed order
+          const int valid = min(BT, M - m0);
+          const int per = (valid + sc.S - 1) / sc.S;
+          const int r0 = split * per, r1 = min(valid, r0 + per);
+#pragma unroll 2
+          for (int row = r0; row < r1; row++) {
+            float v = 0.f;
+            if (n_ok) {
+              const size_t o = (size_t)(m0 + row) * ldo + n;
+              float acc = 0.f;
+#pragma unroll 8
+              for (int sp = 0; sp < sc.S; sp++) acc += __ldcg(out + (size_t)sp * split_stride + o);
+              const size_t xi = (size_t)(m0 + row) * N + n;
+              v = fz.x[xi] + fz.m * (acc + b);
+              fz.x[xi] = v;
+              fz.xb[xi] = __float2bfloat16_rn(v);
+            }
+            const float tot = warp_sum(v * v);
+            if (lane == 0) ssq_rows[q][row - r0] = tot;
+          }
+          named_bar(2, 128);
+          for (int i = et; i < r1 - r0; i += 128)
+            fz.ssq[(size_t)nt * fz.ssq_ld + m0 + r0 + i] =
+                ((ssq_rows[0][i] + ssq_rows[1][i]) + ssq_rows[2][i]) + ssq_rows[3][i];
+          if (et == 0) {
+            if (atomicAdd(fz.done + tile_id, 1u) == (unsigned)sc.S - 1) {  // everyone is past the wait
+              fz.arrive[tile_id] = 0;
+              fz.done[tile_id] = 0;
+            }
+          }
+        }
       } else {
         // GELU branch: gelu_tanh(h + b1)   (transformer.go:67-78)
         const float b = (epi_bias && n_ok) ? epi_bias[n] : 0.f;
@@ -410,6 +578,10 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
           if (m0 + c0 >= M) break;
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
+          if (rs) {
+#pragma unroll
+            for (int c = 0; c < 32; c++) r[c] = __float_as_uint(__uint_as_float(r[c]) * rs[c0 + c]);
+          }
           if (n_ok) {
             bf16* op = obase + (size_t)(m0 + c0) * epi_ld;
             if (m0 + c0 + 32 <= M) {
@@ -548,6 +720,18 @@ int tc5_splits(int M, int N, int K, int sm_count) {
   return best;
 }
 
+int tc5_resid_splits(int M, int N, int K, int sm_count) {
+  const int bt = pick_bt(M);
+  const long tiles = (long)ceil_div(N, TC_BN) * ceil_div(M, bt);
+  int S = tc5_splits(M, N, K, sm_count);
+  if (tiles >= sm_count) return 1;
+  while (S > 1 && tiles * S > sm_count) S--;
+  // keep the slice count one the k-blocks divide into without an empty tail slice
+  const int nkb = ceil_div(K, TC_BK);
+  while (S > 1 && ceil_div(nkb, ceil_div(nkb, S)) != S) S--;
+  return S;
+}
+
 bool carveout_known(const void* fn) {
   static std::mutex mu;
   static std::map<std::pair<const void*, int>, bool> seen;
@@ -635,6 +819,13 @@ static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* t
   }
   sc.units = sc.n_tiles * m_tiles * sc.S;
   const int grid = min(sc.units, max(1, sm_counts[dev]));
+  Tc5Fuse fz{a.rs_ssq, a.rs_parts, a.rs_ld, a.rs_inv_h, a.rs_eps, a.res_x, (bf16*)a.res_xb, a.res_ssq,
+             a.res_ssq_ld, a.res_bias, a.res_m, a.res_arrive, a.res_done};
+  if (a.epi == TC5_EPI_RESID) {
+    if (!a.res_x || !a.res_xb || !a.res_ssq || a.g_experts > 0) return cudaErrorInvalidValue;
+    // the k-splits of a tile wait for each other inside the kernel: every unit needs its own SM
+    if (sc.S > 1 && (sc.units > grid || !a.res_arrive || !a.res_done)) return cudaErrorInvalidValue;
+  }
   const bool w_reused = a.g_experts > 0 ? a.M > 2 * BT * a.g_experts : m_tiles > 1;
   return launch_k(gemm_tc5_kernel<BT, STAGES>, dim3(grid), dim3(TC_THREADS), smem, st,
                   *reinterpret_cast<const CUtensorMap*>(tw),
@@ -642,7 +833,7 @@ static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* t
                   a.split_stride, a.alpha, w_reused ? 1 : 0, a.epi, (bf16*)a.epi_out, a.epi_ld,
                   a.epi_bias, prefetch_flags(),
                   (const uint8_t*)((prefetch_flags() & 4) ? nullptr : a.pf_ptr),
-                  (unsigned long long)((prefetch_flags() & 4) ? 0 : a.pf_bytes), next_trace(1));
+                  (unsigned long long)((prefetch_flags() & 4) ? 0 : a.pf_bytes), fz, next_trace(1));
 }
 
 // a.S is the requested number of splits; the number actually written is returned in *S_out
@@ -662,12 +853,14 @@ cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int* S_out) {
   int S = grouped ? 1 : max(1, min(a.S, nkb));
   const int kbps = ceil_div(nkb, S);
   S = ceil_div(nkb, kbps);
-  if (a.epi != TC5_EPI_PARTIAL) {
+  if (a.epi != TC5_EPI_PARTIAL && a.epi != TC5_EPI_RESID) {
     if (!a.epi_out || (a.epi == TC5_EPI_SWIGLU && (a.N & 1))) return cudaErrorInvalidValue;
     S = 1;
   }
   if (S_out) *S_out = S;
-  if (a.epi == TC5_EPI_PARTIAL && a.out_capacity && (size_t)S * a.split_stride > a.out_capacity) return cudaErrorInvalidValue;
+  if ((a.epi == TC5_EPI_PARTIAL || (a.epi == TC5_EPI_RESID && S > 1)) && a.out_capacity &&
+      (size_t)S * a.split_stride > a.out_capacity)
+    return cudaErrorInvalidValue;
   switch (bt) {
     case 32: return launch_bt<32, 10>(st, a, tw, ta, S);
     case 64: {

@@ -55,6 +55,12 @@ struct Workspace {
   void* attn_out = nullptr;  // [T, nh hd]
   void* hbuf = nullptr;      // [T, F] or [T k, I]
   void* xn_last = nullptr;   // [n, H]
+  // folded RMSNorm (forward.cu): the residual stream rounded to bf16, UN-normalised, the
+  // per-column-tile row sums of squares [parts][T_cap] of it, and the arrival / done counters of
+  // the two fused-residual GEMM sites of a layer (O projection, FFN down projection)
+  void* xb = nullptr;
+  float* ssq = nullptr;
+  unsigned* res_ctr = nullptr;  // [2 sites][arrive | done][RES_CTR_TILES]
   float* logits_p = nullptr; // [S][n][ldl]
   float* logits = nullptr;   // [n][ldl]  (tp > 1: [tp][n][Vl], rank-major slices)
   float* tp_buf = nullptr;   // [T, H] fp32 partial sums handed to the all-reduce (tp > 1)
@@ -140,6 +146,10 @@ struct nvllm_handle {
   uint64_t seed = 0, rng_counter = 0;
   int graphs_enabled = 1;
   int use_tc5 = 1;
+  // RMSNorm folded into the GEMMs that consume it: norm weights multiplied into the QKV / W1
+  // weight columns at finalize, the row statistic applied to the accumulators (dense RMSNorm
+  // models, bf16, tp == 1; NVLLM_FOLD=0 switches it off)
+  bool fold = false;
   // accounting
   uint64_t weight_bytes = 0, kv_bytes = 0, ws_bytes = 0;
   int launches = 0;  // kernels launched by the current step

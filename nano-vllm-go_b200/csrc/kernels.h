@@ -24,9 +24,13 @@ constexpr int KV_BLOCK = 256;
 
 // ---------------------------------------------------------------- elementwise.cu
 // x[t,:] = (wte[tok[t],:] (+ wpe[pos[t],:] if wpe && pos < max_pos)) * mult   (mult==0 => 1)
+// xb / ssq (both or neither): also write the row rounded to bf16 and its sum of squares ssq[t]
+// (what a GEMM with a folded RMSNorm reads instead of a normed activation)
 cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int* positions,
                          const void* wte, const void* wpe, int max_pos, float mult, float* x, int T,
-                         int H);
+                         int H, void* xb = nullptr, float* ssq = nullptr);
+// W[r, k] *= g[k] (bf16 weights [rows, K], fp32 g): fold a norm weight into the linear after it
+cudaError_t launch_fold_cols(cudaStream_t st, void* W, size_t rows, int K, const float* g);
 
 struct NormArgs {
   float* x;            // [*, H] residual stream, updated in place when p1/p2 given
@@ -40,7 +44,7 @@ struct NormArgs {
   size_t stride2;
   float m2;
   const float* bias2;
-  const float* w;      // [H]
+  const float* w;      // [H]; null = all ones (the weight is folded into the next GEMM)
   const float* b;      // [H] or null => RMSNorm (tensor.go:197)
   float eps;
   void* y;             // [n_rows, H] dtype ydt (may be null: residual update only)
@@ -190,6 +194,28 @@ struct Tc5Args {
   void* epi_out;        // bf16 [M, epi_ld]
   int epi_ld;
   const float* epi_bias;  // [N] or null (GELU)
+  // ---- RMSNorm folded into the GEMMs (forward.cu "fold"): the norm weight lives in W, the
+  // row statistic is applied to the accumulator instead of the activations.
+  // consumer side, rs_ssq != null: A holds the UN-normalised residual stream (bf16) and every
+  // accumulator row m is multiplied by 1 / sqrt(sum_p rs_ssq[p * rs_ld + m] * rs_inv_h + rs_eps)
+  // before the epilogue proper (partials, SwiGLU, GELU)
+  const float* rs_ssq;
+  int rs_parts, rs_ld;
+  float rs_inv_h, rs_eps;
+  // producer side, epi == TC5_EPI_RESID (N = hidden size): x[m, n] += res_m * (acc + res_bias[n])
+  // in place (fp32), the same value rounded to bf16 into res_xb, and the row's sum of squares
+  // over this CTA's 128 columns into res_ssq[n_tile * res_ssq_ld + m] — the next GEMM's rs_ssq.
+  // With S > 1 the split-K slices go through `out` as usual and the CTAs of one output tile
+  // meet at res_arrive[tile] (all co-resident: units <= #SM is required), then each reduces its
+  // share of the tile's token rows; res_done re-arms the counters.
+  float* res_x;
+  void* res_xb;
+  float* res_ssq;
+  int res_ssq_ld;
+  const float* res_bias;
+  float res_m;
+  unsigned* res_arrive;  // [n_tiles * m_tiles], zero between launches
+  unsigned* res_done;
   // weights of a later GEMM to pull into L2 while this one waits / drains (decode only)
   const void* pf_ptr;
   size_t pf_bytes;
@@ -204,7 +230,10 @@ struct Tc5Args {
   const int* g_tile_rows;
   const int* g_n_tiles;  // [1] on the device
 };
-enum { TC5_EPI_PARTIAL = 0, TC5_EPI_SWIGLU = 1, TC5_EPI_GELU = 2 };
+enum { TC5_EPI_PARTIAL = 0, TC5_EPI_SWIGLU = 1, TC5_EPI_GELU = 2, TC5_EPI_RESID = 3 };
+// split-K slices for a TC5_EPI_RESID GEMM: like tc5_splits, but every unit must own an SM
+// (the CTAs of a tile wait for each other); 0 = the shape cannot take the fused epilogue
+int tc5_resid_splits(int M, int N, int K, int sm_count);
 // token-tile rows for a grouped GEMM averaging `rows_per_expert` rows per expert
 int tc5_group_tile(int rows_per_expert);
 bool tc5_supported(int M, int N, int K);
