@@ -136,6 +136,8 @@ __global__ void __launch_bounds__(512) norm_kernel(NormArgs a, Trace tr) {
               for (int j = 0; j < 8; j++) acc[j] += cw[q] * pv[q][j];
             }
         }
+      } else if (a.p1_bf16) {
+        load8(reinterpret_cast<const bf16*>(a.p1) + (size_t)r * H + i, acc);
       } else {
         sum_partials8(a.p1 + (size_t)r * H + i, a.S1, a.stride1, acc);
       }

@@ -237,6 +237,7 @@ struct Pending {  // a GEMM result still to be added to the residual stream
   size_t stride = 0;
   float m = 1.f;
   const float* bias = nullptr;
+  bool bf16 = false;  // p is one bf16 slice (all-reduced over the tensor-parallel ranks)
   // mixture-of-experts: p holds the expert outputs by sorted row; the addend of token r is
   // sum_s comb_w[r, s] * p[comb_rows[r, s], :]  (fused into the consuming norm kernel)
   const int* comb_rows = nullptr;
@@ -363,7 +364,12 @@ static bool fold_gemm_ok(const nvllm_handle* h, int M, int N, int K, int lda) {
 }
 static bool resid_gemm_ok(const nvllm_handle* h, int M, int N, int K, int lda) {
   if (!fold_gemm_ok(h, M, N, K, lda) || N != h->H) return false;
-  return tc5_resid_splits(M, N, K, h->sm_count) >= 1;  // S > 1 implies tiles < #SM <= RES_CTR_TILES
+  // Split-K shapes (decode batches) keep the norm kernel by default: the in-kernel meeting of a
+  // tile's k-splits costs more than the norm launch it removes (measured on cfg2 decode: 1086 ->
+  // 1432 us/step with the first version of the reduce).  NVLLM_RESID_SPLITK=1 turns it on.
+  static const bool splitk = getenv("NVLLM_RESID_SPLITK") && atoi(getenv("NVLLM_RESID_SPLITK")) != 0;
+  const int S = tc5_resid_splits(M, N, K, h->sm_count);
+  return splitk ? S >= 1 : (S == 1 && tc5_splits(M, N, K, h->sm_count) == 1);
 }
 
 static int run_norm(nvllm_handle* h, float* x, Pending* p1, Pending* p2, const float* w,
@@ -375,6 +381,7 @@ static int run_norm(nvllm_handle* h, float* x, Pending* p1, Pending* p2, const f
   double bytes = (double)n_rows * h->H * (4 + dt_size(h->adt)), impl = 0.0;
   if (p1 && p1->p) {
     a.p1 = p1->p; a.S1 = p1->S; a.stride1 = p1->stride; a.m1 = p1->m; a.bias1 = p1->bias;
+    a.p1_bf16 = p1->bf16 ? 1 : 0;
     a.comb_rows = p1->comb_rows; a.comb_w = p1->comb_w; a.comb_k = p1->comb_k;
     bytes += (double)n_rows * h->H * 4 * 2;
     impl += (double)n_rows * h->H * 4 * ((p1->comb_rows ? p1->comb_k : p1->S) - 1);
@@ -410,10 +417,16 @@ static int tp_reduce_pending(nvllm_handle* h, Pending* p1, Pending* p2, int T) {
   if (!a) { a = b; b = nullptr; }
   if (!a) return NVLLM_OK;
   Workspace& w = h->ws;
+  // large (prefill) messages travel as bf16 in bf16 mode: half the bytes of the exposed
+  // all-reduce; the sum over ranks of the per-rank addends is rounded once more, the residual
+  // stream itself stays fp32.  NVLLM_TP_BF16=0 keeps fp32 on the wire.
+  static const bool wire_bf16_ok = !(getenv("NVLLM_TP_BF16") && atoi(getenv("NVLLM_TP_BF16")) == 0);
+  const bool p2p = tp_p2p_fits(h, (size_t)T * h->H);
+  const bool wire_bf16 = !p2p && wire_bf16_ok && h->adt == DT_BF16 && ((size_t)T * h->H % 8) == 0;
   {
     const double n = (double)T * h->H * 4;
-    ProfScope ps(h, NVLLM_K_COMM, n * (a->S + (b ? b->S : 0) + 1) + 2.0 * n, 0);
-    if (tp_p2p_fits(h, (size_t)T * h->H)) {
+    ProfScope ps(h, NVLLM_K_COMM, (wire_bf16 ? 1.0 : 2.0) * n, 0, n * (a->S + (b ? b->S : 0) + 1));
+    if (p2p) {
       // one kernel: partial sums + all-reduce over NVLink peer memory (tp.cu)
       LAUNCH(h, launch_tp_allreduce_p2p(h, T, h->H, a->p, a->S, a->stride, a->m, a->bias,
                                         b ? b->p : nullptr, b ? b->S : 0, b ? b->stride : 0,
@@ -421,8 +434,8 @@ static int tp_reduce_pending(nvllm_handle* h, Pending* p1, Pending* p2, int T) {
     } else {
       LAUNCH(h, launch_tp_partial(h->stream, T, h->H, a->p, a->S, a->stride, a->m, a->bias,
                                   b ? b->p : nullptr, b ? b->S : 0, b ? b->stride : 0,
-                                  b ? b->m : 0.f, b ? b->bias : nullptr, w.tp_buf));
-      int rc = tp_all_reduce_f32(h, w.tp_buf, (size_t)T * h->H);
+                                  b ? b->m : 0.f, b ? b->bias : nullptr, w.tp_buf, wire_bf16));
+      int rc = tp_all_reduce(h, w.tp_buf, (size_t)T * h->H, wire_bf16);
       if (rc) return rc;
       h->launches++;
     }
@@ -431,6 +444,7 @@ static int tp_reduce_pending(nvllm_handle* h, Pending* p1, Pending* p2, int T) {
   if (p2) *p2 = Pending();
   Pending& o = p1 ? *p1 : *p2;
   o.p = w.tp_buf; o.S = 1; o.stride = 0; o.m = 1.f; o.bias = nullptr;
+  o.bf16 = wire_bf16;
   return NVLLM_OK;
 }
 

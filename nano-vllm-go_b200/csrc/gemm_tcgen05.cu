@@ -191,7 +191,6 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   __shared__ __align__(16) uint8_t epi_stage[4][32 * 48];
   __shared__ float rstd_s[2][BT];       // row scales of the unit in flight (double-buffered)
   __shared__ float ssq_s[2][4][32];     // RESID: per-warp row sums of squares of a 32-token chunk
-  __shared__ float ssq_rows[4][BT];     // RESID, S > 1: per-warp sums of this CTA's token rows
   constexpr uint32_t W_BYTES = TC_BN * TC_BK * 2;
   constexpr uint32_t A_BYTES = BT * TC_BK * 2;
   constexpr uint32_t STAGE_BYTES = W_BYTES + A_BYTES;
@@ -538,30 +537,53 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
             }
           }
           named_bar(2, 128);
-          // (3) reduce this split's share of the tile's token rows, slices in a fixed order
+          // (3) reduce this split's share of the tile's token rows, slices in a fixed order.
+          // One warp-iteration covers one token row of the tile (32 lanes x float4 = 128
+          // columns), all its loads are issued together, and the warp sum IS the row's sum of
+          // squares over this column tile: no cross-warp step.
           const int valid = min(BT, M - m0);
           const int per = (valid + sc.S - 1) / sc.S;
           const int r0 = split * per, r1 = min(valid, r0 + per);
-#pragma unroll 2
-          for (int row = r0; row < r1; row++) {
-            float v = 0.f;
-            if (n_ok) {
-              const size_t o = (size_t)(m0 + row) * ldo + n;
-              float acc = 0.f;
-#pragma unroll 8
-              for (int sp = 0; sp < sc.S; sp++) acc += __ldcg(out + (size_t)sp * split_stride + o);
-              const size_t xi = (size_t)(m0 + row) * N + n;
-              v = fz.x[xi] + fz.m * (acc + b);
-              fz.x[xi] = v;
-              fz.xb[xi] = __float2bfloat16_rn(v);
+          const int ncol = n0 + lane * 4;
+          const bool c_ok = ncol + 3 < N;  // N % 4 == 0 is checked by the launcher
+          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (fz.bias && c_ok) b4 = *reinterpret_cast<const float4*>(fz.bias + ncol);
+          for (int row = r0 + q; row < r1; row += 4) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c_ok) {
+              const size_t o = (size_t)(m0 + row) * ldo + ncol;
+              const size_t xi = (size_t)(m0 + row) * N + ncol;
+              const float4 xv = __ldcg(reinterpret_cast<const float4*>(fz.x + xi));
+              float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (sc.S <= 8) {
+                float4 pz[8];
+#pragma unroll
+                for (int sp = 0; sp < 8; sp++)
+                  if (sp < sc.S) pz[sp] = __ldcg(reinterpret_cast<const float4*>(out + (size_t)sp * split_stride + o));
+#pragma unroll
+                for (int sp = 0; sp < 8; sp++)
+                  if (sp < sc.S) { acc.x += pz[sp].x; acc.y += pz[sp].y; acc.z += pz[sp].z; acc.w += pz[sp].w; }
+              } else {
+                for (int sp = 0; sp < sc.S; sp++) {
+                  const float4 pv = __ldcg(reinterpret_cast<const float4*>(out + (size_t)sp * split_stride + o));
+                  acc.x += pv.x; acc.y += pv.y; acc.z += pv.z; acc.w += pv.w;
+                }
+              }
+              v.x = xv.x + fz.m * (acc.x + b4.x);
+              v.y = xv.y + fz.m * (acc.y + b4.y);
+              v.z = xv.z + fz.m * (acc.z + b4.z);
+              v.w = xv.w + fz.m * (acc.w + b4.w);
+              *reinterpret_cast<float4*>(fz.x + xi) = v;
+              __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+              uint2 pk;
+              pk.x = *reinterpret_cast<uint32_t*>(&lo);
+              pk.y = *reinterpret_cast<uint32_t*>(&hi);
+              *reinterpret_cast<uint2*>(fz.xb + xi) = pk;
             }
-            const float tot = warp_sum(v * v);
-            if (lane == 0) ssq_rows[q][row - r0] = tot;
+            const float tot = warp_sum((v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w));
+            if (lane == 0) fz.ssq[(size_t)nt * fz.ssq_ld + m0 + row] = tot;
           }
           named_bar(2, 128);
-          for (int i = et; i < r1 - r0; i += 128)
-            fz.ssq[(size_t)nt * fz.ssq_ld + m0 + r0 + i] =
-                ((ssq_rows[0][i] + ssq_rows[1][i]) + ssq_rows[2][i]) + ssq_rows[3][i];
           if (et == 0) {
             if (atomicAdd(fz.done + tile_id, 1u) == (unsigned)sc.S - 1) {  // everyone is past the wait
               fz.arrive[tile_id] = 0;
@@ -824,7 +846,8 @@ static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* t
   if (a.epi == TC5_EPI_RESID) {
     if (!a.res_x || !a.res_xb || !a.res_ssq || a.g_experts > 0) return cudaErrorInvalidValue;
     // the k-splits of a tile wait for each other inside the kernel: every unit needs its own SM
-    if (sc.S > 1 && (sc.units > grid || !a.res_arrive || !a.res_done)) return cudaErrorInvalidValue;
+    if (sc.S > 1 && (sc.units > grid || !a.res_arrive || !a.res_done || (a.N & 3) || (a.ldo & 3)))
+      return cudaErrorInvalidValue;
   }
   const bool w_reused = a.g_experts > 0 ? a.M > 2 * BT * a.g_experts : m_tiles > 1;
   return launch_k(gemm_tc5_kernel<BT, STAGES>, dim3(grid), dim3(TC_THREADS), smem, st,

@@ -234,7 +234,7 @@ int set_weight_src(nvllm_handle* h, int id, int layer, int dtype, const void* ho
 int tp_unique_id(uint8_t out_id[128]);
 int tp_init(nvllm_handle* h, const uint8_t* id);  // ncclCommInitRank(tp, id, rank)
 void tp_destroy(nvllm_handle* h);
-int tp_all_reduce_f32(nvllm_handle* h, float* buf, size_t count);           // in place, sum
+int tp_all_reduce(nvllm_handle* h, void* buf, size_t count, bool bf16_wire);  // in place, sum
 // peer-memory path: true when the fused partial-sum + all-reduce kernel can take T x H floats
 bool tp_p2p_fits(const nvllm_handle* h, size_t count);
 cudaError_t launch_tp_allreduce_p2p(nvllm_handle* h, int T, int H, const float* p1, int S1,

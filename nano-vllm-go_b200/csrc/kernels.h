@@ -35,6 +35,7 @@ cudaError_t launch_fold_cols(cudaStream_t st, void* W, size_t rows, int K, const
 struct NormArgs {
   float* x;            // [*, H] residual stream, updated in place when p1/p2 given
   const float* p1;     // partials [S1][rows_total][H] or null
+  int p1_bf16;         // p1 is ONE slice of bf16 (a tensor-parallel all-reduce result)
   int S1;
   size_t stride1;      // elements between slices
   float m1;            // x += m1 * (sum_s p1 + bias1)
@@ -136,9 +137,10 @@ cudaError_t launch_fill(cudaStream_t st, float* p, size_t n, float v);
 // ---------------------------------------------------------------- tp.cu
 // out[t,:] = m1 * (sum_s p1 + bias1) + m2 * (sum_s p2 + bias2): a rank's share of a residual
 // update, summed over ranks by the all-reduce that follows (p2 may be null)
+// out_bf16: the addend goes on the wire as bf16 (half the all-reduce bytes of a prefill step)
 cudaError_t launch_tp_partial(cudaStream_t st, int T, int H, const float* p1, int S1, size_t stride1,
                               float m1, const float* bias1, const float* p2, int S2, size_t stride2,
-                              float m2, const float* bias2, float* out);
+                              float m2, const float* bias2, void* out, bool out_bf16 = false);
 
 // ---------------------------------------------------------------- gemm_simt.cu
 struct GemmArgs {

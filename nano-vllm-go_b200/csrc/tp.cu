@@ -199,9 +199,10 @@ void tp_destroy(nvllm_handle* h) {
   h->nccl = nullptr;
 }
 
-int tp_all_reduce_f32(nvllm_handle* h, float* buf, size_t count) {
+int tp_all_reduce(nvllm_handle* h, void* buf, size_t count, bool bf16_wire) {
   NcclApi* a = nccl_api();
-  ncclResult_t r = a->AllReduce(buf, buf, count, ncclFloat32, ncclSum, (ncclComm_t)h->nccl, h->stream);
+  ncclResult_t r = a->AllReduce(buf, buf, count, bf16_wire ? ncclBfloat16 : ncclFloat32, ncclSum,
+                                (ncclComm_t)h->nccl, h->stream);
   if (r != ncclSuccess)
     return set_err(h, NVLLM_ERR_NCCL, "ncclAllReduce: %s", a->GetErrorString(r));
   return NVLLM_OK;
@@ -455,10 +456,11 @@ tp_allreduce_p2p_kernel(P2PPeers peers, int tp, int me, size_t cap, uint32_t epo
 //   out[t, :] = m1 * (sum_s p1[s][t, :] + bias1) + m2 * (sum_s p2[s][t, :] + bias2)
 // (generic_model.go:320-326 / :359-365 / :405-416 — the update itself is applied by the norm
 // kernel after the all-reduce.)  Row-parallel biases are zero on ranks other than 0.
+template <typename OT>
 __global__ void tp_partial_kernel(size_t n8, int H, const float* __restrict__ p1, int S1,
                                   size_t stride1, float m1, const float* __restrict__ bias1,
                                   const float* __restrict__ p2, int S2, size_t stride2, float m2,
-                                  const float* __restrict__ bias2, float* __restrict__ out) {
+                                  const float* __restrict__ bias2, OT* __restrict__ out) {
   pdl_launch_dependents();
   pdl_wait();
   for (size_t v = (size_t)blockIdx.x * blockDim.x + threadIdx.x; v < n8;
@@ -506,12 +508,15 @@ __global__ void tp_partial_kernel(size_t n8, int H, const float* __restrict__ p1
 
 cudaError_t launch_tp_partial(cudaStream_t st, int T, int H, const float* p1, int S1, size_t stride1,
                               float m1, const float* bias1, const float* p2, int S2, size_t stride2,
-                              float m2, const float* bias2, float* out) {
+                              float m2, const float* bias2, void* out, bool out_bf16) {
   const size_t n8 = (size_t)T * H / 8;
   if (!n8) return cudaSuccess;
   const int blocks = (int)std::min<size_t>((size_t)148 * 8, (n8 + 255) / 256);
-  return launch_k(tp_partial_kernel, dim3(blocks), dim3(256), 0, st, n8, H, p1, S1, stride1, m1,
-                  bias1, p2, S2, stride2, m2, bias2, out);
+  if (out_bf16)
+    return launch_k(tp_partial_kernel<bf16>, dim3(blocks), dim3(256), 0, st, n8, H, p1, S1, stride1,
+                    m1, bias1, p2, S2, stride2, m2, bias2, (bf16*)out);
+  return launch_k(tp_partial_kernel<float>, dim3(blocks), dim3(256), 0, st, n8, H, p1, S1, stride1, m1,
+                  bias1, p2, S2, stride2, m2, bias2, (float*)out);
 }
 
 // NVLLM_TP_TWOSHOT=1 routes EVERY size through the two-shot peer-memory kernel (experiments and
