@@ -236,10 +236,29 @@ class Job:
         return h2d, d2h, tok
 
 
-def make_runner(cfg, job, device, keep_host=None, tp_size=1, tp_rank=0, tp_id=None):
+def device_random_weights(cfg, device, seed=1234):
+    """Random-init weights of the same distributions as W.random_weights, drawn on the GPU and
+    handed over as bf16 bit patterns (uint16): a 7 B model takes seconds instead of minutes of
+    host RNG.  Every rank of a tensor-parallel group draws the SAME full tensors (same Philox
+    seed per tensor).  Not bit-equal to the host generator: used where no CPU oracle is run on
+    the same weights (the full-depth Falcon-7B timing)."""
+    import torch
+    g = torch.Generator(device=f"cuda:{device}")
+    for wid, layer, shape, std, mean in W.weight_specs(cfg):
+        g.manual_seed((seed * 1000003 + wid * 7919 + (layer + 1) * 104729) & 0x7FFFFFFF)
+        t = torch.empty(shape, dtype=torch.float32, device=f"cuda:{device}")
+        t.normal_(mean, std, generator=g)
+        yield wid, layer, t.to(torch.bfloat16).view(torch.int16).cpu().numpy().view(np.uint16)
+        del t
+
+
+def make_runner(cfg, job, device, keep_host=None, tp_size=1, tp_rank=0, tp_id=None, fast_weights=False):
     R = nvllm_pkg.sub("runner")
 
     def gen():
+        if fast_weights:
+            yield from device_random_weights(cfg, device)
+            return
         for wid, layer, a in W.random_weights(cfg, 1234, round_bf16=True):
             if keep_host is not None:
                 keep_host.append((wid, layer, a))
@@ -248,7 +267,8 @@ def make_runner(cfg, job, device, keep_host=None, tp_size=1, tp_rank=0, tp_id=No
     max_T = max(len(g) for g in job.prefill_steps) * job.P
     return R.CudaModelRunner(cfg, gen(), precision=C.PREC_BF16, num_kv_blocks=job.num_blocks,
                              device=device, max_num_seqs=job.n, max_batched_tokens=max_T,
-                             weight_dtype=C.DT_BF16, tp_size=tp_size, tp_rank=tp_rank, tp_id=tp_id,
+                             weight_dtype=None if fast_weights else C.DT_BF16, tp_size=tp_size,
+                             tp_rank=tp_rank, tp_id=tp_id,
                              sampling=None)  # greedy rows: the job is BASELINE's greedy decode
 
 
@@ -302,6 +322,108 @@ def gpu_parity(run, ref):
                        "(full-size model, free-running greedy)"}
 
 
+def tp_leg(dist, rank, world, device, steps, warmup, barrier):
+    """BASELINE.json configs[3] on ALL ranks of this launch as ONE tensor-parallel group (tp =
+    world; tp = 1 is the anchor of the strong-scaling curve): Falcon-7B bf16, full depth, one
+    2048-token prompt + 32 greedy decode steps, random-init weights drawn on the device.  Then
+    the parity check the single-GPU test-suite cannot run at tp > 1: a 2-layer full-width
+    Falcon-7B (host-generated, bf16-rounded weights) against the CPU oracle on rank 0."""
+    from dataclasses import replace
+    D = nvllm_pkg.sub("dist")
+    spec = CONFIGS[4]
+    cfg = C.PRESETS[spec["model"]]()
+    need = spec["prompt_len"] + spec["decode_steps"] + 1
+    if cfg.max_seq_len < need:
+        cfg = replace(cfg, max_seq_len=need + 31)
+    tp = world
+    tp_id = D.share_tp_id(dist, rank, nvllm_pkg.sub("lib").tp_unique_id) if tp > 1 else None
+    job = Job(cfg, spec["batch"], spec["prompt_len"], spec["decode_steps"], seed0=4321)
+    t0 = time.perf_counter()
+    run = make_runner(cfg, job, device, None, tp_size=tp, tp_rank=rank if tp > 1 else 0, tp_id=tp_id,
+                      fast_weights=True)
+    load_s = time.perf_counter() - t0
+    run.set_speculation(False)
+    job.stage(run)
+    for _ in range(warmup):
+        job.run_resident(run)
+    run.sync()
+    barrier()
+    run.timer_start()
+    for _ in range(steps):
+        job.run_resident(run)
+    ms = D.reduce_max(dist, run.timer_stop(), f"cuda:{device}")
+    barrier()
+    # phase times (un-instrumented) and the communication share (events around every launch:
+    # the only instrument that sees the NCCL calls; serialised, so shares not absolutes)
+    job.stage(run)
+    run.sync()
+    barrier()
+    run.timer_start()
+    run.rerun()
+    t_prefill = D.reduce_max(dist, run.timer_stop(), f"cuda:{device}")
+    run.timer_start()
+    for _ in range(job.D):
+        run.run_resident()
+    t_decode = D.reduce_max(dist, run.timer_stop(), f"cuda:{device}")
+    job.stage(run)
+    run.set_profile(1)
+    run.rerun()
+    pp = run.get_profile()
+    run.set_profile(1)
+    for _ in range(job.D):
+        run.run_resident()
+    pd = run.get_profile()
+    run.set_profile(0)
+    run.close()
+    out = {"config": f"{cfg.name} bf16, {spec['label']}", "tp": tp, "scaling": "strong",
+           "value": job.tokens_per_step * steps / (ms / 1e3), "unit": "tokens/s",
+           "ms_per_step": ms / steps, "steps": steps,
+           "prefill_tok_s": job.P / (t_prefill / 1e3), "decode_tok_s": job.D / (t_decode / 1e3),
+           "prefill_ms": t_prefill, "decode_ms": t_decode, "weights_load_s": load_s,
+           "prefill_gemm_TFLOPs_per_rank": (pp["gemm_tc5"]["flops"] / (pp["gemm_tc5"]["ms"] * 1e9))
+           if "gemm_tc5" in pp else None}
+    if tp > 1 and "comm" in pp:
+        tot = sum(e["ms"] for e in pp.values())
+        c = pp["comm"]
+        algbw = c["bytes"] / (c["ms"] * 1e6)
+        out.update({"comm_ms": c["ms"] * t_prefill / tot, "comm_share": c["ms"] / tot,
+                    "comm_calls": c["launches"], "wire_MB_per_call": c["bytes"] / c["launches"] / 1e6,
+                    "busbw_GBs": algbw * 2 * (tp - 1) / tp,
+                    "decode_comm_share": pd["comm"]["ms"] / sum(e["ms"] for e in pd.values())
+                    if "comm" in pd else None,
+                    "comm_note": "shares from the per-launch event pass (serialised); comm_ms = "
+                                 "share x the un-instrumented prefill time"})
+    # ---- parity at tp = world: 2 layers at full width against the oracle
+    cfg2 = replace(cfg, num_layers=2)
+    ws = list(W.random_weights(cfg2, 1234, round_bf16=True))
+    R = nvllm_pkg.sub("runner")
+    tp_id2 = D.share_tp_id(dist, rank, nvllm_pkg.sub("lib").tp_unique_id) if tp > 1 else None
+    r2 = R.CudaModelRunner(cfg2, ws, precision=C.PREC_BF16, num_kv_blocks=4, device=device,
+                           weight_dtype=C.DT_BF16, tp_size=tp, tp_rank=rank if tp > 1 else 0,
+                           tp_id=tp_id2, sampling=None)
+    prompt = [int(t) for t in W.random_prompt(cfg2.vocab_size, 16, 4321)]
+    toks, got = list(prompt), []
+    n_steps = 4
+    for i in range(n_steps):
+        o, lg = r2.run_flat([toks], i == 0, [0], [[0]], [0.0], want_logits=True)
+        got.append((int(o[0]), lg[0].copy()))
+        toks.append(int(o[0]))
+    r2.close()
+    if rank == 0:
+        from oracle import oracle as O
+        m = O.OracleModel(cfg2, ws)
+        ref_toks, ref_logits = m.greedy(np.asarray(prompt, dtype=np.int32), n_steps)
+        worst = max(float(np.abs(got[i][1] - ref_logits[i]).max() / np.abs(ref_logits[i]).max())
+                    for i in range(n_steps))
+        out["parity"] = {"max_rel_err": worst, "tolerance": 2e-2, "within_tolerance": bool(worst <= 2e-2),
+                         "tokens_equal": bool(all(got[i][0] == int(ref_toks[i]) for i in range(n_steps))),
+                         "steps": n_steps, "prompt_tokens": len(prompt),
+                         "against": "oracle/nvllm_oracle.c, Falcon-7B width, 2 of 32 layers, same "
+                                    "bf16-rounded weights"}
+    barrier()
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -317,6 +439,8 @@ def main():
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-profile", action="store_true")
+    ap.add_argument("--no-tp", action="store_true",
+                    help="skip the Falcon-7B tensor-parallel leg (configs[3] at tp = --gpus)")
     args = ap.parse_args()
 
     D = nvllm_pkg.sub("dist")
@@ -384,7 +508,8 @@ def main():
     # replicas draw disjoint request sets; the ranks of a tensor-parallel group share one
     job = Job(cfg, spec["batch"], spec["prompt_len"], spec["decode_steps"],
               seed0=D.request_seed(4321, rank, tp), shared_prefix=spec["shared_prefix"])
-    keep = [] if (rank == 0 and not args.no_cpu_baseline) else None
+    # cpu_baseline (and the oracle parity it enables) on rank 0 at N = 1 only
+    keep = [] if (rank == 0 and world == 1 and not args.no_cpu_baseline) else None
     tp_id = None
     if tp > 1:
         tp_id = D.share_tp_id(dist, rank, nvllm_pkg.sub("lib").tp_unique_id)
@@ -539,12 +664,20 @@ def main():
         del _m
         if tp == 1:
             parity = gpu_parity(run, r)
-        run.close()
         cpu = {"value": r["tokens"] / r["seconds"], "unit": "tokens/s", "cores": 1, "kind": "port",
                "sample": f"1 sequence, {r['prefill_tokens']}-token prefill + {r['decode_tokens']} decode "
                          f"steps, full-size {cfg.name} (bf16-rounded weights as fp32)",
                "prefill_tok_s": r["prefill_tok_s"], "decode_tok_s": r["decode_tok_s"],
                "host_cores": os.cpu_count()}
+    run.close()
+    del keep
+    # the one config whose path shards with a collective: Falcon-7B at tp = N, every N incl. 1
+    tp_line = None
+    if args.config == 2 and not args.no_tp and args.model is None:
+        try:
+            tp_line = tp_leg(dist, rank, world, device, max(2, min(args.steps, 5)), 3, barrier)
+        except Exception as ex:  # the headline line must survive a failure of the extra leg
+            tp_line = {"error": f"{type(ex).__name__}: {ex}"[:400]}
     if rank == 0:
         line = {"metric": metric, "value": value, "unit": "tokens/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
@@ -555,7 +688,7 @@ def main():
                         "speculative_next_step": {"value": e2e_spec, "unit": "tokens/s",
                                                   "h2d_bytes_per_step": h2d_spec // args.steps}},
                 "gpu_launches": launches, "roofline": roofline, "cpu_baseline": cpu,
-                "parity": parity,
+                "parity": parity, "tp": tp_line,
                 "phases": phases, "kernels": kernels, "memory": mem}
         print(json.dumps(line))
     if dist is not None:

@@ -374,9 +374,21 @@ static bool resid_gemm_ok(const nvllm_handle* h, int M, int N, int K, int lda) {
 
 static int run_norm(nvllm_handle* h, float* x, Pending* p1, Pending* p2, const float* w,
                     const float* b, void* y, float* y_f32, const int* row_idx, int n_rows,
-                    const RouterArgs* route = nullptr) {
+                    const RouterArgs* route = nullptr, const void* pf_ptr = nullptr,
+                    size_t pf_bytes = 0) {
   NormArgs a{};
   a.x = x;
+  // Experiment, OFF by default (NVLLM_NORM_PF=1): a decode-sized norm is latency-bound and leaves
+  // HBM idle, so it could pull the next GEMM's weights into L2.  Measured on cfg2 decode: the
+  // GEMMs gain 175 -> 168.5 ms but the norm CTAs stay resident until their bulk prefetches
+  // drain, 49 -> 130 ms (1130 -> 1440 us/step).
+  static const bool pf_on = getenv("NVLLM_NORM_PF") && atoi(getenv("NVLLM_NORM_PF")) != 0;
+  static const size_t pf_max = getenv("NVLLM_NORM_PF_MB") ? (size_t)atol(getenv("NVLLM_NORM_PF_MB")) << 20
+                                                           : (size_t)32 << 20;
+  if (pf_on && pf_ptr && n_rows <= 256 && h->wdt == DT_BF16) {
+    a.pf_ptr = pf_ptr;
+    a.pf_bytes = std::min(pf_bytes, pf_max);
+  }
   // algorithmic: x in, y out, and (when a GEMM result is pending) that result once + x back
   double bytes = (double)n_rows * h->H * (4 + dt_size(h->adt)), impl = 0.0;
   if (p1 && p1->p) {
@@ -530,7 +542,8 @@ int forward_step(nvllm_handle* h) {
         return rc;
     } else {
       if ((rc = run_norm(h, w.x, &p1, &p2, h->fold ? nullptr : lw.attn_norm_w, lw.attn_norm_b, w.xn,
-                         nullptr, nullptr, T)))
+                         nullptr, nullptr, T, nullptr, lw.wqkv,
+                         (size_t)h->qkv_cols * H * dt_size(h->wdt))))
         return rc;
       if ((rc = run_gemm(h, w.xn, H, lw.wqkv, T, h->qkv_cols, H, 1.f, w.ws_a, w.ws_a_floats,
                          h->qkv_cols, &qkv)))
@@ -594,7 +607,9 @@ int forward_step(nvllm_handle* h) {
       const bool skip_norm = xb_parts > 0 && !h->moe && fold_gemm_ok(h, T, h->w1_cols, H, H);
       if (!skip_norm) {
         if ((rc = run_norm(h, w.x, &p1, nullptr, h->fold ? nullptr : lw.ffn_norm_w, lw.ffn_norm_b,
-                           w.xn, nullptr, nullptr, T, &ra)))
+                           w.xn, nullptr, nullptr, T, &ra, h->moe ? lw.moe_in : lw.w1,
+                           h->moe ? (size_t)h->E * 2 * h->F * H * dt_size(h->wdt)
+                                  : (size_t)h->w1_cols * H * dt_size(h->wdt))))
           return rc;
         xb_parts = 0;
       }
@@ -708,7 +723,8 @@ int forward_step(nvllm_handle* h) {
   // final norm on the last token of each sequence only (the reference norms and projects all
   // T rows, generic_model.go:464-470, then keeps row T-1, :595-604)
   if ((rc = tp_reduce_pending(h, &p1, &p2, T))) return rc;
-  if ((rc = run_norm(h, w.x, &p1, &p2, h->lnf_w, h->lnf_b, w.xn_last, nullptr, d + L.last_row, n)))
+  if ((rc = run_norm(h, w.x, &p1, &p2, h->lnf_w, h->lnf_b, w.xn_last, nullptr, d + L.last_row, n,
+                     nullptr, h->lm_head, (size_t)(h->tp > 1 ? h->Vl_valid : h->V) * H * dt_size(h->wdt))))
     return rc;
   const float alpha = (c.logits_scaling != 0.f) ? 1.0f / c.logits_scaling : 1.f;
   Pending lg;

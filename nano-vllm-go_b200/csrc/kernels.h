@@ -45,6 +45,10 @@ struct NormArgs {
   size_t stride2;
   float m2;
   const float* bias2;
+  // weights the NEXT GEMM will stream, pulled into L2 while this (latency-bound, HBM-idle)
+  // kernel waits for its dependency: decode-sized steps only
+  const void* pf_ptr;
+  size_t pf_bytes;
   const float* w;      // [H]; null = all ones (the weight is folded into the next GEMM)
   const float* b;      // [H] or null => RMSNorm (tensor.go:197)
   float eps;
