@@ -165,7 +165,8 @@ static cudaError_t prefill_dispatch(cudaStream_t st, const AttnArgs& a) {
 }
 
 int attn_prefill_qtile(int qdt, int kvdt, int hd) {
-  return attn_mma_supported(qdt, kvdt, hd) ? 64 : ATTN_PREFILL_QTILE;
+  if (attn_mma_supported(qdt, kvdt, hd)) return attn_prefill_tc5_enabled() ? 128 : 64;
+  return ATTN_PREFILL_QTILE;
 }
 
 int attn_decode_splits(int qdt, int kvdt, int n_seqs, int nh, int nkv, int hd, int max_len,
@@ -193,7 +194,11 @@ int attn_decode_splits(int qdt, int kvdt, int n_seqs, int nh, int nkv, int hd, i
 
 cudaError_t launch_attn_prefill(cudaStream_t st, const AttnArgs& a) {
   if (a.n_qtiles <= 0) return cudaSuccess;
-  if (attn_mma_supported(a.qdt, a.kvdt, a.hd)) return launch_attn_prefill_mma(st, a);
+  if (attn_mma_supported(a.qdt, a.kvdt, a.hd)) {
+    if (attn_prefill_tc5_enabled() && a.pool_blocks > 0 && a.total_rows > 0)
+      return launch_attn_prefill_tc5(st, a);
+    return launch_attn_prefill_mma(st, a);
+  }
   if (a.qdt == DT_F32 && a.kvdt == DT_F32) return prefill_dispatch<float, float>(st, a);
   if (a.qdt == DT_F32 && a.kvdt == DT_BF16) return prefill_dispatch<float, bf16>(st, a);
   if (a.qdt == DT_BF16 && a.kvdt == DT_BF16) return prefill_dispatch<bf16, bf16>(st, a);

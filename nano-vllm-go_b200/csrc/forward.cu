@@ -503,6 +503,7 @@ int forward_step(nvllm_handle* h) {
   at.seq_len = d + L.seq_len;
   at.ws = w.attn_ws;
   at.pool_blocks = h->num_blocks;
+  at.total_rows = T;
   at.sm_count = h->sm_count;
   if (!is_prefill) {
     static const bool use_sk = [] {

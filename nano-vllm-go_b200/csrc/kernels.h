@@ -288,6 +288,7 @@ struct AttnArgs {
   // kernels; total_tiles = host LOWER bound of the key tiles in the step (caps the grid)
   int* tickets;
   int pool_blocks;     // blocks in the layer's K / V pool (tensor-map extent)
+  int total_rows;      // rows of q / out in this step (tensor-map extent; tcgen05 prefill kernel)
   int sm_count;
   long long total_tiles;
 };
@@ -306,6 +307,10 @@ bool attn_mma_supported(int qdt, int kvdt, int hd);
 int attn_decode_mma_tile(int hd);
 cudaError_t launch_attn_prefill_mma(cudaStream_t st, const AttnArgs& a);
 cudaError_t launch_attn_decode_mma(cudaStream_t st, const AttnArgs& a);
+// attention_tc5.cu: tcgen05 / TMEM / TMA prefill kernel (bf16, hd 64 / 128; 128-query tiles;
+// needs AttnArgs::pool_blocks and total_rows).  NVLLM_ATTN_PREFILL_TC5=0 keeps the mma.sync one.
+bool attn_prefill_tc5_enabled();
+cudaError_t launch_attn_prefill_tc5(cudaStream_t st, const AttnArgs& a);
 // attention_dec.cu: decode kernel for query-head groups of <= 8 (needs AttnArgs::pool_blocks)
 bool attn_decode_t_supported(const AttnArgs& a);
 cudaError_t launch_attn_decode_t(cudaStream_t st, const AttnArgs& a);
