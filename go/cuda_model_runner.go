@@ -52,15 +52,9 @@ func lastError(h *C.nvllm_handle) error {
 	return fmt.Errorf("nvllm: %s", C.GoString(C.nvllm_last_error(h)))
 }
 
-// NewCudaModelRunner replaces NewTensorModelRunner (tensor_model_runner.go:21-32): it loads
-// the model with the reference's own loader and hands every tensor, in the layout the loader
-// leaves it in (generic_loader.go:184-265,353-604), to the library.
-func NewCudaModelRunner(modelDir string, engineCfg *Config, device int, bf16 bool) (*CudaModelRunner, error) {
-	model, err := tensor.LoadModelFromDirectory(modelDir)
-	if err != nil {
-		return nil, fmt.Errorf("failed to load model: %w", err)
-	}
-	mc := model.Config
+// fillConfig maps tensor.ModelConfig (purego/tensor/config.go:58-122) and the engine's pool
+// sizing (nanovllm/config.go:9-20) onto nvllm_config.
+func fillConfig(mc *tensor.ModelConfig, engineCfg *Config, device int, bf16 bool, tied bool) C.nvllm_config {
 	var cc C.nvllm_config
 	cc.abi_version = C.NVLLM_ABI_VERSION
 	cc.vocab_size = C.int32_t(mc.VocabSize)
@@ -76,7 +70,7 @@ func NewCudaModelRunner(modelDir string, engineCfg *Config, device int, bf16 boo
 	cc.position_type = C.int32_t(posEnum(mc.PositionType))
 	cc.activation_type = C.int32_t(actEnum(mc.ActivationType))
 	cc.block_style = C.int32_t(blockEnum(mc.BlockStyle))
-	if model.LMHead == nil || mc.TiedEmbedding {
+	if tied {
 		cc.tied_embedding = 1
 	}
 	if mc.UseMoE {
@@ -98,6 +92,75 @@ func NewCudaModelRunner(modelDir string, engineCfg *Config, device int, bf16 boo
 	cc.max_batched_tokens = C.int32_t(engineCfg.MaxNumBatchedTokens)
 	cc.tp_size = 1
 	cc.device = C.int32_t(device)
+	return cc
+}
+
+// NewCudaModelRunnerFromDir is the constructor to prefer: only config.json goes through the
+// reference's Go code (tensor.LoadModelConfig, generic_loader.go:808-973); the weights are read
+// by the library itself, straight from model.safetensors or the sharded index into device
+// memory (nvllm_load_safetensors), instead of being decoded to fp32 Go slices first
+// (tensor.LoadModelFromDirectory, generic_loader.go:1016-1163).
+func NewCudaModelRunnerFromDir(modelDir string, engineCfg *Config, device int, bf16 bool) (*CudaModelRunner, error) {
+	mc, err := tensor.LoadModelConfig(modelDir + "/config.json")
+	if err != nil {
+		if mc, err = tensor.LoadModelConfig(modelDir + "/model_info.json"); err != nil {
+			return nil, fmt.Errorf("no valid config found: %w", err)
+		}
+	}
+	var arch C.int
+	switch mc.Architecture {
+	case tensor.ArchGPT2:
+		arch = C.NVLLM_ARCH_GPT2
+	case tensor.ArchFalcon:
+		arch = C.NVLLM_ARCH_FALCON
+	case tensor.ArchLlama:
+		arch = C.NVLLM_ARCH_LLAMA
+	case tensor.ArchGranite:
+		if !mc.UseMoE {
+			return nil, fmt.Errorf("granite hybrid (Mamba2) checkpoints are not supported by the CUDA runner")
+		}
+		arch = C.NVLLM_ARCH_GRANITE_MOE
+	default:
+		return nil, fmt.Errorf("unsupported architecture: %s", mc.Architecture)
+	}
+	// an untied config whose checkpoint has no lm_head falls back to the embedding inside the
+	// library, like generic_loader.go:255-259
+	cc := fillConfig(mc, engineCfg, device, bf16, mc.TiedEmbedding)
+	runtime.LockOSThread()
+	defer runtime.UnlockOSThread()
+	var h *C.nvllm_handle
+	if rc := C.nvllm_create(&cc, nil, &h); rc != 0 {
+		return nil, lastError(nil)
+	}
+	fail := func() (*CudaModelRunner, error) {
+		e := lastError(h)
+		C.nvllm_destroy(h)
+		return nil, e
+	}
+	if rc := C.nvllm_set_sampling(h, C.float(1.0), C.int(0), C.float(1.2)); rc != 0 {
+		return fail()
+	}
+	dir := C.CString(modelDir)
+	defer C.free(unsafe.Pointer(dir))
+	if rc := C.nvllm_load_safetensors(h, dir, arch, nil, nil); rc != 0 {
+		return fail()
+	}
+	if rc := C.nvllm_finalize(h); rc != 0 {
+		return fail()
+	}
+	return &CudaModelRunner{h: h, cfg: mc, temperature: 1.0}, nil
+}
+
+// NewCudaModelRunner replaces NewTensorModelRunner (tensor_model_runner.go:21-32): it loads
+// the model with the reference's own loader and hands every tensor, in the layout the loader
+// leaves it in (generic_loader.go:184-265,353-604), to the library.
+func NewCudaModelRunner(modelDir string, engineCfg *Config, device int, bf16 bool) (*CudaModelRunner, error) {
+	model, err := tensor.LoadModelFromDirectory(modelDir)
+	if err != nil {
+		return nil, fmt.Errorf("failed to load model: %w", err)
+	}
+	mc := model.Config
+	cc := fillConfig(mc, engineCfg, device, bf16, model.LMHead == nil || mc.TiedEmbedding)
 
 	runtime.LockOSThread()
 	defer runtime.UnlockOSThread()

@@ -29,7 +29,7 @@ VAR_TYPES = {
     "s": ("nanovllm", "Sequence"),
     "t": ("tensor", "Tensor"),
 }
-CGO_BUILTINS = {"int", "float", "double", "int32_t", "uint64_t", "GoString", "uint8_t"}
+CGO_BUILTINS = {"int", "float", "double", "int32_t", "uint64_t", "GoString", "uint8_t", "CString", "free"}
 
 
 def _code():
