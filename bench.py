@@ -33,7 +33,7 @@ import nvllm_pkg  # noqa: E402
 
 C = nvllm_pkg.sub("config")
 W = nvllm_pkg.sub("weights")
-E = nvllm_pkg.sub("engine")
+from harness import go_engine as E  # noqa: E402  (restated Go scheduler / block manager: test + bench harness)
 
 
 def load_peaks():
@@ -124,7 +124,7 @@ CONFIGS = {
 class Job:
     """One bench "step" on one replica (or one tensor-parallel group): the prefill step(s) the Go
     scheduler would issue for the request set, then D decode steps.  Block tables and
-    NumCachedTokens come from the restated Go block manager (nano-vllm-go_b200/engine.py)."""
+    NumCachedTokens come from the restated Go block manager (harness/go_engine.py)."""
 
     def __init__(self, cfg, batch, prompt_len, decode_steps, seed0, shared_prefix=0):
         self.cfg, self.n, self.P, self.D = cfg, batch, prompt_len, decode_steps

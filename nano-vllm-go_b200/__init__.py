@@ -5,4 +5,4 @@ The directory name carries a hyphen (it is the name the build contract asks
 for), so it is imported through ``nvllm_pkg.py`` at the repo root, which
 registers it as the module ``nano_vllm_go_b200``.
 """
-__all__ = ["config", "weights", "engine", "lib", "runner", "build"]
+__all__ = ["config", "weights", "lib", "runner", "build"]

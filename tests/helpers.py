@@ -11,7 +11,7 @@ import nvllm_pkg  # noqa: E402
 
 C = nvllm_pkg.sub("config")
 W = nvllm_pkg.sub("weights")
-E = nvllm_pkg.sub("engine")
+from harness import go_engine as E  # noqa: E402  (restated Go scheduler / block manager: test + bench harness)
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 # must match tests/golden/make_hf_golden.py::CASES

@@ -1,6 +1,6 @@
 """Ports of the reference's own unit tests for the bookkeeping that produces the hot path's
 integer inputs (block tables, NumCachedTokens): nanovllm/block_manager_test.go and
-nanovllm/sequence_test.go, against the restatement in nano-vllm-go_b200/engine.py; plus
+nanovllm/sequence_test.go, against the restatement in harness/go_engine.py; plus
 scheduler behaviour (prefill-first, preemption) driven with the MockModelRunner
 (nanovllm/model_runner.go:19-55)."""
 import struct
