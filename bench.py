@@ -402,22 +402,38 @@ def tp_leg(dist, rank, world, device, steps, warmup, barrier):
                            weight_dtype=C.DT_BF16, tp_size=tp, tp_rank=rank if tp > 1 else 0,
                            tp_id=tp_id2, sampling=None)
     prompt = [int(t) for t in W.random_prompt(cfg2.vocab_size, 16, 4321)]
-    toks, got = list(prompt), []
     n_steps = 4
-    for i in range(n_steps):
-        o, lg = r2.run_flat([toks], i == 0, [0], [[0]], [0.0], want_logits=True)
-        got.append((int(o[0]), lg[0].copy()))
-        toks.append(int(o[0]))
-    r2.close()
+    # rank 0 runs the oracle first; every rank then feeds the ORACLE's tokens (teacher forcing:
+    # random-init logits are nearly flat, a near-tie flip would make the later steps incomparable)
+    box = [None]
+    ref_logits = None
     if rank == 0:
         from oracle import oracle as O
         m = O.OracleModel(cfg2, ws)
         ref_toks, ref_logits = m.greedy(np.asarray(prompt, dtype=np.int32), n_steps)
-        worst = max(float(np.abs(got[i][1] - ref_logits[i]).max() / np.abs(ref_logits[i]).max())
-                    for i in range(n_steps))
-        out["parity"] = {"max_rel_err": worst, "tolerance": 2e-2, "within_tolerance": bool(worst <= 2e-2),
-                         "tokens_equal": bool(all(got[i][0] == int(ref_toks[i]) for i in range(n_steps))),
-                         "steps": n_steps, "prompt_tokens": len(prompt),
+        box[0] = [int(t) for t in ref_toks]
+        del m
+    if dist is not None:
+        dist.broadcast_object_list(box, src=0)
+    ref_toks = box[0]
+    toks, got = list(prompt), []
+    for i in range(n_steps):
+        o, lg = r2.run_flat([toks], i == 0, [0], [[0]], [0.0], want_logits=True)
+        got.append((int(o[0]), lg[0].copy()))
+        toks.append(ref_toks[i])
+    r2.close()
+    if rank == 0:
+        errs = [float(np.abs(got[i][1] - ref_logits[i]).max() / np.abs(ref_logits[i]).max())
+                for i in range(n_steps)]
+        flips = [i for i in range(n_steps) if got[i][0] != ref_toks[i]]
+        # a flip is only forgiven when the oracle's own margin to the GPU's token is inside the gate
+        margins = [float((ref_logits[i][ref_toks[i]] - ref_logits[i][got[i][0]]) / np.abs(ref_logits[i]).max())
+                   for i in flips]
+        out["parity"] = {"max_rel_err": max(errs), "tolerance": 2e-2,
+                         "within_tolerance": bool(max(errs) <= 2e-2),
+                         "tokens_equal": not flips, "flipped_steps": flips,
+                         "flip_margins_rel": margins, "steps": n_steps, "prompt_tokens": len(prompt),
+                         "teacher_forced": True,
                          "against": "oracle/nvllm_oracle.c, Falcon-7B width, 2 of 32 layers, same "
                                     "bf16-rounded weights"}
     barrier()

@@ -35,17 +35,68 @@ static GemvPlan gemv_plan(int M, int N, int K) {
 }
 int gemv_splits(int M, int N, int K) { return gemv_plan(M, N, K).S; }
 
+// 8 weight elements as loaded (the conversion to fp32 is deferred to the use)
+template <typename WT> struct Raw8;
+template <> struct Raw8<bf16> {
+  uint4 v;
+  __device__ __forceinline__ void ld(const bf16* p) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  }
+  __device__ __forceinline__ void cvt(float (&o)[8]) const {
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      float2 f = __bfloat1622float2(h[i]);
+      o[2 * i] = f.x;
+      o[2 * i + 1] = f.y;
+    }
+  }
+};
+template <> struct Raw8<float> {
+  float4 a, b;
+  __device__ __forceinline__ void ld(const float* p) {
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "l"(p));
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w) : "l"(p + 4));
+  }
+  __device__ __forceinline__ void cvt(float (&o)[8]) const {
+    o[0] = a.x; o[1] = a.y; o[2] = a.z; o[3] = a.w;
+    o[4] = b.x; o[5] = b.y; o[6] = b.z; o[7] = b.w;
+  }
+};
+
+// The weights are immutable: every warp issues the loads of its first GEMV_PF k-iterations
+// BEFORE griddepcontrol.wait, so the HBM stream of this GEMV runs under the tail of the kernel
+// in front of it (a single-sequence decode step is a chain of ~100 such dependent launches).
+constexpr int GEMV_PF = 2;
 template <typename AT, typename WT, int M, int R>
 __global__ void __launch_bounds__(256)
 gemv_kernel(const AT* __restrict__ A, int lda, const WT* __restrict__ W, int N, int K, int KC,
             float* __restrict__ out, int ldo, size_t split_stride, float alpha, Trace tr) {
   TRACE_ENTRY(tr);
   pdl_launch_dependents();
-  pdl_wait();
   extern __shared__ float a_s[];  // [M][KC]
   const int ks = blockIdx.y * KC;
   const int ke = min(K, ks + KC);
   const int klen = ke - ks;
+  Raw8<WT> wpre[GEMV_PF][R];
+  {
+    const int lane_ = threadIdx.x & 31, warp_ = threadIdx.x >> 5, nw_ = blockDim.x >> 5;
+    const int n0_ = (blockIdx.x * nw_ + warp_) * R;
+    if (n0_ < N) {
+#pragma unroll
+      for (int it = 0; it < GEMV_PF; it++) {
+        const int k = lane_ * 8 + it * 256;
+        if (k < klen) {
+#pragma unroll
+          for (int r = 0; r < R; r++) wpre[it][r].ld(W + (size_t)min(n0_ + r, N - 1) * K + ks + k);
+        }
+      }
+    }
+  }
+  pdl_wait();
   for (int i = threadIdx.x * 8; i < M * KC; i += blockDim.x * 8) {
     const int m = i / KC, k = i % KC;
     float v[8];
@@ -70,8 +121,29 @@ gemv_kernel(const AT* __restrict__ A, int lda, const WT* __restrict__ W, int N, 
 #pragma unroll
   for (int r = 0; r < R; r++) wrow[r] = W + (size_t)min(n0 + r, N - 1) * K + ks;
 
+  auto fma_block = [&](const float (&w)[R][8], int k) {
+#pragma unroll
+    for (int m = 0; m < M; m++) {
+      float a[8];
+      load8(a_s + m * KC + k, a);
+#pragma unroll
+      for (int r = 0; r < R; r++)
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc[r][m] = fmaf(w[r][j], a[j], acc[r][m]);
+    }
+  };
+#pragma unroll
+  for (int it = 0; it < GEMV_PF; it++) {
+    const int k = lane * 8 + it * 256;
+    if (k < klen) {
+      float w[R][8];
+#pragma unroll
+      for (int r = 0; r < R; r++) wpre[it][r].cvt(w[r]);
+      fma_block(w, k);
+    }
+  }
 #pragma unroll 2
-  for (int k = lane * 8; k < klen; k += 256) {
+  for (int k = lane * 8 + GEMV_PF * 256; k < klen; k += 256) {
     float w[R][8];
 #pragma unroll
     for (int r = 0; r < R; r++) load8_stream(wrow[r] + k, w[r]);
