@@ -13,11 +13,12 @@
 //   MMA warp      S = Q K_j^T   (128 x BN, K-major x K-major, accumulator in TMEM)
 //                 O_j = P_j V_j (128 x hd; P from shared memory, V as the MN-major operand —
 //                 the pool keeps V [key][hd], so no transpose anywhere)
-//   softmax warps thread r owns query row r (TMEM lane r): two passes over S in TMEM (row max,
-//                 then exp2 / row sum / bf16 P written in the swizzled K-major operand layout),
-//                 then O_j is read back and folded into the thread's fp32 accumulator with the
-//                 running-max correction (the flash recurrence; nothing but the P tile and the
-//                 final output ever leaves the SM)
+//   softmax warps thread r owns query row r (TMEM lane r): the S row is read into registers
+//                 once (all tcgen05.ld issued, one wait), row max, exp2 / row sum, bf16 P
+//                 written in the swizzled K-major operand layout.  O stays in TMEM across the
+//                 tiles (accumulating MMAs); it is rescaled there only when the running
+//                 maximum has grown by more than a factor 2^8 ("lazy" flash rescaling), and
+//                 read once at the end — nothing but P and the final output leaves the SM
 #include <cuda.h>
 #include <stdlib.h>
 
@@ -183,7 +184,7 @@ attn_prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
           for (int kk = 0; kk < BN / 16; kk++) {
             const uint64_t pd = make_smem_desc(sP + (kk / 4) * (PT_BM * 128)) + 2 * (kk % 4);
             const uint64_t vd = make_smem_desc_mn(sV + kk * 2048, BN * 128);
-            tc_mma_bf16(tO, pd, vd, idesc_o, kk != 0);
+            tc_mma_bf16(tO, pd, vd, idesc_o, (j | kk) != 0);
           }
           tc_commit(b_vempty);
           tc_commit(b_ofull);
@@ -199,48 +200,62 @@ attn_prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
     const int qpos = start + q0 + r;
     const float sl2 = a.scale * 1.4426950408889634f;
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-    float m_run = -INFINITY, l_run = 0.f;
-    float o[HD];
-#pragma unroll
-    for (int i = 0; i < HD; i++) o[i] = 0.f;
+    // O accumulates in TMEM across the key tiles (the P V MMAs run with accumulate = 1).  The
+    // exponent reference m_used only follows the running maximum when it has grown by more than
+    // 2^RESCALE_LOG2 in probability — then, and only then, O (TMEM) and l are rescaled; in
+    // between, p = exp2(s - m_used) may exceed 1 by at most that factor, harmless in fp32 / bf16.
+    constexpr float RESCALE_LOG2 = 8.f;
+    float m_used = -INFINITY, l_run = 0.f;
     for (int j = 0; j < n_tiles; j++) {
       const int k0 = j * BN;
       // the warp's rows see every key of the tile when its last key <= the first row's position
       const bool need_mask = (k0 + BN - 1) > (start + q0 + q * 32);
-      mbar_wait(b_sfull, j & 1);
+      mbar_wait(b_sfull, j & 1);  // also: every earlier P V MMA has retired (in-order pipe)
       tc_fence_after();
-      // pass 1: row maximum (raw score units)
-      float mx = m_run;
+      // the whole S row of this tile in registers: all loads issued, one wait
+      uint32_t sr[BN];
+#pragma unroll
+      for (int c0 = 0; c0 < BN; c0 += 32) tmem_ld_32x32_nowait(tS + lane_off + (uint32_t)c0, &sr[c0]);
+      tmem_ld_wait();
+      float mx = -INFINITY;
+      if (need_mask) {
+#pragma unroll
+        for (int c = 0; c < BN; c++) {
+          if (k0 + c > qpos) sr[c] = 0xff800000u;  // -inf: p = 0
+          mx = fmaxf(mx, __uint_as_float(sr[c]));
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < BN; c++) mx = fmaxf(mx, __uint_as_float(sr[c]));
+      }
+      // rows of the tile that see no key yet (mx = -inf) keep their reference
+      const bool grow = (mx - m_used) * sl2 > RESCALE_LOG2 || (m_used == -INFINITY && mx > -INFINITY);
+      if (__any_sync(0xffffffffu, grow)) {
+        const float m_new = grow ? mx : m_used;
+        const float corr = (m_used == -INFINITY) ? 0.f : ex2((m_used - m_new) * sl2);
+        l_run *= corr;
+        m_used = m_new;
+        if (j > 0) {  // tile 0's P V overwrites O: nothing to rescale yet
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t rr[32];
-        tmem_ld_32x32(tS + lane_off + (uint32_t)c0, rr);
-        if (need_mask) {
+          for (int c0 = 0; c0 < HD; c0 += 32) {
+            uint32_t rr[32];
+            tmem_ld_32x32(tO + lane_off + (uint32_t)c0, rr);
 #pragma unroll
-          for (int c = 0; c < 32; c++)
-            if (k0 + c0 + c <= qpos) mx = fmaxf(mx, __uint_as_float(rr[c]));
-        } else {
-#pragma unroll
-          for (int c = 0; c < 32; c++) mx = fmaxf(mx, __uint_as_float(rr[c]));
+            for (int c = 0; c < 32; c++) rr[c] = __float_as_uint(__uint_as_float(rr[c]) * corr);
+            tmem_st_32x32(tO + lane_off + (uint32_t)c0, rr);
+          }
+          tmem_st_wait();
         }
       }
-      const float corr = ex2((m_run - mx) * sl2);
-      const float mb = mx * sl2;
-      // pass 2: p = exp2(s * scale * log2 e - max), row sum, bf16 P in the swizzled K-major layout
+      const float mb = (m_used == -INFINITY) ? 0.f : m_used * sl2;
       float sum = 0.f;
-#pragma unroll 1
+#pragma unroll
       for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t rr[32];
-        tmem_ld_32x32(tS + lane_off + (uint32_t)c0, rr);
         uint32_t pk[16];
 #pragma unroll
         for (int c = 0; c < 32; c += 2) {
-          float p0 = ex2(fmaf(__uint_as_float(rr[c]), sl2, -mb));
-          float p1 = ex2(fmaf(__uint_as_float(rr[c + 1]), sl2, -mb));
-          if (need_mask) {
-            if (k0 + c0 + c > qpos) p0 = 0.f;
-            if (k0 + c0 + c + 1 > qpos) p1 = 0.f;
-          }
+          const float p0 = ex2(fmaf(__uint_as_float(sr[c0 + c]), sl2, -mb));
+          const float p1 = ex2(fmaf(__uint_as_float(sr[c0 + c + 1]), sl2, -mb));
           sum += p0 + p1;
           __nv_bfloat162 b2 = __floats2bfloat162_rn(p0, p1);
           pk[c >> 1] = *reinterpret_cast<uint32_t*>(&b2);
@@ -254,35 +269,34 @@ attn_prefill_tc5_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_co
                        : "memory");
         }
       }
-      l_run = l_run * corr + sum;
-      m_run = mx;
+      l_run += sum;
       tc_fence_before();
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(b_pready);
-      // fold O_j into the accumulator: o = o * corr + P_j V_j
-      mbar_wait(b_ofull, j & 1);
-      tc_fence_after();
+    }
+    // o_full completes once per tile and is only waited for here.  s_full of the last tile
+    // implied that P V of tile n_tiles - 2 had retired, so the barrier is at least in phase
+    // n_tiles - 1 now and the parity test below can only pass on the last tile's completion.
+    mbar_wait(b_ofull, (n_tiles - 1) & 1);
+    tc_fence_after();
+    const float inv = 1.0f / l_run;
+    bf16* op = (bf16*)a.out + (size_t)(row0 + q0 + r) * a.nh * HD + (size_t)head * HD;
+#pragma unroll 1
+    for (int c0 = 0; c0 < HD; c0 += 32) {
+      uint32_t rr[32];
+      tmem_ld_32x32(tO + lane_off + (uint32_t)c0, rr);
+      if (r < rows_valid) {
 #pragma unroll
-      for (int c0 = 0; c0 < HD; c0 += 32) {
-        uint32_t rr[32];
-        tmem_ld_32x32(tO + lane_off + (uint32_t)c0, rr);
+        for (int c = 0; c < 32; c += 8) {
+          float v[8];
 #pragma unroll
-        for (int c = 0; c < 32; c++) o[c0 + c] = fmaf(o[c0 + c], corr, __uint_as_float(rr[c]));
+          for (int i = 0; i < 8; i++) v[i] = __uint_as_float(rr[c + i]) * inv;
+          store8(op + c0 + c, v);
+        }
       }
     }
     tc_fence_before();
-    if (r < rows_valid) {
-      const float inv = 1.0f / l_run;
-      bf16* op = (bf16*)a.out + (size_t)(row0 + q0 + r) * a.nh * HD + (size_t)head * HD;
-#pragma unroll
-      for (int c = 0; c < HD; c += 8) {
-        float v[8];
-#pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = o[c + i] * inv;
-        store8(op + c, v);
-      }
-    }
   }
   __syncthreads();
   if (warp == 5) {
