@@ -437,7 +437,7 @@ static int tp_reduce_pending(nvllm_handle* h, Pending* p1, Pending* p2, int T) {
   const bool wire_bf16 = !p2p && wire_bf16_ok && h->adt == DT_BF16 && ((size_t)T * h->H % 8) == 0;
   {
     const double n = (double)T * h->H * 4;
-    ProfScope ps(h, NVLLM_K_COMM, (wire_bf16 ? 1.0 : 2.0) * n, 0, n * (a->S + (b ? b->S : 0) + 1));
+    ProfScope ps(h, NVLLM_K_COMM, (wire_bf16 ? 0.5 : 1.0) * n, 0, n * (a->S + (b ? b->S : 0) + 1));  // bytes on the wire per rank
     if (p2p) {
       // one kernel: partial sums + all-reduce over NVLink peer memory (tp.cu)
       LAUNCH(h, launch_tp_allreduce_p2p(h, T, h->H, a->p, a->S, a->stride, a->m, a->bias,
