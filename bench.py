@@ -401,7 +401,10 @@ def tp_leg(dist, rank, world, device, steps, warmup, barrier):
     r2 = R.CudaModelRunner(cfg2, ws, precision=C.PREC_BF16, num_kv_blocks=4, device=device,
                            weight_dtype=C.DT_BF16, tp_size=tp, tp_rank=rank if tp > 1 else 0,
                            tp_id=tp_id2, sampling=None)
-    prompt = [int(t) for t in W.random_prompt(cfg2.vocab_size, 16, 4321)]
+    # prompt seed 4330: the oracle's top-2 margin stays >= 0.044 of max|logit| over these steps
+    # (seed 4321 has a 0.0008 near-tie at step 0, inside the 2e-2 gate: an argmax flip there says
+    # nothing; found by scanning seeds 4321..4334 with the CPU oracle)
+    prompt = [int(t) for t in W.random_prompt(cfg2.vocab_size, 16, 4330)]
     n_steps = 4
     # rank 0 runs the oracle first; every rank then feeds the ORACLE's tokens (teacher forcing:
     # random-init logits are nearly flat, a near-tie flip would make the later steps incomparable)
