@@ -24,7 +24,7 @@ void free_workspace(nvllm_handle* h) {
   Workspace& w = h->ws;
   h->drop_graphs();  // the captured decode steps hold these pointers
   void* ptrs[] = {w.tp_buf, w.x, w.xn, w.xn_f32, w.ws_a, w.ws_b, w.ws_c, w.q, w.attn_out, w.hbuf, w.xn_last,
-                  w.xb, w.ssq, w.res_ctr, w.logits_p, w.logits, w.attn_ws, w.attn_tickets, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
+                  w.xb, w.ssq, w.res_ctr, w.chain_ctr, w.logits_p, w.logits, w.attn_ws, w.attn_tickets, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
                   w.sort.counts, w.sort.offsets, w.sort.cursor, w.sort.sorted_pair, w.sort.pair_row,
                   w.sort.a_rows, w.sort.tile_expert, w.sort.tile_row0, w.sort.tile_rows,
                   w.sort.n_tiles, w.moe_Y, w.moe_y, w.moe_xs};
@@ -77,6 +77,9 @@ int ensure_workspace(nvllm_handle* h, int T, int n) {
   WS(w.attn_out, (size_t)Tc * h->q_cols * asz);
   WS(w.hbuf, h->moe ? (size_t)Tc * h->topk * h->F * asz : (size_t)Tc * h->F * asz);
   WS(w.xn_last, nc * H * asz);
+  WS(w.chain_ctr, 256);
+  if (cudaMemsetAsync(w.chain_ctr, 0, 256, h->stream) != cudaSuccess)
+    return set_err(h, NVLLM_ERR_CUDA, "memset(chain counters) failed");
   if (h->fold) {
     WS(w.xb, Tc * H * 2);
     WS(w.ssq, (size_t)ceil_div(h->H, 128) * Tc * 4);
@@ -485,6 +488,9 @@ int forward_step(nvllm_handle* h) {
   // Folded RMSNorm (h->fold): while `xb_parts` > 0, w.xb holds bf16(x) of the CURRENT residual
   // stream and w.ssq its row sums of squares in xb_parts column-tile slices — the next GEMM
   // that would read a normed activation reads w.xb instead and the norm kernel is not launched.
+  // read per step (not cached): the parity tests switch it between runs
+  const char* chain_env = getenv("NVLLM_CHAIN");
+  const bool chain_on = !(chain_env && atoi(chain_env) == 0);
   int xb_parts = h->fold ? 1 : 0;
   const int h_tiles = ceil_div(H, 128);
   // generic_model.go:359-365: res + rm * x when ResidualMultiplier != 0, else plain add
@@ -694,6 +700,34 @@ int forward_step(nvllm_handle* h) {
       pf.p = w.moe_Y; pf.S = 1; pf.stride = 0; pf.bias = nullptr;
       pf.comb_rows = w.sort.pair_row; pf.comb_w = w.topk_w; pf.comb_k = k;
     } else {
+      // decode-sized steps: W1 (+ fused activation) and W2 in ONE launch — W2's weight stream
+      // starts under W1's epilogues and the launch / drain / release gap between the two
+      // GEMMs is gone (gemm_tcgen05.cu, Tc5Chain).  NVLLM_CHAIN=0 keeps two launches.
+      const long w1_tiles = ceil_div(h->w1_cols, 128);
+      if (chain_on && T > 8 && T <= 128 && xb_parts == 0 && h->wdt == DT_BF16 && h->use_tc5 &&
+          tc5_supported(T, h->w1_cols, H) && tc5_supported(T, H, h->F) &&
+          (tc5_splits(T, h->w1_cols, H, h->sm_count) == 1 || 2 * w1_tiles >= h->sm_count)) {
+        Tc5Args t1{};
+        t1.A = w.xn; t1.W = lw.w1; t1.M = T; t1.N = h->w1_cols; t1.K = H; t1.S = 1; t1.alpha = 1.f;
+        t1.epi = h->swiglu ? TC5_EPI_SWIGLU : TC5_EPI_GELU; t1.epi_out = w.hbuf; t1.epi_ld = h->F;
+        t1.epi_bias = lw.b1;
+        Tc5Args t2{};
+        t2.A = w.hbuf; t2.W = lw.w2; t2.M = T; t2.N = H; t2.K = h->F; t2.alpha = 1.f;
+        t2.out = ffn_out; t2.ldo = H; t2.split_stride = (size_t)T * H; t2.out_capacity = w.ws_b_floats;
+        t2.S = tc5_splits(T, H, h->F, h->sm_count);
+        while (t2.S > 1 && (size_t)t2.S * T * H > w.ws_b_floats) t2.S--;
+        int S2 = 1;
+        {
+          const double wsz = dt_size(h->wdt);
+          ProfScope ps(h, NVLLM_K_GEMM_TC5, ((double)h->w1_cols * H + (double)H * h->F) * wsz,
+                       2.0 * T * ((double)h->w1_cols * H + (double)H * h->F),
+                       (double)T * H * asz + 2.0 * T * h->F * asz + 4.0 * t2.S * T * H);
+          LAUNCH(h, launch_gemm_tc5_chain(st, t1, t2, w.chain_ctr, &S2));
+        }
+        pf.p = ffn_out; pf.S = S2; pf.stride = (size_t)T * H; pf.bias = lw.b2;
+        pf.m = h->parallel ? (par_scaled ? c.residual_multiplier : 1.f) : m_res;
+        continue;
+      }
       Pending h1;
       RowScale rsc{xb_parts > 0 ? w.ssq : nullptr, xb_parts};
       if ((rc = run_gemm(h, xb_parts > 0 ? w.xb : w.xn, H, lw.w1, T, h->w1_cols, H, 1.f, w.ws_a,

@@ -71,6 +71,22 @@ struct Tc5Fuse {
   unsigned* arrive;
   unsigned* done;
 };
+// A second GEMM chained behind the first inside ONE launch (the FFN pair of a decode step:
+// W1 + activation, then W2): every CTA runs its units of problem 1, then its units of problem 2.
+// Problem 2 reads what problem 1's epilogues wrote, so its activation tiles wait for
+// ctr[0] == units of problem 1 — but its WEIGHT tiles are requested as soon as ring slots free
+// up, i.e. under problem 1's epilogues and the wait, and there is no launch / drain / release
+// gap between the two GEMMs.  ctr[1] counts the CTAs past the wait; the last one re-arms both.
+struct Tc5Chain {
+  Tc5Sched sc;  // units == 0: no chain
+  int N;
+  float* out;
+  int ldo;
+  size_t split_stride;
+  float alpha;
+  unsigned* ctr;
+  int n_waiters;  // CTAs owning at least one unit of problem 2
+};
 __device__ __forceinline__ void named_bar(int id, int n) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory");
 }
@@ -132,10 +148,11 @@ __device__ __forceinline__ int tc5_kb(int kb0, int kb, int rot, int nkb) {
 template <int BT, int STAGES>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__ CUtensorMap tmA,
-                int M, int N, Tc5Sched sc, float* __restrict__ out, int ldo, size_t split_stride,
-                float alpha, int w_reused, int epi, bf16* __restrict__ epi_out, int epi_ld,
+                const __grid_constant__ CUtensorMap tmW2, const __grid_constant__ CUtensorMap tmA2,
+                int M, int N_a, Tc5Sched sc, float* __restrict__ out_a, int ldo_a, size_t split_stride_a,
+                float alpha_a, int w_reused, int epi_a, bf16* __restrict__ epi_out, int epi_ld,
                 const float* __restrict__ epi_bias, int prefetch, const uint8_t* __restrict__ pf_ptr,
-                unsigned long long pf_bytes, Tc5Fuse fz, Trace tr) {
+                unsigned long long pf_bytes, Tc5Fuse fz, Tc5Chain ch, Trace tr) {
   const unsigned long long t_entry = trace_on(tr) ? gtime() : 0ull;
   unsigned long long t_wait = 0;
   __shared__ unsigned long long tr_mma, tr_epi0, tr_epi1, tr_x[6];
@@ -255,28 +272,61 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     }
     pdl_wait();
     if (trace_on(tr)) t_wait = gtime();
-    const int units = grouped ? *sc.g_ntiles * sc.n_tiles : sc.units;
     // (2) their activation tiles, then (3) the steady state
-    int u = blockIdx.x, kb = 0, i = 0;
-    while (u < units) {
-      const Tc5Unit t = tc5_unit(sc, u, BT, M);
-      for (; kb < t.nkb; kb++, i++) {
-        const int s = i % STAGES;
-        const uint32_t full = bars + 8 * s;
-        const uint32_t dst = tiles + s * STAGE_BYTES;
-        const int k = tc5_kb(t.kb0, kb, t.rot, t.nkb) * TC_BK;
-        if (i >= pre) mbar_wait(bars + 8 * (STAGES + s), ((i / STAGES) & 1) ^ 1);
-        if (elect_one()) {
-          if (i >= pre) {
-            mbar_expect_tx(full, (prefetch & 2) ? W_BYTES : STAGE_BYTES);
-            tma_load_2d_hint(dst, &tmW, full, k, t.wrow, pol_w);
+    int i = 0;
+    int ahead_lo = 0, ahead_hi = pre;  // k-block range [lo, hi) whose weight tile is already in flight
+    for (int p = 0; p < 2; p++) {
+      const Tc5Sched& scp = p ? ch.sc : sc;
+      const CUtensorMap* mW = p ? &tmW2 : &tmW;
+      const CUtensorMap* mA = p ? &tmA2 : &tmA;
+      const int units = p ? ch.sc.units : (grouped ? *sc.g_ntiles * sc.n_tiles : sc.units);
+      if (p == 1 && (int)blockIdx.x < units) {
+        // chained GEMM: weight tiles of the first k-blocks now, activations after problem 1 is done
+        const Tc5Unit t = tc5_unit(scp, blockIdx.x, BT, M);
+        const int na = min(STAGES, t.nkb);
+        for (int kb = 0; kb < na; kb++) {
+          const int ii = i + kb, s = ii % STAGES;
+          mbar_wait(bars + 8 * (STAGES + s), ((ii / STAGES) & 1) ^ 1);
+          if (elect_one()) {
+            mbar_expect_tx(bars + 8 * s, STAGE_BYTES);
+            tma_load_2d_hint(tiles + s * STAGE_BYTES, mW, bars + 8 * s,
+                             tc5_kb(t.kb0, kb, t.rot, t.nkb) * TC_BK, t.wrow, pol_w);
           }
-          if (!(prefetch & 2)) tma_load_2d_hint(dst + W_BYTES, &tmA, full, k, t.m0, pol_a);
+          __syncwarp();
+        }
+        ahead_lo = i;
+        ahead_hi = i + na;
+        if (elect_one()) {
+          while (ld_acquire_u32(ch.ctr) < (unsigned)sc.units) {
+          }
+          if (atomicAdd(ch.ctr + 1, 1u) == (unsigned)ch.n_waiters - 1) {  // everyone is past the wait
+            ch.ctr[0] = 0;
+            ch.ctr[1] = 0;
+          }
         }
         __syncwarp();
+        // the activations were written through the generic proxy by other CTAs; TMA reads them
+        asm volatile("fence.proxy.async;" ::: "memory");
       }
-      kb = 0;
-      u += grid;
+      for (int u = blockIdx.x; u < units; u += grid) {
+        const Tc5Unit t = tc5_unit(scp, u, BT, M);
+        for (int kb = 0; kb < t.nkb; kb++, i++) {
+          const int s = i % STAGES;
+          const uint32_t full = bars + 8 * s;
+          const uint32_t dst = tiles + s * STAGE_BYTES;
+          const int k = tc5_kb(t.kb0, kb, t.rot, t.nkb) * TC_BK;
+          const bool w_ahead = i >= ahead_lo && i < ahead_hi;
+          if (!w_ahead) mbar_wait(bars + 8 * (STAGES + s), ((i / STAGES) & 1) ^ 1);
+          if (elect_one()) {
+            if (!w_ahead) {
+              mbar_expect_tx(full, (prefetch & 2) ? W_BYTES : STAGE_BYTES);
+              tma_load_2d_hint(dst, mW, full, k, t.wrow, pol_w);
+            }
+            if (!(prefetch & 2)) tma_load_2d_hint(dst + W_BYTES, mA, full, k, t.m0, pol_a);
+          }
+          __syncwarp();
+        }
+      }
     }
   } else if (warp == 1) {
     // instruction descriptor (cute/arch/mma_sm100_desc.hpp): fp32 accumulate, bf16 x bf16,
@@ -284,10 +334,12 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     constexpr uint32_t idesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BT >> 3) << 17) |
                                ((uint32_t)(TC_BN >> 4) << 24);
     if (grouped) pdl_wait();  // the tile list is the previous kernel's output
-    const int units = grouped ? *sc.g_ntiles * sc.n_tiles : sc.units;
     int i = 0, lu = 0;
+    for (int p = 0; p < 2; p++) {
+    const Tc5Sched& scp = p ? ch.sc : sc;
+    const int units = p ? ch.sc.units : (grouped ? *sc.g_ntiles * sc.n_tiles : sc.units);
     for (int u = blockIdx.x; u < units; u += grid, lu++) {
-      const int nkb = tc5_unit(sc, u, BT, M).nkb;
+      const int nkb = tc5_unit(scp, u, BT, M).nkb;
       const int buf = lu & 1;
       mbar_wait(bar_tempty + 8 * buf, ((lu >> 1) & 1) ^ 1);  // epilogue drained this buffer
       tc_fence_after();
@@ -316,20 +368,28 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       }
       if (tr.buf && lane == 0) tr_mma = gtime();
     }
+    }
   } else {
     // epilogue: warp w may touch TMEM lanes [32 (w % 4), +32)
     const int q = warp & 3;
     pdl_wait();  // global stores below must follow the previous kernel's completion
-    const int units = grouped ? *sc.g_ntiles * sc.n_tiles : sc.units;
     int lu = 0;
+    for (int p = 0; p < 2; p++) {
+    const Tc5Sched& scp = p ? ch.sc : sc;
+    const int units = p ? ch.sc.units : (grouped ? *sc.g_ntiles * sc.n_tiles : sc.units);
+    // problem 2 of a chain always writes plain fp32 split-K partials
+    const int N = p ? ch.N : N_a, ldo = p ? ch.ldo : ldo_a, epi = p ? (int)TC5_EPI_PARTIAL : epi_a;
+    float* const out = p ? ch.out : out_a;
+    const size_t split_stride = p ? ch.split_stride : split_stride_a;
+    const float alpha = p ? ch.alpha : alpha_a;
     for (int u = blockIdx.x; u < units; u += grid, lu++) {
-      const Tc5Unit t = tc5_unit(sc, u, BT, M);
+      const Tc5Unit t = tc5_unit(scp, u, BT, M);
       const int n0 = t.n0, m0 = t.m0, split = t.split;
       const int M = t.m_end;  // rows past the tile's extent belong to the next expert / are padding
       const int buf = lu & 1;
       const int et = threadIdx.x - 64;  // 0..127 over the four epilogue warps
       const float* rs = nullptr;
-      if (fz.rs_ssq) {
+      if (fz.rs_ssq && p == 0) {
         // folded RMSNorm: 1 / sqrt(mean(x^2) + eps) per token row (tensor.go:211-224), from the
         // per-column-tile sums the producing GEMM (or the embedding kernel) left; computed while
         // the MMAs of this unit run
@@ -423,7 +483,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
         // sub-block needs: the row rounded to bf16 and its sum of squares over this column tile
         const float b = (fz.bias && n_ok) ? fz.bias[n] : 0.f;
         const int nt = n0 / TC_BN;
-        if (sc.S == 1) {
+        if (scp.S == 1) {
           int chunk = 0;
 #pragma unroll 1
           for (int c0 = 0; c0 < BT; c0 += 32, chunk++) {
@@ -479,12 +539,12 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
             }
           }
           // (2) meet the other k-splits of this output tile (all resident: units <= #SM)
-          const int tile_id = (m0 / BT) * sc.n_tiles + nt;
+          const int tile_id = (m0 / BT) * scp.n_tiles + nt;
           __threadfence();
           named_bar(2, 128);
           if (et == 0) {
             atomicAdd(fz.arrive + tile_id, 1u);
-            while (ld_acquire_u32(fz.arrive + tile_id) < (unsigned)sc.S) {
+            while (ld_acquire_u32(fz.arrive + tile_id) < (unsigned)scp.S) {
             }
           }
           named_bar(2, 128);
@@ -493,7 +553,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
           // columns), all its loads are issued together, and the warp sum IS the row's sum of
           // squares over this column tile: no cross-warp step.
           const int valid = min(BT, M - m0);
-          const int per = (valid + sc.S - 1) / sc.S;
+          const int per = (valid + scp.S - 1) / scp.S;
           const int r0 = split * per, r1 = min(valid, r0 + per);
           const int ncol = n0 + lane * 4;
           const bool c_ok = ncol + 3 < N;  // N % 4 == 0 is checked by the launcher
@@ -506,16 +566,16 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
               const size_t xi = (size_t)(m0 + row) * N + ncol;
               const float4 xv = __ldcg(reinterpret_cast<const float4*>(fz.x + xi));
               float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (sc.S <= 8) {
+              if (scp.S <= 8) {
                 float4 pz[8];
 #pragma unroll
                 for (int sp = 0; sp < 8; sp++)
-                  if (sp < sc.S) pz[sp] = __ldcg(reinterpret_cast<const float4*>(out + (size_t)sp * split_stride + o));
+                  if (sp < scp.S) pz[sp] = __ldcg(reinterpret_cast<const float4*>(out + (size_t)sp * split_stride + o));
 #pragma unroll
                 for (int sp = 0; sp < 8; sp++)
-                  if (sp < sc.S) { acc.x += pz[sp].x; acc.y += pz[sp].y; acc.z += pz[sp].z; acc.w += pz[sp].w; }
+                  if (sp < scp.S) { acc.x += pz[sp].x; acc.y += pz[sp].y; acc.z += pz[sp].z; acc.w += pz[sp].w; }
               } else {
-                for (int sp = 0; sp < sc.S; sp++) {
+                for (int sp = 0; sp < scp.S; sp++) {
                   const float4 pv = __ldcg(reinterpret_cast<const float4*>(out + (size_t)sp * split_stride + o));
                   acc.x += pv.x; acc.y += pv.y; acc.z += pv.z; acc.w += pv.w;
                 }
@@ -536,7 +596,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
           }
           named_bar(2, 128);
           if (et == 0) {
-            if (atomicAdd(fz.done + tile_id, 1u) == (unsigned)sc.S - 1) {  // everyone is past the wait
+            if (atomicAdd(fz.done + tile_id, 1u) == (unsigned)scp.S - 1) {  // everyone is past the wait
               fz.arrive[tile_id] = 0;
               fz.done[tile_id] = 0;
             }
@@ -576,6 +636,12 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       __syncwarp();
       if (tr.buf && warp == 2 && lane == 0) tr_epi1 = gtime();
       if (lane == 0) mbar_arrive(bar_tempty + 8 * buf);
+      if (p == 0 && ch.sc.units > 0) {  // publish this tile of problem 1 to the chained GEMM
+        __threadfence();
+        named_bar(3, 128);
+        if (et == 0) atomicAdd(ch.ctr, 1u);
+      }
+    }
     }
   }
   tc_fence_before();
@@ -756,7 +822,9 @@ bool pdl_enabled() { return g_pdl; }
 
 template <int BT, int STAGES>
 static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* tw,
-                             const TmaDesc* ta, int S) {
+                             const TmaDesc* ta, int S, const Tc5Args* a2 = nullptr,
+                             const TmaDesc* tw2 = nullptr, const TmaDesc* ta2 = nullptr, int S2 = 0,
+                             unsigned* chain_ctr = nullptr) {
   constexpr size_t smem = (size_t)STAGES * (TC_BN + BT) * TC_BK * 2 + 1024 + 16 * STAGES + 64;
   static_assert(smem <= 232448, "shared memory budget");
   static uint64_t attr_mask = 0;  // per device
@@ -801,13 +869,62 @@ static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* t
       return cudaErrorInvalidValue;
   }
   const bool w_reused = a.g_experts > 0 ? a.M > 2 * BT * a.g_experts : m_tiles > 1;
-  return launch_k(gemm_tc5_kernel<BT, STAGES>, dim3(grid), dim3(TC_THREADS), smem, st,
+  Tc5Chain ch{};
+  int grid_l = grid;
+  if (a2) {
+    // chained second GEMM: same token tile, plain split-K partials; its k-splits wait inside
+    // the kernel for problem 1, so every CTA must be resident (grid <= #SM holds by construction)
+    if (a.g_experts > 0 || m_tiles != 1 || !chain_ctr || a2->M != a.M) return cudaErrorInvalidValue;
+    ch.sc.nkb_total = ceil_div(a2->K, TC_BK);
+    ch.sc.kbps = ceil_div(ch.sc.nkb_total, S2);
+    ch.sc.S = ceil_div(ch.sc.nkb_total, ch.sc.kbps);
+    ch.sc.n_tiles = ceil_div(a2->N, TC_BN);
+    ch.sc.units = ch.sc.n_tiles * ch.sc.S;
+    ch.N = a2->N;
+    ch.out = a2->out;
+    ch.ldo = a2->ldo;
+    ch.split_stride = a2->split_stride;
+    ch.alpha = a2->alpha;
+    ch.ctr = chain_ctr;
+    grid_l = min(max(sc.units, ch.sc.units), max(1, sm_counts[dev]));
+    ch.n_waiters = min(grid_l, ch.sc.units);
+  }
+  return launch_k(gemm_tc5_kernel<BT, STAGES>, dim3(grid_l), dim3(TC_THREADS), smem, st,
                   *reinterpret_cast<const CUtensorMap*>(tw),
-                  *reinterpret_cast<const CUtensorMap*>(ta), a.M, a.N, sc, a.out, a.ldo,
+                  *reinterpret_cast<const CUtensorMap*>(ta),
+                  *reinterpret_cast<const CUtensorMap*>(a2 ? tw2 : tw),
+                  *reinterpret_cast<const CUtensorMap*>(a2 ? ta2 : ta), a.M, a.N, sc, a.out, a.ldo,
                   a.split_stride, a.alpha, w_reused ? 1 : 0, a.epi, (bf16*)a.epi_out, a.epi_ld,
                   a.epi_bias, prefetch_flags(),
                   (const uint8_t*)((prefetch_flags() & 4) ? nullptr : a.pf_ptr),
-                  (unsigned long long)((prefetch_flags() & 4) ? 0 : a.pf_bytes), fz, next_trace(1));
+                  (unsigned long long)((prefetch_flags() & 4) ? 0 : a.pf_bytes), fz, ch, next_trace(1));
+}
+
+// a1: GEMM with a fused activation epilogue (S = 1) writing the bf16 matrix that is a2's A;
+// a2: plain split-K GEMM.  Both for the same M <= 128 tokens.  ctr: two zeroed counters.
+cudaError_t launch_gemm_tc5_chain(cudaStream_t st, const Tc5Args& a1, const Tc5Args& a2,
+                                  unsigned* ctr, int* S2_out) {
+  if (!tc5_supported(a1.M, a1.N, a1.K) || !tc5_supported(a2.M, a2.N, a2.K)) return cudaErrorInvalidValue;
+  if (a1.g_experts > 0 || a2.g_experts > 0 || a1.M != a2.M || a1.M > 128) return cudaErrorInvalidValue;
+  if ((a1.epi != TC5_EPI_SWIGLU && a1.epi != TC5_EPI_GELU) || !a1.epi_out || a2.epi != TC5_EPI_PARTIAL)
+    return cudaErrorInvalidValue;
+  if (a1.epi == TC5_EPI_SWIGLU && (a1.N & 1)) return cudaErrorInvalidValue;
+  const int bt = pick_bt(a1.M);
+  const TmaDesc* tw = cached_map(a1.W, a1.N, a1.K, TC_BN);
+  const TmaDesc* ta = cached_map(a1.A, a1.M, a1.K, bt);
+  const TmaDesc* tw2 = cached_map(a2.W, a2.N, a2.K, TC_BN);
+  const TmaDesc* ta2 = cached_map(a2.A, a2.M, a2.K, bt);
+  if (!tw || !ta || !tw2 || !ta2) return cudaErrorInvalidValue;
+  const int nkb2 = ceil_div(a2.K, TC_BK);
+  int S2 = max(1, min(a2.S, nkb2));
+  S2 = ceil_div(nkb2, ceil_div(nkb2, S2));
+  if (S2_out) *S2_out = S2;
+  if (a2.out_capacity && (size_t)S2 * a2.split_stride > a2.out_capacity) return cudaErrorInvalidValue;
+  switch (bt) {
+    case 32: return launch_bt<32, 10>(st, a1, tw, ta, 1, &a2, tw2, ta2, S2, ctr);
+    case 64: return launch_bt<64, 8>(st, a1, tw, ta, 1, &a2, tw2, ta2, S2, ctr);
+    default: return launch_bt<128, 6>(st, a1, tw, ta, 1, &a2, tw2, ta2, S2, ctr);
+  }
 }
 
 // a.S is the requested number of splits; the number actually written is returned in *S_out

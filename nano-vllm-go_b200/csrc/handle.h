@@ -61,6 +61,7 @@ struct Workspace {
   void* xb = nullptr;
   float* ssq = nullptr;
   unsigned* res_ctr = nullptr;  // [2 sites][arrive | done][RES_CTR_TILES]
+  unsigned* chain_ctr = nullptr;  // [2] counters of the chained W1 -> W2 GEMM launch (zero between launches)
   float* logits_p = nullptr; // [S][n][ldl]
   float* logits = nullptr;   // [n][ldl]  (tp > 1: [tp][n][Vl], rank-major slices)
   float* tp_buf = nullptr;   // [T, H] fp32 partial sums handed to the all-reduce (tp > 1)

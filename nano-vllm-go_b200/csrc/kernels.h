@@ -247,6 +247,11 @@ int tc5_splits(int M, int N, int K, int sm_count);
 // *S_out = slices actually written (<= a.S)
 cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int* S_out);
 int tc5_box_rows_act(int M);  // token-tile rows (UMMA N) the kernel uses for M tokens
+// Two GEMMs in one launch (decode FFN: W1 + fused activation, then W2 on its output): a2's
+// weight stream starts under a1's epilogues, no launch / drain gap in between.  M <= 128.
+// ctr = two zeroed device counters kept by the caller.  *S2_out = slices of a2 actually written.
+cudaError_t launch_gemm_tc5_chain(cudaStream_t st, const Tc5Args& a1, const Tc5Args& a2,
+                                  unsigned* ctr, int* S2_out);
 
 // ---------------------------------------------------------------- attention.cu
 struct AttnArgs {

@@ -163,3 +163,35 @@ def test_cfg2_llama_1b_full_width_fp32_mode():
     cfg = replace(C.llama32_1b(), num_layers=2)
     prompts, tables = _plain_batch(cfg, 8, 12, 3)
     _batch_parity(cfg, C.PREC_FP32, prompts, 3, tables)
+
+
+@pytest.mark.parametrize("family,batch", [("llama", 12), ("gpt2", 40), ("falcon", 70)])
+def test_chained_ffn_gemms_bit_identical_to_two_launches(family, batch, monkeypatch):
+    """Decode batches of 9..128 rows run W1 (+ activation) and W2 as ONE chained launch
+    (gemm_tcgen05.cu Tc5Chain): same tiles, same split-K slices, same summation order as the two
+    separate launches (NVLLM_CHAIN=0), so logits must be bit-identical; and within the bf16
+    gate of the oracle.  Covers SwiGLU (llama), GELU + biases (gpt2), the parallel block (falcon)
+    and the three token-tile widths 32 / 64 / 128."""
+    from helpers import TINY
+    cfg = TINY[family]()
+    prompts, tables = _plain_batch(cfg, batch, 9, 3)
+    n = len(prompts)
+    outs = {}
+    for chain in ("1", "0"):
+        monkeypatch.setenv("NVLLM_CHAIN", chain)
+        run = _runner(cfg, C.PREC_BF16, num_kv_blocks=n, max_num_seqs=n, max_batched_tokens=4096)
+        try:
+            seqs = [[int(t) for t in p] for p in prompts]
+            got = []
+            for i in range(3):
+                out, logits = run.run_flat(seqs, i == 0, None, tables, [0.0] * n, want_logits=True)
+                got.append(logits.copy())
+                for s in range(n):
+                    seqs[s].append(int(out[s]))
+            outs[chain] = (np.stack(got), [list(x) for x in seqs])
+        finally:
+            run.close()
+    assert outs["1"][1] == outs["0"][1]
+    assert np.array_equal(outs["1"][0], outs["0"][0])
+    monkeypatch.setenv("NVLLM_CHAIN", "1")
+    _batch_parity(cfg, C.PREC_BF16, prompts, 3, tables)

@@ -15,7 +15,7 @@ if os.environ.get("NVLLM_NCU_LAYERS"):
     from dataclasses import replace
     cfg = replace(cfg, num_layers=int(os.environ["NVLLM_NCU_LAYERS"]))
 job = bench.Job(cfg, batch, plen, steps, 4321)
-run = bench.make_runner(cfg, job, 0, fast_weights=True)
+run = bench.make_runner(cfg, job, 0, fast_weights=not os.environ.get("NVLLM_NCU_HOST_WEIGHTS"))
 # ncu serialises and replays kernels: capture-free launches keep -k / -s / -c counting simple
 run.set_graphs(bool(int(os.environ.get('NVLLM_GRAPHS', '0'))))
 job.stage(run)
