@@ -663,8 +663,8 @@ def main():
         traffic = None
         try:  # per-launch DRAM bytes of the dominant kernel from the committed ncu --set full capture
             tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-            ent = tr.get(f"{phase}.{name}")
-            if ent and ent.get("workload", "").split()[0] == cfg.name.lower():
+            ent = tr.get(cfg.name.lower(), {}).get(f"{phase}.{name}")
+            if ent:
                 traffic = ent["dram_bytes_per_launch"]
         except (OSError, ValueError, KeyError):
             traffic = None
