@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(512) norm_kernel(NormArgs a, Trace tr) {
   pdl_wait();
   const unsigned long long t_wait = trace_on(tr) ? gtime() : 0ull;
   const int orow = blockIdx.x;
-  const int r = a.row_idx ? a.row_idx[orow] : orow;
+  const int r = a.row_idx ? a.row_idx[orow] - a.row_bias : orow;
   float* xr = a.x + (size_t)r * H;
   const bool upd = (a.p1 != nullptr) || (a.p2 != nullptr);
   float lsum = 0.f;

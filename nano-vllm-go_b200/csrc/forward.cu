@@ -310,6 +310,7 @@ static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int 
     t.A = A; t.W = W; t.M = M; t.N = N; t.K = K; t.out = out; t.ldo = ldo;
     t.split_stride = res->stride; t.alpha = alpha; t.out_capacity = cap;
     t.S = tc5_splits(M, N, K, h->sm_count);
+    t.max_ctas = h->gemm_max_ctas;
     if (rs && rs->ssq) {
       t.rs_ssq = rs->ssq; t.rs_parts = rs->parts; t.rs_ld = h->ws.T_cap;
       t.rs_inv_h = 1.0f / (float)h->H; t.rs_eps = h->cfg.norm_eps;
@@ -415,6 +416,7 @@ static int run_norm(nvllm_handle* h, float* x, Pending* p1, Pending* p2, const f
   }
   a.w = w; a.b = b; a.eps = h->cfg.norm_eps; a.y = y; a.ydt = h->adt; a.y_f32 = y_f32;
   a.row_idx = row_idx; a.n_rows = n_rows; a.H = h->H;
+  a.row_bias = row_idx ? h->view_r0 : 0;  // row_idx holds rows of the whole step
   ProfScope ps(h, NVLLM_K_NORM, bytes, 0, impl);
   LAUNCH(h, launch_norm(h->stream, a));
   if (p1) *p1 = Pending();
@@ -436,7 +438,9 @@ static int tp_reduce_pending(nvllm_handle* h, Pending* p1, Pending* p2, int T) {
   // all-reduce; the sum over ranks of the per-rank addends is rounded once more, the residual
   // stream itself stays fp32.  NVLLM_TP_BF16=0 keeps fp32 on the wire.
   static const bool wire_bf16_ok = !(getenv("NVLLM_TP_BF16") && atoi(getenv("NVLLM_TP_BF16")) == 0);
-  const bool p2p = tp_p2p_fits(h, (size_t)T * h->H);
+  // the peer-memory kernel keeps one flag / epoch state per handle: the two chunks of a pipelined
+  // prefill must not use it concurrently
+  const bool p2p = h->pipe_role == 0 && tp_p2p_fits(h, (size_t)T * h->H);
   const bool wire_bf16 = !p2p && wire_bf16_ok && h->adt == DT_BF16 && ((size_t)T * h->H % 8) == 0;
   {
     const double n = (double)T * h->H * 4;
@@ -501,7 +505,11 @@ int forward_step(nvllm_handle* h) {
   const size_t kv_layer_bytes = h->kv_layer_elems * dt_size(h->kvdt);
 
   AttnArgs at{};
-  at.q = w.q; at.out = w.attn_out; at.qdt = h->adt; at.kvdt = h->kvdt;
+  // the attention kernels index rows of the WHOLE step (cu_q + q0): a chunk's view of the
+  // workspace starts view_r0 rows in
+  at.q = (char*)w.q - (size_t)h->view_r0 * h->q_cols * dt_size(h->adt);
+  at.out = (char*)w.attn_out - (size_t)h->view_r0 * h->q_cols * dt_size(h->adt);
+  at.qdt = h->adt; at.kvdt = h->kvdt;
   at.n_seqs = n; at.nh = h->nh; at.nkv = h->nkv; at.hd = h->hd; at.scale = h->attn_scale;
   at.block_tables = d + L.block_tables; at.max_blocks = L.max_blocks;
   at.cu_q = d + L.cu_q; at.seq_start = d + L.seq_start;
@@ -509,7 +517,7 @@ int forward_step(nvllm_handle* h) {
   at.seq_len = d + L.seq_len;
   at.ws = w.attn_ws;
   at.pool_blocks = h->num_blocks;
-  at.total_rows = T;
+  at.total_rows = h->view_T > 0 ? h->view_T : T;
   at.sm_count = h->sm_count;
   if (!is_prefill) {
     static const bool use_sk = [] {
@@ -573,10 +581,13 @@ int forward_step(nvllm_handle* h) {
                                qkv.stride, lw.bqkv, d_pos, d_slots,
                                h->use_rope ? h->cosT : nullptr, h->use_rope ? h->sinT : nullptr, w.q,
                                kp, vp));
+      if (h->pipe_role == 1) NV_CHECK(h, cudaEventRecord(h->pipe_kv[l], st));
     }
     at.kpool = kp;
     at.vpool = vp;
     if (is_prefill) {
+      // second chunk: its queries attend the first chunk's keys of this layer
+      if (h->pipe_role == 2) NV_CHECK(h, cudaStreamWaitEvent(st, h->pipe_kv[l], 0));
       ProfScope ps(h, NVLLM_K_ATTN_PREFILL, attn_bytes, attn_flops, qo_bytes);
       LAUNCH(h, launch_attn_prefill(st, at));
     } else {
@@ -755,6 +766,7 @@ int forward_step(nvllm_handle* h) {
     }
     if (pf.p) pf.m = h->parallel ? (par_scaled ? c.residual_multiplier : 1.f) : m_res;
   }
+  if (h->skip_head) return NVLLM_OK;  // no sequence ends in this chunk: its last residual update is never read
   // final norm on the last token of each sequence only (the reference norms and projects all
   // T rows, generic_model.go:464-470, then keeps row T-1, :595-604)
   if ((rc = tp_reduce_pending(h, &p1, &p2, T))) return rc;
@@ -811,6 +823,85 @@ int forward_step(nvllm_handle* h) {
     }
   }
   h->ws.logits_final = logits;
+  return NVLLM_OK;
+}
+
+// Tensor-parallel prefill of ONE long sequence as two token chunks in flight at once: chunk A
+// (rows [0, r0)) on the handle's stream and communicator, chunk B (rows [r0, T)) on stream2 with
+// the duplicate communicator.  Each chunk is a complete forward pass over its rows — causal
+// attention only needs the earlier chunk's K / V of the same layer, handed over by one event
+// per layer — so B's GEMMs run while A's per-layer all-reduce is on the wire and vice versa
+// (SURVEY.md 8e / hard part 3: "token-chunk pipelining").  The persistent GEMM grids leave 16
+// SMs to the collective kernels.  Only B holds the sequence's last token: A skips the head.
+// NVLLM_TP_PIPE=0 (read at tp_init) or NVLLM_TP_PIPE_MIN_T change when this is used.
+int forward_step_auto(nvllm_handle* h) {
+  const StepLayout L = h->lay;
+  static const int min_T = getenv("NVLLM_TP_PIPE_MIN_T") ? atoi(getenv("NVLLM_TP_PIPE_MIN_T")) : 1024;
+  const int qtile = attn_prefill_qtile(h->adt, h->kvdt, h->hd);
+  const int ts = L.n_qtiles / 2, r0 = ts * qtile;
+  if (!(h->tp > 1 && h->nccl2 && L.prefill && L.n == 1 && !h->profile && !h->moe && L.T >= min_T &&
+        ts >= 1 && r0 < L.T && (r0 % 8) == 0))
+    return forward_step(h);
+  const Workspace W0 = h->ws;
+  cudaStream_t s0 = h->stream;
+  static bool said = false;
+  if (!said && getenv("NVLLM_TP_DEBUG")) {
+    said = true;
+    fprintf(stderr, "[nvllm] rank %d/%d: two-chunk prefill pipeline, rows [0, %d) + [%d, %d)\n", h->rank,
+            h->tp, r0, r0, L.T);
+  }
+  NV_CHECK(h, cudaEventRecord(h->pipe_fork, s0));
+  NV_CHECK(h, cudaStreamWaitEvent(h->stream2, h->pipe_fork, 0));
+  const size_t asz = dt_size(h->adt);
+  int rc = NVLLM_OK;
+  for (int role = 1; role <= 2 && rc == NVLLM_OK; role++) {
+    const int rb = role == 1 ? 0 : r0, Tc = role == 1 ? r0 : L.T - r0;
+    Workspace v = W0;
+    v.x = W0.x + (size_t)rb * h->H;
+    v.xn = (char*)W0.xn + (size_t)rb * h->H * asz;
+    v.q = (char*)W0.q + (size_t)rb * h->q_cols * asz;
+    v.attn_out = (char*)W0.attn_out + (size_t)rb * h->q_cols * asz;
+    v.hbuf = (char*)W0.hbuf + (size_t)rb * h->F * asz;
+    if (W0.tp_buf) v.tp_buf = W0.tp_buf + (size_t)rb * h->H;
+    // split-K partial buffers: one half each
+    v.ws_a_floats = W0.ws_a_floats / 2;
+    v.ws_b_floats = W0.ws_b_floats / 2;
+    if (role == 2) {
+      v.ws_a = W0.ws_a + v.ws_a_floats;
+      v.ws_b = W0.ws_b + v.ws_b_floats;
+      if (W0.ws_c) v.ws_c = W0.ws_c + v.ws_b_floats;
+    }
+    StepLayout Lv = L;
+    Lv.T = Tc;
+    Lv.tokens += rb;
+    Lv.positions += rb;
+    Lv.slots += rb;
+    Lv.tile_seq += role == 1 ? 0 : ts;
+    Lv.tile_q0 += role == 1 ? 0 : ts;
+    Lv.n_qtiles = role == 1 ? ts : L.n_qtiles - ts;
+    h->ws = v;
+    h->lay = Lv;
+    h->stream = role == 1 ? s0 : h->stream2;
+    h->pipe_role = role;
+    h->view_r0 = rb;
+    h->view_T = L.T;
+    h->skip_head = role == 1;
+    h->gemm_max_ctas = std::max(1, h->sm_count - 16);
+    rc = forward_step(h);
+    const float* lf = h->ws.logits_final;
+    h->ws = W0;
+    h->ws.logits_final = lf;
+  }
+  h->lay = L;
+  h->stream = s0;
+  h->pipe_role = 0;
+  h->view_r0 = 0;
+  h->view_T = 0;
+  h->skip_head = false;
+  h->gemm_max_ctas = 0;
+  if (rc) return rc;
+  NV_CHECK(h, cudaEventRecord(h->pipe_join, h->stream2));
+  NV_CHECK(h, cudaStreamWaitEvent(s0, h->pipe_join, 0));
   return NVLLM_OK;
 }
 

@@ -859,7 +859,8 @@ static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* t
     m_tiles = min(a.g_max_tiles, a.M / BT + a.g_experts);  // upper bound; the kernel reads the count
   }
   sc.units = sc.n_tiles * m_tiles * sc.S;
-  const int grid = min(sc.units, max(1, sm_counts[dev]));
+  int grid = min(sc.units, max(1, sm_counts[dev]));
+  if (a.max_ctas > 0 && a.epi != TC5_EPI_RESID) grid = max(1, min(grid, a.max_ctas));
   Tc5Fuse fz{a.rs_ssq, a.rs_parts, a.rs_ld, a.rs_inv_h, a.rs_eps, a.res_x, (bf16*)a.res_xb, a.res_ssq,
              a.res_ssq_ld, a.res_bias, a.res_m, a.res_arrive, a.res_done};
   if (a.epi == TC5_EPI_RESID) {

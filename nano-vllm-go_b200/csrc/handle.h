@@ -107,6 +107,18 @@ struct nvllm_handle {
   int Vl = 0;        // LM-head rows per rank (slot width of the gathered logits), multiple of 8
   int Vl_valid = 0;  // rows of this rank's slice that exist (last rank may be short)
   void* nccl = nullptr;  // ncclComm_t
+  // two-chunk prefill pipeline of a tensor-parallel step (forward.cu): the second chunk runs on
+  // stream2 with its own communicator, so its GEMMs hide the first chunk's all-reduces
+  void* nccl2 = nullptr;
+  cudaStream_t stream2 = nullptr;
+  cudaEvent_t pipe_fork = nullptr, pipe_join = nullptr;
+  std::vector<cudaEvent_t> pipe_kv;  // [L]: the first chunk's K / V rows of layer l are in the pool
+  int pipe_role = 0;       // 0 = plain step, 1 = first chunk (records pipe_kv), 2 = second (waits)
+  int view_r0 = 0;         // first row of the current chunk within the step
+  int view_T = 0;          // rows of the whole step (0 = no chunking)
+  bool skip_head = false;  // the chunk holds no sequence end: no final norm / LM head / sampling
+  int gemm_max_ctas = 0;   // > 0: persistent GEMM grids leave SMs to the collective kernels
+  void* nccl_cur() const { return (pipe_role == 2 && nccl2) ? nccl2 : nccl; }
   // NVLink peer-memory all-reduce (tp.cu): this rank's region, the peers' mapped regions
   float* p2p_peer[8] = {nullptr};  // [rank] base pointers (own entry = p2p_own)
   float* p2p_own = nullptr;
@@ -216,6 +228,7 @@ extern thread_local std::string g_create_error;
 void free_workspace(nvllm_handle* h);
 int ensure_workspace(nvllm_handle* h, int T, int n);
 int forward_step(nvllm_handle* h);  // runs h->lay
+int forward_step_auto(nvllm_handle* h);  // forward_step, or the two-chunk tensor-parallel prefill pipeline
 int prof_collect(nvllm_handle* h);
 
 int set_err(nvllm_handle* h, int code, const char* fmt, ...);

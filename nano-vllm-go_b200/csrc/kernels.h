@@ -55,7 +55,8 @@ struct NormArgs {
   void* y;             // [n_rows, H] dtype ydt (may be null: residual update only)
   int ydt;
   float* y_f32;        // optional extra fp32 copy of y (MoE router input)
-  const int* row_idx;  // optional gather: output row i reads x row row_idx[i]
+  const int* row_idx;  // optional gather: output row i reads x row row_idx[i] - row_bias
+  int row_bias;
   int n_rows;
   int H;
   // mixture-of-experts fusions (moe.cu holds the stand-alone kernels)
@@ -222,6 +223,7 @@ struct Tc5Args {
   float res_m;
   unsigned* res_arrive;  // [n_tiles * m_tiles], zero between launches
   unsigned* res_done;
+  int max_ctas;  // > 0: cap of the persistent grid (leave SMs to a concurrent collective)
   // weights of a later GEMM to pull into L2 while this one waits / drains (decode only)
   const void* pf_ptr;
   size_t pf_bytes;

@@ -371,7 +371,7 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
   bool used_graph = false;
   if (!is_prefill && graph_usable(h, n)) {
     if ((rc = graphed_step(h, 1, [] { return (int)NVLLM_OK; }, &used_graph))) return rc;
-  } else if ((rc = forward_step(h))) {
+  } else if ((rc = is_prefill ? forward_step_auto(h) : forward_step(h))) {
     return rc;
   }
   NV_CHECK(h, cudaEventRecord(h->ev1, st));
@@ -519,7 +519,7 @@ extern "C" int nvllm_rerun(nvllm_handle* h, nvllm_run_stats* stats) {
   h->res_nb = h->spec_nb;
   NV_CHECK(h, cudaEventRecord(h->ev0, h->stream));
   h->launches = 0;
-  int rc = forward_step(h);
+  int rc = forward_step_auto(h);
   if (rc) return rc;
   NV_CHECK(h, cudaEventRecord(h->ev1, h->stream));
   h->resident_ok = true;

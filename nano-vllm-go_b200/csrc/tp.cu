@@ -38,6 +38,8 @@ struct NcclApi {
   ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t,
                             cudaStream_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  // optional (NCCL >= 2.18): a second communicator over the same ranks for the pipelined prefill
+  ncclResult_t (*CommSplit)(ncclComm_t, int, int, ncclComm_t*, ncclConfig_t*) = nullptr;
   std::string why;
 };
 
@@ -68,6 +70,7 @@ NcclApi* nccl_api() {
     SYM(AllGather, "ncclAllGather");
     SYM(GetErrorString, "ncclGetErrorString");
 #undef SYM
+    api.CommSplit = reinterpret_cast<decltype(api.CommSplit)>(dlsym(api.lib, "ncclCommSplit"));
   });
   return &api;
 }
@@ -183,6 +186,26 @@ int tp_init(nvllm_handle* h, const uint8_t* id_bytes) {
     return set_err(h, NVLLM_ERR_NCCL, "ncclCommInitRank(rank %d of %d): %s", h->rank, h->tp,
                    a->GetErrorString(r));
   h->nccl = comm;
+  // second communicator (same ranks) + stream + events for the two-chunk prefill pipeline
+  // (forward.cu): two chunks may then have collectives in flight at the same time.  Every rank
+  // takes the same branch (same library, same environment).
+  if (a->CommSplit && !(getenv("NVLLM_TP_PIPE") && atoi(getenv("NVLLM_TP_PIPE")) == 0)) {
+    ncclComm_t c2 = nullptr;
+    if (a->CommSplit(comm, 0, h->rank, &c2, nullptr) == ncclSuccess && c2) {
+      h->nccl2 = c2;
+      bool ok = cudaStreamCreateWithFlags(&h->stream2, cudaStreamNonBlocking) == cudaSuccess &&
+                cudaEventCreateWithFlags(&h->pipe_fork, cudaEventDisableTiming) == cudaSuccess &&
+                cudaEventCreateWithFlags(&h->pipe_join, cudaEventDisableTiming) == cudaSuccess;
+      h->pipe_kv.resize(h->L, nullptr);
+      for (int l = 0; ok && l < h->L; l++)
+        ok = cudaEventCreateWithFlags(&h->pipe_kv[l], cudaEventDisableTiming) == cudaSuccess;
+      if (!ok) {
+        (void)cudaGetLastError();
+        a->CommDestroy(c2);
+        h->nccl2 = nullptr;
+      }
+    }
+  }
   p2p_setup(h);  // optional: on failure the NCCL all-reduce stays in use
   return NVLLM_OK;
 }
@@ -193,8 +216,18 @@ void tp_destroy(nvllm_handle* h) {
   if (h->p2p_own) cudaFree(h->p2p_own);
   h->p2p_own = nullptr;
   h->p2p_ok = false;
+  for (auto e : h->pipe_kv)
+    if (e) cudaEventDestroy(e);
+  h->pipe_kv.clear();
+  if (h->pipe_fork) cudaEventDestroy(h->pipe_fork);
+  if (h->pipe_join) cudaEventDestroy(h->pipe_join);
+  if (h->stream2) cudaStreamDestroy(h->stream2);
+  h->pipe_fork = h->pipe_join = nullptr;
+  h->stream2 = nullptr;
   if (!h->nccl) return;
   NcclApi* a = nccl_api();
+  if (a->lib && h->nccl2) a->CommDestroy((ncclComm_t)h->nccl2);
+  h->nccl2 = nullptr;
   if (a->lib) a->CommDestroy((ncclComm_t)h->nccl);
   h->nccl = nullptr;
 }
@@ -202,7 +235,7 @@ void tp_destroy(nvllm_handle* h) {
 int tp_all_reduce(nvllm_handle* h, void* buf, size_t count, bool bf16_wire) {
   NcclApi* a = nccl_api();
   ncclResult_t r = a->AllReduce(buf, buf, count, bf16_wire ? ncclBfloat16 : ncclFloat32, ncclSum,
-                                (ncclComm_t)h->nccl, h->stream);
+                                (ncclComm_t)h->nccl_cur(), h->stream);
   if (r != ncclSuccess)
     return set_err(h, NVLLM_ERR_NCCL, "ncclAllReduce: %s", a->GetErrorString(r));
   return NVLLM_OK;
@@ -211,7 +244,7 @@ int tp_all_reduce(nvllm_handle* h, void* buf, size_t count, bool bf16_wire) {
 int tp_all_gather_f32(nvllm_handle* h, float* buf, size_t count_per_rank) {
   NcclApi* a = nccl_api();
   ncclResult_t r = a->AllGather(buf + (size_t)h->rank * count_per_rank, buf, count_per_rank,
-                                ncclFloat32, (ncclComm_t)h->nccl, h->stream);
+                                ncclFloat32, (ncclComm_t)h->nccl_cur(), h->stream);
   if (r != ncclSuccess)
     return set_err(h, NVLLM_ERR_NCCL, "ncclAllGather: %s", a->GetErrorString(r));
   return NVLLM_OK;

@@ -52,14 +52,17 @@ def main():
     # two sequences of different length in one ragged batch, crossing a KV block boundary
     prompts = [W.random_prompt(cfg.vocab_size, 250, 4321), W.random_prompt(cfg.vocab_size, 37, 4322)]
     steps = 8
+    bts = [[0, 1], [2]]
+    if os.environ.get("TP_SINGLE"):
+        # ONE sequence long enough for the two-chunk prefill pipeline (NVLLM_TP_PIPE_MIN_T)
+        prompts, steps, bts = [W.random_prompt(cfg.vocab_size, 300, 4321)], 4, [[0, 1]]
     refs = [orc.greedy(p, steps) for p in prompts]
     toks = [[int(t) for t in p] for p in prompts]
-    bts = [[0, 1], [2]]
     worst = 0.0
     for i in range(steps):
-        out, logits = run.run_flat(toks, is_prefill=(i == 0), num_cached=[0, 0], block_tables=bts,
-                                   temperature=[0.0, 0.0], want_logits=True)
-        for s in range(2):
+        out, logits = run.run_flat(toks, is_prefill=(i == 0), num_cached=[0] * len(toks), block_tables=bts,
+                                   temperature=[0.0] * len(toks), want_logits=True)
+        for s in range(len(toks)):
             ref_toks, ref_logits = refs[s]
             err = rel_err(logits[s], ref_logits[i])
             worst = max(worst, err)
@@ -72,10 +75,10 @@ def main():
                     f"rank {rank} {case} seq {s} step {i}: token {out[s]} != {ref_toks[i]}"
             toks[s].append(int(ref_toks[i]))
     # temperature sampling through the gathered (rank-major) logits
-    uni = [0.3, 0.9]
+    uni = [0.3, 0.9][:len(toks)]
     out, logits = run.run_flat(toks, is_prefill=False, num_cached=None, block_tables=bts,
-                               temperature=[0.8, 1.3], uniforms=uni, want_logits=True)
-    for s in range(2):
+                               temperature=[0.8, 1.3][:len(toks)], uniforms=uni, want_logits=True)
+    for s in range(len(toks)):
         assert int(out[s]) == O.sample(logits[s], None, [0.8, 1.3][s], u=uni[s]), "sampled token differs"
     prof_ok = run.last_stats.kernel_launches > 0
     run.close()
