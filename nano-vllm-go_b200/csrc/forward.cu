@@ -833,7 +833,8 @@ int forward_step(nvllm_handle* h) {
 // per layer — so B's GEMMs run while A's per-layer all-reduce is on the wire and vice versa
 // (SURVEY.md 8e / hard part 3: "token-chunk pipelining").  The persistent GEMM grids leave 16
 // SMs to the collective kernels.  Only B holds the sequence's last token: A skips the head.
-// NVLLM_TP_PIPE=0 (read at tp_init) or NVLLM_TP_PIPE_MIN_T change when this is used.
+// Opt-in: NVLLM_TP_PIPE=1 (read at tp_init; measured slower at tp 2, see tp.cu), threshold
+// NVLLM_TP_PIPE_MIN_T.
 int forward_step_auto(nvllm_handle* h) {
   const StepLayout L = h->lay;
   static const int min_T = getenv("NVLLM_TP_PIPE_MIN_T") ? atoi(getenv("NVLLM_TP_PIPE_MIN_T")) : 1024;

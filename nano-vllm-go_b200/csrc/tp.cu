@@ -189,7 +189,11 @@ int tp_init(nvllm_handle* h, const uint8_t* id_bytes) {
   // second communicator (same ranks) + stream + events for the two-chunk prefill pipeline
   // (forward.cu): two chunks may then have collectives in flight at the same time.  Every rank
   // takes the same branch (same library, same environment).
-  if (a->CommSplit && !(getenv("NVLLM_TP_PIPE") && atoi(getenv("NVLLM_TP_PIPE")) == 0)) {
+  // OFF by default (NVLLM_TP_PIPE=1 turns it on): measured at tp 2 on Falcon-7B the pipelined
+  // 2048-token prefill is slower (19.9 vs 17.7 ms) — two chunks' persistent GEMMs contend for the
+  // SMs (the second kernel's first CTAs land on the SMs meant for the collective), which costs
+  // more than the 15 % of exposed all-reduce it hides.
+  if (a->CommSplit && getenv("NVLLM_TP_PIPE") && atoi(getenv("NVLLM_TP_PIPE")) != 0) {
     ncclComm_t c2 = nullptr;
     if (a->CommSplit(comm, 0, h->rank, &c2, nullptr) == ncclSuccess && c2) {
       h->nccl2 = c2;

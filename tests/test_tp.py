@@ -91,5 +91,5 @@ def test_tp_two_chunk_prefill_pipeline_matches_oracle(tp, case, prec):
     sequential blocks with two reductions per layer (llama), SIMT and tcgen05 attention."""
     if _n_gpus() < tp:
         pytest.skip(f"needs {tp} GPUs")
-    _launch(tp, case, prec, extra_env={"TP_SINGLE": "1", "NVLLM_TP_PIPE_MIN_T": "64"},
+    _launch(tp, case, prec, extra_env={"TP_SINGLE": "1", "NVLLM_TP_PIPE": "1", "NVLLM_TP_PIPE_MIN_T": "64"},
             expect="two-chunk prefill pipeline")
