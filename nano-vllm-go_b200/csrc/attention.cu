@@ -391,13 +391,6 @@ static cudaError_t decode_dispatch(cudaStream_t st, const AttnArgs& a) {
   return cudaErrorInvalidValue;
 }
 
-static bool attn_use_sk() {
-  static const bool use_sk = [] {
-    const char* e = getenv("NVLLM_ATTN_SK");
-    return e ? atoi(e) != 0 : false;
-  }();
-  return use_sk;
-}
 // true: launch_attn_decode takes the QKV GEMM partials (AttnArgs::qkv_p) and does the RoPE +
 // KV append of the decoded token itself; the caller then skips launch_rope_kv
 bool attn_decode_fuses_rope(int qdt, int kvdt, int hd) {
@@ -405,15 +398,12 @@ bool attn_decode_fuses_rope(int qdt, int kvdt, int hd) {
     const char* e = getenv("NVLLM_FUSE_ROPE");
     return e ? atoi(e) != 0 : true;
   }();
-  return on && attn_mma_supported(qdt, kvdt, hd) && !attn_use_sk();
+  return on && attn_mma_supported(qdt, kvdt, hd);
 }
 
 cudaError_t launch_attn_decode(cudaStream_t st, const AttnArgs& a) {
   if (a.n_seqs <= 0) return cudaSuccess;
-  const bool use_sk = attn_use_sk();
   if (a.qkv_p && !attn_decode_fuses_rope(a.qdt, a.kvdt, a.hd)) return cudaErrorInvalidValue;
-  if (attn_mma_supported(a.qdt, a.kvdt, a.hd) && a.tickets && use_sk)
-    return launch_attn_decode_sk(st, a, a.tickets, a.sm_count, a.total_tiles);
   if (attn_mma_supported(a.qdt, a.kvdt, a.hd)) {
     // small head groups: TMA-fed, keys-as-M-rows kernel (attention_dec.cu); Falcon's 71-head
     // MQA group keeps the 16-query-row kernel

@@ -572,392 +572,8 @@ cudaError_t launch_attn_decode_mma(cudaStream_t st, const AttnArgs& a_in) {
   AttnArgs a = a_in;
   a.ablate = abl;
   const int G = a.nh / a.nkv, chunks = (G + 15) / 16;
-  static const int bn_env = getenv("NVLLM_ATTN_BN") ? atoi(getenv("NVLLM_ATTN_BN")) : 0;
-  if (a.hd == 64) {
-    if (bn_env == 64) return decode_launch<64, 64, 3>(st, a, G, chunks);
-    if (bn_env == 644) return decode_launch<64, 64, 4>(st, a, G, chunks);
-    return decode_launch<64, 128, 3>(st, a, G, chunks);
-  }
+  if (a.hd == 64) return decode_launch<64, 128, 3>(st, a, G, chunks);
   return decode_launch<128, 64, 3>(st, a, G, chunks);
-}
-
-// ------------------------------------------------------------------ decode, stream-K
-// EXPERIMENTAL (NVLLM_ATTN_SK=1; default off): parity-green, but on B200 it measured 24.7 us
-// per layer against 22.4 us for attn_decode_mma_kernel at cfg2 (64 seqs, ctx ~520) — the
-// lock-step CTAs see a longer load latency than the dynamically scheduled 512-CTA grid.
-// The decode step's attention is a pure HBM stream (every K/V byte of every sequence once),
-// so what matters is that all SMs stream for the same time.  One CTA per (sequence, kv head)
-// cannot do that: 512 CTAs over 296 resident slots is 1.7 waves.  Here the (sequence, kv head,
-// head chunk, key tile) space is flattened and cut into gridDim.x equal contiguous ranges,
-// one per resident CTA; the cp.async ring runs straight through the range.  A CTA whose range
-// covers only part of an item writes an unnormalised partial (o, m, l) record; the last CTA
-// to finish an item (atomic ticket) merges the records in CTA order — deterministic — and
-// writes the output, so there is no separate combine kernel.
-struct SkCursor {
-  int s, kc, tile, tiles_s;
-  long long x;
-};
-
-// K/V tiles arrive by TMA (one elected lane issues 2 * HD/64 bulk tensor copies per tile,
-// SWIZZLE_128B, completion on an mbarrier) instead of 16 cp.async + address arithmetic per
-// thread per tile: the ncu instruction mix of the cp.async version was 55 % integer / address
-// work and the kernel was issue-bound at 2.2 TB/s.
-template <int HD, int BN, int STAGES>
-__global__ void __launch_bounds__(128)
-attn_decode_sk_kernel(const __grid_constant__ CUtensorMap tmK, const __grid_constant__ CUtensorMap tmV,
-                      AttnArgs a, int G, int chunks, int red_rows, int* __restrict__ tickets,
-                      Trace tr) {
-  const unsigned long long t_entry = trace_on(tr) ? gtime() : 0ull;
-  pdl_launch_dependents();
-  constexpr int PANELS = HD / 64;
-  constexpr uint32_t TILE_BYTES = BN * HD * 2;
-  constexpr int WK = BN / 4;  // keys per warp per tile
-  constexpr int QSLOT = 16 * HD * 2;
-  constexpr int RS = HD + 2;
-  extern __shared__ uint8_t smem_raw[];
-  const uint32_t raw = smem_u32(smem_raw);
-  const uint32_t sK = (raw + 1023u) & ~1023u;  // SWIZZLE_128B panels need 1024 B alignment
-  uint8_t* smem = smem_raw + (sK - raw);
-  const uint32_t sV = sK + STAGES * TILE_BYTES;
-  const uint32_t sQ = sV + STAGES * TILE_BYTES;  // 3 slots: the issue side runs <= 2 tiles ahead
-  float* red = reinterpret_cast<float*>(smem + 2 * STAGES * TILE_BYTES + 3 * QSLOT);
-  int* pfx = reinterpret_cast<int*>(red + 4 * red_rows * RS);  // [n_seqs + 1]
-  const uint32_t bars = sQ + 3 * QSLOT + 4 * red_rows * RS * 4 + (((a.n_seqs + 1) * 4 + 7) & ~7);
-  __shared__ int s_ticket;
-  const int n = a.n_seqs;
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int g = lane >> 2, t = lane & 3;
-  const int F = a.nkv * chunks;  // items per sequence
-
-  if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; s++) mbar_init(bars + 8 * s, 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmK) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmV) : "memory");
-  }
-  // ---- tiles prefix over the sequences (seq_len is step state: stable before the wait)
-  if (warp == 0) {
-    const int per = (n + 31) / 32;
-    int sum = 0;
-    for (int i = 0; i < per; i++) {
-      const int s = lane * per + i;
-      if (s < n) sum += (a.seq_len[s] + BN - 1) / BN;
-    }
-    int incl = sum;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const int v = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += v;
-    }
-    int run = incl - sum;
-    if (lane == 0) pfx[0] = 0;
-    for (int i = 0; i < per; i++) {
-      const int s = lane * per + i;
-      if (s < n) {
-        run += (a.seq_len[s] + BN - 1) / BN;
-        pfx[s + 1] = run;
-      }
-    }
-  }
-  __syncthreads();
-  const long long Ttot = (long long)pfx[n] * F;
-  const long long Gr = gridDim.x, c = blockIdx.x;
-  const long long x_begin = c * Ttot / Gr, x_end = (c + 1) * Ttot / Gr;
-  if (x_begin >= x_end) {
-    pdl_wait();
-    return;
-  }
-  auto cursor_at = [&](long long x) {
-    SkCursor cu;
-    int lo = 0, hi = n - 1;  // last s with pfx[s] * F <= x
-    while (lo < hi) {
-      const int mid = (lo + hi + 1) >> 1;
-      if ((long long)pfx[mid] * F <= x) lo = mid;
-      else hi = mid - 1;
-    }
-    cu.s = lo;
-    cu.tiles_s = pfx[lo + 1] - pfx[lo];
-    const long long y = x - (long long)pfx[lo] * F;
-    cu.kc = (int)(y / cu.tiles_s);
-    cu.tile = (int)(y % cu.tiles_s);
-    cu.x = x;
-    return cu;
-  };
-  auto advance = [&](SkCursor& cu) {
-    cu.x++;
-    if (++cu.tile == cu.tiles_s) {
-      cu.tile = 0;
-      if (++cu.kc == F) {
-        cu.kc = 0;
-        cu.s++;
-        cu.tiles_s = (cu.s < n) ? pfx[cu.s + 1] - pfx[cu.s] : 1;
-      }
-    }
-  };
-  // K/V tile of the cursor -> stage (warp 0 only; one elected lane issues).  Rows past the
-  // sequence end hold whatever the pool block holds (zeros or finite stale values): their
-  // scores are masked to -inf, so they contribute exactly 0.
-  auto issue_kv = [&](const SkCursor& cu, int stage) {
-    const int kvh = cu.kc / chunks;
-    const int k0 = cu.tile * BN;
-    const int blk = a.block_tables[(size_t)cu.s * a.max_blocks + k0 / KV_BLOCK];
-    const int row = (blk * a.nkv + kvh) * KV_BLOCK + (k0 % KV_BLOCK);
-    const uint32_t full = bars + 8 * stage;
-    if (elect_one()) {
-      mbar_expect_tx(full, 2 * TILE_BYTES);
-#pragma unroll
-      for (int p = 0; p < PANELS; p++) {
-        tma_load_2d(sK + stage * TILE_BYTES + p * (BN * 128), &tmK, full, p * 64, row);
-        tma_load_2d(sV + stage * TILE_BYTES + p * (BN * 128), &tmV, full, p * 64, row);
-      }
-    }
-    __syncwarp();
-  };
-  // Q rows of the segment the cursor opens -> slot (all threads, cp.async)
-  auto issue_q = [&](const SkCursor& cu, int qslot) {
-    const int kvh = cu.kc / chunks, chunk = cu.kc % chunks;
-    const int h0 = kvh * G + chunk * 16;
-    const int rows = min(16, G - chunk * 16);
-    load_tile<HD, 128>(sQ + qslot * QSLOT,
-                       (const bf16*)a.q + (size_t)cu.s * a.nh * HD + (size_t)h0 * HD, 16, rows, HD);
-    cp_async_commit();
-  };
-  auto tile_is_old = [&](const SkCursor& cu) {
-    return (cu.tile + 1) * BN <= a.seq_len[cu.s] - 1;
-  };
-  const int n_local = (int)(x_end - x_begin);
-
-  // ---- prologue: K/V tiles written by earlier steps start before the dependency resolves
-  SkCursor ci = cursor_at(x_begin);
-  unsigned pre_mask = 0;
-  if (warp == 0) {
-    SkCursor cp = ci;
-#pragma unroll
-    for (int s = 0; s < STAGES - 1; s++) {
-      if (s < n_local) {
-        if (tile_is_old(cp)) {
-          issue_kv(cp, s);
-          pre_mask |= 1u << s;
-        }
-        advance(cp);
-      }
-    }
-  }
-  pdl_wait();
-  const unsigned long long t_wait = trace_on(tr) ? gtime() : 0ull;
-  int seg_issue = -1;  // index of the segment the issue cursor is in
-#pragma unroll
-  for (int s = 0; s < STAGES - 1; s++) {
-    if (s < n_local) {
-      if (s == 0 || ci.tile == 0) issue_q(ci, (++seg_issue) % 3);
-      if (warp == 0 && !(pre_mask >> s & 1)) issue_kv(ci, s);
-      advance(ci);
-    }
-  }
-
-  uint32_t qf[HD / 16][4];
-  float o[HD / 8][4];
-  float m[2], l[2];
-  const float scale_log2 = a.scale * 1.4426950408889634f;
-  SkCursor cc = cursor_at(x_begin);
-  int seg = -1;
-  bool seg_from_start = false;
-
-  for (int j = 0; j < n_local; j++) {
-    const int stage = j % STAGES;
-    const bool opens = (j == 0) || cc.tile == 0;
-    if (opens) cp_async_wait<0>();  // this segment's Q (issued >= 1 iteration ago, or prologue)
-    __syncthreads();  // everyone finished tile j - 1: its stage may be refilled; Q visible
-    if (j + STAGES - 1 < n_local) {
-      if (ci.tile == 0) issue_q(ci, (++seg_issue) % 3);
-      if (warp == 0) issue_kv(ci, (j + STAGES - 1) % STAGES);
-      advance(ci);
-    }
-    const int len = a.seq_len[cc.s];
-    if (opens) {
-      seg++;
-      seg_from_start = cc.tile == 0;
-      const uint32_t q = sQ + (seg % 3) * QSLOT;
-      const int mi = lane >> 3, lr = lane & 7;
-#pragma unroll
-      for (int ks = 0; ks < HD / 16; ks++)
-        ldsm_x4(q + swz<HD>(lr + (mi & 1) * 8, ks * 2 + (mi >> 1)), qf[ks][0], qf[ks][1], qf[ks][2],
-                qf[ks][3]);
-#pragma unroll
-      for (int dn = 0; dn < HD / 8; dn++)
-#pragma unroll
-        for (int i = 0; i < 4; i++) o[dn][i] = 0.f;
-      m[0] = m[1] = -INFINITY;
-      l[0] = l[1] = 0.f;
-    }
-    mbar_wait(bars + 8 * stage, (j / STAGES) & 1);
-    const int k0 = cc.tile * BN;
-    const int limit[2] = {len - 1, len - 1};
-    attn_block<HD, WK / 8, BN>(qf, sK + stage * TILE_BYTES, sV + stage * TILE_BYTES, warp * WK,
-                               k0 + warp * WK, limit, k0 + BN > len, scale_log2, m, l, o);
-    const bool seg_ends = (cc.tile == cc.tiles_s - 1) || (j == n_local - 1);
-    if (seg_ends) {
-      const bool to_end = cc.tile == cc.tiles_s - 1;
-      const int kvh = cc.kc / chunks, chunk = cc.kc % chunks;
-      const int h0 = kvh * G + chunk * 16;
-      const int rows = min(16, G - chunk * 16);
-#pragma unroll
-      for (int i = 0; i < 2; i++) {
-        l[i] += __shfl_xor_sync(0xffffffffu, l[i], 1);
-        l[i] += __shfl_xor_sync(0xffffffffu, l[i], 2);
-      }
-      // merge the 4 warps (each covered different keys) through shared memory
-#pragma unroll
-      for (int i = 0; i < 2; i++) {
-        const int r = g + 8 * i;
-        if (r < rows) {
-          float* rr = red + ((size_t)warp * red_rows + r) * RS;
-#pragma unroll
-          for (int dn = 0; dn < HD / 8; dn++) {
-            rr[dn * 8 + 2 * t] = o[dn][2 * i];
-            rr[dn * 8 + 2 * t + 1] = o[dn][2 * i + 1];
-          }
-          if (t == 0) {
-            rr[HD] = m[i];
-            rr[HD + 1] = l[i];
-          }
-        }
-      }
-      __syncthreads();
-      const bool whole = seg_from_start && to_end;
-      const int item = cc.s * F + cc.kc;
-      float* rec = a.ws + ((size_t)(2 * c + (seg == 0 ? 0 : 1)) * 16) * RS;
-      for (int idx = threadIdx.x; idx < rows * HD; idx += 128) {
-        const int r = idx / HD, d = idx % HD;
-        float mn = -INFINITY;
-#pragma unroll
-        for (int w = 0; w < 4; w++) mn = fmaxf(mn, red[((size_t)w * red_rows + r) * RS + HD]);
-        float lt = 0.f, at = 0.f;
-#pragma unroll
-        for (int w = 0; w < 4; w++) {
-          const float* rr = red + ((size_t)w * red_rows + r) * RS;
-          const float cf = (rr[HD] == -INFINITY) ? 0.f : exp2f((rr[HD] - mn) * scale_log2);
-          lt += rr[HD + 1] * cf;
-          at += rr[d] * cf;
-        }
-        if (whole) {
-          ((bf16*)a.out)[(size_t)cc.s * a.nh * HD + (size_t)(h0 + r) * HD + d] =
-              __float2bfloat16_rn(at / lt);
-        } else {
-          rec[r * RS + d] = at;
-          if (d == 0) {
-            rec[r * RS + HD] = mn;  // raw score units; merged with scale_log2 below
-            rec[r * RS + HD + 1] = lt;
-          }
-        }
-      }
-      if (!whole) {
-        // publish the record, take a ticket; the last part of the item merges
-        const long long item_x0 = ((long long)pfx[cc.s] * F) + (long long)cc.kc * cc.tiles_s;
-        const long long item_x1 = item_x0 + cc.tiles_s - 1;
-        const int c_first = (int)(((item_x0 + 1) * Gr + Ttot - 1) / Ttot - 1);
-        const int c_last = (int)(((item_x1 + 1) * Gr + Ttot - 1) / Ttot - 1);
-        const int first_slot = ((long long)c_first * Ttot / Gr < item_x0) ? 1 : 0;
-        __syncthreads();  // all records written (CTA scope) ...
-        if (threadIdx.x == 0) {
-          __threadfence();  // ... and published at GPU scope (fences are cumulative)
-          s_ticket = atomicAdd(tickets + item, 1);
-          __threadfence();
-        }
-        __syncthreads();
-        if (s_ticket == c_last - c_first) {
-          const int P = c_last - c_first + 1;
-          for (int idx = threadIdx.x; idx < rows * HD; idx += 128) {
-            const int r = idx / HD, d = idx % HD;
-            float at;
-            if (P <= 4) {
-              // all parts' (m, l, o[d]) loads in flight together: one L2 round trip
-              float pm[4], pl[4], po[4];
-#pragma unroll
-              for (int q = 0; q < 4; q++) {
-                const int cp = min(c_first + q, c_last);
-                const int slot = (cp == c_first) ? first_slot : 0;
-                const float* rp = a.ws + ((size_t)(2 * cp + slot) * 16 + r) * RS;
-                pm[q] = __ldcg(rp + HD);
-                pl[q] = __ldcg(rp + HD + 1);
-                po[q] = __ldcg(rp + d);
-              }
-              float mn = -INFINITY;
-#pragma unroll
-              for (int q = 0; q < 4; q++)
-                if (q < P) mn = fmaxf(mn, pm[q]);
-              float lt = 0.f, acc = 0.f;
-#pragma unroll
-              for (int q = 0; q < 4; q++)
-                if (q < P) {
-                  const float cf = (pm[q] == -INFINITY) ? 0.f : exp2f((pm[q] - mn) * scale_log2);
-                  lt += pl[q] * cf;
-                  acc += po[q] * cf;
-                }
-              at = acc / lt;
-            } else {
-              float mn = -INFINITY;
-              for (int cp = c_first; cp <= c_last; cp++) {
-                const int slot = (cp == c_first) ? first_slot : 0;
-                const float* rp = a.ws + ((size_t)(2 * cp + slot) * 16 + r) * RS;
-                mn = fmaxf(mn, __ldcg(rp + HD));
-              }
-              float lt = 0.f, acc = 0.f;
-              for (int cp = c_first; cp <= c_last; cp++) {
-                const int slot = (cp == c_first) ? first_slot : 0;
-                const float* rp = a.ws + ((size_t)(2 * cp + slot) * 16 + r) * RS;
-                const float mp = __ldcg(rp + HD);
-                const float cf = (mp == -INFINITY) ? 0.f : exp2f((mp - mn) * scale_log2);
-                lt += __ldcg(rp + HD + 1) * cf;
-                acc += __ldcg(rp + d) * cf;
-              }
-              at = acc / lt;
-            }
-            ((bf16*)a.out)[(size_t)cc.s * a.nh * HD + (size_t)(h0 + r) * HD + d] =
-                __float2bfloat16_rn(at);
-          }
-          if (threadIdx.x == 0) tickets[item] = 0;  // re-arm for the next step
-        }
-      }
-    }
-    advance(cc);
-  }
-  cp_async_wait<0>();
-  if (threadIdx.x == 0) trace_rec(tr, t_entry, t_wait, 0);
-}
-
-template <int HD, int BN, int STAGES>
-static cudaError_t decode_sk_launch(cudaStream_t st, const AttnArgs& a, int G, int chunks,
-                                    int* tickets, int grid) {
-  const int red_rows = min(16, G);
-  const size_t smem = 1024 + (size_t)2 * STAGES * BN * HD * 2 + (size_t)3 * 16 * HD * 2 +
-                      (size_t)4 * red_rows * (HD + 2) * 4 + (size_t)(((a.n_seqs + 1) * 4 + 7) & ~7) +
-                      8 * STAGES;
-  const int pool_rows = a.pool_blocks * a.nkv * KV_BLOCK;
-  const TmaDesc* tk = tma_map_cached(a.kpool, pool_rows, HD, BN);
-  const TmaDesc* tv = tma_map_cached(a.vpool, pool_rows, HD, BN);
-  if (!tk || !tv) return cudaErrorInvalidValue;
-  cudaError_t e = cudaFuncSetAttribute(attn_decode_sk_kernel<HD, BN, STAGES>,
-                                       cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
-  (void)launch_k(attn_decode_sk_kernel<HD, BN, STAGES>, dim3(grid), dim3(128), smem, st,
-                 *reinterpret_cast<const CUtensorMap*>(tk), *reinterpret_cast<const CUtensorMap*>(tv),
-                 a, G, chunks, red_rows, tickets, next_trace(4));
-  return cudaGetLastError();
-}
-
-// floats of partial-record workspace / ints of tickets the stream-K kernel needs
-size_t attn_decode_sk_ws_floats(int hd, int sm_count) {
-  return (size_t)2 * (2 * sm_count) * 16 * (hd + 2);
-}
-cudaError_t launch_attn_decode_sk(cudaStream_t st, const AttnArgs& a, int* tickets, int sm_count,
-                                  long long total_tiles_hint) {
-  if (a.n_seqs <= 0) return cudaSuccess;
-  const int G = a.nh / a.nkv, chunks = (G + 15) / 16;
-  long long grid = 2LL * sm_count;
-  if (total_tiles_hint > 0 && total_tiles_hint < grid) grid = total_tiles_hint;
-  if (a.hd == 64) return decode_sk_launch<64, 128, 3>(st, a, G, chunks, tickets, (int)grid);
-  return decode_sk_launch<128, 64, 3>(st, a, G, chunks, tickets, (int)grid);
 }
 
 }  // namespace nvllm

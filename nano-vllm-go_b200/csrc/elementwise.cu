@@ -99,20 +99,6 @@ __global__ void __launch_bounds__(512) norm_kernel(NormArgs a, Trace tr) {
     if (a.p1 && a.bias1) load8(a.bias1 + i0, bias1_0);
     if (a.p2 && a.bias2) load8(a.bias2 + i0, bias2_0);
   }
-  if (a.pf_bytes) {
-    // immutable weights: legal before the dependency resolves.  16 KB pieces, spread over the
-    // grid; the GEMM's TMA loads then hit L2.
-    constexpr size_t PIECE = 16384;
-    const size_t pieces = (a.pf_bytes + PIECE - 1) / PIECE;
-    for (size_t pc = (size_t)blockIdx.x * blockDim.x + threadIdx.x; pc < pieces;
-         pc += (size_t)gridDim.x * blockDim.x) {
-      const size_t o = pc * PIECE;
-      const uint32_t sz = (uint32_t)((a.pf_bytes - o < PIECE ? a.pf_bytes - o : PIECE) & ~(size_t)15);
-      if (sz)
-        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"((const char*)a.pf_ptr + o), "r"(sz)
-                     : "memory");
-    }
-  }
   pdl_wait();
   const unsigned long long t_wait = trace_on(tr) ? gtime() : 0ull;
   const int orow = blockIdx.x;

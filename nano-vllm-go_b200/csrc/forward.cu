@@ -24,7 +24,7 @@ void free_workspace(nvllm_handle* h) {
   Workspace& w = h->ws;
   h->drop_graphs();  // the captured decode steps hold these pointers
   void* ptrs[] = {w.tp_buf, w.x, w.xn, w.xn_f32, w.ws_a, w.ws_b, w.ws_c, w.q, w.attn_out, w.hbuf, w.xn_last,
-                  w.xb, w.ssq, w.res_ctr, w.chain_ctr, w.logits_p, w.logits, w.attn_ws, w.attn_tickets, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
+                  w.xb, w.ssq, w.res_ctr, w.chain_ctr, w.logits_p, w.logits, w.attn_ws, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
                   w.sort.counts, w.sort.offsets, w.sort.cursor, w.sort.sorted_pair, w.sort.pair_row,
                   w.sort.a_rows, w.sort.tile_expert, w.sort.tile_row0, w.sort.tile_rows,
                   w.sort.n_tiles, w.moe_Y, w.moe_y, w.moe_xs};
@@ -93,15 +93,8 @@ int ensure_workspace(nvllm_handle* h, int T, int n) {
   w.logits_p_floats = (size_t)std::max(nc, 64) * lcols;
   WS(w.logits_p, w.logits_p_floats * 4);
   WS(w.logits, (size_t)nc * lcols * h->tp * 4);
-  w.attn_ws_floats = std::max((size_t)nc * h->nh * 32 * (h->hd + 2),
-                              attn_decode_sk_ws_floats(h->hd, h->sm_count));
+  w.attn_ws_floats = (size_t)nc * h->nh * 32 * (h->hd + 2);
   WS(w.attn_ws, w.attn_ws_floats * 4);
-  {
-    const size_t nt = (size_t)nc * h->nkv * ((h->nh / h->nkv + 15) / 16);
-    WS(w.attn_tickets, nt * 4);
-    if (cudaMemsetAsync(w.attn_tickets, 0, nt * 4, h->stream) != cudaSuccess)
-      return set_err(h, NVLLM_ERR_CUDA, "memset(attention tickets) failed");
-  }
   WS(w.out_tokens, (size_t)nc * 4);
   WS(w.amax, (size_t)nc * 8);
   WS(w.amax_ticket, (size_t)nc * 4);
@@ -378,21 +371,9 @@ static bool resid_gemm_ok(const nvllm_handle* h, int M, int N, int K, int lda) {
 
 static int run_norm(nvllm_handle* h, float* x, Pending* p1, Pending* p2, const float* w,
                     const float* b, void* y, float* y_f32, const int* row_idx, int n_rows,
-                    const RouterArgs* route = nullptr, const void* pf_ptr = nullptr,
-                    size_t pf_bytes = 0) {
+                    const RouterArgs* route = nullptr) {
   NormArgs a{};
   a.x = x;
-  // Experiment, OFF by default (NVLLM_NORM_PF=1): a decode-sized norm is latency-bound and leaves
-  // HBM idle, so it could pull the next GEMM's weights into L2.  Measured on cfg2 decode: the
-  // GEMMs gain 175 -> 168.5 ms but the norm CTAs stay resident until their bulk prefetches
-  // drain, 49 -> 130 ms (1130 -> 1440 us/step).
-  static const bool pf_on = getenv("NVLLM_NORM_PF") && atoi(getenv("NVLLM_NORM_PF")) != 0;
-  static const size_t pf_max = getenv("NVLLM_NORM_PF_MB") ? (size_t)atol(getenv("NVLLM_NORM_PF_MB")) << 20
-                                                           : (size_t)32 << 20;
-  if (pf_on && pf_ptr && n_rows <= 256 && h->wdt == DT_BF16) {
-    a.pf_ptr = pf_ptr;
-    a.pf_bytes = std::min(pf_bytes, pf_max);
-  }
   // algorithmic: x in, y out, and (when a GEMM result is pending) that result once + x back
   double bytes = (double)n_rows * h->H * (4 + dt_size(h->adt)), impl = 0.0;
   if (p1 && p1->p) {
@@ -519,26 +500,8 @@ int forward_step(nvllm_handle* h) {
   at.pool_blocks = h->num_blocks;
   at.total_rows = h->view_T > 0 ? h->view_T : T;
   at.sm_count = h->sm_count;
-  if (!is_prefill) {
-    static const bool use_sk = [] {
-      const char* e = getenv("NVLLM_ATTN_SK");
-      return e ? atoi(e) != 0 : false;
-    }();
-    if (attn_mma_supported(h->adt, h->kvdt, h->hd) && use_sk) {
-      at.n_splits = 1;
-      at.tickets = w.attn_tickets;
-      at.pool_blocks = h->num_blocks;
-      at.sm_count = h->sm_count;
-      const int bn = attn_decode_mma_tile(h->hd);
-      // LOWER bound of the step's key tiles (sum over sequences of ceil(len / bn)): the grid
-      // never exceeds it, so every CTA of the stream-K partition owns at least one tile
-      at.total_tiles = std::max<long long>(n, (L.sum_len + bn - 1) / bn) * h->nkv *
-                       ((h->nh / h->nkv + 15) / 16);
-    } else {
-      at.n_splits = attn_decode_splits(h->adt, h->kvdt, n, h->nh, h->nkv, h->hd, L.max_len,
-                                       h->sm_count);
-    }
-  }
+  if (!is_prefill)
+    at.n_splits = attn_decode_splits(h->adt, h->kvdt, n, h->nh, h->nkv, h->hd, L.max_len, h->sm_count);
   const double qo_bytes = 2.0 * T * h->q_cols * asz;
   const double attn_flops = 4.0 * h->nh * h->hd * L.attn_pairs;
   // algorithmic: every K/V row of the contexts once (+ the new rows appended by a fused decode
@@ -557,8 +520,7 @@ int forward_step(nvllm_handle* h) {
         return rc;
     } else {
       if ((rc = run_norm(h, w.x, &p1, &p2, h->fold ? nullptr : lw.attn_norm_w, lw.attn_norm_b, w.xn,
-                         nullptr, nullptr, T, nullptr, lw.wqkv,
-                         (size_t)h->qkv_cols * H * dt_size(h->wdt))))
+                         nullptr, nullptr, T)))
         return rc;
       if ((rc = run_gemm(h, w.xn, H, lw.wqkv, T, h->qkv_cols, H, 1.f, w.ws_a, w.ws_a_floats,
                          h->qkv_cols, &qkv)))
@@ -625,9 +587,7 @@ int forward_step(nvllm_handle* h) {
       const bool skip_norm = xb_parts > 0 && !h->moe && fold_gemm_ok(h, T, h->w1_cols, H, H);
       if (!skip_norm) {
         if ((rc = run_norm(h, w.x, &p1, nullptr, h->fold ? nullptr : lw.ffn_norm_w, lw.ffn_norm_b,
-                           w.xn, nullptr, nullptr, T, &ra, h->moe ? lw.moe_in : lw.w1,
-                           h->moe ? (size_t)h->E * 2 * h->F * H * dt_size(h->wdt)
-                                  : (size_t)h->w1_cols * H * dt_size(h->wdt))))
+                           w.xn, nullptr, nullptr, T, &ra)))
           return rc;
         xb_parts = 0;
       }
@@ -770,8 +730,7 @@ int forward_step(nvllm_handle* h) {
   // final norm on the last token of each sequence only (the reference norms and projects all
   // T rows, generic_model.go:464-470, then keeps row T-1, :595-604)
   if ((rc = tp_reduce_pending(h, &p1, &p2, T))) return rc;
-  if ((rc = run_norm(h, w.x, &p1, &p2, h->lnf_w, h->lnf_b, w.xn_last, nullptr, d + L.last_row, n,
-                     nullptr, h->lm_head, (size_t)(h->tp > 1 ? h->Vl_valid : h->V) * H * dt_size(h->wdt))))
+  if ((rc = run_norm(h, w.x, &p1, &p2, h->lnf_w, h->lnf_b, w.xn_last, nullptr, d + L.last_row, n)))
     return rc;
   const float alpha = (c.logits_scaling != 0.f) ? 1.0f / c.logits_scaling : 1.f;
   Pending lg;

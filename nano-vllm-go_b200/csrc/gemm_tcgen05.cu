@@ -740,9 +740,9 @@ int tc5_splits(int M, int N, int K, int sm_count) {
   double best_cost = 1e30;
   // The consumer of the partials sums up to 8 slices with one batch of loads (sum_partials8); a
   // 9th slice costs it a second L2 round trip, more than the GEMM gains from the finer split
-  // (cfg2 decode, W2 GEMM K = 8192: S = 9 -> 1105 us/step, capped at 8 -> 1079; 6 -> 1099).
-  // NVLLM_TC5_SMAX overrides the cap.
-  static const int smax = getenv("NVLLM_TC5_SMAX") ? atoi(getenv("NVLLM_TC5_SMAX")) : 8;
+  // (cfg2 decode, W2 GEMM K = 8192: S = 9 -> 1105 us/step, capped at 8 -> 1079; 6 -> 1099 /
+  // 1219 with the fused residual; 4 -> 1371).
+  constexpr int smax = 8;
   for (int s = 1; s <= smax && s <= nkb; s++) {
     const int kbps = ceil_div(nkb, s);
     if (s > 1 && kbps < 2) break;
@@ -955,15 +955,7 @@ cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int* S_out) {
     return cudaErrorInvalidValue;
   switch (bt) {
     case 32: return launch_bt<32, 10>(st, a, tw, ta, S);
-    case 64: {
-      // ring depth experiment: a shallower ring (<= ~110 KB) lets the NEXT kernel's CTAs
-      // become resident (and prefetch) while this one drains
-      static const int st64 = getenv("NVLLM_TC5_ST64") ? atoi(getenv("NVLLM_TC5_ST64")) : 8;
-      if (st64 == 4) return launch_bt<64, 4>(st, a, tw, ta, S);
-      if (st64 == 5) return launch_bt<64, 5>(st, a, tw, ta, S);
-      if (st64 == 6) return launch_bt<64, 6>(st, a, tw, ta, S);
-      return launch_bt<64, 8>(st, a, tw, ta, S);
-    }
+    case 64: return launch_bt<64, 8>(st, a, tw, ta, S);
     case 128: return launch_bt<128, 6>(st, a, tw, ta, S);
     default: return launch_bt<256, 4>(st, a, tw, ta, S);
   }

@@ -68,7 +68,6 @@ struct Workspace {
   const float* logits_final = nullptr;  // where the last step's summed logits live
   int n_cap_out = 0;
   size_t logits_p_floats = 0;
-  int* attn_tickets = nullptr;  // stream-K decode attention, [n * nkv * chunks]
   float* attn_ws = nullptr;
   size_t attn_ws_floats = 0;
   int* out_tokens = nullptr;  // [n]

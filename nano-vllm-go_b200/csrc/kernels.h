@@ -45,10 +45,6 @@ struct NormArgs {
   size_t stride2;
   float m2;
   const float* bias2;
-  // weights the NEXT GEMM will stream, pulled into L2 while this (latency-bound, HBM-idle)
-  // kernel waits for its dependency: decode-sized steps only
-  const void* pf_ptr;
-  size_t pf_bytes;
   const float* w;      // [H]; null = all ones (the weight is folded into the next GEMM)
   const float* b;      // [H] or null => RMSNorm (tensor.go:197)
   float eps;
@@ -293,7 +289,7 @@ struct AttnArgs {
   int ablate;             // timing experiments only (NVLLM_ATTN_ABL): 1 = no math, 2 = no K/V loads
   // stream-K decode (attention_mma.cu): ticket per (seq, kv head, head chunk), zero between
   // kernels; total_tiles = host LOWER bound of the key tiles in the step (caps the grid)
-  int* tickets;
+  int* tickets;        // unused (stream-K experiment removed)
   int pool_blocks;     // blocks in the layer's K / V pool (tensor-map extent)
   int total_rows;      // rows of q / out in this step (tensor-map extent; tcgen05 prefill kernel)
   int sm_count;
@@ -321,9 +317,6 @@ cudaError_t launch_attn_prefill_tc5(cudaStream_t st, const AttnArgs& a);
 // attention_dec.cu: decode kernel for query-head groups of <= 8 (needs AttnArgs::pool_blocks)
 bool attn_decode_t_supported(const AttnArgs& a);
 cudaError_t launch_attn_decode_t(cudaStream_t st, const AttnArgs& a);
-size_t attn_decode_sk_ws_floats(int hd, int sm_count);
-cudaError_t launch_attn_decode_sk(cudaStream_t st, const AttnArgs& a, int* tickets, int sm_count,
-                                  long long total_tiles_hint);
 
 // ---------------------------------------------------------------- moe.cu
 // Router: probs = softmax(x @ R) over all E, top-k (descending), weights renormalised
