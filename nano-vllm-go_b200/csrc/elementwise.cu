@@ -16,7 +16,7 @@ template <typename WT>
 __global__ void embed_kernel(const int* __restrict__ tokens, const int* __restrict__ positions,
                              const WT* __restrict__ wte, const WT* __restrict__ wpe, int max_pos,
                              float mult, float* __restrict__ x, int H, bf16* __restrict__ xb,
-                             float* __restrict__ ssq, Trace tr) {
+                             float* __restrict__ ssq, const float* __restrict__ g, Trace tr) {
   TRACE_ENTRY(tr);
   pdl_wait();  // step prologue: later kernels may read the step state before their own wait
   pdl_launch_dependents();
@@ -43,9 +43,14 @@ __global__ void embed_kernel(const int* __restrict__ tokens, const int* __restri
     }
     store8(x + (size_t)t * H + i, v);
     if (xb) {
-      store8(xb + (size_t)t * H + i, v);
+      float gv[8], o[8];
+      load8(g + i, gv);
 #pragma unroll
-      for (int j = 0; j < 8; j++) lsq += v[j] * v[j];
+      for (int j = 0; j < 8; j++) {
+        lsq += v[j] * v[j];
+        o[j] = v[j] * gv[j];
+      }
+      store8(xb + (size_t)t * H + i, o);
     }
   }
   if (xb) {
@@ -57,16 +62,16 @@ __global__ void embed_kernel(const int* __restrict__ tokens, const int* __restri
 
 cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int* positions,
                          const void* wte, const void* wpe, int max_pos, float mult, float* x, int T,
-                         int H, void* xb, float* ssq) {
+                         int H, void* xb, float* ssq, const float* g) {
   if (T <= 0) return cudaSuccess;
-  if ((xb == nullptr) != (ssq == nullptr)) return cudaErrorInvalidValue;
+  if ((xb == nullptr) != (ssq == nullptr) || (xb && !g)) return cudaErrorInvalidValue;
   int threads = min(256, max(32, ((H / 8 + 31) / 32) * 32));
   if (wdt == DT_F32)
     (void)launch_k(embed_kernel<float>, dim3(T), dim3(threads), 0, st, tokens, positions, (const float*)wte,
-                                               (const float*)wpe, max_pos, mult, x, H, (bf16*)xb, ssq, next_trace(5));
+                                               (const float*)wpe, max_pos, mult, x, H, (bf16*)xb, ssq, g, next_trace(5));
   else
     (void)launch_k(embed_kernel<bf16>, dim3(T), dim3(threads), 0, st, tokens, positions, (const bf16*)wte,
-                                              (const bf16*)wpe, max_pos, mult, x, H, (bf16*)xb, ssq, next_trace(5));
+                                              (const bf16*)wpe, max_pos, mult, x, H, (bf16*)xb, ssq, g, next_trace(5));
   return cudaGetLastError();
 }
 
@@ -819,26 +824,6 @@ cudaError_t launch_copy_rows(cudaStream_t st, int sdt_api, const void* src, size
     else CR(__half, bf16);
   }
 #undef CR
-  return cudaGetLastError();
-}
-
-__global__ void fold_cols_kernel(bf16* __restrict__ W, size_t n8, int K, const float* __restrict__ g) {
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8;
-       i += (size_t)gridDim.x * blockDim.x) {
-    const int k = (int)((i * 8) % K);
-    float w[8], s[8];
-    load8(W + i * 8, w);
-    load8(g + k, s);
-#pragma unroll
-    for (int j = 0; j < 8; j++) w[j] *= s[j];
-    store8(W + i * 8, w);
-  }
-}
-cudaError_t launch_fold_cols(cudaStream_t st, void* W, size_t rows, int K, const float* g) {
-  if (rows == 0) return cudaSuccess;
-  if (K % 8) return cudaErrorInvalidValue;
-  const size_t n8 = rows * (size_t)K / 8;
-  fold_cols_kernel<<<(int)min((size_t)148 * 16, (n8 + 255) / 256), 256, 0, st>>>((bf16*)W, n8, K, g);
   return cudaGetLastError();
 }
 

@@ -253,6 +253,7 @@ struct Resid {
   float m = 1.f;
   const float* bias = nullptr;
   int site = 0;  // 0 = attention output projection, 1 = FFN down projection (counter sets)
+  const float* g = nullptr;  // weight of the norm that reads x next (folded into the bf16 copy)
 };
 
 struct RouterArgs {  // expert routing fused into the FFN norm of a MoE layer
@@ -314,7 +315,7 @@ static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int 
       while (t.S > 1 && (size_t)t.S * M * ldo > cap) t.S--;
       t.epi = TC5_EPI_RESID;
       t.res_x = h->ws.x; t.res_xb = h->ws.xb; t.res_ssq = h->ws.ssq; t.res_ssq_ld = h->ws.T_cap;
-      t.res_bias = rd->bias; t.res_m = rd->m;
+      t.res_bias = rd->bias; t.res_m = rd->m; t.res_g = rd->g;
       t.res_arrive = h->ws.res_ctr + (size_t)rd->site * 2 * RES_CTR_TILES;
       t.res_done = t.res_arrive + RES_CTR_TILES;
       const double xrw = (double)M * N * (4 + 4 + 2);
@@ -468,7 +469,7 @@ int forward_step(nvllm_handle* h) {
     ProfScope ps(h, NVLLM_K_EMBED, (double)T * H * (4 + dt_size(h->wdt)), 0);
     LAUNCH(h, launch_embed(st, h->wdt, d_tokens, d_pos, h->wte, h->wpe, c.max_seq_len,
                            c.embedding_multiplier, w.x, T, H, h->fold ? w.xb : nullptr,
-                           h->fold ? w.ssq : nullptr));
+                           h->fold ? w.ssq : nullptr, h->fold ? h->layers[0].attn_norm_w : nullptr));
   }
   // Folded RMSNorm (h->fold): while `xb_parts` > 0, w.xb holds bf16(x) of the CURRENT residual
   // stream and w.ssq its row sums of squares in xb_parts column-tile slices — the next GEMM
@@ -519,7 +520,7 @@ int forward_step(nvllm_handle* h) {
                          h->qkv_cols, &qkv, 0, nullptr, 0, nullptr, nullptr, 0, 0.0, &rsc)))
         return rc;
     } else {
-      if ((rc = run_norm(h, w.x, &p1, &p2, h->fold ? nullptr : lw.attn_norm_w, lw.attn_norm_b, w.xn,
+      if ((rc = run_norm(h, w.x, &p1, &p2, lw.attn_norm_w, lw.attn_norm_b, w.xn,
                          nullptr, nullptr, T)))
         return rc;
       if ((rc = run_gemm(h, w.xn, H, lw.wqkv, T, h->qkv_cols, H, 1.f, w.ws_a, w.ws_a_floats,
@@ -561,7 +562,7 @@ int forward_step(nvllm_handle* h) {
       if (at.n_splits > 1) h->launches++;
     }
     if (resid_gemm_ok(h, T, H, h->q_cols, h->q_cols)) {
-      Resid rd{m_res, lw.bo, 0};
+      Resid rd{m_res, lw.bo, 0, lw.ffn_norm_w};
       if ((rc = run_gemm(h, w.attn_out, h->q_cols, lw.wo, T, H, h->q_cols, 1.f, w.ws_b,
                          w.ws_b_floats, H, &p1, 0, nullptr, 0, nullptr, nullptr, 0, 0.0, nullptr, &rd)))
         return rc;
@@ -586,7 +587,7 @@ int forward_step(nvllm_handle* h) {
       }
       const bool skip_norm = xb_parts > 0 && !h->moe && fold_gemm_ok(h, T, h->w1_cols, H, H);
       if (!skip_norm) {
-        if ((rc = run_norm(h, w.x, &p1, nullptr, h->fold ? nullptr : lw.ffn_norm_w, lw.ffn_norm_b,
+        if ((rc = run_norm(h, w.x, &p1, nullptr, lw.ffn_norm_w, lw.ffn_norm_b,
                            w.xn, nullptr, nullptr, T, &ra)))
           return rc;
         xb_parts = 0;
@@ -713,7 +714,8 @@ int forward_step(nvllm_handle* h) {
                              w.hbuf));
       }
       if (!h->parallel && resid_gemm_ok(h, T, H, h->F, h->F)) {
-        Resid rd{m_res, lw.b2, 1};
+        // the next reader of x is layer l + 1's attention norm (the final norm reads fp32 x)
+        Resid rd{m_res, lw.b2, 1, l + 1 < h->L ? h->layers[l + 1].attn_norm_w : nullptr};
         if ((rc = run_gemm(h, w.hbuf, h->F, lw.w2, T, H, h->F, 1.f, ffn_out, w.ws_b_floats, H, &pf, 0,
                            nullptr, 0, nullptr, nullptr, 0, 0.0, nullptr, &rd)))
           return rc;

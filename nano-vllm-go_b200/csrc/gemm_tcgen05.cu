@@ -70,6 +70,7 @@ struct Tc5Fuse {
   float m;
   unsigned* arrive;
   unsigned* done;
+  const float* g;  // weight of the norm that reads x next: xb = bf16(x * g); null = ones
 };
 // A second GEMM chained behind the first inside ONE launch (the FFN pair of a decode step:
 // W1 + activation, then W2): every CTA runs its units of problem 1, then its units of problem 2.
@@ -482,6 +483,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
         // 383-389: x = x + m * (proj + bias)), plus what the FOLDED RMSNorm of the next
         // sub-block needs: the row rounded to bf16 and its sum of squares over this column tile
         const float b = (fz.bias && n_ok) ? fz.bias[n] : 0.f;
+        const float gn = (fz.g && n_ok) ? fz.g[n] : 1.f;
         const int nt = n0 / TC_BN;
         if (scp.S == 1) {
           int chunk = 0;
@@ -500,7 +502,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
               for (int c = 0; c < 32; c++) {
                 const float v = xv[c] + fz.m * (alpha * __uint_as_float(r[c]) + b);
                 fz.x[base + (size_t)c * N] = v;
-                fz.xb[base + (size_t)c * N] = __float2bfloat16_rn(v);
+                fz.xb[base + (size_t)c * N] = __float2bfloat16_rn(v * gn);
                 sq[c] = v * v;
               }
             } else {
@@ -510,7 +512,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
                 if (n_ok && m0 + c0 + c < M) {
                   const float v = fz.x[base + (size_t)c * N] + fz.m * (alpha * __uint_as_float(r[c]) + b);
                   fz.x[base + (size_t)c * N] = v;
-                  fz.xb[base + (size_t)c * N] = __float2bfloat16_rn(v);
+                  fz.xb[base + (size_t)c * N] = __float2bfloat16_rn(v * gn);
                   sq[c] = v * v;
                 }
               }
@@ -557,8 +559,9 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
           const int r0 = split * per, r1 = min(valid, r0 + per);
           const int ncol = n0 + lane * 4;
           const bool c_ok = ncol + 3 < N;  // N % 4 == 0 is checked by the launcher
-          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f), g4 = make_float4(1.f, 1.f, 1.f, 1.f);
           if (fz.bias && c_ok) b4 = *reinterpret_cast<const float4*>(fz.bias + ncol);
+          if (fz.g && c_ok) g4 = *reinterpret_cast<const float4*>(fz.g + ncol);
           for (int row = r0 + q; row < r1; row += 4) {
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
             if (c_ok) {
@@ -585,7 +588,8 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
               v.z = xv.z + fz.m * (acc.z + b4.z);
               v.w = xv.w + fz.m * (acc.w + b4.w);
               *reinterpret_cast<float4*>(fz.x + xi) = v;
-              __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+              __nv_bfloat162 lo = __floats2bfloat162_rn(v.x * g4.x, v.y * g4.y),
+                             hi = __floats2bfloat162_rn(v.z * g4.z, v.w * g4.w);
               uint2 pk;
               pk.x = *reinterpret_cast<uint32_t*>(&lo);
               pk.y = *reinterpret_cast<uint32_t*>(&hi);
@@ -862,7 +866,7 @@ static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* t
   int grid = min(sc.units, max(1, sm_counts[dev]));
   if (a.max_ctas > 0 && a.epi != TC5_EPI_RESID) grid = max(1, min(grid, a.max_ctas));
   Tc5Fuse fz{a.rs_ssq, a.rs_parts, a.rs_ld, a.rs_inv_h, a.rs_eps, a.res_x, (bf16*)a.res_xb, a.res_ssq,
-             a.res_ssq_ld, a.res_bias, a.res_m, a.res_arrive, a.res_done};
+             a.res_ssq_ld, a.res_bias, a.res_m, a.res_arrive, a.res_done, a.res_g};
   if (a.epi == TC5_EPI_RESID) {
     if (!a.res_x || !a.res_xb || !a.res_ssq || a.g_experts > 0) return cudaErrorInvalidValue;
     // the k-splits of a tile wait for each other inside the kernel: every unit needs its own SM

@@ -55,7 +55,7 @@ struct Workspace {
   void* attn_out = nullptr;  // [T, nh hd]
   void* hbuf = nullptr;      // [T, F] or [T k, I]
   void* xn_last = nullptr;   // [n, H]
-  // folded RMSNorm (forward.cu): the residual stream rounded to bf16, UN-normalised, the
+  // folded RMSNorm (forward.cu): bf16(x * g) of the residual stream (g = the next norm's weight), the
   // per-column-tile row sums of squares [parts][T_cap] of it, and the arrival / done counters of
   // the two fused-residual GEMM sites of a layer (O projection, FFN down projection)
   void* xb = nullptr;
@@ -158,9 +158,9 @@ struct nvllm_handle {
   uint64_t seed = 0, rng_counter = 0;
   int graphs_enabled = 1;
   int use_tc5 = 1;
-  // RMSNorm folded into the GEMMs that consume it: norm weights multiplied into the QKV / W1
-  // weight columns at finalize, the row statistic applied to the accumulators (dense RMSNorm
-  // models, bf16, tp == 1; NVLLM_FOLD=0 switches it off)
+  // RMSNorm folded into the GEMMs that consume it: whoever produces x also writes bf16(x * g),
+  // the row statistic is applied to the accumulators (dense RMSNorm models, bf16, tp == 1;
+  // NVLLM_FOLD=0 switches it off)
   bool fold = false;
   // accounting
   uint64_t weight_bytes = 0, kv_bytes = 0, ws_bytes = 0;

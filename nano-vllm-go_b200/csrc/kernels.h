@@ -24,13 +24,12 @@ constexpr int KV_BLOCK = 256;
 
 // ---------------------------------------------------------------- elementwise.cu
 // x[t,:] = (wte[tok[t],:] (+ wpe[pos[t],:] if wpe && pos < max_pos)) * mult   (mult==0 => 1)
-// xb / ssq (both or neither): also write the row rounded to bf16 and its sum of squares ssq[t]
-// (what a GEMM with a folded RMSNorm reads instead of a normed activation)
+// xb / ssq / g (all or none): also write bf16(row * g) — g = the weight of the RMSNorm that reads
+// the row next — and the row's sum of squares ssq[t] (what a GEMM with a folded RMSNorm reads
+// instead of a normed activation)
 cudaError_t launch_embed(cudaStream_t st, int wdt, const int* tokens, const int* positions,
                          const void* wte, const void* wpe, int max_pos, float mult, float* x, int T,
-                         int H, void* xb = nullptr, float* ssq = nullptr);
-// W[r, k] *= g[k] (bf16 weights [rows, K], fp32 g): fold a norm weight into the linear after it
-cudaError_t launch_fold_cols(cudaStream_t st, void* W, size_t rows, int K, const float* g);
+                         int H, void* xb = nullptr, float* ssq = nullptr, const float* g = nullptr);
 
 struct NormArgs {
   float* x;            // [*, H] residual stream, updated in place when p1/p2 given
@@ -197,9 +196,9 @@ struct Tc5Args {
   void* epi_out;        // bf16 [M, epi_ld]
   int epi_ld;
   const float* epi_bias;  // [N] or null (GELU)
-  // ---- RMSNorm folded into the GEMMs (forward.cu "fold"): the norm weight lives in W, the
-  // row statistic is applied to the accumulator instead of the activations.
-  // consumer side, rs_ssq != null: A holds the UN-normalised residual stream (bf16) and every
+  // ---- RMSNorm folded into the GEMMs (forward.cu "fold"): the producer of x writes
+  // bf16(x * g) (g = norm weight), the row statistic is applied to the accumulator.
+  // consumer side, rs_ssq != null: A holds bf16(x * g), not yet divided by the row's rms, and every
   // accumulator row m is multiplied by 1 / sqrt(sum_p rs_ssq[p * rs_ld + m] * rs_inv_h + rs_eps)
   // before the epilogue proper (partials, SwiGLU, GELU)
   const float* rs_ssq;
@@ -217,6 +216,7 @@ struct Tc5Args {
   int res_ssq_ld;
   const float* res_bias;
   float res_m;
+  const float* res_g;    // [N] weight of the norm that consumes x next: res_xb = bf16(x * g)
   unsigned* res_arrive;  // [n_tiles * m_tiles], zero between launches
   unsigned* res_done;
   int max_ctas;  // > 0: cap of the persistent grid (leave SMs to a concurrent collective)

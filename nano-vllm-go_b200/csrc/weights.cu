@@ -296,25 +296,18 @@ extern "C" int nvllm_finalize(nvllm_handle* h) {
   }
 #undef NEED
 
-  // Fold the RMSNorm weights into the linears that consume the normed activations
-  // (y = (x * rstd * g) W^T = rstd * (x (W diag g)^T)): W_qkv <- W_qkv diag(attn_norm_w),
-  // W1 <- W1 diag(ffn_norm_w).  The GEMMs then read the un-normalised bf16 residual stream and
-  // apply rstd to their accumulators (gemm_tcgen05.cu); the norm kernels that remain on the
-  // fall-back paths (single-sequence GEMV decode) run without a weight.
+  // RMSNorm folded into the GEMMs (forward.cu, gemm_tcgen05.cu): y = (x * rstd * g) W^T =
+  // rstd * ((x * g) W^T) — the kernel that PRODUCES x (embedding, O / FFN-down GEMM epilogue)
+  // also writes bf16(x * g) with the weight g of the norm that reads x next and the row's sum
+  // of squares; the consuming GEMM reads that matrix and scales its accumulator rows by rstd.
+  // The weights stay exactly the bf16 values the reference loader would hold, and the
+  // activation is rounded to bf16 once, as on the un-fused path.
   {
     const char* env = getenv("NVLLM_FOLD");
     bool rms = !have(-1, NVLLM_W_FINAL_NORM_B);
     for (int l = 0; l < h->L; l++) rms = rms && !have(l, NVLLM_W_ATTN_NORM_B) && !have(l, NVLLM_W_FFN_NORM_B);
     h->fold = rms && !h->moe && !h->parallel && h->tp == 1 && h->wdt == DT_BF16 && h->adt == DT_BF16 &&
               h->use_tc5 && (h->H % 8) == 0 && !(env && atoi(env) == 0);
-    if (h->fold) {
-      for (int l = 0; l < h->L; l++) {
-        LayerW& w = h->layers[l];
-        cudaError_t fe = launch_fold_cols(h->stream, w.wqkv, (size_t)h->qkv_cols, h->H, w.attn_norm_w);
-        if (fe == cudaSuccess) fe = launch_fold_cols(h->stream, w.w1, (size_t)h->w1_cols, h->H, w.ffn_norm_w);
-        if (fe != cudaSuccess) return set_err(h, NVLLM_ERR_CUDA, "norm fold: %s", cudaGetErrorString(fe));
-      }
-    }
   }
 
   // RoPE tables, computed in double exactly like rope.go:18-50 (cos/sin of pos * base^(-2i/hd)),
