@@ -283,7 +283,9 @@ def cpu_oracle_sample(cfg, weights, budget_s, prompt_tokens=None):
     m.forward(prompt[:2], m.new_cache())
     t_tok = (time.perf_counter() - t0) / 2
     total = int(max(4, min(48, budget_s / max(t_tok, 1e-3))))
-    p = prompt_tokens if prompt_tokens else max(2, (2 * total) // 3)
+    # a FIXED 12-token prompt whenever the budget allows (the parity check below then runs on the
+    # same prompt on every box); slow models fall back to 2/3 of what fits
+    p = prompt_tokens if prompt_tokens else (12 if total >= 18 else max(2, (2 * total) // 3))
     d = max(1, total - p)
     cache = m.new_cache()
     t0 = time.perf_counter()
@@ -305,21 +307,29 @@ def cpu_oracle_sample(cfg, weights, budget_s, prompt_tokens=None):
 
 def gpu_parity(run, ref):
     """The same prompt through nvllm_run (bf16 weights, the library's production kernels at the
-    full model size): free-running greedy, last-token logits of every step against the oracle's.
-    Gate (BASELINE.json north_star, bf16 mode): max|dlogit| / max|logit| <= 2e-2 per step and
-    identical greedy tokens."""
+    full model size), last-token logits of every step against the oracle's.  Teacher-forced with
+    the ORACLE's greedy tokens, so a near-tie flip (random-init logits are nearly flat) does not
+    make the later steps incomparable; every flip is reported with the oracle's own margin
+    between the two tokens.  Gate (BASELINE.json north_star, bf16 mode): max|dlogit| /
+    max|logit| <= 2e-2 per step and identical greedy tokens."""
     toks = list(ref["prompt"])
-    worst, equal, steps = 0.0, True, len(ref["greedy"])
+    steps = len(ref["greedy"])
+    errs, flips, margins = [], [], []
     for i in range(steps):
         out, logits = run.run_flat([toks], i == 0, [0], [[0]], [0.0], want_logits=True)
         r = ref["logits"][i]
-        worst = max(worst, float(np.abs(logits[0] - r).max() / np.abs(r).max()))
-        equal = equal and int(out[0]) == ref["greedy"][i]
-        toks.append(int(out[0]))
-    return {"max_rel_err": worst, "tolerance": 2e-2, "tokens_equal": bool(equal), "steps": steps,
+        errs.append(float(np.abs(logits[0] - r).max() / np.abs(r).max()))
+        if int(out[0]) != ref["greedy"][i]:
+            flips.append(i)
+            margins.append(float((r[ref["greedy"][i]] - r[int(out[0])]) / np.abs(r).max()))
+        toks.append(ref["greedy"][i])
+    worst = max(errs)
+    return {"max_rel_err": worst, "tolerance": 2e-2, "tokens_equal": not flips, "steps": steps,
             "prompt_tokens": len(ref["prompt"]), "within_tolerance": bool(worst <= 2e-2),
+            "flipped_steps": flips, "flip_margins_rel": margins, "teacher_forced": True,
+            "per_step_rel_err": [round(e, 5) for e in errs],
             "against": "oracle/nvllm_oracle.c on the same bf16-rounded weights and prompt "
-                       "(full-size model, free-running greedy)"}
+                       "(full-size model)"}
 
 
 def tp_leg(dist, rank, world, device, steps, warmup, barrier):
