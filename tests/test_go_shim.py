@@ -139,3 +139,44 @@ def test_defaults_match_new_tensor_model_runner():
     import nvllm_pkg
     R = nvllm_pkg.sub("runner")
     assert R.DEFAULT_SAMPLING == dict(temperature=1.0, top_p=1.0, top_k=0, repetition_penalty=1.2)
+
+
+# ---- go/engine_fixes.go: same static discipline
+FIXES = os.path.join(ROOT, "go", "engine_fixes.go")
+FIX_VARS = {  # variable -> struct of package nanovllm
+    "seq": "Sequence", "last": "Sequence", "v": "Sequence", "s": "Scheduler", "config": "Config",
+}
+
+
+def _fix_code():
+    src = open(FIXES, encoding="utf-8").read()
+    return "\n".join(ln.split("//")[0] for ln in src.split("\n"))
+
+
+def test_engine_fixes_selectors_exist_in_the_reference():
+    code, syms = _fix_code(), _syms()["nanovllm"]
+    for var, struct in FIX_VARS.items():
+        members = set(syms["structs"][struct]) | set(syms["methods"].get(struct, []))
+        for sel in set(re.findall(rf"(?<![\w.]){var}\.([A-Za-z]\w*)", code)):
+            assert sel in members, f"{var}.{sel}: {struct} has no such field or method"
+    # chained selectors on the scheduler's block manager and queues
+    for sel in set(re.findall(r"s\.blockManager\.(\w+)", code)):
+        assert sel in syms["methods"]["BlockManager"], f"BlockManager.{sel} does not exist"
+    for ident in ("NewScheduler", "StatusRunning", "StatusFinished", "Sequence", "Scheduler", "Config"):
+        assert ident in syms["exports"]
+    # the runner methods the fixes call exist in the shim
+    shim = _code()
+    for meth in set(re.findall(r"(?<![\w.])r\.(\w+)\(", code)):
+        assert re.search(rf"func \(r \*CudaModelRunner\) {meth}\(", shim) or \
+            re.search(rf"func \(r \*CudaModelRunner\) {meth}\(", code), f"CudaModelRunner.{meth} is not defined"
+
+
+def test_engine_fixes_match_the_python_mirror():
+    """Both files must implement the same four fixes (names kept in step by hand)."""
+    code = _fix_code()
+    mirror = open(os.path.join(ROOT, "harness", "engine_fixes.py")).read()
+    for go_name, py_name in (("ScheduleMixed", "schedule_mixed"), ("PostprocessMixed", "postprocess_mixed"),
+                             ("GenerateByRequest", "def generate"), ("CheckBlockSize", "check_block_size"),
+                             ("NumKVBlocksFromFreeHBM", "num_kv_blocks_from_free_hbm"),
+                             ("blockReady", "block_ready"), ("allocLen", "alloc_len")):
+        assert go_name in code and py_name in mirror
