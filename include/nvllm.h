@@ -102,7 +102,13 @@ typedef struct nvllm_config {
   int32_t tp_size;            /* 1 = no TP */
   int32_t tp_rank;
   int32_t device;             /* CUDA device ordinal for this handle */
-  int32_t reserved[5];
+  /* Mamba2 layers of the Granite-4 hybrid (purego/tensor/mamba2.go:30-66, config.go:100-115);
+   * all 0 = the model has none.  expand * hidden = mamba_num_heads * mamba_head_dim. */
+  int32_t mamba_num_heads;
+  int32_t mamba_head_dim;
+  int32_t mamba_state_size;
+  int32_t mamba_n_groups;
+  int32_t mamba_conv_kernel;
 } nvllm_config;
 
 /* Weight identifiers. Layouts are the reference's POST-LOAD layouts
@@ -135,7 +141,17 @@ enum nvllm_weight_id {
   NVLLM_W_FFN_B2 = 32,         /* optional */
   NVLLM_W_MOE_ROUTER = 33,     /* [H, E]            (generic_loader.go:576) */
   NVLLM_W_MOE_INPUT = 34,      /* [E, 2I, H] HF layout, un-transposed (generic_loader.go:578-586) */
-  NVLLM_W_MOE_OUTPUT = 35      /* [E, H, I]  HF layout */
+  NVLLM_W_MOE_OUTPUT = 35,     /* [E, H, I]  HF layout */
+  /* Mamba2 layers (Mamba2Layer, mamba2.go:9-28; loaded un-transposed, generic_loader.go:461-498).
+   * E = mamba_num_heads * mamba_head_dim, conv_dim = E + 2 * n_groups * state_size. */
+  NVLLM_W_MAMBA_IN_PROJ = 36,  /* [E + conv_dim + heads, H]  rows = [gate | xBC | dt] (mamba2.go:80-98) */
+  NVLLM_W_MAMBA_CONV_W = 37,   /* [conv_dim, 1, conv_kernel] */
+  NVLLM_W_MAMBA_CONV_B = 38,   /* [conv_dim] */
+  NVLLM_W_MAMBA_DT_BIAS = 39,  /* [heads] */
+  NVLLM_W_MAMBA_A_LOG = 40,    /* [heads] */
+  NVLLM_W_MAMBA_D = 41,        /* [heads] */
+  NVLLM_W_MAMBA_NORM = 42,     /* [E]  RMSNormGated weight */
+  NVLLM_W_MAMBA_OUT_PROJ = 43  /* [H, E] */
 };
 
 typedef struct nvllm_handle nvllm_handle;
@@ -162,6 +178,11 @@ int nvllm_tp_unique_id(uint8_t out_id[128]);
  * Replaces tensor.LoadModelFromDirectory inside NewTensorModelRunner
  * (tensor_model_runner.go:21-32) together with set_weight/finalize. */
 int nvllm_create(const nvllm_config* cfg, const uint8_t* tp_id, nvllm_handle** out);
+
+/* Hybrid models (ModelConfig.HybridLayers, config.go:113): types[l] = 1 makes layer l a Mamba2
+ * block (norm -> Mamba2 -> residual, norm -> FFN -> residual; generic_model.go:162-202), 0 an
+ * attention block.  Call before the first nvllm_set_weight; needs the mamba_* config fields. */
+int nvllm_set_layer_types(nvllm_handle* h, const int32_t* types, int n_layers);
 
 /* Hand one tensor in the reference's post-load layout; the library converts /
  * repacks / TP-shards on its own and keeps no pointer.  numel is checked. */

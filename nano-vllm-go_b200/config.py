@@ -29,6 +29,8 @@ DT_F32, DT_BF16, DT_F16 = 0, 1, 2
 # enum nvllm_weight_id
 W_TOKEN_EMBEDDING, W_POS_EMBEDDING, W_FINAL_NORM_W, W_FINAL_NORM_B, W_LM_HEAD = 0, 1, 2, 3, 4
 W_ATTN_NORM_W, W_ATTN_NORM_B, W_FFN_NORM_W, W_FFN_NORM_B = 16, 17, 18, 19
+(W_MAMBA_IN_PROJ, W_MAMBA_CONV_W, W_MAMBA_CONV_B, W_MAMBA_DT_BIAS, W_MAMBA_A_LOG, W_MAMBA_D,
+ W_MAMBA_NORM, W_MAMBA_OUT_PROJ) = 36, 37, 38, 39, 40, 41, 42, 43
 W_Q, W_K, W_V, W_KV, W_O = 20, 21, 22, 23, 24
 W_Q_BIAS, W_K_BIAS, W_V_BIAS, W_O_BIAS = 25, 26, 27, 28
 W_FFN_W1, W_FFN_B1, W_FFN_W2, W_FFN_B2 = 29, 30, 31, 32
@@ -70,7 +72,11 @@ class CConfig(ctypes.Structure):
         ("tp_size", ctypes.c_int32),
         ("tp_rank", ctypes.c_int32),
         ("device", ctypes.c_int32),
-        ("reserved", ctypes.c_int32 * 5),
+        ("mamba_num_heads", ctypes.c_int32),
+        ("mamba_head_dim", ctypes.c_int32),
+        ("mamba_state_size", ctypes.c_int32),
+        ("mamba_n_groups", ctypes.c_int32),
+        ("mamba_conv_kernel", ctypes.c_int32),
     ]
 
 
@@ -102,6 +108,22 @@ class ModelConfig:
     logits_scaling: float = 0.0
     has_ffn_bias: bool = False  # GPT-2 c_fc/c_proj biases; optional at the boundary
     eos_token_id: int = -1
+    # Granite-4 hybrid (purego/tensor/config.go:100-115): hybrid_layers[l] = True -> Mamba2 block
+    mamba_num_heads: int = 0
+    mamba_head_dim: int = 0
+    mamba_state_size: int = 0
+    mamba_n_groups: int = 0
+    mamba_conv_kernel: int = 0
+    hybrid_layers: tuple = ()
+
+    def is_mamba(self, layer: int) -> bool:
+        return bool(self.hybrid_layers) and bool(self.hybrid_layers[layer])
+
+    def mamba_dims(self):
+        """(E = expand * hidden, conv_dim, in_proj rows)."""
+        E = self.mamba_num_heads * self.mamba_head_dim
+        conv = E + 2 * self.mamba_n_groups * self.mamba_state_size
+        return E, conv, E + conv + self.mamba_num_heads
 
     def kv_heads(self) -> int:
         if self.attention_type == ATTN_MQA:
@@ -162,6 +184,11 @@ class ModelConfig:
         c.tp_size = tp_size
         c.tp_rank = tp_rank
         c.device = device
+        c.mamba_num_heads = self.mamba_num_heads
+        c.mamba_head_dim = self.mamba_head_dim
+        c.mamba_state_size = self.mamba_state_size
+        c.mamba_n_groups = self.mamba_n_groups
+        c.mamba_conv_kernel = self.mamba_conv_kernel
         return c
 
 
@@ -221,6 +248,17 @@ def tiny_granite(**kw) -> ModelConfig:
              ffn_dim=64, max_seq_len=1024, num_experts=8, num_experts_per_tok=2)
     d.update(kw)
     return tiny(granite_moe_1b(), **d)
+
+
+def tiny_hybrid(**kw) -> ModelConfig:
+    """Granite-4-style hybrid: Mamba2 and GQA attention blocks (no positional encoding,
+    config.go:241-300), shared SwiGLU MLP, muP multipliers."""
+    d = dict(vocab_size=1000, hidden=128, num_layers=4, num_heads=4, num_kv_heads=2, head_dim=32,
+             ffn_dim=256, max_seq_len=1024, position_type=POS_NONE, use_moe=False, num_experts=0,
+             num_experts_per_tok=0, mamba_num_heads=8, mamba_head_dim=32, mamba_state_size=16,
+             mamba_n_groups=2, mamba_conv_kernel=4, hybrid_layers=(True, False, True, True))
+    d.update(kw)
+    return replace(tiny(granite_moe_1b(), **d), name="granite-4-hybrid-tiny")
 
 
 def tiny_falcon(**kw) -> ModelConfig:

@@ -239,7 +239,7 @@ struct WeightSrc {
   size_t col0 = 0;      //      (vectors: elements [col0, col0 + n) of a longer vector of ld)
 };
 // internal weight ids (never cross the C ABI): the two halves of a SwiGLU W1, each [H, F]
-enum { W_INT_FFN_GATE = 40, W_INT_FFN_UP = 41 };
+enum { W_INT_FFN_GATE = 60, W_INT_FFN_UP = 61 };
 int set_weight_src(nvllm_handle* h, int id, int layer, int dtype, const void* host, uint64_t numel,
                    const WeightSrc& src);
 

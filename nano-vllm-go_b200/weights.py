@@ -68,6 +68,23 @@ def weight_specs(cfg: C.ModelConfig):
             yield C.W_FFN_NORM_W, l, (H,), s, 1.0
             if layer_norm:
                 yield C.W_FFN_NORM_B, l, (H,), s, 0.0
+        if cfg.is_mamba(l):
+            # Mamba2 block (mamba2.go:9-28; tensors as the loader leaves them, un-transposed):
+            # norms + the layer + the shared MLP, no attention tensors
+            E, conv, rows = cfg.mamba_dims()
+            nhm = cfg.mamba_num_heads
+            yield C.W_MAMBA_IN_PROJ, l, (rows, H), s, 0.0
+            yield C.W_MAMBA_CONV_W, l, (conv, 1, cfg.mamba_conv_kernel), 0.3, 0.0
+            yield C.W_MAMBA_CONV_B, l, (conv,), s, 0.0
+            yield C.W_MAMBA_DT_BIAS, l, (nhm,), 0.5, 0.0
+            yield C.W_MAMBA_A_LOG, l, (nhm,), 0.5, 0.0
+            yield C.W_MAMBA_D, l, (nhm,), s, 1.0
+            yield C.W_MAMBA_NORM, l, (E,), s, 1.0
+            yield C.W_MAMBA_OUT_PROJ, l, (H, E), so, 0.0
+            w1_out = 2 * F if cfg.activation_type == C.ACT_SWIGLU else F
+            yield C.W_FFN_W1, l, (H, w1_out), s, 0.0
+            yield C.W_FFN_W2, l, (F, H), so, 0.0
+            continue
         yield C.W_Q, l, (H, q), s, 0.0
         if cfg.attention_type == C.ATTN_MQA:
             yield C.W_KV, l, (H, 2 * cfg.head_dim), s, 0.0

@@ -39,6 +39,8 @@ typedef struct {
   const float *q_b, *k_b, *v_b, *o_b;
   const float *w1, *b1, *w2, *b2;
   const float *router, *moe_in, *moe_out;
+  /* Mamba2Layer (mamba2.go:9-28), un-transposed as the loader leaves them */
+  const float *m_in_proj, *m_conv_w, *m_conv_b, *m_dt_bias, *m_a_log, *m_d, *m_norm, *m_out_proj;
 } layer_w;
 
 typedef struct oracle {
@@ -47,6 +49,7 @@ typedef struct oracle {
   float* lm_head_owned;
   layer_w L[MAX_LAYERS];
   float *rope_cos, *rope_sin; /* [max_seq_len, hd]  rope.go:18-50 */
+  int is_mamba[MAX_LAYERS];   /* ModelConfig.HybridLayers (config.go:113) */
   char err[256];
 } oracle;
 
@@ -57,6 +60,11 @@ typedef struct okv {
   int n_layers, n_kv, hd, cap, len;
   float* k; /* [L][n_kv][cap][hd] */
   float* v;
+  /* Mamba2Layer.SSMState (mamba2.go:27) of every layer, [L][heads][head_dim][state]; the
+   * reference keeps it in the layer object and resets it on a new prompt
+   * (generic_model.go:285-292) — per sequence here, zero at creation / reset */
+  float* ssm;
+  size_t ssm_layer;
 } okv;
 
 /* ---------------------------------------------------------------- helpers */
@@ -357,6 +365,96 @@ static void moe_forward(const oracle* o, const layer_w* w, const float* x, float
   free(eout);
 }
 
+/* Mamba2Layer.Forward (mamba2.go:72-207) for one sequence: x [T, H] -> out [T, H]; `state` is
+ * the layer's SSMState [heads][head_dim][state_size] (updated in place).  Every loop keeps the
+ * reference's accumulation order; exp / log / sqrt go through double where the Go code does.
+ * Quirk kept on purpose: the causal convolution is zero-padded at the start of EVERY call
+ * (causalConv1d :209-270 never reads ConvCache), so a decode step convolves its single token
+ * with nothing but the last tap. */
+static void mamba_forward(const oracle* o, const layer_w* w, const float* x, float* out, int T,
+                          float* state) {
+  const nvllm_config* g = &o->cfg;
+  const int H = g->hidden, nh = g->mamba_num_heads, hd = g->mamba_head_dim, N = g->mamba_state_size;
+  const int G = g->mamba_n_groups, K = g->mamba_conv_kernel;
+  const int E = nh * hd, conv = E + 2 * G * N, P = E + conv + nh;
+  float* proj = (float*)malloc(sizeof(float) * (size_t)T * P);
+  float* xbc = (float*)malloc(sizeof(float) * (size_t)T * conv);
+  float* y = (float*)malloc(sizeof(float) * (size_t)T * E);
+  /* :86-87 projected = MatMul(xFlat, Transpose(InProj)), InProj [P, H] */
+  for (int t = 0; t < T; t++)
+    for (int n = 0; n < P; n++) {
+      float acc = 0.f;
+      const float* wr = w->m_in_proj + (size_t)n * H;
+      for (int p = 0; p < H; p++) acc += x[(size_t)t * H + p] * wr[p];
+      proj[(size_t)t * P + n] = acc;
+    }
+  /* :95-98 split [gate | xBC | dt]; :105 causal conv on xBC (:209-270); :108 SiLU */
+  for (int t = 0; t < T; t++)
+    for (int c = 0; c < conv; c++) {
+      float sum = 0.f;
+      for (int k = 0; k < K; k++) {
+        const int src = t + k - (K - 1); /* padded position t + k; the first K - 1 are zeros */
+        const float v = src >= 0 ? proj[(size_t)src * P + E + c] : 0.f;
+        sum += v * w->m_conv_w[(size_t)c * K + k];
+      }
+      if (w->m_conv_b) sum += w->m_conv_b[c];
+      xbc[(size_t)t * conv + c] = silu1(sum);
+    }
+  /* :121-131 delta = softplus(dt + bias); :134 selectiveScan (:273-351) */
+  for (int t = 0; t < T; t++) {
+    for (int h = 0; h < nh; h++) {
+      float dt = proj[(size_t)t * P + E + conv + h];
+      if (w->m_dt_bias) dt += w->m_dt_bias[h];
+      dt = (float)log(1.0 + exp((double)dt));
+      float abar = 1.0f;
+      if (w->m_a_log) {
+        const float A = -(float)exp((double)w->m_a_log[h]);
+        abar = (float)exp((double)(A * dt));
+      }
+      int grp = h * G / nh;
+      if (grp >= G) grp = G - 1;
+      const float* u = xbc + (size_t)t * conv + (size_t)h * hd;
+      const float* Bt = xbc + (size_t)t * conv + E + (size_t)grp * N;
+      const float* Ct = xbc + (size_t)t * conv + E + (size_t)G * N + (size_t)grp * N;
+      float* st = state + (size_t)h * hd * N;
+      for (int d = 0; d < hd; d++)
+        for (int s2 = 0; s2 < N; s2++) {
+          const float old = st[(size_t)d * N + s2];
+          st[(size_t)d * N + s2] = abar * old + dt * Bt[s2] * u[d];
+        }
+      for (int d = 0; d < hd; d++) {
+        float sum = 0.f;
+        for (int s2 = 0; s2 < N; s2++) sum += Ct[s2] * st[(size_t)d * N + s2];
+        if (w->m_d) sum += w->m_d[h] * u[d];
+        y[(size_t)t * E + (size_t)h * hd + d] = sum;
+      }
+    }
+  }
+  /* :139-173 RMSNormGated: y *= silu(gate); rms over E with eps 1e-5; * Norm */
+  for (int t = 0; t < T; t++) {
+    float* yr = y + (size_t)t * E;
+    for (int d = 0; d < E; d++) yr[d] *= silu1(proj[(size_t)t * P + d]);
+    float var = 0.f;
+    for (int d = 0; d < E; d++) var += yr[d] * yr[d];
+    var /= (float)E;
+    const float rms = 1.0f / (float)sqrt((double)(var + 1e-5f));
+    for (int d = 0; d < E; d++) yr[d] *= rms;
+    if (w->m_norm)
+      for (int d = 0; d < E; d++) yr[d] *= w->m_norm[d];
+  }
+  /* :177-179 output = MatMul(yFlat, Transpose(OutProj)), OutProj [H, E] */
+  for (int t = 0; t < T; t++)
+    for (int n = 0; n < H; n++) {
+      float acc = 0.f;
+      const float* wr = w->m_out_proj + (size_t)n * E;
+      for (int p = 0; p < E; p++) acc += y[(size_t)t * E + p] * wr[p];
+      out[(size_t)t * H + n] = acc;
+    }
+  free(proj);
+  free(xbc);
+  free(y);
+}
+
 /* residual combine used by every sequential branch (generic_model.go:320-326 etc.) */
 static void residual_add(const oracle* o, float* x, const float* residual, size_t n) {
   float rm = o->cfg.residual_multiplier;
@@ -526,6 +624,14 @@ int oracle_set_weight(oracle* o, int id, int layer, const float* p) {
     case NVLLM_W_MOE_ROUTER: w->router = p; break;
     case NVLLM_W_MOE_INPUT: w->moe_in = p; break;
     case NVLLM_W_MOE_OUTPUT: w->moe_out = p; break;
+    case NVLLM_W_MAMBA_IN_PROJ: w->m_in_proj = p; break;
+    case NVLLM_W_MAMBA_CONV_W: w->m_conv_w = p; break;
+    case NVLLM_W_MAMBA_CONV_B: w->m_conv_b = p; break;
+    case NVLLM_W_MAMBA_DT_BIAS: w->m_dt_bias = p; break;
+    case NVLLM_W_MAMBA_A_LOG: w->m_a_log = p; break;
+    case NVLLM_W_MAMBA_D: w->m_d = p; break;
+    case NVLLM_W_MAMBA_NORM: w->m_norm = p; break;
+    case NVLLM_W_MAMBA_OUT_PROJ: w->m_out_proj = p; break;
     default: return -1;
   }
   return 0;
@@ -542,15 +648,26 @@ okv* oracle_kv_create(const oracle* o) {
   size_t n = (size_t)c->n_layers * c->n_kv * c->cap * c->hd;
   c->k = (float*)malloc(sizeof(float) * n);
   c->v = (float*)malloc(sizeof(float) * n);
+  c->ssm_layer = (size_t)g->mamba_num_heads * g->mamba_head_dim * g->mamba_state_size;
+  if (c->ssm_layer) c->ssm = (float*)calloc((size_t)c->n_layers * c->ssm_layer, sizeof(float));
   return c;
 }
 void oracle_kv_destroy(okv* c) {
   if (!c) return;
   free(c->k);
   free(c->v);
+  free(c->ssm);
   free(c);
 }
-void oracle_kv_reset(okv* c) { c->len = 0; }
+void oracle_kv_reset(okv* c) {
+  c->len = 0;
+  if (c->ssm) memset(c->ssm, 0, sizeof(float) * (size_t)c->n_layers * c->ssm_layer);
+}
+int oracle_set_layer_types(oracle* o, const int32_t* types, int n) {
+  if (n != o->cfg.num_layers) return -1;
+  for (int i = 0; i < n; i++) o->is_mamba[i] = types[i] != 0;
+  return 0;
+}
 int oracle_kv_len(const okv* c) { return c->len; }
 /* copy out K or V of (layer, kv head): [len, hd] — lets tests compare the device KV pool */
 void oracle_kv_read(const okv* c, int layer, int head, int which, float* out) {
@@ -597,9 +714,24 @@ int oracle_forward(oracle* o, const int32_t* tokens, int T, okv* c, int pos_offs
   if (g->embedding_multiplier != 0.f) /* :298-302 */
     for (size_t i = 0; i < n; i++) x[i] *= g->embedding_multiplier;
 
+  /* generic_model.go:285-292: a brand-new prompt resets every Mamba2 state */
+  if (pos_offset == 0 && T > 1 && c->ssm)
+    memset(c->ssm, 0, sizeof(float) * (size_t)c->n_layers * c->ssm_layer);
+
   for (int l = 0; l < g->num_layers; l++) {
     const layer_w* w = &o->L[l];
-    if (g->attention_type == NVLLM_ATTN_MQA && g->block_style == NVLLM_BLOCK_PARALLEL) {
+    if (o->is_mamba[l]) {
+      /* generic_model.go:457-459 -> GenericBlock.Forward -> forwardMamba2 (:162-202):
+       * norm + Mamba2 + residual, norm + FFN (shared MLP, never MoE) + residual */
+      layer_norm(x, w->attn_norm_w, w->attn_norm_b, g->norm_eps, xn, T, H);
+      mamba_forward(o, w, xn, a, T, c->ssm + (size_t)l * c->ssm_layer);
+      residual_add(o, a, x, n);
+      memcpy(x, a, sizeof(float) * n);
+      layer_norm(x, w->ffn_norm_w, w->ffn_norm_b, g->norm_eps, xn, T, H);
+      ffn_forward(o, w, xn, f, T);
+      residual_add(o, f, x, n);
+      memcpy(x, f, sizeof(float) * n);
+    } else if (g->attention_type == NVLLM_ATTN_MQA && g->block_style == NVLLM_BLOCK_PARALLEL) {
       /* :395-418 parallel block */
       layer_norm(x, w->attn_norm_w, w->attn_norm_b, g->norm_eps, xn, T, H);
       if (attention_forward(o, w, l, xn, a, T, c, pos_offset)) {
@@ -797,6 +929,10 @@ void oracle_split_gpt2_qkv(const float* qkv, int hidden, float* Q, float* K, flo
 }
 
 /* stand-alone ops for unit parity of single kernels */
+/* one Mamba2 layer on its own (tests: checked against an independent numpy restatement) */
+void oracle_mamba_layer(oracle* o, int layer, const float* x, float* out, int T, float* state) {
+  mamba_forward(o, &o->L[layer], x, out, T, state);
+}
 void oracle_matmul(const float* a, const float* b, float* c, int m, int k, int n) {
   matmul(a, b, c, m, k, n);
 }

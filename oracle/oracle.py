@@ -41,6 +41,8 @@ def lib():
         L.oracle_create.argtypes = [ctypes.c_void_p]
         L.oracle_destroy.argtypes = [ctypes.c_void_p]
         L.oracle_set_weight.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, _f32p]
+        L.oracle_set_layer_types.argtypes = [ctypes.c_void_p, _i32p, ctypes.c_int]
+        L.oracle_mamba_layer.argtypes = [ctypes.c_void_p, ctypes.c_int, _f32p, _f32p, ctypes.c_int, _f32p]
         L.oracle_kv_create.restype = ctypes.c_void_p
         L.oracle_kv_create.argtypes = [ctypes.c_void_p]
         L.oracle_kv_destroy.argtypes = [ctypes.c_void_p]
@@ -108,11 +110,22 @@ class OracleModel:
         if not self._p:
             raise RuntimeError("oracle_create failed")
         self._keep = []
+        if getattr(cfg, "hybrid_layers", ()):
+            types = np.asarray([1 if t else 0 for t in cfg.hybrid_layers], dtype=np.int32)
+            if lib().oracle_set_layer_types(self._p, _ip(types), len(types)) != 0:
+                raise ValueError("hybrid_layers must name every layer")
         for wid, layer, arr in weights:
             a = np.ascontiguousarray(arr, dtype=np.float32)
             self._keep.append(a)
             if lib().oracle_set_weight(self._p, wid, layer, _fp(a)) != 0:
                 raise ValueError(f"oracle_set_weight({wid},{layer}) failed")
+
+    def mamba_layer(self, layer: int, x: np.ndarray, state: np.ndarray) -> np.ndarray:
+        """Mamba2Layer.Forward of one layer: x [T, H] -> [T, H]; `state` [heads, hd, N] is updated."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        out = np.empty_like(x)
+        lib().oracle_mamba_layer(self._p, layer, _fp(x), _fp(out), x.shape[0], _fp(state))
+        return out
 
     def new_cache(self) -> OracleKV:
         return OracleKV(self)
