@@ -24,7 +24,7 @@ void free_workspace(nvllm_handle* h) {
   Workspace& w = h->ws;
   h->drop_graphs();  // the captured decode steps hold these pointers
   void* ptrs[] = {w.tp_buf, w.x, w.xn, w.xn_f32, w.ws_a, w.ws_b, w.ws_c, w.q, w.attn_out, w.hbuf, w.xn_last,
-                  w.xb, w.ssq, w.res_ctr, w.chain_ctr, w.logits_p, w.logits, w.attn_ws, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
+                  w.xb, w.ssq, w.res_ctr, w.chain_ctr, w.m_xbc, w.m_dt, w.m_y, w.m_yn, w.logits_p, w.logits, w.attn_ws, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
                   w.sort.counts, w.sort.offsets, w.sort.cursor, w.sort.sorted_pair, w.sort.pair_row,
                   w.sort.a_rows, w.sort.tile_expert, w.sort.tile_row0, w.sort.tile_rows,
                   w.sort.n_tiles, w.moe_Y, w.moe_y, w.moe_xs};
@@ -67,6 +67,7 @@ int ensure_workspace(nvllm_handle* h, int T, int n) {
   WS(w.x, Tc * H * 4);
   WS(w.xn, Tc * H * asz);
   size_t a_cols = std::max(h->qkv_cols, h->moe ? 0 : h->w1_cols);
+  if (h->n_mamba) a_cols = std::max(a_cols, (size_t)h->m_P);
   w.ws_a_floats = rows * a_cols;
   if (h->moe) w.ws_a_floats = std::max(w.ws_a_floats, (size_t)Tc * h->topk * 2 * h->F);
   w.ws_b_floats = rows * H;
@@ -78,6 +79,12 @@ int ensure_workspace(nvllm_handle* h, int T, int n) {
   WS(w.hbuf, h->moe ? (size_t)Tc * h->topk * h->F * asz : (size_t)Tc * h->F * asz);
   WS(w.xn_last, nc * H * asz);
   WS(w.chain_ctr, 256);
+  if (h->n_mamba) {
+    WS(w.m_xbc, (size_t)Tc * h->m_conv * 4);
+    WS(w.m_dt, (size_t)Tc * h->m_nh * 4);
+    WS(w.m_y, (size_t)Tc * h->m_E * 4);
+    WS(w.m_yn, (size_t)Tc * h->m_E * asz);
+  }
   if (cudaMemsetAsync(w.chain_ctr, 0, 256, h->stream) != cudaSuccess)
     return set_err(h, NVLLM_ERR_CUDA, "memset(chain counters) failed");
   if (h->fold) {
@@ -511,6 +518,39 @@ int forward_step(nvllm_handle* h) {
 
   for (int l = 0; l < h->L; l++) {
     const LayerW& lw = h->layers[l];
+    if (!h->is_mamba.empty() && h->is_mamba[l]) {
+      // ---- Mamba2 sub-block (generic_model.go:162-181, mamba2.go:72-207): norm -> in_proj GEMM
+      // -> conv + SiLU + softplus -> selective scan -> gate + RMS norm -> out_proj GEMM, whose
+      // result is added to the residual stream by the next norm like an attention output
+      if ((rc = run_norm(h, w.x, &p1, &p2, lw.attn_norm_w, lw.attn_norm_b, w.xn, nullptr, nullptr, T)))
+        return rc;
+      Pending pr;
+      if ((rc = run_gemm(h, w.xn, H, lw.m_in_proj, T, h->m_P, H, 1.f, w.ws_a, w.ws_a_floats, h->m_P, &pr)))
+        return rc;
+      MambaArgs ma{};
+      ma.T = T; ma.n_seqs = n;
+      ma.nh = h->m_nh; ma.hd = h->m_hd; ma.N = h->m_N; ma.G = h->m_G; ma.K = h->m_K; ma.E = h->m_E;
+      ma.conv = h->m_conv; ma.P = h->m_P;
+      ma.proj = pr.p; ma.S = pr.S; ma.stride = pr.stride;
+      ma.conv_w = lw.m_conv_w; ma.conv_b = lw.m_conv_b; ma.dt_bias = lw.m_dt_bias; ma.a_log = lw.m_a_log;
+      ma.d_skip = lw.m_d; ma.norm_w = lw.m_norm;
+      ma.xbc = w.m_xbc; ma.dt = w.m_dt; ma.y = w.m_y;
+      ma.cu_q = d + L.cu_q; ma.positions = d_pos; ma.block_tables = d + L.block_tables;
+      ma.max_blocks = L.max_blocks;
+      ma.ssm_pool = h->ssm_pool; ma.n_mamba = h->n_mamba; ma.layer = h->mamba_idx[l];
+      {
+        const double state_bytes = 2.0 * n * h->m_nh * h->m_hd * h->m_N * 4;  // SSM state in + out
+        ProfScope ps(h, NVLLM_K_MISC, (double)T * (h->m_P * 4.0 + h->m_E * asz) + state_bytes, 0,
+                     (double)T * (h->m_conv + h->m_nh + 2.0 * h->m_E) * 4 + (double)T * h->m_P * 4 * (pr.S - 1));
+        LAUNCH(h, launch_mamba_conv(st, ma));
+        LAUNCH(h, launch_mamba_scan(st, ma));
+        LAUNCH(h, launch_mamba_gate_norm(st, ma, h->adt, w.m_yn));
+      }
+      if ((rc = run_gemm(h, w.m_yn, h->m_E, lw.m_out_proj, T, H, h->m_E, 1.f, w.ws_b, w.ws_b_floats, H, &p1)))
+        return rc;
+      p1.bias = nullptr;
+      p1.m = m_res;
+    } else {
     // ---- attention sub-block
     if ((rc = tp_reduce_pending(h, &p1, &p2, T))) return rc;
     Pending qkv;
@@ -574,6 +614,7 @@ int forward_step(nvllm_handle* h) {
       p1.bias = lw.bo;
       p1.m = h->parallel ? (par_scaled ? c.attention_multiplier : 1.f) : m_res;
     }
+    }  // attention / Mamba2 sub-block
     // ---- feed-forward sub-block
     float* ffn_out = w.ws_b;
     if (h->parallel) {

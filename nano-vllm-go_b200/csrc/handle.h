@@ -27,6 +27,10 @@ struct LayerW {
   void* moe_in = nullptr;   // [E, 2I, H]
   void* moe_out = nullptr;  // [E, H, I]
   bool has_bq = false, has_bk = false, has_bv = false;
+  // Mamba2 block (mamba.cu): in_proj [P, H] / out_proj [H, E] in the weight dtype, the rest fp32
+  void *m_in_proj = nullptr, *m_out_proj = nullptr;
+  float *m_conv_w = nullptr, *m_conv_b = nullptr, *m_dt_bias = nullptr, *m_a_log = nullptr,
+        *m_d = nullptr, *m_norm = nullptr;
 };
 
 // one engine step's integer inputs, packed in a single pinned host buffer and copied with
@@ -55,6 +59,10 @@ struct Workspace {
   void* attn_out = nullptr;  // [T, nh hd]
   void* hbuf = nullptr;      // [T, F] or [T k, I]
   void* xn_last = nullptr;   // [n, H]
+  float* m_xbc = nullptr;    // [T, conv_dim] Mamba2: conv + SiLU output (x | B | C)
+  float* m_dt = nullptr;     // [T, heads]    softplus(dt + bias)
+  float* m_y = nullptr;      // [T, E] fp32 scan output
+  void* m_yn = nullptr;      // [T, E] gated + normed, act dtype (out_proj input)
   // folded RMSNorm (forward.cu): bf16(x * g) of the residual stream (g = the next norm's weight), the
   // per-column-tile row sums of squares [parts][T_cap] of it, and the arrival / done counters of
   // the two fused-residual GEMM sites of a layer (O projection, FFN down projection)
@@ -124,6 +132,16 @@ struct nvllm_handle {
   size_t p2p_cap = 0;              // floats per data buffer
   uint32_t p2p_epoch = 0;
   bool p2p_ok = false;
+  // Granite-4 hybrid: Mamba2 layers (nvllm_set_layer_types).  SSM state is kept PER KV BLOCK:
+  // ssm_pool[block][mamba layer][heads][head_dim][state] holds the state after the last token
+  // written into that block, so it is addressed through the block table like K / V — no
+  // per-sequence bookkeeping at the boundary, and a prefix-cache hit finds the state of the
+  // cached prefix in its last block.
+  std::vector<uint8_t> is_mamba;  // [L]
+  std::vector<int> mamba_idx;     // [L] index among the Mamba2 layers, -1 for attention layers
+  int n_mamba = 0;
+  int m_nh = 0, m_hd = 0, m_N = 0, m_G = 0, m_K = 0, m_E = 0, m_conv = 0, m_P = 0;
+  float* ssm_pool = nullptr;
   // weights
   void *wte = nullptr, *wpe = nullptr, *lm_head = nullptr;
   bool lm_head_owned = false;

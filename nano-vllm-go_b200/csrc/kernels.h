@@ -318,6 +318,30 @@ cudaError_t launch_attn_prefill_tc5(cudaStream_t st, const AttnArgs& a);
 bool attn_decode_t_supported(const AttnArgs& a);
 cudaError_t launch_attn_decode_t(cudaStream_t st, const AttnArgs& a);
 
+// ---------------------------------------------------------------- mamba.cu
+// Mamba2 block between its two projections (mamba2.go:72-351), ragged batch
+struct MambaArgs {
+  int T, n_seqs;
+  int nh, hd, N, G, K, E, conv, P;  // heads, head dim, state size, groups, conv taps, E = nh hd,
+                                    // conv = E + 2 G N, P = E + conv + nh
+  const float* proj;   // [S][T][P] split-K slices of x @ in_proj^T: [gate | xBC | dt]
+  int S;
+  size_t stride;
+  const float *conv_w, *conv_b, *dt_bias, *a_log, *d_skip, *norm_w;
+  float* xbc;          // [T, conv]  SiLU(conv1d(xBC))
+  float* dt;           // [T, nh]    softplus(dt + bias)
+  float* y;            // [T, E]     scan output
+  const int* cu_q;         // [n_seqs + 1] rows of each sequence
+  const int* positions;    // [T]
+  const int* block_tables; // [n_seqs, max_blocks]
+  int max_blocks;
+  float* ssm_pool;     // [blocks][n_mamba][nh][hd][N]: state after the last token of each block
+  int n_mamba, layer;  // Mamba2 layers in the model, index of this one among them
+};
+cudaError_t launch_mamba_conv(cudaStream_t st, const MambaArgs& a);
+cudaError_t launch_mamba_scan(cudaStream_t st, const MambaArgs& a);
+cudaError_t launch_mamba_gate_norm(cudaStream_t st, const MambaArgs& a, int odt, void* out);
+
 // ---------------------------------------------------------------- moe.cu
 // Router: probs = softmax(x @ R) over all E, top-k (descending), weights renormalised
 // (moe.go:63-103).  x fp32 [T,H]; R fp32 [E,H].

@@ -250,6 +250,52 @@ int nvllm_create(const nvllm_config* c, const uint8_t* tp_id, nvllm_handle** out
   return NVLLM_OK;
 }
 
+// ModelConfig.HybridLayers (config.go:113): which blocks are Mamba2.  Allocates their tensors.
+int nvllm_set_layer_types(nvllm_handle* h, const int32_t* types, int n_layers) {
+  if (!h || !types) return NVLLM_ERR_INVALID;
+  if (h->finalized) return set_err(h, NVLLM_ERR_STATE, "set_layer_types after finalize");
+  if (n_layers != h->L) return set_err(h, NVLLM_ERR_INVALID, "%d layer types for %d layers", n_layers, h->L);
+  const nvllm_config& c = h->cfg;
+  bool any = false;
+  for (int l = 0; l < n_layers; l++) any = any || types[l] != 0;
+  if (!any) return NVLLM_OK;
+  if (h->n_mamba) return set_err(h, NVLLM_ERR_STATE, "layer types are already set");
+  if (c.mamba_num_heads <= 0 || c.mamba_head_dim <= 0 || c.mamba_state_size <= 0 || c.mamba_n_groups <= 0 ||
+      c.mamba_conv_kernel <= 0 || c.mamba_conv_kernel > 8 || c.mamba_state_size > 128 ||
+      c.mamba_head_dim > 128 || c.mamba_num_heads % c.mamba_n_groups != 0 ||
+      (c.mamba_num_heads * c.mamba_head_dim) % 8 != 0)
+    return set_err(h, NVLLM_ERR_INVALID, "Mamba2 layers need valid mamba_* config fields");
+  if (h->tp > 1 || h->moe || h->parallel)
+    return set_err(h, NVLLM_ERR_INVALID, "Mamba2 layers: sequential dense blocks on one GPU only");
+  NV_CHECK(h, cudaSetDevice(h->dev));
+  h->m_nh = c.mamba_num_heads; h->m_hd = c.mamba_head_dim; h->m_N = c.mamba_state_size;
+  h->m_G = c.mamba_n_groups; h->m_K = c.mamba_conv_kernel;
+  h->m_E = h->m_nh * h->m_hd;
+  h->m_conv = h->m_E + 2 * h->m_G * h->m_N;
+  h->m_P = h->m_E + h->m_conv + h->m_nh;
+  h->is_mamba.assign(h->L, 0);
+  h->mamba_idx.assign(h->L, -1);
+  const size_t wsz = dt_size(h->wdt);
+  for (int l = 0; l < h->L; l++) {
+    if (!types[l]) continue;
+    h->is_mamba[l] = 1;
+    h->mamba_idx[l] = h->n_mamba++;
+    LayerW& w = h->layers[l];
+    const size_t sizes[8] = {(size_t)h->m_P * h->H * wsz, (size_t)h->H * h->m_E * wsz,
+                             (size_t)h->m_conv * h->m_K * 4, (size_t)h->m_conv * 4, (size_t)h->m_nh * 4,
+                             (size_t)h->m_nh * 4, (size_t)h->m_nh * 4, (size_t)h->m_E * 4};
+    void** ptrs[8] = {&w.m_in_proj, &w.m_out_proj, (void**)&w.m_conv_w, (void**)&w.m_conv_b,
+                      (void**)&w.m_dt_bias, (void**)&w.m_a_log, (void**)&w.m_d, (void**)&w.m_norm};
+    for (int i = 0; i < 8; i++) {
+      cudaError_t e = cudaMalloc(ptrs[i], sizes[i]);
+      if (e != cudaSuccess) return set_err(h, NVLLM_ERR_NOMEM, "Mamba2 weights: %s", cudaGetErrorString(e));
+      h->weight_bytes += sizes[i];
+    }
+  }
+  h->spec_enabled = 0;  // a discarded speculative step would leave its SSM state in the block
+  return NVLLM_OK;
+}
+
 int nvllm_destroy(nvllm_handle* h) {
   if (!h) return NVLLM_OK;
   cudaSetDevice(h->dev);
@@ -265,12 +311,15 @@ int nvllm_destroy(nvllm_handle* h) {
   for (auto& w : h->layers) {
     F(w.attn_norm_w); F(w.attn_norm_b); F(w.ffn_norm_w); F(w.ffn_norm_b);
     F(w.wqkv); F(w.bqkv); F(w.wo); F(w.bo); F(w.w1); F(w.b1); F(w.w2); F(w.b2);
+    F(w.m_in_proj); F(w.m_out_proj); F(w.m_conv_w); F(w.m_conv_b); F(w.m_dt_bias); F(w.m_a_log);
+    F(w.m_d); F(w.m_norm);
     F(w.router); F(w.moe_in); F(w.moe_out);
   }
   F(h->cosT);
   F(h->sinT);
   F(h->kpool);
   F(h->vpool);
+  F(h->ssm_pool);
   F(h->d_stage);
   h->drop_graphs();
   F(h->d_stage2);
@@ -335,7 +384,7 @@ int nvllm_set_graphs(nvllm_handle* h, int enabled) {
 
 int nvllm_set_speculation(nvllm_handle* h, int enabled) {
   if (!h) return NVLLM_ERR_INVALID;
-  h->spec_enabled = enabled;
+  h->spec_enabled = (enabled && h->n_mamba == 0) ? 1 : 0;  // see nvllm_set_layer_types
   return NVLLM_OK;
 }
 

@@ -259,6 +259,14 @@ extern "C" int nvllm_run(nvllm_handle* h, int n, int is_prefill, const int32_t* 
       int nc = num_cached ? num_cached[i] : 0;
       if (nc < 0) return set_err(h, NVLLM_ERR_INVALID, "sequence %d: num_cached < 0", i);
       start = std::min(nc, len - 1);  // a fully cached prompt still computes its last token
+      // Mamba2 layers: the reference's causal conv restarts (zero padding) at the first token of
+      // every forward call (mamba2.go:209-270 never reads ConvCache), so a prompt computed in two
+      // calls differs from the same prompt in one.  A cached prefix is therefore only accepted
+      // when the call is decode-shaped (one new token, the reference's own decode semantics).
+      if (h->n_mamba && start > 0 && len - start > 1)
+        return set_err(h, NVLLM_ERR_INVALID,
+                       "sequence %d: hybrid (Mamba2) models cannot prefill %d tokens on top of %d cached "
+                       "ones; disable prefix caching / chunked prefill for them", i, len - start, start);
     }
     const int n_new = len - start;
     T += n_new;

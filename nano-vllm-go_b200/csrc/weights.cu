@@ -181,6 +181,31 @@ int nvllm::set_weight_src(nvllm_handle* h, int id, int layer, int dtype, const v
     case NVLLM_W_MOE_OUTPUT:
       if (!h->moe) return set_err(h, NVLLM_ERR_INVALID, "not a MoE model");
       r.to_f32 = false; r.dst = w->moe_out; r.N = -1; expect = (size_t)h->E * H * Fg; break;
+    // Mamba2Layer tensors (mamba2.go:9-28): the reference keeps in_proj / out_proj as loaded,
+    // [out, in] (it multiplies by their transpose, :87,:178) — already the device orientation
+    case NVLLM_W_MAMBA_IN_PROJ:
+    case NVLLM_W_MAMBA_OUT_PROJ:
+    case NVLLM_W_MAMBA_CONV_W:
+    case NVLLM_W_MAMBA_CONV_B:
+    case NVLLM_W_MAMBA_DT_BIAS:
+    case NVLLM_W_MAMBA_A_LOG:
+    case NVLLM_W_MAMBA_D:
+    case NVLLM_W_MAMBA_NORM: {
+      if (h->is_mamba.empty() || !h->is_mamba[layer])
+        return set_err(h, NVLLM_ERR_INVALID, "layer %d is not a Mamba2 layer (nvllm_set_layer_types)", layer);
+      r.N = -1;
+      switch (id) {
+        case NVLLM_W_MAMBA_IN_PROJ: r.to_f32 = false; r.dst = w->m_in_proj; expect = (size_t)h->m_P * H; break;
+        case NVLLM_W_MAMBA_OUT_PROJ: r.to_f32 = false; r.dst = w->m_out_proj; expect = (size_t)H * h->m_E; break;
+        case NVLLM_W_MAMBA_CONV_W: r.dst = w->m_conv_w; expect = (size_t)h->m_conv * h->m_K; break;
+        case NVLLM_W_MAMBA_CONV_B: r.dst = w->m_conv_b; expect = h->m_conv; break;
+        case NVLLM_W_MAMBA_DT_BIAS: r.dst = w->m_dt_bias; expect = h->m_nh; break;
+        case NVLLM_W_MAMBA_A_LOG: r.dst = w->m_a_log; expect = h->m_nh; break;
+        case NVLLM_W_MAMBA_D: r.dst = w->m_d; expect = h->m_nh; break;
+        default: r.dst = w->m_norm; expect = h->m_E; break;
+      }
+      break;
+    }
     default: return set_err(h, NVLLM_ERR_INVALID, "unknown weight id %d", id);
   }
   // `numel` is what the caller's buffer holds: the tensor itself, or the wider matrix it is a
@@ -271,14 +296,19 @@ extern "C" int nvllm_finalize(nvllm_handle* h) {
     if (!have(l, NVLLM_W_ATTN_NORM_B)) { cudaFree(w.attn_norm_b); w.attn_norm_b = nullptr; }
     if (!h->parallel) NEED(l, NVLLM_W_FFN_NORM_W);
     if (!have(l, NVLLM_W_FFN_NORM_B)) { cudaFree(w.ffn_norm_b); w.ffn_norm_b = nullptr; }
-    NEED(l, NVLLM_W_Q);
-    if (mqa) {
-      NEED(l, NVLLM_W_KV);
+    if (!h->is_mamba.empty() && h->is_mamba[l]) {
+      for (int id = NVLLM_W_MAMBA_IN_PROJ; id <= NVLLM_W_MAMBA_OUT_PROJ; id++)
+        if ((rc = need(l, id, "NVLLM_W_MAMBA_*")) != 0) return rc;
     } else {
-      NEED(l, NVLLM_W_K);
-      NEED(l, NVLLM_W_V);
+      NEED(l, NVLLM_W_Q);
+      if (mqa) {
+        NEED(l, NVLLM_W_KV);
+      } else {
+        NEED(l, NVLLM_W_K);
+        NEED(l, NVLLM_W_V);
+      }
+      NEED(l, NVLLM_W_O);
     }
-    NEED(l, NVLLM_W_O);
     // biases: MHA adds Q/K/V/O biases (attention.go:66-86), MQA adds Q and O biases when present
     // (mqa.go:101-114,88-96), GQA has none
     if (!(w.has_bq || w.has_bk || w.has_bv)) { cudaFree(w.bqkv); w.bqkv = nullptr; }
@@ -306,7 +336,7 @@ extern "C" int nvllm_finalize(nvllm_handle* h) {
     const char* env = getenv("NVLLM_FOLD");
     bool rms = !have(-1, NVLLM_W_FINAL_NORM_B);
     for (int l = 0; l < h->L; l++) rms = rms && !have(l, NVLLM_W_ATTN_NORM_B) && !have(l, NVLLM_W_FFN_NORM_B);
-    h->fold = rms && !h->moe && !h->parallel && h->tp == 1 && h->wdt == DT_BF16 && h->adt == DT_BF16 &&
+    h->fold = rms && !h->moe && !h->parallel && h->n_mamba == 0 && h->tp == 1 && h->wdt == DT_BF16 && h->adt == DT_BF16 &&
               h->use_tc5 && (h->H % 8) == 0 && !(env && atoi(env) == 0);
   }
 
@@ -342,6 +372,16 @@ extern "C" int nvllm_finalize(nvllm_handle* h) {
   NV_CHECK(h, cudaMemsetAsync(h->kpool, 0, pool_bytes, h->stream));
   NV_CHECK(h, cudaMemsetAsync(h->vpool, 0, pool_bytes, h->stream));
   h->kv_bytes = 2 * pool_bytes;
+  if (h->n_mamba) {
+    // SSM state snapshot of every (KV block, Mamba2 layer): see handle.h
+    const size_t ssm_bytes = (size_t)h->num_blocks * h->n_mamba * h->m_nh * h->m_hd * h->m_N * 4;
+    e = cudaMalloc((void**)&h->ssm_pool, ssm_bytes);
+    if (e != cudaSuccess)
+      return set_err(h, NVLLM_ERR_NOMEM, "SSM state pool of %d blocks (%.1f GB) does not fit: %s",
+                     h->num_blocks, ssm_bytes / 1e9, cudaGetErrorString(e));
+    NV_CHECK(h, cudaMemsetAsync(h->ssm_pool, 0, ssm_bytes, h->stream));
+    h->kv_bytes += ssm_bytes;
+  }
 
   NV_CHECK(h, cudaStreamSynchronize(h->stream));
   h->finalized = true;

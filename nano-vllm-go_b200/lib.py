@@ -80,6 +80,7 @@ SIGNATURES = {
     "nvllm_set_sampling": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_float, ctypes.c_int,
                                           ctypes.c_float]),
     "nvllm_set_seed": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_uint64]),
+    "nvllm_set_layer_types": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_int32), ctypes.c_int]),
     "nvllm_load_safetensors": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int, _u64p,
                                               ctypes.POINTER(ctypes.c_int32)]),
     "nvllm_safetensors_find": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_char_p,

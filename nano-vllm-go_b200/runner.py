@@ -80,6 +80,10 @@ class CudaModelRunner:
         L.check(self._lib.nvllm_create(ctypes.byref(cc), idbuf, ctypes.byref(self._h)))
         self.loaded_bytes, self.loaded_tensors = 0, 0
         try:
+            if getattr(cfg, "hybrid_layers", ()):
+                # ModelConfig.HybridLayers (config.go:113): Mamba2 blocks of the Granite-4 hybrid
+                types = (ctypes.c_int32 * cfg.num_layers)(*[1 if t else 0 for t in cfg.hybrid_layers])
+                L.check(self._lib.nvllm_set_layer_types(self._h, types, cfg.num_layers), self._h)
             if model_dir is not None:
                 nb, nt = ctypes.c_uint64(), ctypes.c_int32()
                 L.check(self._lib.nvllm_load_safetensors(self._h, os.fsencode(model_dir), int(arch),
