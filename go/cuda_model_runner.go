@@ -92,7 +92,34 @@ func fillConfig(mc *tensor.ModelConfig, engineCfg *Config, device int, bf16 bool
 	cc.max_batched_tokens = C.int32_t(engineCfg.MaxNumBatchedTokens)
 	cc.tp_size = 1
 	cc.device = C.int32_t(device)
+	// Granite-4 hybrid (config.go:100-115); which layers are Mamba2 goes through
+	// nvllm_set_layer_types (setLayerTypes below)
+	cc.mamba_num_heads = C.int32_t(mc.Mamba2NumHeads)
+	cc.mamba_head_dim = C.int32_t(mc.Mamba2HeadDim)
+	cc.mamba_state_size = C.int32_t(mc.Mamba2StateSize)
+	cc.mamba_n_groups = C.int32_t(mc.Mamba2NGroups)
+	cc.mamba_conv_kernel = C.int32_t(mc.Mamba2ConvKernel)
 	return cc
+}
+
+// setLayerTypes tells the library which blocks are Mamba2 (ModelConfig.HybridLayers,
+// "mamba" / "mamba2" as in generic_model.go:74-75).  The library keeps the SSM state per KV
+// block, so hybrid models need nothing else at the boundary — but the engine must not use the
+// prefix cache or chunked prefill for them (the reference's causal conv restarts per call).
+func setLayerTypes(h *C.nvllm_handle, mc *tensor.ModelConfig) error {
+	if len(mc.HybridLayers) == 0 {
+		return nil
+	}
+	types := make([]C.int32_t, len(mc.HybridLayers))
+	for i, t := range mc.HybridLayers {
+		if t == "mamba" || t == "mamba2" {
+			types[i] = 1
+		}
+	}
+	if rc := C.nvllm_set_layer_types(h, &types[0], C.int(len(types))); rc != 0 {
+		return lastError(h)
+	}
+	return nil
 }
 
 // NewCudaModelRunnerFromDir is the constructor to prefer: only config.json goes through the
@@ -174,6 +201,10 @@ func NewCudaModelRunner(modelDir string, engineCfg *Config, device int, bf16 boo
 		C.nvllm_destroy(h)
 		return nil, e
 	}
+	if e := setLayerTypes(h, mc); e != nil {
+		C.nvllm_destroy(h)
+		return nil, e
+	}
 	set := func(id C.int, layer int, t *tensor.Tensor) error {
 		if t == nil || len(t.Data) == 0 {
 			return nil // optional tensors (biases) are simply not sent
@@ -239,6 +270,13 @@ func (r *CudaModelRunner) setBlock(set func(C.int, int, *tensor.Tensor) error, l
 				set(C.NVLLM_W_K_BIAS, l, &tensor.Tensor{Data: a.KVBias.Data[:hd], Shape: []int{hd}}),
 				set(C.NVLLM_W_V_BIAS, l, &tensor.Tensor{Data: a.KVBias.Data[hd : 2*hd], Shape: []int{hd}}))
 		}
+	case *tensor.Mamba2Layer:
+		// kept as loaded, [out, in] (mamba2.go:87,178 multiply by the transpose); XProj / DtProj are
+		// never read by Forward and ConvCache / SSMState are run-time state: not sent
+		es = append(es, set(C.NVLLM_W_MAMBA_IN_PROJ, l, a.InProj), set(C.NVLLM_W_MAMBA_CONV_W, l, a.ConvWeight),
+			set(C.NVLLM_W_MAMBA_CONV_B, l, a.ConvBias), set(C.NVLLM_W_MAMBA_DT_BIAS, l, a.DeltaBias),
+			set(C.NVLLM_W_MAMBA_A_LOG, l, a.ALog), set(C.NVLLM_W_MAMBA_D, l, a.D),
+			set(C.NVLLM_W_MAMBA_NORM, l, a.Norm), set(C.NVLLM_W_MAMBA_OUT_PROJ, l, a.OutProj))
 	}
 	if b.MoE != nil {
 		es = append(es, set(C.NVLLM_W_MOE_ROUTER, l, b.MoE.Router), set(C.NVLLM_W_MOE_INPUT, l, b.MoE.InputLinear),
