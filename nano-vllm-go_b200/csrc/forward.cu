@@ -288,7 +288,8 @@ static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int 
                     float alpha, float* out, size_t cap, int ldo, Pending* res, int epi = 0,
                     void* epi_out = nullptr, int epi_ld = 0, const float* epi_bias = nullptr,
                     const void* pf_ptr = nullptr, size_t pf_bytes = 0, double alg_out = 0.0,
-                    const RowScale* rs = nullptr, const Resid* rd = nullptr) {
+                    const RowScale* rs = nullptr, const Resid* rd = nullptr,
+                    const GemvPre* gp = nullptr) {
   res->p = out;
   res->stride = (size_t)M * ldo;
   const double flops = 2.0 * M * N * K;
@@ -301,8 +302,14 @@ static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int 
     g.A = A; g.adt = h->adt; g.lda = lda; g.W = W; g.wdt = h->wdt;
     g.M = M; g.N = N; g.K = K; g.out = out; g.ldo = ldo; g.split_stride = res->stride;
     g.alpha = alpha; g.out_capacity = cap;
-    ProfScope ps(h, NVLLM_K_GEMV, io, flops, a_in + 4.0 * gemv_splits(M, N, K) * M * N);
-    LAUNCH(h, launch_gemv(h->stream, g));
+    // a fused pre-stage reads what the activation kernel would have read
+    double pre_alg = 0.0, pre_impl = 0.0;
+    if (gp && gp->mode == 2) {
+      pre_alg = (double)M * gp->hld * 4 - (double)M * K * dt_size(h->adt);
+      pre_impl = (double)M * gp->hld * 4 * (gp->Sh - 1);
+    }
+    ProfScope ps(h, NVLLM_K_GEMV, io + pre_alg, flops, a_in + pre_impl + 4.0 * gemv_splits(M, N, K) * M * N);
+    LAUNCH(h, launch_gemv(h->stream, g, gp));
     res->S = g.S;
     return NVLLM_OK;
   }
@@ -484,6 +491,11 @@ int forward_step(nvllm_handle* h) {
   // read per step (not cached): the parity tests switch it between runs
   const char* chain_env = getenv("NVLLM_CHAIN");
   const bool chain_on = !(chain_env && atoi(chain_env) == 0);
+  // Steps of <= 8 rows (GEMV shapes): the FFN activation is built inside the W2 GEMV — one
+  // launch per layer less on a chain of ~100 dependent launches.  NVLLM_GEMV_PRE=0 keeps the
+  // stand-alone activation kernel (read per step: the parity tests switch it).
+  const char* gpre_env = getenv("NVLLM_GEMV_PRE");
+  const bool gpre_act = !(gpre_env && atoi(gpre_env) == 0) && T <= 8 && !h->moe;
   int xb_parts = h->fold ? 1 : 0;
   const int h_tiles = ceil_div(H, 128);
   // generic_model.go:359-365: res + rm * x when ResidualMultiplier != 0, else plain add
@@ -748,6 +760,17 @@ int forward_step(nvllm_handle* h) {
                          w.hbuf, h->F, lw.b1, nullptr, 0, 0.0, &rsc)))
         return rc;
       xb_parts = 0;
+      if (h1.S > 0 && gpre_act) {
+        GemvPre ga{};
+        ga.mode = 2; ga.hp = h1.p; ga.Sh = h1.S; ga.hstride = h1.stride; ga.hld = h->w1_cols;
+        ga.hbias = lw.b1; ga.swiglu = h->swiglu ? 1 : 0;
+        if ((rc = run_gemm(h, w.hbuf, h->F, lw.w2, T, H, h->F, 1.f, ffn_out, w.ws_b_floats, H, &pf, 0,
+                           nullptr, 0, nullptr, nullptr, 0, 0.0, nullptr, nullptr, &ga)))
+          return rc;
+        pf.bias = lw.b2;
+        pf.m = h->parallel ? (par_scaled ? c.residual_multiplier : 1.f) : m_res;
+        continue;
+      }
       if (h1.S > 0) {
         ProfScope ps(h, NVLLM_K_ACT, (double)T * h->w1_cols * 4 + (double)T * h->F * asz, 0,
                      (double)T * h->w1_cols * 4 * (h1.S - 1));

@@ -74,7 +74,7 @@ constexpr int GEMV_PF = 2;
 template <typename AT, typename WT, int M, int R>
 __global__ void __launch_bounds__(256)
 gemv_kernel(const AT* __restrict__ A, int lda, const WT* __restrict__ W, int N, int K, int KC,
-            float* __restrict__ out, int ldo, size_t split_stride, float alpha, Trace tr) {
+            float* __restrict__ out, int ldo, size_t split_stride, float alpha, GemvPre pre, Trace tr) {
   TRACE_ENTRY(tr);
   pdl_launch_dependents();
   extern __shared__ float a_s[];  // [M][KC]
@@ -97,16 +97,44 @@ gemv_kernel(const AT* __restrict__ A, int lda, const WT* __restrict__ W, int N, 
     }
   }
   pdl_wait();
-  for (int i = threadIdx.x * 8; i < M * KC; i += blockDim.x * 8) {
-    const int m = i / KC, k = i % KC;
-    float v[8];
-    if (k < klen) {
-      load8(A + (size_t)m * lda + ks + k, v);
-    } else {
+  if (pre.mode == 0) {
+    for (int i = threadIdx.x * 8; i < M * KC; i += blockDim.x * 8) {
+      const int m = i / KC, k = i % KC;
+      float v[8];
+      if (k < klen) {
+        load8(A + (size_t)m * lda + ks + k, v);
+      } else {
 #pragma unroll
-      for (int j = 0; j < 8; j++) v[j] = 0.f;
+        for (int j = 0; j < 8; j++) v[j] = 0.f;
+      }
+      store8(a_s + i, v);
     }
-    store8(a_s + i, v);
+  } else {
+    // the activation kernel's work (act_kernel): SwiGLU over interleaved gate / up columns or
+    // tanh-GELU of the FFN up projection's split-K slices (transformer.go:50-78)
+    for (int i = threadIdx.x; i < M * KC; i += blockDim.x) {
+      const int m = i / KC, k = i % KC;
+      float y = 0.f;
+      if (k < klen) {
+        const int col = ks + k;
+        if (pre.swiglu) {
+          float g = 0.f, u = 0.f;
+          for (int sl = 0; sl < pre.Sh; sl++) {
+            const float* hrow = pre.hp + (size_t)sl * pre.hstride + (size_t)m * pre.hld + 2 * col;
+            g += hrow[0];
+            u += hrow[1];
+          }
+          y = silu(g) * u;
+        } else {
+          float hsum = 0.f;
+          for (int sl = 0; sl < pre.Sh; sl++) hsum += pre.hp[(size_t)sl * pre.hstride + (size_t)m * pre.hld + col];
+          if (pre.hbias) hsum += pre.hbias[col];
+          y = gelu_tanh(hsum);
+        }
+        y = to_f32(from_f32<AT>(y));
+      }
+      a_s[i] = y;
+    }
   }
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -169,13 +197,13 @@ gemv_kernel(const AT* __restrict__ A, int lda, const WT* __restrict__ W, int N, 
 }
 
 template <typename AT, typename WT, int M>
-static cudaError_t gemv_dispatch_r(cudaStream_t st, const GemmArgs& g, const GemvPlan& p) {
+static cudaError_t gemv_dispatch_r(cudaStream_t st, const GemmArgs& g, const GemvPlan& p, const GemvPre& pre) {
   dim3 grid(ceil_div(g.N, p.warps * p.R), p.S);
   size_t smem = (size_t)M * p.KC * sizeof(float);
 #define GV(RR)                                                                                     \
   (void)launch_k(gemv_kernel<AT, WT, M, RR>, dim3(grid), dim3(p.warps * 32), smem, st,                                     \
       (const AT*)g.A, g.lda, (const WT*)g.W, g.N, g.K, p.KC, g.out, g.ldo, g.split_stride, g.alpha, \
-      next_trace(11))
+      pre, next_trace(11))
   if (p.R == 4) GV(4);
   else if (p.R == 2) GV(2);
   else GV(1);
@@ -183,28 +211,31 @@ static cudaError_t gemv_dispatch_r(cudaStream_t st, const GemmArgs& g, const Gem
   return cudaGetLastError();
 }
 template <typename AT, typename WT>
-static cudaError_t gemv_dispatch_m(cudaStream_t st, const GemmArgs& g, const GemvPlan& p) {
+static cudaError_t gemv_dispatch_m(cudaStream_t st, const GemmArgs& g, const GemvPlan& p, const GemvPre& pre) {
   switch (g.M) {
-    case 1: return gemv_dispatch_r<AT, WT, 1>(st, g, p);
-    case 2: return gemv_dispatch_r<AT, WT, 2>(st, g, p);
-    case 3: return gemv_dispatch_r<AT, WT, 3>(st, g, p);
-    case 4: return gemv_dispatch_r<AT, WT, 4>(st, g, p);
-    case 5: return gemv_dispatch_r<AT, WT, 5>(st, g, p);
-    case 6: return gemv_dispatch_r<AT, WT, 6>(st, g, p);
-    case 7: return gemv_dispatch_r<AT, WT, 7>(st, g, p);
-    case 8: return gemv_dispatch_r<AT, WT, 8>(st, g, p);
+    case 1: return gemv_dispatch_r<AT, WT, 1>(st, g, p, pre);
+    case 2: return gemv_dispatch_r<AT, WT, 2>(st, g, p, pre);
+    case 3: return gemv_dispatch_r<AT, WT, 3>(st, g, p, pre);
+    case 4: return gemv_dispatch_r<AT, WT, 4>(st, g, p, pre);
+    case 5: return gemv_dispatch_r<AT, WT, 5>(st, g, p, pre);
+    case 6: return gemv_dispatch_r<AT, WT, 6>(st, g, p, pre);
+    case 7: return gemv_dispatch_r<AT, WT, 7>(st, g, p, pre);
+    case 8: return gemv_dispatch_r<AT, WT, 8>(st, g, p, pre);
   }
   return cudaErrorInvalidValue;
 }
 
-cudaError_t launch_gemv(cudaStream_t st, GemmArgs& g) {
+cudaError_t launch_gemv(cudaStream_t st, GemmArgs& g, const GemvPre* pre_in) {
+  GemvPre pre{};
+  if (pre_in) pre = *pre_in;
   if (g.M < 1 || g.M > 8 || (g.K % 8) != 0) return cudaErrorInvalidValue;
+  if (pre.mode != 0 && pre.mode != 2) return cudaErrorInvalidValue;
   GemvPlan p = gemv_plan(g.M, g.N, g.K);
   g.S = p.S;
   if (g.out_capacity && (size_t)p.S * g.split_stride > g.out_capacity) return cudaErrorInvalidValue;
-  if (g.adt == DT_F32 && g.wdt == DT_F32) return gemv_dispatch_m<float, float>(st, g, p);
-  if (g.adt == DT_F32 && g.wdt == DT_BF16) return gemv_dispatch_m<float, bf16>(st, g, p);
-  if (g.adt == DT_BF16 && g.wdt == DT_BF16) return gemv_dispatch_m<bf16, bf16>(st, g, p);
+  if (g.adt == DT_F32 && g.wdt == DT_F32) return gemv_dispatch_m<float, float>(st, g, p, pre);
+  if (g.adt == DT_F32 && g.wdt == DT_BF16) return gemv_dispatch_m<float, bf16>(st, g, p, pre);
+  if (g.adt == DT_BF16 && g.wdt == DT_BF16) return gemv_dispatch_m<bf16, bf16>(st, g, p, pre);
   return cudaErrorInvalidValue;
 }
 

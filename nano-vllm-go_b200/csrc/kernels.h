@@ -166,9 +166,26 @@ struct GemmArgs {
   size_t expert_stride;    // elements
   int max_tiles;
 };
+// Single-sequence decode (M <= 8) is a chain of ~100 dependent launches of ~3 us: the W2 GEMV
+// builds its own activation from the W1 GEMV's split-K slices instead of reading what an
+// activation kernel stored (one launch per layer less; every CTA only touches its own k-chunk,
+// so nothing is read twice).
+//  mode 2: A = act(sum_s hp[s] + hbias): SwiGLU over interleaved gate / up columns, or tanh-GELU,
+//          rounded to `adt` exactly like the stand-alone kernel rounds what it stores.
+// (The same trick for the norms — every CTA re-deriving the row statistics from x + the pending
+// slices — was measured on cfg1 and lost: 313 -> 334 us per decode step; removed.)
+struct GemvPre {
+  int mode;  // 0 = none, 2 = activation
+  const float* hp;  // [Sh][M][hld] split-K slices of the FFN up projection
+  int Sh;
+  size_t hstride;
+  int hld;
+  const float* hbias;  // [K] (GELU branch) or null
+  int swiglu;
+};
 // split-K slices a skinny GEMV will produce for (M,N,K); workspace must hold S*M*N floats
 int gemv_splits(int M, int N, int K);
-cudaError_t launch_gemv(cudaStream_t st, GemmArgs& g);       // M <= 8
+cudaError_t launch_gemv(cudaStream_t st, GemmArgs& g, const GemvPre* pre = nullptr);  // M <= 8
 cudaError_t launch_gemm_simt(cudaStream_t st, GemmArgs& g);  // any M (fp32 parity mode, MoE)
 
 // ---------------------------------------------------------------- gemm_tcgen05.cu

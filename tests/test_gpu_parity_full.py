@@ -195,3 +195,37 @@ def test_chained_ffn_gemms_bit_identical_to_two_launches(family, batch, monkeypa
     assert np.array_equal(outs["1"][0], outs["0"][0])
     monkeypatch.setenv("NVLLM_CHAIN", "1")
     _batch_parity(cfg, C.PREC_BF16, prompts, 3, tables)
+
+
+@pytest.mark.parametrize("family", ["llama", "gpt2", "falcon"])
+@pytest.mark.parametrize("batch", [1, 3, 8])
+def test_w2_gemv_builds_its_own_activation(family, batch, monkeypatch):
+    """Steps of <= 8 rows: the W2 GEMV computes the SwiGLU / GELU of the W1 GEMV's split-K slices
+    itself (GemvPre mode 2, gemm_simt.cu) instead of reading what the activation kernel stored.
+    Same slices, same summation order, same rounding: logits are bit-identical with the
+    stand-alone kernel (NVLLM_GEMV_PRE=0), and inside the oracle gates — prefill of a short
+    prompt and decode steps, sequential and parallel blocks."""
+    from helpers import TINY
+    cfg = TINY[family]()
+    prompts, tables = _plain_batch(cfg, batch, 5 if batch == 1 else 1, 3)
+    n = len(prompts)
+    outs = {}
+    for pre in ("1", "0"):
+        monkeypatch.setenv("NVLLM_GEMV_PRE", pre)
+        run = _runner(cfg, C.PREC_FP32, num_kv_blocks=n, max_num_seqs=n, max_batched_tokens=4096)
+        try:
+            seqs = [[int(t) for t in p] for p in prompts]
+            got = []
+            for i in range(4):
+                out, logits = run.run_flat(seqs, i == 0, None, tables, [0.0] * n, want_logits=True)
+                got.append(logits.copy())
+                for s in range(n):
+                    seqs[s].append(int(out[s]))
+            outs[pre] = (np.stack(got), [list(x) for x in seqs])
+        finally:
+            run.close()
+    assert outs["1"][1] == outs["0"][1]
+    assert np.array_equal(outs["1"][0], outs["0"][0])
+    monkeypatch.setenv("NVLLM_GEMV_PRE", "1")
+    _batch_parity(cfg, C.PREC_FP32, prompts, 3, tables)
+    _batch_parity(cfg, C.PREC_BF16, prompts, 3, tables)
