@@ -17,14 +17,13 @@
 
 namespace nvllm {
 
-constexpr int RES_CTR_TILES = 4096;  // output tiles a split-K fused-residual GEMM may have
 
 // ------------------------------------------------------------------ workspace
 void free_workspace(nvllm_handle* h) {
   Workspace& w = h->ws;
   h->drop_graphs();  // the captured decode steps hold these pointers
   void* ptrs[] = {w.tp_buf, w.x, w.xn, w.xn_f32, w.ws_a, w.ws_b, w.ws_c, w.q, w.attn_out, w.hbuf, w.xn_last,
-                  w.xb, w.ssq, w.res_ctr, w.chain_ctr, w.m_xbc, w.m_dt, w.m_y, w.m_yn, w.logits_p, w.logits, w.attn_ws, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
+                  w.xb, w.ssq, w.chain_ctr, w.m_xbc, w.m_dt, w.m_y, w.m_yn, w.logits_p, w.logits, w.attn_ws, w.out_tokens, w.amax, w.amax_ticket, w.topk_idx, w.topk_w,
                   w.sort.counts, w.sort.offsets, w.sort.cursor, w.sort.sorted_pair, w.sort.pair_row,
                   w.sort.a_rows, w.sort.tile_expert, w.sort.tile_row0, w.sort.tile_rows,
                   w.sort.n_tiles, w.moe_Y, w.moe_y, w.moe_xs};
@@ -90,9 +89,6 @@ int ensure_workspace(nvllm_handle* h, int T, int n) {
   if (h->fold) {
     WS(w.xb, Tc * H * 2);
     WS(w.ssq, (size_t)ceil_div(h->H, 128) * Tc * 4);
-    WS(w.res_ctr, (size_t)4 * RES_CTR_TILES * 4);
-    if (cudaMemsetAsync(w.res_ctr, 0, (size_t)4 * RES_CTR_TILES * 4, h->stream) != cudaSuccess)
-      return set_err(h, NVLLM_ERR_CUDA, "memset(fused-residual counters) failed");
   }
   if (h->tp > 1) WS(w.tp_buf, Tc * H * 4);
   // tp > 1: this rank's LM-head slice is Vl wide and the gathered logits are [tp][n][Vl]
@@ -325,17 +321,13 @@ static int run_gemm(nvllm_handle* h, const void* A, int lda, const void* W, int 
     }
     if (rd) {
       // x += m (A W^T + bias) inside the GEMM; nothing is left pending for a norm kernel
+      // split-K shapes (decode batches): the k-splits of a tile are one thread-block cluster and
+      // meet in shared memory — no partials in global memory either way
       t.S = tc5_resid_splits(M, N, K, h->sm_count);
-      while (t.S > 1 && (size_t)t.S * M * ldo > cap) t.S--;
       t.epi = TC5_EPI_RESID;
       t.res_x = h->ws.x; t.res_xb = h->ws.xb; t.res_ssq = h->ws.ssq; t.res_ssq_ld = h->ws.T_cap;
       t.res_bias = rd->bias; t.res_m = rd->m; t.res_g = rd->g;
-      t.res_arrive = h->ws.res_ctr + (size_t)rd->site * 2 * RES_CTR_TILES;
-      t.res_done = t.res_arrive + RES_CTR_TILES;
-      const double xrw = (double)M * N * (4 + 4 + 2);
-      ProfScope ps(h, NVLLM_K_GEMM_TC5, io + (double)M * N * 4 * 2, flops,
-                   a_in + (double)M * N * 2 + (t.S > 1 ? 4.0 * t.S * M * N * 2 : 0.0));
-      (void)xrw;
+      ProfScope ps(h, NVLLM_K_GEMM_TC5, io + (double)M * N * 4 * 2, flops, a_in + (double)M * N * 2);
       LAUNCH(h, launch_gemm_tc5(h->stream, t, nullptr));
       *res = Pending();
       return NVLLM_OK;
@@ -376,12 +368,17 @@ static bool fold_gemm_ok(const nvllm_handle* h, int M, int N, int K, int lda) {
 }
 static bool resid_gemm_ok(const nvllm_handle* h, int M, int N, int K, int lda) {
   if (!fold_gemm_ok(h, M, N, K, lda) || N != h->H) return false;
-  // Split-K shapes (decode batches) keep the norm kernel by default: the in-kernel meeting of a
-  // tile's k-splits costs more than the norm launch it removes (measured on cfg2 decode: 1086 ->
-  // 1432 us/step with the first version of the reduce).  NVLLM_RESID_SPLITK=1 turns it on.
-  static const bool splitk = getenv("NVLLM_RESID_SPLITK") && atoi(getenv("NVLLM_RESID_SPLITK")) != 0;
   const int S = tc5_resid_splits(M, N, K, h->sm_count);
-  return splitk ? S >= 1 : (S == 1 && tc5_splits(M, N, K, h->sm_count) == 1);
+  if (S <= 1) return S == 1 && tc5_splits(M, N, K, h->sm_count) == 1;
+  // Split-K shapes (decode batches) can run the k-splits of an output tile as one thread-block
+  // cluster that reduces through distributed shared memory and finishes the residual update
+  // itself (gemm_tcgen05.cu) — no norm kernel behind the O and W2 GEMMs.  Parity-green, but
+  // measured SLOWER on cfg2 decode (1150 -> 1195 us/step, DESIGN.md "rejected"): B200 places at
+  // most 15 clusters of 8 such CTAs (16 tiles need a second wave) so the split drops to 6 = 96
+  // CTAs streaming the weights instead of 128, and the in-cluster exchange + reduce costs more
+  // than the norm launch it removes.  Opt-in: NVLLM_RESID_CLUSTER=1 (read per step).
+  const char* ce = getenv("NVLLM_RESID_CLUSTER");
+  return ce && atoi(ce) != 0;
 }
 
 static int run_norm(nvllm_handle* h, float* x, Pending* p1, Pending* p2, const float* w,

@@ -68,9 +68,8 @@ struct Tc5Fuse {
   int ssq_ld;
   const float* bias;
   float m;
-  unsigned* arrive;
-  unsigned* done;
   const float* g;  // weight of the norm that reads x next: xb = bf16(x * g); null = ones
+  int cl;          // > 1: the S k-splits of an output tile are one thread-block cluster of `cl` CTAs
 };
 // A second GEMM chained behind the first inside ONE launch (the FFN pair of a decode step:
 // W1 + activation, then W2): every CTA runs its units of problem 1, then its units of problem 2.
@@ -94,6 +93,38 @@ __device__ __forceinline__ void named_bar(int id, int n) {
 __device__ __forceinline__ unsigned ld_acquire_u32(const unsigned* p) {
   unsigned v;
   asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+// thread-block cluster primitives (the fused-residual split-K epilogue)
+__device__ __forceinline__ void cluster_arrive_relaxed() {
+  asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_arrive_release() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void cluster_wait_acquire() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_map(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+// bulk copy from this CTA's shared memory into a peer's (both 16-byte aligned, bytes % 16 == 0);
+// completion is signalled as `bytes` of transaction count on the PEER's mbarrier
+__device__ __forceinline__ void dsmem_bulk_copy(uint32_t dst_cluster, uint32_t src_cta, uint32_t bytes,
+                                                uint32_t bar_cluster) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+      ::"r"(dst_cluster), "r"(src_cta), "r"(bytes), "r"(bar_cluster)
+      : "memory");
+}
+__device__ __forceinline__ void st_shared_f32(uint32_t addr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ float4 ld_shared_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
   return v;
 }
 // v[c] of every lane -> lane l gets sum over lanes of v[l]  (31 shuffles instead of 32 x 5)
@@ -156,7 +187,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
                 unsigned long long pf_bytes, Tc5Fuse fz, Tc5Chain ch, Trace tr) {
   const unsigned long long t_entry = trace_on(tr) ? gtime() : 0ull;
   unsigned long long t_wait = 0;
-  __shared__ unsigned long long tr_mma, tr_epi0, tr_epi1, tr_x[6];
+  __shared__ unsigned long long tr_mma, tr_epi0, tr_epi1, tr_x[6], tr_c[4];
   __shared__ __align__(16) uint8_t epi_stage[4][32 * 48];
   __shared__ float rstd_s[2][BT];       // row scales of the unit in flight (double-buffered)
   __shared__ float ssq_s[2][4][32];     // RESID: per-warp row sums of squares of a 32-token chunk
@@ -170,6 +201,15 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   const uint32_t bar_tfull = bars + 16 * STAGES;
   const uint32_t bar_tempty = bar_tfull + 16;
   const uint32_t tmem_slot = bar_tempty + 16;
+  // cluster mode only (the launcher adds the bytes):  xch [source rank][per][128] fp32, the rows
+  // this CTA owns as the peers' bulk copies deliver them — never part of the TMA ring, a peer may
+  // be ahead of this CTA's main loop;  stg [BT][128], this CTA's partial tile (the copies'
+  // source): written after this CTA's own last MMA has retired, so it reuses the ring's first
+  // stages;  bar_x counts the delivered bytes
+  const uint32_t bar_x = tmem_slot + 8;
+  const uint32_t xch = (tmem_slot + 16 + 127u) & ~127u;
+  const uint32_t stg = tiles;
+  static_assert((size_t)BT * TC_BN * 4 <= (size_t)STAGES * STAGE_BYTES, "staging tile fits the ring");
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(
       smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -186,6 +226,7 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       mbar_init(bar_tfull + 8 * b, 1);
       mbar_init(bar_tempty + 8 * b, 4);  // one arrival per epilogue warp
     }
+    if (fz.cl > 1) mbar_init(bar_x, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmW) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmA) : "memory");
@@ -201,6 +242,9 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
   const int grid = gridDim.x;
+  // cluster phase A ("this CTA runs": its shared memory may be written by peers), waited for by
+  // each warp right before its phase-B arrival; phase B = "my slices are in the owners' buffers"
+  if (fz.cl > 1) cluster_arrive_relaxed();
 
   // The producer and MMA warps run their loops with ALL 32 lanes (warp-uniform control flow)
   // and elect one lane only around the issue instructions: TMA and tcgen05 instructions take
@@ -329,6 +373,11 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
         }
       }
     }
+    if (fz.cl > 1) {
+      cluster_wait_acquire();
+      cluster_arrive_release();
+      cluster_wait_acquire();
+    }
   } else if (warp == 1) {
     // instruction descriptor (cute/arch/mma_sm100_desc.hpp): fp32 accumulate, bf16 x bf16,
     // both K-major, N = BT, M = 128
@@ -370,6 +419,11 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
       if (tr.buf && lane == 0) tr_mma = gtime();
     }
     }
+    if (fz.cl > 1) {
+      cluster_wait_acquire();
+      cluster_arrive_release();
+      cluster_wait_acquire();
+    }
   } else {
     // epilogue: warp w may touch TMEM lanes [32 (w % 4), +32)
     const int q = warp & 3;
@@ -406,6 +460,30 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
         }
         named_bar(1, 128);
         rs = w;
+      }
+      // cluster split-K fused residual: what this CTA, as the owner of token rows [r0, r1) of the
+      // tile, needs from global memory (its x rows, bias, norm weight) depends on no peer and on
+      // no MMA: fetched NOW, under the main loop — by the time the epilogue runs, the next
+      // kernel's weight prefetch has the memory system queued up and a load takes microseconds
+      constexpr int OWN = BT > 64 ? 1 : BT / 16;  // rows one warp finishes: ceil(BT / S / 4) with S >= 4
+      const bool cl_resid = p == 0 && epi == TC5_EPI_RESID && scp.S > 1;
+      const int valid = min(BT, M - m0);
+      const int per = (valid + scp.S - 1) / scp.S;
+      const int r0 = split * per, r1 = min(valid, r0 + per);
+      const int ncol = n0 + lane * 4;
+      const bool c_ok = ncol + 3 < N;  // N % 4 == 0 is checked by the launcher
+      float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f), g4 = make_float4(1.f, 1.f, 1.f, 1.f);
+      float4 xv[OWN];
+      if (cl_resid) {
+        if (fz.bias && c_ok) b4 = *reinterpret_cast<const float4*>(fz.bias + ncol);
+        if (fz.g && c_ok) g4 = *reinterpret_cast<const float4*>(fz.g + ncol);
+#pragma unroll
+        for (int j = 0; j < OWN; j++) {
+          const int row = r0 + q + 4 * j;
+          xv[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (row < r1 && c_ok)
+            xv[j] = __ldcg(reinterpret_cast<const float4*>(fz.x + (size_t)(m0 + row) * N + ncol));
+        }
       }
       mbar_wait(bar_tfull + 8 * buf, (lu >> 1) & 1);
       tc_fence_after();
@@ -526,67 +604,69 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
                   ssq_s[chunk & 1][3][lane];
           }
         } else {
-          // (1) this split's partial tile, as TC5_EPI_PARTIAL writes it
-          float* obase = out + (size_t)split * split_stride + n;
+          // Split-K: the S CTAs of this output tile are ONE thread-block cluster (rank == split).
+          // Token rows are dealt out to the ranks; every CTA stages its partial tile in its own
+          // shared memory and bulk-copies each owner's rows into that owner's shared memory
+          // (DSMEM, completion counted on the owner's mbarrier); each owner then sums the S slices
+          // of its rows in rank order and finishes them — no global round trip, no counters, no
+          // norm kernel behind this GEMM.  (Per-lane st.shared::cluster stores instead of bulk
+          // copies were measured at ~14 us per 32 KB tile: the SM-to-SM path is transaction-bound.)
+          // (1) the partial tile into the staging buffer, rows grouped by owner
+          {
+            const uint32_t col = (uint32_t)((q * 32 + lane) * 4);
 #pragma unroll 1
-          for (int c0 = 0; c0 < BT; c0 += 32) {
-            if (m0 + c0 >= M) break;
-            uint32_t r[32];
-            tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
-            if (n_ok) {
-              float* op = obase + (size_t)(m0 + c0) * ldo;
+            for (int c0 = 0; c0 < BT; c0 += 32) {
+              if (c0 >= valid) break;
+              uint32_t r[32];
+              tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(buf * BT + c0), r);
 #pragma unroll
               for (int c = 0; c < 32; c++)
-                if (m0 + c0 + c < M) op[(size_t)c * ldo] = alpha * __uint_as_float(r[c]);
+                if (c0 + c < valid)  // row index == token index: owner o holds rows [o per, o per + per)
+                  st_shared_f32(stg + (uint32_t)((c0 + c) * TC_BN * 4) + col, alpha * __uint_as_float(r[c]));
             }
           }
-          // (2) meet the other k-splits of this output tile (all resident: units <= #SM)
-          const int tile_id = (m0 / BT) * scp.n_tiles + nt;
-          __threadfence();
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic writes -> bulk-copy reads
           named_bar(2, 128);
-          if (et == 0) {
-            atomicAdd(fz.arrive + tile_id, 1u);
-            while (ld_acquire_u32(fz.arrive + tile_id) < (unsigned)scp.S) {
+          if (tr.buf && warp == 2 && lane == 0) tr_c[0] = gtime();
+          cluster_wait_acquire();  // phase A: every peer is running and has initialised its bar_x
+          // (2) one bulk copy per peer: its rows of my slice -> slot `split` of its xch
+          if (q == 0) {
+            const int o = lane;
+            if (o < scp.S && o != split) {
+              const int o0 = o * per, o1 = min(valid, o0 + per);
+              if (o1 > o0)
+                dsmem_bulk_copy(cluster_map(xch, (uint32_t)o) + (uint32_t)(split * per * TC_BN * 4),
+                                stg + (uint32_t)(o0 * TC_BN * 4), (uint32_t)((o1 - o0) * TC_BN * 4),
+                                cluster_map(bar_x, (uint32_t)o));
             }
+            if (lane == 0) mbar_expect_tx(bar_x, (uint32_t)((scp.S - 1) * max(r1 - r0, 0) * TC_BN * 4));
           }
-          named_bar(2, 128);
-          // (3) reduce this split's share of the tile's token rows, slices in a fixed order.
-          // One warp-iteration covers one token row of the tile (32 lanes x float4 = 128
-          // columns), all its loads are issued together, and the warp sum IS the row's sum of
-          // squares over this column tile: no cross-warp step.
-          const int valid = min(BT, M - m0);
-          const int per = (valid + scp.S - 1) / scp.S;
-          const int r0 = split * per, r1 = min(valid, r0 + per);
-          const int ncol = n0 + lane * 4;
-          const bool c_ok = ncol + 3 < N;  // N % 4 == 0 is checked by the launcher
-          float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f), g4 = make_float4(1.f, 1.f, 1.f, 1.f);
-          if (fz.bias && c_ok) b4 = *reinterpret_cast<const float4*>(fz.bias + ncol);
-          if (fz.g && c_ok) g4 = *reinterpret_cast<const float4*>(fz.g + ncol);
-          for (int row = r0 + q; row < r1; row += 4) {
+          mbar_wait(bar_x, 0);  // (3) the S - 1 peer slices of my rows have landed
+          if (tr.buf && warp == 2 && lane == 0) tr_c[1] = gtime();
+          const int nt_ = nt;
+#pragma unroll
+          for (int j = 0; j < OWN; j++) {
+            const int row = r0 + q + 4 * j;
+            if (row >= r1) break;
+            float4 pv[8];  // all S shared-memory loads in flight before the first add
+#pragma unroll
+            for (int sp = 0; sp < 8; sp++)
+              if (sp < scp.S)
+                pv[sp] = ld_shared_f4(sp == split ? stg + (uint32_t)((row * TC_BN + lane * 4) * 4)
+                                                  : xch + (uint32_t)(((sp * per + (row - r0)) * TC_BN + lane * 4) * 4));
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
             if (c_ok) {
-              const size_t o = (size_t)(m0 + row) * ldo + ncol;
-              const size_t xi = (size_t)(m0 + row) * N + ncol;
-              const float4 xv = __ldcg(reinterpret_cast<const float4*>(fz.x + xi));
               float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-              if (scp.S <= 8) {
-                float4 pz[8];
 #pragma unroll
-                for (int sp = 0; sp < 8; sp++)
-                  if (sp < scp.S) pz[sp] = __ldcg(reinterpret_cast<const float4*>(out + (size_t)sp * split_stride + o));
-#pragma unroll
-                for (int sp = 0; sp < 8; sp++)
-                  if (sp < scp.S) { acc.x += pz[sp].x; acc.y += pz[sp].y; acc.z += pz[sp].z; acc.w += pz[sp].w; }
-              } else {
-                for (int sp = 0; sp < scp.S; sp++) {
-                  const float4 pv = __ldcg(reinterpret_cast<const float4*>(out + (size_t)sp * split_stride + o));
-                  acc.x += pv.x; acc.y += pv.y; acc.z += pv.z; acc.w += pv.w;
+              for (int sp = 0; sp < 8; sp++)
+                if (sp < scp.S) {
+                  acc.x += pv[sp].x; acc.y += pv[sp].y; acc.z += pv[sp].z; acc.w += pv[sp].w;
                 }
-              }
-              v.x = xv.x + fz.m * (acc.x + b4.x);
-              v.y = xv.y + fz.m * (acc.y + b4.y);
-              v.z = xv.z + fz.m * (acc.z + b4.z);
-              v.w = xv.w + fz.m * (acc.w + b4.w);
+              const size_t xi = (size_t)(m0 + row) * N + ncol;
+              v.x = xv[j].x + fz.m * (acc.x + b4.x);
+              v.y = xv[j].y + fz.m * (acc.y + b4.y);
+              v.z = xv[j].z + fz.m * (acc.z + b4.z);
+              v.w = xv[j].w + fz.m * (acc.w + b4.w);
               *reinterpret_cast<float4*>(fz.x + xi) = v;
               __nv_bfloat162 lo = __floats2bfloat162_rn(v.x * g4.x, v.y * g4.y),
                              hi = __floats2bfloat162_rn(v.z * g4.z, v.w * g4.w);
@@ -596,15 +676,16 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
               *reinterpret_cast<uint2*>(fz.xb + xi) = pk;
             }
             const float tot = warp_sum((v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w));
-            if (lane == 0) fz.ssq[(size_t)nt * fz.ssq_ld + m0 + row] = tot;
+            if (lane == 0) fz.ssq[(size_t)nt_ * fz.ssq_ld + m0 + row] = tot;
           }
-          named_bar(2, 128);
-          if (et == 0) {
-            if (atomicAdd(fz.done + tile_id, 1u) == (unsigned)scp.S - 1) {  // everyone is past the wait
-              fz.arrive[tile_id] = 0;
-              fz.done[tile_id] = 0;
-            }
+          if (tr.buf && warp == 2 && lane == 0) {
+            tr_c[2] = gtime();
+            tr_c[3] = tr_c[2];
           }
+          // phase B: once every CTA of the cluster is past its own wait, every copy OUT of this
+          // CTA's staging buffer has completed too — only then may the CTA exit
+          cluster_arrive_release();
+          cluster_wait_acquire();
         }
       } else {
         // GELU branch: gelu_tanh(h + b1)   (transformer.go:67-78)
@@ -659,7 +740,14 @@ gemm_tc5_kernel(const __grid_constant__ CUtensorMap tmW, const __grid_constant__
     Trace t2 = tr;
     t2.kid = 9;
     t2.agg = nullptr;
-    trace_rec(t2, tr_x[0] - t_wait, tr_x[1] - t_wait, ((tr_x[2] - t_wait) << 32) | (tr_x[3] - t_wait));
+    if (fz.cl > 1) {
+      // cluster epilogue: staged, phase A passed, peer slices landed, rows finished (16-bit ns after the wait)
+      unsigned long long pk = 0;
+      for (int i = 0; i < 4; i++) pk = (pk << 16) | ((tr_c[i] - t_wait) & 0xffffull);
+      trace_rec(t2, tr_x[0] - t_wait, tr_x[1] - t_wait, pk);
+    } else {
+      trace_rec(t2, tr_x[0] - t_wait, tr_x[1] - t_wait, ((tr_x[2] - t_wait) << 32) | (tr_x[3] - t_wait));
+    }
   }
   if (warp == 1) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
@@ -763,16 +851,65 @@ int tc5_splits(int M, int N, int K, int sm_count) {
   return best;
 }
 
+// ring depths of the cluster variant (the receive buffer takes 36 / 20 KB of the ring's room)
+constexpr int CL_STAGES_32 = 9, CL_STAGES_64 = 7;
+constexpr size_t tc5_smem_bytes(int BT, int STAGES, bool CL) {
+  return (size_t)STAGES * (TC_BN + BT) * TC_BK * 2 + 1024 + 16 * STAGES + 64 +
+         (CL ? (size_t)(BT + 8) * TC_BN * 4 + 128 : 0);
+}
+// how many clusters of S CTAs of the fused-residual GEMM can be resident at once on this device
+// (1 CTA per SM, all CTAs of a cluster on one GPC); 0 when there is no device
+template <int BT, int STAGES>
+static int max_clusters(int S) {
+  static int cache[64][9];
+  static bool known[64][9] = {};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64 || S < 2 || S > 8) return 0;
+  if (known[dev][S]) return cache[dev][S];
+  const size_t smem = tc5_smem_bytes(BT, STAGES, true);
+  int n = 0;
+  if (cudaFuncSetAttribute(gemm_tc5_kernel<BT, STAGES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                           (int)smem) == cudaSuccess) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(S * 16);
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = (unsigned)S;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (cudaOccupancyMaxActiveClusters(&n, gemm_tc5_kernel<BT, STAGES>, &cfg) != cudaSuccess) n = 0;
+  }
+  (void)cudaGetLastError();
+  if (getenv("NVLLM_DEBUG_CLUSTER"))
+    fprintf(stderr, "nvllm: clusters of %d x gemm_tc5<%d,%d>: %d co-resident\n", S, BT, STAGES, n);
+  cache[dev][S] = n;
+  known[dev][S] = true;
+  return n;
+}
+
+// Split count of the fused-residual GEMM (TC5_EPI_RESID): 1 = enough output tiles on their own;
+// 2..8 = the k-splits of a tile run as one thread-block cluster — the largest count whose clusters
+// are ALL resident at once (a second wave of clusters doubles the kernel: B200 places 15 clusters
+// of 8 such CTAs, one short of the 16 tiles of a 2048-wide model); 0 = not available for this shape
 int tc5_resid_splits(int M, int N, int K, int sm_count) {
   const int bt = pick_bt(M);
   const long tiles = (long)ceil_div(N, TC_BN) * ceil_div(M, bt);
-  int S = tc5_splits(M, N, K, sm_count);
   if (tiles >= sm_count) return 1;
-  while (S > 1 && tiles * S > sm_count) S--;
-  // keep the slice count one the k-blocks divide into without an empty tail slice
+  int S = tc5_splits(M, N, K, sm_count);
+  if (S == 1) return 1;
+  if (bt > 64 || (N & 3)) return 0;
   const int nkb = ceil_div(K, TC_BK);
-  while (S > 1 && ceil_div(nkb, ceil_div(nkb, S)) != S) S--;
-  return S;
+  for (; S >= 4; S--) {  // >= 4: an owner warp finishes at most BT / 16 rows (kernel, OWN)
+    if (tiles * S > sm_count) continue;
+    if (ceil_div(nkb, ceil_div(nkb, S)) != S) continue;  // no empty tail slice
+    const int fit = bt == 32 ? max_clusters<32, CL_STAGES_32>(S) : max_clusters<64, CL_STAGES_64>(S);
+    if (tiles <= fit) return S;
+  }
+  return 0;
 }
 
 bool carveout_known(const void* fn) {
@@ -824,13 +961,16 @@ static bool g_pdl = true;
 void set_pdl_enabled(bool on) { g_pdl = on; }
 bool pdl_enabled() { return g_pdl; }
 
-template <int BT, int STAGES>
+// CL: the fused-residual split-K variant — the k-splits of a tile form a thread-block cluster and
+// exchange their slices through (BT + 8) x 128 fp32 of extra shared memory per CTA
+template <int BT, int STAGES, bool CL = false>
 static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* tw,
                              const TmaDesc* ta, int S, const Tc5Args* a2 = nullptr,
                              const TmaDesc* tw2 = nullptr, const TmaDesc* ta2 = nullptr, int S2 = 0,
                              unsigned* chain_ctr = nullptr) {
-  constexpr size_t smem = (size_t)STAGES * (TC_BN + BT) * TC_BK * 2 + 1024 + 16 * STAGES + 64;
-  static_assert(smem <= 232448, "shared memory budget");
+  constexpr size_t smem = tc5_smem_bytes(BT, STAGES, CL);
+  static_assert(smem + 8192 + (BT > 64 ? 2560 : 1024) <= 232448,
+                "shared memory budget (dynamic + the kernel's static arrays)");
   static uint64_t attr_mask = 0;  // per device
   static int sm_counts[64] = {0};
   int dev = 0;
@@ -866,12 +1006,23 @@ static cudaError_t launch_bt(cudaStream_t st, const Tc5Args& a, const TmaDesc* t
   int grid = min(sc.units, max(1, sm_counts[dev]));
   if (a.max_ctas > 0 && a.epi != TC5_EPI_RESID) grid = max(1, min(grid, a.max_ctas));
   Tc5Fuse fz{a.rs_ssq, a.rs_parts, a.rs_ld, a.rs_inv_h, a.rs_eps, a.res_x, (bf16*)a.res_xb, a.res_ssq,
-             a.res_ssq_ld, a.res_bias, a.res_m, a.res_arrive, a.res_done, a.res_g};
+             a.res_ssq_ld, a.res_bias, a.res_m, a.res_g, CL ? sc.S : 0};
   if (a.epi == TC5_EPI_RESID) {
     if (!a.res_x || !a.res_xb || !a.res_ssq || a.g_experts > 0) return cudaErrorInvalidValue;
-    // the k-splits of a tile wait for each other inside the kernel: every unit needs its own SM
-    if (sc.S > 1 && (sc.units > grid || !a.res_arrive || !a.res_done || (a.N & 3) || (a.ldo & 3)))
-      return cudaErrorInvalidValue;
+    // split-K only as a cluster: one CTA per unit, one token tile, cluster = the S splits of a tile
+    if ((sc.S > 1) != CL) return cudaErrorInvalidValue;
+    if (CL && (sc.S > 8 || sc.S < 4 || m_tiles != 1 || (a.N & 3) || a2)) return cudaErrorInvalidValue;
+  } else if (CL) {
+    return cudaErrorInvalidValue;
+  }
+  if (CL) {
+    return launch_k_cluster(gemm_tc5_kernel<BT, STAGES>, dim3(sc.units), dim3(TC_THREADS), smem, st, sc.S,
+                            *reinterpret_cast<const CUtensorMap*>(tw),
+                            *reinterpret_cast<const CUtensorMap*>(ta),
+                            *reinterpret_cast<const CUtensorMap*>(tw),
+                            *reinterpret_cast<const CUtensorMap*>(ta), a.M, a.N, sc, a.out, a.ldo,
+                            a.split_stride, a.alpha, 0, a.epi, (bf16*)a.epi_out, a.epi_ld, a.epi_bias,
+                            prefetch_flags(), (const uint8_t*)nullptr, 0ull, fz, Tc5Chain{}, next_trace(1));
   }
   const bool w_reused = a.g_experts > 0 ? a.M > 2 * BT * a.g_experts : m_tiles > 1;
   Tc5Chain ch{};
@@ -954,9 +1105,15 @@ cudaError_t launch_gemm_tc5(cudaStream_t st, const Tc5Args& a, int* S_out) {
     S = 1;
   }
   if (S_out) *S_out = S;
-  if ((a.epi == TC5_EPI_PARTIAL || (a.epi == TC5_EPI_RESID && S > 1)) && a.out_capacity &&
-      (size_t)S * a.split_stride > a.out_capacity)
+  if (a.epi == TC5_EPI_PARTIAL && a.out_capacity && (size_t)S * a.split_stride > a.out_capacity)
     return cudaErrorInvalidValue;
+  if (a.epi == TC5_EPI_RESID && S > 1) {
+    switch (bt) {
+      case 32: return launch_bt<32, CL_STAGES_32, true>(st, a, tw, ta, S);
+      case 64: return launch_bt<64, CL_STAGES_64, true>(st, a, tw, ta, S);
+      default: return cudaErrorInvalidValue;
+    }
+  }
   switch (bt) {
     case 32: return launch_bt<32, 10>(st, a, tw, ta, S);
     case 64: return launch_bt<64, 8>(st, a, tw, ta, S);

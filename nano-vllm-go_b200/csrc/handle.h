@@ -64,11 +64,9 @@ struct Workspace {
   float* m_y = nullptr;      // [T, E] fp32 scan output
   void* m_yn = nullptr;      // [T, E] gated + normed, act dtype (out_proj input)
   // folded RMSNorm (forward.cu): bf16(x * g) of the residual stream (g = the next norm's weight), the
-  // per-column-tile row sums of squares [parts][T_cap] of it, and the arrival / done counters of
-  // the two fused-residual GEMM sites of a layer (O projection, FFN down projection)
+  // per-column-tile row sums of squares [parts][T_cap] of it
   void* xb = nullptr;
   float* ssq = nullptr;
-  unsigned* res_ctr = nullptr;  // [2 sites][arrive | done][RES_CTR_TILES]
   unsigned* chain_ctr = nullptr;  // [2] counters of the chained W1 -> W2 GEMM launch (zero between launches)
   float* logits_p = nullptr; // [S][n][ldl]
   float* logits = nullptr;   // [n][ldl]  (tp > 1: [tp][n][Vl], rank-major slices)

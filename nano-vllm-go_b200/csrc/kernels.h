@@ -224,9 +224,9 @@ struct Tc5Args {
   // producer side, epi == TC5_EPI_RESID (N = hidden size): x[m, n] += res_m * (acc + res_bias[n])
   // in place (fp32), the same value rounded to bf16 into res_xb, and the row's sum of squares
   // over this CTA's 128 columns into res_ssq[n_tile * res_ssq_ld + m] — the next GEMM's rs_ssq.
-  // With S > 1 the split-K slices go through `out` as usual and the CTAs of one output tile
-  // meet at res_arrive[tile] (all co-resident: units <= #SM is required), then each reduces its
-  // share of the tile's token rows; res_done re-arms the counters.
+  // With S > 1 (token tile <= 64 rows) the S CTAs of an output tile are launched as ONE
+  // thread-block cluster: the slices meet in the owners' shared memory (DSMEM), nothing goes
+  // through `out`, and each CTA finishes its share of the tile's token rows.
   float* res_x;
   void* res_xb;
   float* res_ssq;
@@ -234,8 +234,6 @@ struct Tc5Args {
   const float* res_bias;
   float res_m;
   const float* res_g;    // [N] weight of the norm that consumes x next: res_xb = bf16(x * g)
-  unsigned* res_arrive;  // [n_tiles * m_tiles], zero between launches
-  unsigned* res_done;
   int max_ctas;  // > 0: cap of the persistent grid (leave SMs to a concurrent collective)
   // weights of a later GEMM to pull into L2 while this one waits / drains (decode only)
   const void* pf_ptr;

@@ -229,3 +229,49 @@ def test_w2_gemv_builds_its_own_activation(family, batch, monkeypatch):
     monkeypatch.setenv("NVLLM_GEMV_PRE", "1")
     _batch_parity(cfg, C.PREC_FP32, prompts, 3, tables)
     _batch_parity(cfg, C.PREC_BF16, prompts, 3, tables)
+
+
+@pytest.mark.parametrize("hidden,heads,kv,ffn,batch", [
+    (1024, 16, 4, 4096, 12),    # 32-token tile, 8 tiles x 8 splits (O: K 1024, W2: K 4096)
+    (1024, 16, 4, 4096, 40),    # 64-token tile
+    (1024, 16, 4, 4096, 64),    # full tile: 8 token rows per cluster rank
+    (1088, 17, 1, 2560, 33),    # 8.5 column tiles (a half-empty one), uneven row shares
+    (3072, 24, 8, 8192, 20),    # Llama-3B width: 24 tiles x 6 splits, clusters of 6
+])
+def test_decode_fused_residual_through_cluster_shared_memory(hidden, heads, kv, ffn, batch, monkeypatch):
+    """Decode batches of 9..64 rows of a dense RMSNorm model (bf16): the O and W2 GEMMs run their
+    k-splits as one thread-block cluster per output tile, reduce the slices through distributed
+    shared memory and apply the residual update + the folded-norm outputs themselves
+    (gemm_tcgen05.cu, TC5_EPI_RESID with S > 1) — no norm kernel in the layer.  Opt-in
+    (NVLLM_RESID_CLUSTER=1: measured slower than partials + norm kernel).  Checked
+    against the oracle (bf16 gate) and against the default path, whose logits must agree to bf16
+    noise."""
+    cfg = C.tiny_llama(vocab_size=2048, hidden=hidden, num_heads=heads, num_kv_heads=kv, head_dim=64,
+                       ffn_dim=ffn, num_layers=2, max_seq_len=512)
+    prompts, tables = _plain_batch(cfg, batch, 7, 3)
+    n = len(prompts)
+    outs, launches = {}, {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("NVLLM_RESID_CLUSTER", mode)
+        run = _runner(cfg, C.PREC_BF16, num_kv_blocks=n, max_num_seqs=n, max_batched_tokens=4096)
+        try:
+            seqs = [[int(t) for t in p] for p in prompts]
+            got = []
+            for i in range(3):
+                out, logits = run.run_flat(seqs, i == 0, None, tables, [0.0] * n, want_logits=True)
+                got.append(logits.copy())
+                for s in range(n):
+                    seqs[s].append(int(out[s]))
+            outs[mode] = np.stack(got)
+            run.set_profile(True)
+            run.run_flat(seqs, False, None, tables, [0.0] * n)
+            launches[mode] = run.get_profile()["norm"]["launches"]
+            run.set_profile(False)
+        finally:
+            run.close()
+    # the decode step keeps the final norm only; the default path has two more per layer
+    assert launches == {"1": 1, "0": 1 + 2 * cfg.num_layers}, launches
+    scale = float(np.abs(outs["0"]).max())
+    assert float(np.abs(outs["1"][:2] - outs["0"][:2]).max()) <= 2e-2 * scale
+    monkeypatch.setenv("NVLLM_RESID_CLUSTER", "1")
+    _batch_parity(cfg, C.PREC_BF16, prompts, 3, tables)

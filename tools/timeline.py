@@ -52,8 +52,12 @@ for sq in seqs:
         ax = aux[aux[:, 0] == sq]
         if len(ax):
             e7 = ax[:, 7]
-            extra += (f" | first_full {np.median(ax[:,4].astype(np.int64))/1e3:.2f} last_full {np.median(ax[:,5].astype(np.int64))/1e3:.2f}"
-                      f" ldtm0 {np.median((e7 >> np.uint64(32)).astype(np.int64))/1e3:.2f} st0 {np.median((e7 & np.uint64(0xffffffff)).astype(np.int64))/1e3:.2f}")
+            extra += f" | first_full {np.median(ax[:,4].astype(np.int64))/1e3:.2f} last_full {np.median(ax[:,5].astype(np.int64))/1e3:.2f}"
+            if os.environ.get("TIMELINE_CLUSTER") and len(r) in (96, 112):  # cluster epilogue stamps (16-bit ns)
+                f16 = [((e7 >> np.uint64(sh)) & np.uint64(0xffff)).astype(np.int64) for sh in (48, 32, 16, 0)]
+                extra += " cluster: " + " ".join(f"{nm} {np.median(v)/1e3:.2f}/{np.max(v)/1e3:.2f}" for nm, v in zip(("staged", "landed", "rows_done", "-"), f16)) + " (median/max)"
+            else:
+                extra += f" ldtm0 {np.median((e7 >> np.uint64(32)).astype(np.int64))/1e3:.2f} st0 {np.median((e7 & np.uint64(0xffffffff)).astype(np.int64))/1e3:.2f}"
     if kid == 4:
         d = (r[:, 6].astype(np.int64) - np.maximum(r[:, 5], r[:, 4]).astype(np.int64)) / 1e3
         extra = " per-CTA dur p10/50/90/max: " + "/".join(f"{np.percentile(d, q):.1f}" for q in (10, 50, 90, 100))
