@@ -255,6 +255,7 @@ def test_decode_fused_residual_through_cluster_shared_memory(hidden, heads, kv, 
         monkeypatch.setenv("NVLLM_RESID_CLUSTER", mode)
         run = _runner(cfg, C.PREC_BF16, num_kv_blocks=n, max_num_seqs=n, max_batched_tokens=4096)
         try:
+            run.set_speculation(False)  # the profiled step below must launch, not be a speculative hit
             seqs = [[int(t) for t in p] for p in prompts]
             got = []
             for i in range(3):
@@ -269,8 +270,9 @@ def test_decode_fused_residual_through_cluster_shared_memory(hidden, heads, kv, 
             run.set_profile(False)
         finally:
             run.close()
-    # the decode step keeps the final norm only; the default path has two more per layer
-    assert launches == {"1": 1, "0": 1 + 2 * cfg.num_layers}, launches
+    # the decode step keeps the final norm only; the default path has two more per layer, less
+    # layer 0's attention norm (folded: the embedding kernel writes bf16(x g) and the row sums)
+    assert launches == {"1": 1, "0": 2 * cfg.num_layers}, launches
     scale = float(np.abs(outs["0"]).max())
     assert float(np.abs(outs["1"][:2] - outs["0"][:2]).max()) <= 2e-2 * scale
     monkeypatch.setenv("NVLLM_RESID_CLUSTER", "1")
