@@ -377,6 +377,22 @@ int nvllm_op_norm(int device, int prec, int rows, int H, const float* x,
 int nvllm_op_argmax(int device, int rows, int V, const float* logits, int32_t* out,
                     int iters, float* avg_ms);
 
+/* Allocation-free split-K GEMV: C[M,N] (fp32) = A[M,K] @ W[N,K]^T on DEVICE pointers, launched on
+ * `stream` (a cudaStream_t, NULL = default stream); asynchronous, nothing is synchronised.
+ * No counterpart in the reference: added for callers that
+ * cannot call cudaMalloc (CUDA graph capture, tight serving loops).  It calls no cudaMalloc /
+ * cudaFree / allocating library routine: the split-K slices live in a static device array of
+ * NVLLM_NOALLOC_MAX_SCRATCH_FLOATS floats (4 MiB, held by every GPU that loads the library
+ * until exit).  prec NVLLM_PREC_FP32: A and W are fp32; NVLLM_PREC_BF16: both bf16; W is
+ * [out, in] row-major as the library keeps weights.  1 <= M <= 8, K % 8 == 0, A and W 16-byte
+ * aligned, and slices(M,N,K) * M * N <= NVLLM_NOALLOC_MAX_SCRATCH_FLOATS, else
+ * NVLLM_ERR_INVALID with the sizes in nvllm_last_error(NULL).  M = N = K = 0 only performs the
+ * per-device set-up (the first call on a device looks the array's address up: make it outside a
+ * capture).  All calls share the one array: calls that overlap on the GPU race. */
+#define NVLLM_NOALLOC_MAX_SCRATCH_FLOATS (1 << 20)
+int nvllm_op_gemv_noalloc(int device, int prec, int M, int N, int K, const void* d_A,
+                          const void* d_W, float* d_C, void* stream);
+
 /* Device properties the host side wants for roofline reporting. */
 int nvllm_device_info(int device, int* sm_count, int* cc_major, int* cc_minor,
                       uint64_t* total_mem, char name[256]);

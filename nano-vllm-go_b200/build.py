@@ -15,7 +15,7 @@ CSRC = os.path.join(_HERE, "csrc")
 OBJ = os.path.join(CSRC, "build")
 LIB = os.path.join(_HERE, "libnvllm_b200.so")
 SOURCES = ["nvllm.cu", "weights.cu", "forward.cu", "run.cu", "ops.cu", "elementwise.cu", "gemm_simt.cu",
-           "gemm_tcgen05.cu", "attention.cu", "attention_mma.cu", "attention_dec.cu", "attention_tc5.cu", "moe.cu", "mamba.cu", "sampling.cu", "tp.cu", "safetensors.cu"]
+           "gemm_tcgen05.cu", "attention.cu", "attention_mma.cu", "attention_dec.cu", "attention_tc5.cu", "moe.cu", "mamba.cu", "sampling.cu", "tp.cu", "safetensors.cu", "noalloc.cu"]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
          "-Xcompiler", "-fPIC"]

@@ -98,6 +98,9 @@ SIGNATURES = {
                                      _f32p, _f32p, ctypes.c_float, _f32p, ctypes.c_int, _f32p]),
     "nvllm_op_argmax": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, _f32p, _i32p,
                                        ctypes.c_int, _f32p]),
+    "nvllm_op_gemv_noalloc": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int,
+                                             ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p,
+                                             ctypes.c_void_p, ctypes.c_void_p]),
     "nvllm_device_info": (ctypes.c_int, [ctypes.c_int, ctypes.POINTER(ctypes.c_int),
                                          ctypes.POINTER(ctypes.c_int), ctypes.POINTER(ctypes.c_int),
                                          _u64p, ctypes.c_char_p]),
