@@ -262,7 +262,6 @@ attn_decode_mma_kernel(AttnArgs a, int G, int chunks, int kpc, Trace tr) {
   const int F = n_tiles * kpc;  // flat (head, tile) work list
 
   auto issue_kv = [&](int f, int stage) {
-    if (a.ablate == 2) return;
     const int hh = f / n_tiles, j = f - hh * n_tiles;
     const int k0 = (tile_begin + j) * BN;
     const int nk = min(BN, len - k0);
@@ -493,9 +492,8 @@ attn_decode_mma_kernel(AttnArgs a, int G, int chunks, int kpc, Trace tr) {
     }
     const int k0 = (tile_begin + j) * BN;
     const bool need_mask = k0 + BN > len;
-    if (a.ablate != 1)
-      attn_block<HD, WK / 8>(qf, sK + stage * TILE_BYTES, sV + stage * TILE_BYTES, warp * WK,
-                             k0 + warp * WK, limit, need_mask, scale_log2, m, l, o);
+    attn_block<HD, WK / 8>(qf, sK + stage * TILE_BYTES, sV + stage * TILE_BYTES, warp * WK,
+                           k0 + warp * WK, limit, need_mask, scale_log2, m, l, o);
     if (j == n_tiles - 1) {
       if (tr.buf && hh == 0) t_fin0 = gtime();
       finish_head(hh);
@@ -544,8 +542,6 @@ static cudaError_t decode_launch(cudaStream_t st, AttnArgs a, int G, int chunks)
            (size_t)(kpc * 2) * (16 * HD * 2 + 2 * HD * 2) + pipe + red <= smem_cap)
       kpc *= 2;
   }
-  static const int kpc_env = getenv("NVLLM_ATTN_KPC") ? atoi(getenv("NVLLM_ATTN_KPC")) : 0;
-  if (kpc_env > 0 && chunks == 1 && a.n_splits == 1 && a.nkv % kpc_env == 0) kpc = kpc_env;
   const size_t q_bytes = (size_t)kpc * 16 * HD * 2;
   const size_t body = kpc > 1 ? pipe + red : (pipe > red ? pipe : red);
   a.newkv_off = (int)(q_bytes + body);
@@ -563,14 +559,11 @@ static cudaError_t decode_launch(cudaStream_t st, AttnArgs a, int G, int chunks)
   return cudaGetLastError();
 }
 int attn_decode_mma_tile(int hd) {
-  static const int bn_env = getenv("NVLLM_ATTN_BN") ? atoi(getenv("NVLLM_ATTN_BN")) : 0;
-  return hd == 64 ? (bn_env ? 64 : 128) : 64;
+  return hd == 64 ? 128 : 64;  // the BN of decode_launch below
 }
 cudaError_t launch_attn_decode_mma(cudaStream_t st, const AttnArgs& a_in) {
   if (a_in.n_seqs <= 0) return cudaSuccess;
-  static const int abl = getenv("NVLLM_ATTN_ABL") ? atoi(getenv("NVLLM_ATTN_ABL")) : 0;
   AttnArgs a = a_in;
-  a.ablate = abl;
   const int G = a.nh / a.nkv, chunks = (G + 15) / 16;
   if (a.hd == 64) return decode_launch<64, 128, 3>(st, a, G, chunks);
   return decode_launch<128, 64, 3>(st, a, G, chunks);

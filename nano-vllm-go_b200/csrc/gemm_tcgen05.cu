@@ -884,8 +884,6 @@ static int max_clusters(int S) {
     if (cudaOccupancyMaxActiveClusters(&n, gemm_tc5_kernel<BT, STAGES>, &cfg) != cudaSuccess) n = 0;
   }
   (void)cudaGetLastError();
-  if (getenv("NVLLM_DEBUG_CLUSTER"))
-    fprintf(stderr, "nvllm: clusters of %d x gemm_tc5<%d,%d>: %d co-resident\n", S, BT, STAGES, n);
   cache[dev][S] = n;
   known[dev][S] = true;
   return n;

@@ -301,7 +301,6 @@ struct AttnArgs {
   const float* cosT;      // [max_pos, hd/2] or null (no RoPE)
   const float* sinT;
   int newkv_off;          // set by the launcher: smem offset of the new K / V rows
-  int ablate;             // timing experiments only (NVLLM_ATTN_ABL): 1 = no math, 2 = no K/V loads
   // stream-K decode (attention_mma.cu): ticket per (seq, kv head, head chunk), zero between
   // kernels; total_tiles = host LOWER bound of the key tiles in the step (caps the grid)
   int* tickets;        // unused (stream-K experiment removed)
