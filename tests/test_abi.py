@@ -79,3 +79,21 @@ def test_product_package_does_not_touch_the_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in text.replace("the oracle", "").replace("CPU oracle", ""), \
                     f"{f} references the oracle"
+
+
+def test_noalloc_entry_point_source_allocates_nothing():
+    """nvllm_op_gemv_noalloc (csrc/noalloc.cu): static check of what its header comment promises —
+    scratch in a file-scope static __device__ array of the size the header states, its address
+    taken with cudaGetSymbolAddress, and no allocating call anywhere in the file."""
+    path = os.path.join(os.path.dirname(HEADER), "..", "nano-vllm-go_b200", "csrc", "noalloc.cu")
+    src = open(path).read()
+    code = re.sub(r"//[^\n]*", "", src)
+    code = re.sub(r"/\*.*?\*/", "", code, flags=re.S)
+    for banned in ("cudaMalloc", "cudaFree", "cudaHostAlloc", "cudaMallocAsync", "malloc(", "new ",
+                   "std::vector", "cudaStreamCreate", "cudaEventCreate"):
+        assert banned not in code, banned
+    assert re.search(r"static\s+__device__\s+__align__\(256\)\s+float\s+\w+\[NOALLOC_FLOATS\]", code)
+    assert "cudaGetSymbolAddress" in code
+    hdr = open(HEADER).read()
+    m = re.search(r"#define\s+NVLLM_NOALLOC_MAX_SCRATCH_FLOATS\s+\(1\s*<<\s*(\d+)\)", hdr)
+    assert m and int(m.group(1)) == 20  # 4 MiB: the limit DESIGN.md and INTEGRATION.md state
