@@ -160,6 +160,55 @@ def build_falcon(cfg, w):
     return m
 
 
+def build_hybrid(cfg, w):
+    """Granite-4 hybrid: Mamba2 and attention blocks, shared SwiGLU MLP, no positional encoding,
+    muP multipliers (reference: generic_model.go:162-202, mamba2.go)."""
+    from transformers.models.granitemoehybrid.configuration_granitemoehybrid import GraniteMoeHybridConfig
+    from transformers.models.granitemoehybrid.modeling_granitemoehybrid import GraniteMoeHybridForCausalLM
+    E, conv, rows = cfg.mamba_dims()
+    hc = GraniteMoeHybridConfig(
+        vocab_size=cfg.vocab_size, hidden_size=cfg.hidden, intermediate_size=cfg.ffn_dim,
+        shared_intermediate_size=cfg.ffn_dim, num_hidden_layers=cfg.num_layers,
+        num_attention_heads=cfg.num_heads, num_key_value_heads=cfg.num_kv_heads,
+        max_position_embeddings=cfg.max_seq_len, rms_norm_eps=cfg.norm_eps, tie_word_embeddings=True,
+        attention_bias=False, attention_dropout=0.0, num_local_experts=0, num_experts_per_tok=0,
+        embedding_multiplier=cfg.embedding_multiplier, attention_multiplier=cfg.attention_multiplier,
+        residual_multiplier=cfg.residual_multiplier, logits_scaling=cfg.logits_scaling,
+        position_embedding_type="nope", hidden_act="silu",
+        layer_types=["mamba" if t else "attention" for t in cfg.hybrid_layers],
+        mamba_n_heads=cfg.mamba_num_heads, mamba_d_head=cfg.mamba_head_dim,
+        mamba_d_state=cfg.mamba_state_size, mamba_n_groups=cfg.mamba_n_groups,
+        mamba_d_conv=cfg.mamba_conv_kernel, mamba_expand=E // cfg.hidden, mamba_chunk_size=8,
+        mamba_conv_bias=True, mamba_proj_bias=False)
+    m = GraniteMoeHybridForCausalLM(hc).float().eval()
+    sd = {"model.embed_tokens.weight": w[(C.W_TOKEN_EMBEDDING, -1)],
+          "model.norm.weight": w[(C.W_FINAL_NORM_W, -1)],
+          "lm_head.weight": w[(C.W_TOKEN_EMBEDDING, -1)]}
+    for l in range(cfg.num_layers):
+        p = f"model.layers.{l}."
+        sd[p + "input_layernorm.weight"] = w[(C.W_ATTN_NORM_W, l)]
+        sd[p + "post_attention_layernorm.weight"] = w[(C.W_FFN_NORM_W, l)]
+        sd[p + "shared_mlp.input_linear.weight"] = w[(C.W_FFN_W1, l)].t().contiguous()   # [2F, H]: gate | up
+        sd[p + "shared_mlp.output_linear.weight"] = w[(C.W_FFN_W2, l)].t().contiguous()
+        if cfg.is_mamba(l):
+            sd[p + "mamba.in_proj.weight"] = w[(C.W_MAMBA_IN_PROJ, l)]
+            sd[p + "mamba.conv1d.weight"] = w[(C.W_MAMBA_CONV_W, l)]
+            sd[p + "mamba.conv1d.bias"] = w[(C.W_MAMBA_CONV_B, l)]
+            sd[p + "mamba.dt_bias"] = w[(C.W_MAMBA_DT_BIAS, l)]
+            sd[p + "mamba.A_log"] = w[(C.W_MAMBA_A_LOG, l)]
+            sd[p + "mamba.D"] = w[(C.W_MAMBA_D, l)]
+            sd[p + "mamba.norm.weight"] = w[(C.W_MAMBA_NORM, l)]
+            sd[p + "mamba.out_proj.weight"] = w[(C.W_MAMBA_OUT_PROJ, l)]
+        else:
+            sd[p + "self_attn.q_proj.weight"] = w[(C.W_Q, l)].t().contiguous()
+            sd[p + "self_attn.k_proj.weight"] = w[(C.W_K, l)].t().contiguous()
+            sd[p + "self_attn.v_proj.weight"] = w[(C.W_V, l)].t().contiguous()
+            sd[p + "self_attn.o_proj.weight"] = w[(C.W_O, l)].t().contiguous()
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected and not [k for k in missing if "rotary" not in k], (missing, unexpected)
+    return m
+
+
 CASES = {
     "gpt2": (lambda: C.tiny_gpt2(vocab_size=320, hidden=64, head_dim=16, ffn_dim=256,
                                  max_seq_len=64), build_gpt2),
@@ -169,13 +218,20 @@ CASES = {
                                        head_dim=16, ffn_dim=32, max_seq_len=64), build_granite),
     "falcon": (lambda: C.tiny_falcon(vocab_size=320, hidden=5 * 16, num_heads=5, head_dim=16,
                                      ffn_dim=4 * 5 * 16, max_seq_len=64), build_falcon),
+    "hybrid": (lambda: C.tiny_hybrid(vocab_size=320, hidden=64, num_heads=4, num_kv_heads=2,
+                                     head_dim=16, ffn_dim=96, max_seq_len=64, mamba_num_heads=8,
+                                     mamba_head_dim=16, mamba_state_size=16, mamba_n_groups=2,
+                                     mamba_conv_kernel=4, norm_eps=1e-5), build_hybrid),
 }
 
 
 def main():
     torch.manual_seed(0)
     out_dir = os.path.dirname(os.path.abspath(__file__))
+    only = sys.argv[1:]  # optional: the cases to (re)generate
     for name, (mk, build) in CASES.items():
+        if only and name not in only:
+            continue
         cfg = mk()
         w = wdict(cfg)
         model = build(cfg, w)

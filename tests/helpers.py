@@ -23,6 +23,11 @@ GOLDEN_CASES = {
                                       head_dim=16, ffn_dim=32, max_seq_len=64),
     "falcon": lambda: C.tiny_falcon(vocab_size=320, hidden=5 * 16, num_heads=5, head_dim=16,
                                     ffn_dim=4 * 5 * 16, max_seq_len=64),
+    # Granite-4 hybrid (Mamba2, attention, Mamba2, Mamba2) against GraniteMoeHybridForCausalLM
+    "hybrid": lambda: C.tiny_hybrid(vocab_size=320, hidden=64, num_heads=4, num_kv_heads=2,
+                                    head_dim=16, ffn_dim=96, max_seq_len=64, mamba_num_heads=8,
+                                    mamba_head_dim=16, mamba_state_size=16, mamba_n_groups=2,
+                                    mamba_conv_kernel=4, norm_eps=1e-5),
 }
 
 # parity-test configs (bigger than the goldens, still seconds on the CPU oracle)
