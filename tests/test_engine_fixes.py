@@ -110,3 +110,57 @@ def test_mixed_engine_on_the_library_matches_the_oracle(family):
         assert any(d > 0 and c > 0 for d, c in eng.steps)
     finally:
         run.close()
+
+
+@pytest.mark.parametrize("seed", range(40))
+def test_randomised_arrivals_pools_and_shared_prefixes(seed):
+    """Fuzz of the mixed scheduler on the scripted runner: random prompt lengths (some sharing
+    whole-block prefixes so that the prefix cache hits, some identical), requests arriving while
+    others run, pools from roomy to barely enough for one sequence, random chunk sizes and token
+    budgets.  Every request must finish with exactly the tokens its own history implies, and every
+    call must respect the budget, the sequence limit and the block tables."""
+    rng = np.random.default_rng(1000 + seed)
+    # long completions cross block boundaries: with a tight pool that forces preemption
+    max_new = int(rng.integers(1, 20)) if seed % 2 else int(rng.integers(200, 400))
+    n_req = int(rng.integers(1, 9))
+    base = list(map(int, rng.integers(0, 90, 700)))
+    prompts = []
+    for _ in range(n_req):
+        kind = rng.integers(0, 4)
+        n = int(rng.integers(1, 700))
+        if kind == 0 and prompts:
+            prompts.append(list(prompts[int(rng.integers(0, len(prompts)))]))           # identical
+        elif kind == 1:
+            prompts.append(base[:n])                                                     # shared prefix
+        elif kind == 2:
+            prompts.append(base[:256 * int(rng.integers(1, 3))] + list(map(int, rng.integers(0, 90, n % 50))))
+        else:
+            prompts.append(list(map(int, rng.integers(0, 90, n))))
+    prompts = [p if p else [1] for p in prompts]
+    longest = max(len(p) for p in prompts) + max_new
+    need_one = (longest + 255) // 256
+    blocks = int(need_one + rng.integers(0, (3 * need_one + 2) if seed % 4 else 2))
+    cfg = G.EngineConfig(max_num_batched_tokens=4096, max_model_len=4096, num_kvcache_blocks=blocks,
+                         max_num_seqs=int(rng.integers(1, 6)))
+    run = ScriptedRunner()
+    eng = F.MixedEngine(cfg, run, chunk_tokens=int(rng.choice([64, 100, 256, 300, 1024])))
+    budget = int(rng.choice([64, 256, 700, 4096]))
+    eng.scheduler.max_num_batched_tokens = budget
+    seqs, arrivals = [], sorted(int(x) for x in rng.integers(0, 12, n_req))
+    step = 0
+    while len(seqs) < n_req or not eng.scheduler.is_finished():
+        while len(seqs) < n_req and arrivals[len(seqs)] <= step:
+            seqs.append(eng.add_request(prompts[len(seqs)], max_new))
+        if not eng.scheduler.is_finished():
+            eng.step()
+        step += 1
+        assert step < 20000, "no progress"
+    for p, s in zip(prompts, seqs):
+        assert s.completion_token_ids() == expected(p, max_new)
+    for (d, c), call in zip(eng.steps, run.calls):
+        assert d + c <= budget and len(call) <= cfg.max_num_seqs
+        for n_tok, cached, bt in call:
+            assert 0 <= cached < n_tok and len(bt) >= (n_tok + 255) // 256
+            assert all(0 <= b < blocks for b in bt)
+    # everything was given back
+    assert len(eng.scheduler.block_manager.free_block_ids) == blocks
