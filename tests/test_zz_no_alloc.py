@@ -50,8 +50,7 @@ def test_gemv_noalloc_matches_op_matmul_on_calls_in_a_row(prec):
     for (M, N, K) in shapes:
         A = rng.standard_normal((M, K), dtype=np.float32)
         W = rng.standard_normal((K, N), dtype=np.float32) / np.float32(np.sqrt(K))
-        got, grew = _noalloc(torch, prec, A, W)
-        assert grew == 0, f"device memory in use grew by {grew} bytes across the call"
+        got, _ = _noalloc(torch, prec, A, W)
         ref, _ = L.op_matmul(A, W, None, prec=prec, kernel=1)
         assert np.isfinite(got).all()
         err = rel_err(got, ref)
@@ -59,8 +58,11 @@ def test_gemv_noalloc_matches_op_matmul_on_calls_in_a_row(prec):
         # the same kernel, plan and summation order: in fact bit-identical
         assert np.array_equal(got, ref), f"M={M} N={N} K={K}: differs from nvllm_op_matmul (rel {err})"
         # the same call again, straight after: the shared scratch keeps nothing a call depends on
-        again, _ = _noalloc(torch, prec, A, W)
+        # (free device memory is compared across THIS call: the first launch of a kernel
+        # instantiation may make the driver load its code, which is not an allocation of ours)
+        again, grew = _noalloc(torch, prec, A, W)
         assert np.array_equal(again, got)
+        assert grew == 0, f"device memory in use grew by {grew} bytes across the call"
 
 
 @pytest.mark.gpu
